@@ -1,0 +1,473 @@
+"""Host-side lowering of the generator / discriminator / encoder conv stacks to
+*pixel-GEMM programs* — the table format executed by the tcgen05 engine in
+`csrc/pixel_gemm.cuh` (and, for bring-up, by the SIMT interpreter of the same tables).
+
+Data model (everything the reference computes with `nn.ConvTranspose2d` / `nn.Conv2d`,
+src/utils/util_dcgan.py:103-149, becomes chains of 128-particle x 64-channel tiles):
+
+* An activation is a bf16 matrix X[P, pitch]: one row per particle, pixels x channels
+  flattened NHWC, channel pitch padded to a multiple of 64 (one 128-byte swizzle row).
+* A *step* multiplies one K-chunk: A = X[p0:p0+128, a_col:a_col+64] (TMA tile, M = particles)
+  with B = Wpack[b_row:b_row+mma_n, 0:64] (K-major weights) into TMEM columns
+  [d_col, d_col+mma_n) of the job's accumulator (overwrite or accumulate).
+* A *job* is a list of steps plus an epilogue: column n of the accumulator gets
+  bias[n], the layer activation, and is stored at out_base + col_map[n] of the output row,
+  if its pixel (n // cc) is enabled in the job's pixel mask.
+
+Geometry (transposed-conv phase structure, borders, paddings) lives entirely in these
+tables, which are verified on the CPU against torch's convolutions by `emulate()` before a
+GPU ever sees them (tests/test_lowering.py).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import List, Optional, Tuple
+
+import numpy as np
+
+KCHUNK = 64           # K elements per step: 64 bf16 = one 128 B swizzle row
+TILE_M = 128          # particles per tile (UMMA M)
+MAX_N = 256           # UMMA N limit / TMEM columns per accumulator buffer
+
+ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3, 4
+STEP_ACCUM, STEP_B_RESIDENT = 1, 2
+ROUND_WEIGHTS = True   # tests switch this off to check the geometry exactly in fp32
+
+# image layouts
+IMG_PAD_ROWS, IMG_PAD_PITCH = 31, 32          # bf16 padded 28x28 image: real (y,x) at (y+1,x+1)
+
+
+def rup(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def cpitch(c: int) -> int:
+    """Channel pitch of an NHWC activation with c channels."""
+    return rup(c, KCHUNK)
+
+
+def to_bf16_f32(x: np.ndarray) -> np.ndarray:
+    """Round-to-nearest-even fp32 -> bf16, returned as fp32 (numpy has no bf16)."""
+    u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    r = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16) << 16
+    return r.astype(np.uint32).view(np.float32).reshape(np.shape(x))
+
+
+def bf16_bits(x: np.ndarray) -> np.ndarray:
+    """fp32 -> bf16 bit pattern (uint16), round-to-nearest-even."""
+    u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    return ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16).reshape(np.shape(x))
+
+
+@dataclass
+class LayerProgram:
+    name: str
+    mma_n: int                    # N of every MMA in this layer (multiple of 16, <= 256)
+    nt: int                       # accumulator columns per job (<= 256)
+    cc: int                       # accumulator columns per output pixel (mask granularity)
+    act: int
+    in_pitch: int                 # elements per particle row of the input activation
+    out_pitch: int                # bf16 output row pitch (0: no bf16 output)
+    out32_pitch: int              # fp32 output row pitch (0: no fp32 output)
+    wpack: np.ndarray             # float32 [rows, 64] (already bf16-rounded values)
+    b_resident: bool              # whole wpack lives in shared memory for the CTA's lifetime
+    steps: np.ndarray             # int32 [n_steps, 4]: a_col, b_row, d_col, flags
+    jobs: np.ndarray              # int32 [n_jobs, 8]: step_begin, step_count, out_base, out32_base, mask_lo, mask_hi, 0, 0
+    col_map: np.ndarray           # int32 [nt] relative bf16 offsets (-1: not stored)
+    col_map32: np.ndarray         # int32 [nt] relative fp32 offsets (-1: not stored)
+    bias: np.ndarray              # float32 [n_bias_rows, nt]; jobs[:, 6] selects the row
+    vec8: bool                    # col_map is contiguous in aligned groups of 8 (16-byte stores)
+    macs_exact: int = 0           # border-aware MACs per particle (reference arithmetic)
+    macs_issued: int = 0          # MACs per particle the MMA chain actually executes
+    meta: dict = field(default_factory=dict)
+
+    @property
+    def n_jobs(self) -> int:
+        return int(self.jobs.shape[0])
+
+    @property
+    def n_steps(self) -> int:
+        return int(self.steps.shape[0])
+
+
+def _finish(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, tiles, b_resident, steps, jobs,
+            col_map, col_map32, bias, macs_exact, meta=None) -> LayerProgram:
+    assert mma_n % 16 == 0 and 16 <= mma_n <= MAX_N and nt <= MAX_N and nt % 16 == 0
+    wpack = np.concatenate(tiles, axis=0).astype(np.float32) if tiles else np.zeros((0, KCHUNK), np.float32)
+    if ROUND_WEIGHTS:
+        wpack = to_bf16_f32(wpack)
+    steps = np.asarray(steps, dtype=np.int32).reshape(-1, 4)
+    jobs = np.asarray(jobs, dtype=np.int64).reshape(-1, 8)
+    jobs = (jobs & 0xFFFFFFFF).astype(np.uint32).view(np.int32)
+    col_map = np.asarray(col_map, dtype=np.int32)
+    col_map32 = np.asarray(col_map32, dtype=np.int32)
+    assert col_map.shape == (nt,) and col_map32.shape == (nt,)
+    assert np.all(steps[:, 0] % 8 == 0), "TMA needs 16-byte aligned K-chunk starts"
+    vec8 = bool(out_pitch and nt % 8 == 0 and all(
+        (col_map[g] >= 0 and col_map[g] % 8 == 0 and np.all(np.diff(col_map[g:g + 8]) == 1)) or
+        np.all(col_map[g:g + 8] < 0) for g in range(0, nt, 8)) and cc % 8 == 0)
+    bias = np.asarray(bias, dtype=np.float32).reshape(-1, nt)
+    assert jobs[:, 6].max(initial=0) < bias.shape[0]
+    return LayerProgram(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, wpack, b_resident, steps, jobs,
+                        col_map, col_map32, bias, vec8, int(macs_exact),
+                        int(steps.shape[0]) * KCHUNK * mma_n, meta or {})
+
+
+def _mask_words(bits: List[bool]) -> Tuple[int, int]:
+    v = 0
+    for i, b in enumerate(bits):
+        if b:
+            v |= 1 << i
+    assert len(bits) <= 64
+    return v & 0xFFFFFFFF, (v >> 32) & 0xFFFFFFFF
+
+
+# ----------------------------------------------------------------------------------------------
+# (a) ConvTranspose2d(z -> C, k, s=1, p=0) on a 1x1 input  == one GEMM  [P,z] x [z, k*k*C]
+#     (first generator block, src/utils/util_dcgan.py:135)
+# ----------------------------------------------------------------------------------------------
+
+def lower_convt_from_1x1(name, w, b, act, in_pitch=None) -> LayerProgram:
+    """w: [Cin, Cout, k, k] fp32 (BN already folded), b: [Cout].  Input X[P, Kp] (z padded to
+    a multiple of 64 with zeros); output NHWC [k*k, Cp]."""
+    cin, cout, k, _ = w.shape
+    kp = rup(cin, KCHUNK)
+    in_pitch = in_pitch or kp
+    cp = cpitch(cout)
+    npix = k * k
+    if cp >= MAX_N:
+        cc, gpix = MAX_N, 1
+    else:
+        cc, gpix = cp, MAX_N // cp
+    nco = cp // cc
+    nt = cc * gpix
+    tiles, steps, jobs = [], [], []
+    wp = np.zeros((kp, cp, k, k), np.float32)
+    wp[:cin, :cout] = w
+    bp = np.zeros(cp, np.float32)
+    bp[:cout] = b
+    for p0 in range(0, npix, gpix):
+        for ch in range(nco):
+            sb = len(steps)
+            for kc in range(kp // KCHUNK):
+                t = np.zeros((nt, KCHUNK), np.float32)
+                for j in range(gpix):
+                    pix = p0 + j
+                    if pix < npix:
+                        ky, kx = divmod(pix, k)
+                        t[j * cc:(j + 1) * cc] = wp[kc * KCHUNK:(kc + 1) * KCHUNK, ch * cc:(ch + 1) * cc, ky, kx].T
+                steps.append((kc * KCHUNK, len(tiles) * nt, 0, STEP_ACCUM if kc else 0))
+                tiles.append(t)
+            lo, hi = _mask_words([p0 + j < npix for j in range(gpix)])
+            jobs.append((sb, len(steps) - sb, p0 * cp + ch * cc, 0, lo, hi, ch, 0))
+    col_map = [(n // cc) * cp + n % cc for n in range(nt)]
+    bias = [[bp[ch * cc + n % cc] for n in range(nt)] for ch in range(nco)]
+    return _finish(name, nt, nt, cc, act, in_pitch, npix * cp, 0, tiles, False, steps, jobs, col_map,
+                   [-1] * nt, bias, macs_exact=cin * cout * npix,
+                   meta=dict(kind="convt1x1", out_hw=(k, k), out_c=cout, out_cp=cp))
+
+
+# ----------------------------------------------------------------------------------------------
+# (b) ConvTranspose2d(Cin -> Cout, k=4, s=2, p=1): H x W -> 2H x 2W
+#     (second / third generator blocks, src/utils/util_dcgan.py:136-137)
+#
+#     Output rows {2q+1, 2q+2} depend on input rows {q, q+1} only (q = -1 .. H-1), with
+#     ky = u%2+2 for the upper input row and ky = u%2 for the lower one.  A block of m x m such
+#     pairs (2m x 2m output pixels) reads (m+1) x (m+1) input pixels; every (input pixel,
+#     K-chunk) is one step whose B tile holds the taps to all output pixels of the block.
+# ----------------------------------------------------------------------------------------------
+
+def _tap(u: int, a: int) -> int:
+    """kernel index connecting local input row a to local output row u (or -1)."""
+    ky = u + 2 - 2 * a
+    return ky if 0 <= ky < 4 else -1
+
+
+def lower_convt_k4s2p1(name, w, b, act, h, wd, *, m=1, image_out=False, in_cp=None) -> LayerProgram:
+    """w: [Cin, Cout, 4, 4], b: [Cout].  Input NHWC [h, wd, Cp_in] -> output NHWC [2h, 2wd, Cp_out],
+    or, with image_out (Cout == 1): bf16 padded image (IMG_PAD layout, only for 28x28) and an
+    fp32 plain [2h*2wd] image."""
+    cin, cout = w.shape[0], w.shape[1]
+    cpi = in_cp or cpitch(cin)
+    ho, wo = 2 * h, 2 * wd
+    npx = (2 * m) ** 2
+    if image_out:
+        assert cout == 1
+        cc, cpo, nco = 1, 1, 1
+        nt = rup(npx, 16)
+    else:
+        cpo = cpitch(cout)
+        cc = min(cpo, MAX_N // npx)
+        assert cc >= 8 and cpo % cc == 0, "block too large for this channel count"
+        nco = cpo // cc
+        nt = npx * cc
+    wp = np.zeros((rup(cin, KCHUNK), cpo if not image_out else 1, 4, 4), np.float32)
+    wp[:cin, :cout] = w
+    bp = np.zeros(cpo if not image_out else 1, np.float32)
+    bp[:cout] = b
+    nkc = rup(cin, KCHUNK) // KCHUNK
+    assert nkc * KCHUNK <= cpi
+
+    # position-independent B tiles: index [(a, bb, kc, ch)]
+    tiles, tile_of = [], {}
+    for a in range(m + 1):
+        for bb in range(m + 1):
+            for kc in range(nkc):
+                for ch in range(nco):
+                    t = np.zeros((nt, KCHUNK), np.float32)
+                    for u in range(2 * m):
+                        ky = _tap(u, a)
+                        if ky < 0:
+                            continue
+                        for v in range(2 * m):
+                            kx = _tap(v, bb)
+                            if kx < 0:
+                                continue
+                            n0 = (u * 2 * m + v) * cc
+                            t[n0:n0 + cc] = wp[kc * KCHUNK:(kc + 1) * KCHUNK, ch * cc:(ch + 1) * cc, ky, kx].T
+                    tile_of[(a, bb, kc, ch)] = len(tiles)
+                    tiles.append(t)
+
+    if image_out:
+        pad_ok = (ho, wo) == (28, 28)
+        row_p, pix_p, base_p = (IMG_PAD_PITCH, 1, IMG_PAD_PITCH + 1) if pad_ok else (0, 0, 0)
+        out_pitch = IMG_PAD_ROWS * IMG_PAD_PITCH if pad_ok else 0
+        row_f, pix_f = wo, 1
+        out32_pitch = ho * wo
+    else:
+        row_p, pix_p, base_p = wo * cpo, cpo, 0
+        out_pitch = ho * wo * cpo
+        out32_pitch = 0
+
+    steps, jobs = [], []
+    for bq in range(-1, h, m):
+        for br in range(-1, wd, m):
+            for ch in range(nco):
+                sb = len(steps)
+                for a in range(m + 1):
+                    iy = bq + a
+                    if not 0 <= iy < h:
+                        continue
+                    for bb in range(m + 1):
+                        ix = br + bb
+                        if not 0 <= ix < wd:
+                            continue
+                        for kc in range(nkc):
+                            steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, tile_of[(a, bb, kc, ch)] * nt, 0,
+                                          STEP_ACCUM if len(steps) > sb else 0))
+                oy0, ox0 = 2 * bq + 1, 2 * br + 1
+                bits = [0 <= oy0 + u < ho and 0 <= ox0 + v < wo for u in range(2 * m) for v in range(2 * m)]
+                if not any(bits):
+                    del steps[sb:]
+                    continue
+                lo, hi = _mask_words(bits)
+                base = base_p + oy0 * row_p + ox0 * pix_p + ch * cc
+                base32 = oy0 * wo + ox0 if image_out else 0
+                jobs.append((sb, len(steps) - sb, base, base32, lo, hi, ch, 0))
+    col_map, col_map32 = [], []
+    bias = np.zeros((nco, nt), np.float32)
+    for n in range(nt):
+        pix, c = divmod(n, cc)
+        if pix >= npx:
+            col_map.append(-1); col_map32.append(-1)
+            continue
+        u, v = divmod(pix, 2 * m)
+        col_map.append(u * row_p + v * pix_p + c if out_pitch else -1)
+        col_map32.append(u * row_f + v * pix_f if image_out else -1)
+        for ch in range(nco):
+            bias[ch, n] = bp[ch * cc + c]
+    meta = dict(kind="convt_k4s2p1", out_hw=(ho, wo), out_c=cout, out_cp=cpo, m=m)
+    # exact MACs: count connected (input, output) pixel pairs inside the borders
+    conn = 0
+    for oy in range(ho):
+        for ky in range(4):
+            num = oy + 1 - ky
+            if num % 2 == 0 and 0 <= num // 2 < h:
+                conn += 1
+    conn_x = 0
+    for ox in range(wo):
+        for kx in range(4):
+            num = ox + 1 - kx
+            if num % 2 == 0 and 0 <= num // 2 < wd:
+                conn_x += 1
+    return _finish(name, nt, nt, cc, act, h * wd * cpi, out_pitch, out32_pitch, tiles, False, steps, jobs,
+                   col_map, col_map32, bias, macs_exact=conn * conn_x * cin * cout, meta=meta)
+
+
+# ----------------------------------------------------------------------------------------------
+# (c) Conv2d(Cin -> Cout, k=4, s=2, p=1): H x W -> H/2 x W/2  (second discriminator / encoder
+#     conv, src/utils/util_dcgan.py:112, 116-121).  One accumulator of mma_n = Cp_out columns
+#     per output pixel, g pixels per job; taps whose input pixel is outside are dropped.
+# ----------------------------------------------------------------------------------------------
+
+def lower_conv_k4s2p1(name, w, b, act, h, wd, in_cp=None) -> LayerProgram:
+    cout, cin = w.shape[0], w.shape[1]
+    cpi = in_cp or cpitch(cin)
+    cpo = cpitch(cout)
+    assert cpo <= MAX_N
+    ho, wo = h // 2, wd // 2
+    g = MAX_N // cpo
+    nt = g * cpo
+    nkc = rup(cin, KCHUNK) // KCHUNK
+    wp = np.zeros((cpo, rup(cin, KCHUNK), 4, 4), np.float32)
+    wp[:cout, :cin] = w
+    bp = np.zeros(cpo, np.float32)
+    bp[:cout] = b
+    tiles, tile_of = [], {}
+    for ky in range(4):
+        for kx in range(4):
+            for kc in range(nkc):
+                tile_of[(ky, kx, kc)] = len(tiles)
+                tiles.append(wp[:, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
+    steps, jobs = [], []
+    macs = 0
+    for oy in range(ho):
+        for ox0 in range(0, wo, g):
+            sb = len(steps)
+            for j in range(g):
+                ox = ox0 + j
+                if ox >= wo:
+                    continue
+                first = True
+                for ky in range(4):
+                    iy = 2 * oy - 1 + ky
+                    if not 0 <= iy < h:
+                        continue
+                    for kx in range(4):
+                        ix = 2 * ox - 1 + kx
+                        if not 0 <= ix < wd:
+                            continue
+                        macs += cin * cout
+                        for kc in range(nkc):
+                            steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, tile_of[(ky, kx, kc)] * cpo, j * cpo,
+                                          0 if first else STEP_ACCUM))
+                            first = False
+            lo, hi = _mask_words([ox0 + j < wo for j in range(g)])
+            jobs.append((sb, len(steps) - sb, (oy * wo + ox0) * cpo, 0, lo, hi, 0, 0))
+    col_map = list(range(nt))
+    bias = [bp[n % cpo] for n in range(nt)]
+    return _finish(name, cpo, nt, cpo, act, h * wd * cpi, ho * wo * cpo, 0, tiles, False, steps, jobs, col_map,
+                   [-1] * nt, bias, macs_exact=macs, meta=dict(kind="conv_k4s2p1", out_hw=(ho, wo), out_c=cout, out_cp=cpo))
+
+
+# ----------------------------------------------------------------------------------------------
+# (d) Conv2d(1 -> Cout, k=4, s=2, p=1) on the padded bf16 28x28 image  (first discriminator /
+#     encoder conv, src/utils/util_dcgan.py:110).  Cin = 1 gives K = 16 per output pixel, far
+#     below an MMA K-chunk, so four image rows (4 x 32 padded columns = 128 contiguous
+#     elements) are the K dimension and a banded weight matrix selects each output pixel's
+#     4x4 window.  Starting the window 8 columns later per group of 4 output pixels makes the
+#     band position-independent: the layer's whole B operand is 2 tiles, resident in SMEM.
+# ----------------------------------------------------------------------------------------------
+
+def lower_conv_image_k4s2p1(name, w, b, act) -> LayerProgram:
+    cout = w.shape[0]
+    assert w.shape[1] == 1 and tuple(w.shape[2:]) == (4, 4)
+    cpo = cpitch(cout)
+    gox = MAX_N // cpo                 # output pixels per job
+    assert gox == 4, "window shift must be a multiple of 8 elements (4 output pixels)"
+    nt = gox * cpo
+    ho = wo = 14
+    tiles = []
+    for kc in range(2):
+        t = np.zeros((nt, KCHUNK), np.float32)
+        for kk in range(KCHUNK):
+            r, j = divmod(kc * KCHUNK + kk, IMG_PAD_PITCH)      # window row 0..3, window column 0..31
+            for oxl in range(gox):
+                kx = j - 2 * oxl
+                if 0 <= kx < 4:
+                    t[oxl * cpo:oxl * cpo + cout, kk] = w[:, 0, r, kx]
+        tiles.append(t)
+    steps, jobs = [], []
+    for oy in range(ho):
+        for g in range((wo + gox - 1) // gox):
+            sb = len(steps)
+            start = 2 * oy * IMG_PAD_PITCH + 2 * gox * g      # padded row 2oy == real row 2oy-1; padded col == real col-1+1
+            for kc in range(2):
+                steps.append((start + kc * KCHUNK, kc * nt, 0, STEP_B_RESIDENT | (STEP_ACCUM if kc else 0)))
+            lo, hi = _mask_words([gox * g + j < wo for j in range(gox)])
+            jobs.append((sb, 2, (oy * wo + gox * g) * cpo, 0, lo, hi, 0, 0))
+    bp = np.zeros(cpo, np.float32)
+    bp[:cout] = b
+    assert steps[-1][0] + KCHUNK <= IMG_PAD_ROWS * IMG_PAD_PITCH
+    # exact MACs: taps inside the image
+    taps = sum(1 for o in range(14) for kk in range(4) if 0 <= 2 * o - 1 + kk < 28)
+    return _finish(name, nt, nt, cpo, act, IMG_PAD_ROWS * IMG_PAD_PITCH, ho * wo * cpo, 0, tiles, True, steps, jobs,
+                   list(range(nt)), [-1] * nt, [bp[n % cpo] for n in range(nt)], macs_exact=taps * taps * cout,
+                   meta=dict(kind="conv_image", out_hw=(ho, wo), out_c=cout, out_cp=cpo))
+
+
+# ----------------------------------------------------------------------------------------------
+# (e) Conv2d(Cin -> Cout, k=7, s=2, p=0) on a 7x7 input == one dot product over the whole map
+#     (discriminator score / encoder latent, src/utils/util_dcgan.py:113,
+#      src/inverter/utils_ae/util_inverter.py:173).  N = Cout padded to 16; fp32 output.
+# ----------------------------------------------------------------------------------------------
+
+def lower_conv_full(name, w, b, act, in_cp=None) -> LayerProgram:
+    cout, cin, k, _ = w.shape
+    cpi = in_cp or cpitch(cin)
+    nt = rup(cout, 16)
+    assert nt <= MAX_N
+    nkc = rup(cin, KCHUNK) // KCHUNK
+    wp = np.zeros((nt, nkc * KCHUNK, k, k), np.float32)
+    wp[:cout, :cin] = w
+    tiles, steps = [], []
+    for pix in range(k * k):
+        ky, kx = divmod(pix, k)
+        for kc in range(nkc):
+            steps.append((pix * cpi + kc * KCHUNK, len(tiles) * nt, 0, STEP_ACCUM if steps else 0))
+            tiles.append(wp[:, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
+    jobs = [(0, len(steps), 0, 0, 1, 0, 0, 0)]
+    bias = np.zeros(nt, np.float32)
+    bias[:cout] = b
+    cm32 = [n if n < cout else -1 for n in range(nt)]
+    return _finish(name, nt, nt, nt, act, k * k * cpi, 0, cout, tiles, False,
+                   steps, jobs, [-1] * nt, cm32, bias, macs_exact=cin * cout * k * k,
+                   meta=dict(kind="conv_full", out_c=cout))
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU emulation of the engine (numpy): the semantics csrc/pixel_gemm.cuh must reproduce.
+# ----------------------------------------------------------------------------------------------
+
+def _act(x, act):
+    if act == ACT_RELU:
+        return np.maximum(x, 0)
+    if act == ACT_LEAKY:
+        return np.where(x > 0, x, np.float32(0.2) * x)
+    if act == ACT_TANH:
+        return np.tanh(x)
+    if act == ACT_SIGMOID:
+        return 1.0 / (1.0 + np.exp(-x))
+    return x
+
+
+def emulate(prog: LayerProgram, x: np.ndarray, round_out=True):
+    """x: float32 [P, in_pitch] holding bf16-representable values.  Returns (y_bf16_as_f32 or
+    None, y_f32 or None)."""
+    p = x.shape[0]
+    assert x.shape[1] >= prog.in_pitch
+    y = np.zeros((p, prog.out_pitch), np.float32) if prog.out_pitch else None
+    y32 = np.zeros((p, prog.out32_pitch), np.float32) if prog.out32_pitch else None
+    for job in prog.jobs:
+        sb, sc, base, base32 = int(job[0]), int(job[1]), int(job[2]), int(job[3])
+        mask = (int(np.uint32(job[4])) | (int(np.uint32(job[5])) << 32))
+        acc = np.zeros((p, prog.nt), np.float32)
+        for a_col, b_row, d_col, flags in prog.steps[sb:sb + sc]:
+            a = x[:, a_col:a_col + KCHUNK]
+            bt = prog.wpack[b_row:b_row + prog.mma_n]
+            contrib = a.astype(np.float32) @ bt.T.astype(np.float32)
+            if flags & STEP_ACCUM:
+                acc[:, d_col:d_col + prog.mma_n] += contrib
+            else:
+                acc[:, d_col:d_col + prog.mma_n] = contrib
+        bias = prog.bias[int(job[6])]
+        v = _act(acc + bias[None, :], prog.act).astype(np.float32)
+        for n in range(prog.nt):
+            pix = n // prog.cc
+            if pix < 64 and not (mask >> pix) & 1:
+                continue
+            if y is not None and prog.col_map[n] >= 0:
+                y[:, base + prog.col_map[n]] = to_bf16_f32(v[:, n]) if round_out else v[:, n]
+            if y32 is not None and prog.col_map32[n] >= 0:
+                y32[:, base32 + prog.col_map32[n]] = v[:, n]
+    return y, y32

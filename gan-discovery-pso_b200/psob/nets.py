@@ -1,0 +1,102 @@
+"""Weight preparation: reference state_dicts -> BN-folded pixel-GEMM layer programs.
+
+Keys follow the reference modules (src/utils/util_dcgan.py:103-149,
+src/inverter/utils_ae/util_inverter.py:164-184,
+src/inverter/utils_vq_vae/util_model.py:283-289): `gen.0.0.weight`, `gen.0.1.running_var`,
+`disc.2.0.weight`, `enc.3.bias`, `decoder.1.0.weight`, ...
+BatchNorm2d in eval() is a per-channel affine of the running statistics, so it folds into
+the preceding ConvTranspose2d: w' = w * g/sqrt(var+eps), b' = (b-mean) * g/sqrt(var+eps) + beta.
+"""
+from __future__ import annotations
+
+from typing import Dict, List
+
+import numpy as np
+
+from . import lowering as L
+
+BN_EPS = 1e-5
+
+
+def _np(v) -> np.ndarray:
+    if hasattr(v, "detach"):
+        v = v.detach().cpu().numpy()
+    return np.asarray(v, dtype=np.float64)
+
+
+def fold_bn_convt(sd: Dict, conv: str, bn: str):
+    """ConvTranspose2d weight [Cin, Cout, k, k] with BN over Cout."""
+    w, b = _np(sd[f"{conv}.weight"]), _np(sd[f"{conv}.bias"])
+    g, beta = _np(sd[f"{bn}.weight"]), _np(sd[f"{bn}.bias"])
+    mean, var = _np(sd[f"{bn}.running_mean"]), _np(sd[f"{bn}.running_var"])
+    s = g / np.sqrt(var + BN_EPS)
+    return (w * s[None, :, None, None]).astype(np.float32), ((b - mean) * s + beta).astype(np.float32)
+
+
+def generator_programs(sd: Dict, prefix: str = "gen", m_last: int = 2) -> List[L.LayerProgram]:
+    """DCGAN / VQ-VAE-GAN decoder 28x28 generator: z -> 7x7x2f -> 14x14xf -> 28x28x1."""
+    w1, b1 = fold_bn_convt(sd, f"{prefix}.0.0", f"{prefix}.0.1")
+    w2, b2 = fold_bn_convt(sd, f"{prefix}.1.0", f"{prefix}.1.1")
+    w3 = _np(sd[f"{prefix}.2.weight"]).astype(np.float32)
+    b3 = _np(sd[f"{prefix}.2.bias"]).astype(np.float32)
+    assert w1.shape[2] == 7 and w2.shape[2] == 4 and w3.shape[1] == 1, "28x28 single-channel generator expected"
+    l1 = L.lower_convt_from_1x1("g.l1", w1, b1, L.ACT_RELU)
+    l2 = L.lower_convt_k4s2p1("g.l2", w2, b2, L.ACT_RELU, 7, 7, m=1)
+    l3 = L.lower_convt_k4s2p1("g.l3", w3, b3, L.ACT_TANH, 14, 14, m=m_last, image_out=True)
+    assert l1.out_pitch == l2.in_pitch and l2.out_pitch == l3.in_pitch
+    return [l1, l2, l3]
+
+
+def g256_programs(sd: Dict, prefix: str = "gen") -> List[L.LayerProgram]:
+    """EXTENSION generator 1x256x256 (oracle/port.py:G256)."""
+    progs = []
+    w, b = fold_bn_convt(sd, f"{prefix}.0.0", f"{prefix}.0.1")
+    progs.append(L.lower_convt_from_1x1("g256.l0", w, b, L.ACT_RELU))
+    h = 4
+    i = 1
+    while f"{prefix}.{i}.0.weight" in sd:
+        w, b = fold_bn_convt(sd, f"{prefix}.{i}.0", f"{prefix}.{i}.1")
+        progs.append(L.lower_convt_k4s2p1(f"g256.l{i}", w, b, L.ACT_RELU, h, h, m=1))
+        h *= 2
+        i += 1
+    w = _np(sd[f"{prefix}.{i}.weight"]).astype(np.float32)
+    b = _np(sd[f"{prefix}.{i}.bias"]).astype(np.float32)
+    progs.append(L.lower_convt_k4s2p1(f"g256.l{i}", w, b, L.ACT_TANH, h, h, m=2, image_out=True))
+    for a, c in zip(progs[:-1], progs[1:]):
+        assert a.out_pitch == c.in_pitch, (a.name, a.out_pitch, c.name, c.in_pitch)
+    return progs
+
+
+def _down_programs(sd: Dict, prefix: str, name: str, last_act: int) -> List[L.LayerProgram]:
+    f32 = lambda k: _np(sd[k]).astype(np.float32)
+    c1 = L.lower_conv_image_k4s2p1(f"{name}.c1", f32(f"{prefix}.0.weight"), f32(f"{prefix}.0.bias"), L.ACT_LEAKY)
+    c2 = L.lower_conv_k4s2p1(f"{name}.c2", f32(f"{prefix}.2.0.weight"), f32(f"{prefix}.2.0.bias"), L.ACT_LEAKY, 14, 14)
+    c3 = L.lower_conv_full(f"{name}.c3", f32(f"{prefix}.3.weight"), f32(f"{prefix}.3.bias"), last_act)
+    assert c1.out_pitch == c2.in_pitch and c2.out_pitch == c3.in_pitch
+    return [c1, c2, c3]
+
+
+def discriminator_programs(sd: Dict, prefix: str = "disc") -> List[L.LayerProgram]:
+    """[P,1,28,28] (padded bf16 image) -> sigmoid score fp32 [P,1]."""
+    return _down_programs(sd, prefix, "d", L.ACT_SIGMOID)
+
+
+def encoder_programs(sd: Dict, prefix: str = "enc") -> List[L.LayerProgram]:
+    """[P,1,28,28] (padded bf16 image) -> latent fp32 [P,enc_dim]."""
+    return _down_programs(sd, prefix, "e", L.ACT_NONE)
+
+
+def pad_image_bf16(img: np.ndarray) -> np.ndarray:
+    """fp32 [P,1,28,28] or [P,784] -> padded layout [P, 31*32] (values bf16-rounded, fp32 storage)."""
+    p = img.shape[0]
+    out = np.zeros((p, L.IMG_PAD_ROWS, L.IMG_PAD_PITCH), np.float32)
+    out[:, 1:29, 1:29] = L.to_bf16_f32(img.reshape(p, 28, 28))
+    return out.reshape(p, -1)
+
+
+def emulate_chain(progs: List[L.LayerProgram], x: np.ndarray, round_out=True):
+    """CPU emulation of a whole stack; returns (last bf16 output, last fp32 output)."""
+    y, y32 = x, None
+    for pr in progs:
+        y, y32 = L.emulate(pr, y, round_out=round_out)
+    return y, y32

@@ -1,0 +1,136 @@
+"""CPU: the pixel-GEMM lowering tables reproduce torch's convolutions (geometry exact in fp32,
+bf16 pipeline within the stated tolerance)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import port
+from psob import lowering as L
+from psob import nets
+from conftest import load_sd
+
+
+@pytest.fixture
+def exact():
+    L.ROUND_WEIGHTS = False
+    yield
+    L.ROUND_WEIGHTS = True
+
+
+def _z_rows(z, pitch):
+    x = np.zeros((z.shape[0], pitch), np.float32)
+    x[:, :z.shape[1]] = z
+    return x
+
+
+@pytest.mark.parametrize("m_last", [1, 2, 4])
+def test_generator_geometry_exact(golden, exact, m_last):
+    sd = load_sd(golden, "gsmall_trained")
+    progs = nets.generator_programs(sd, m_last=m_last)
+    z = golden["gsmall/z"].reshape(6, 10)
+    _, img = nets.emulate_chain(progs, _z_rows(z, progs[0].in_pitch), round_out=False)
+    ref = golden["gsmall_trained/out"].reshape(6, 784)
+    np.testing.assert_allclose(img, ref, rtol=0, atol=2e-6)
+    # exact MAC bookkeeping equals the border-aware count of SURVEY.md §8 (scaled to this net)
+    ones = torch.ones(1, 1, 7, 7)
+    exact_l2 = int(torch.nn.functional.conv_transpose2d(ones, torch.ones(1, 1, 4, 4), stride=2, padding=1).sum())
+    assert progs[1].macs_exact == exact_l2 * 32 * 16
+
+
+def test_generator_full_size_geometry_and_macs(exact):
+    torch.manual_seed(0)
+    gen = port.Generator(100, 1, 64).eval()
+    port.randomize_bn_stats(gen, torch.Generator().manual_seed(1))
+    progs = nets.generator_programs(gen.state_dict())
+    z = torch.randn(3, 100, generator=torch.Generator().manual_seed(2))
+    with torch.no_grad():
+        ref = gen(z.view(3, 100, 1, 1)).reshape(3, 784).numpy()
+    _, img = nets.emulate_chain(progs, _z_rows(z.numpy(), progs[0].in_pitch), round_out=False)
+    np.testing.assert_allclose(img, ref, rtol=0, atol=5e-6)
+    assert [p.macs_exact for p in progs] == [627200, 5537792, 186624]
+    assert progs[1].macs_issued == 6422528                                   # nominal implicit-GEMM count
+    assert progs[1].mma_n == 256 and progs[0].mma_n == 256 and progs[2].mma_n == 16
+
+
+def test_generator_bf16_pipeline_within_tolerance(golden):
+    for regime in ("refinit", "default", "trained"):
+        sd = load_sd(golden, f"gsmall_{regime}")
+        progs = nets.generator_programs(sd)
+        z = L.to_bf16_f32(golden["gsmall/z"].reshape(6, 10))
+        img_pad, img = nets.emulate_chain(progs, _z_rows(z, progs[0].in_pitch))
+        ref = golden[f"gsmall_{regime}/out"].reshape(6, 784)
+        assert np.abs(img - ref).max() <= 2e-2                 # north_star bf16 tolerance
+        assert np.linalg.norm(img - ref) / np.linalg.norm(ref) <= 5e-3   # SURVEY.md §7 relative gate
+        # padded bf16 copy holds the same pixels at (y+1, x+1), zeros elsewhere
+        pad = img_pad.reshape(6, L.IMG_PAD_ROWS, L.IMG_PAD_PITCH)
+        np.testing.assert_array_equal(pad[:, 1:29, 1:29].reshape(6, 784), L.to_bf16_f32(img))
+        assert pad[:, 0].max() == 0 and pad[:, 29:].max() == 0 and pad[:, :, 0].max() == 0 and pad[:, :, 29:].max() == 0
+
+
+def test_discriminator_and_encoder_geometry_exact(golden, exact):
+    x = golden["dsmall/x"]
+    xp = np.zeros((6, L.IMG_PAD_ROWS, L.IMG_PAD_PITCH), np.float32)
+    xp[:, 1:29, 1:29] = x.reshape(6, 28, 28)
+    xp = xp.reshape(6, -1)
+    d = nets.discriminator_programs(load_sd(golden, "dsmall"))
+    _, score = nets.emulate_chain(d, xp, round_out=False)
+    np.testing.assert_allclose(score[:, 0], golden["dsmall/out"].reshape(6), rtol=0, atol=2e-6)
+    e = nets.encoder_programs(load_sd(golden, "esmall"))
+    _, lat = nets.emulate_chain(e, xp, round_out=False)
+    np.testing.assert_allclose(lat, golden["esmall/out"].reshape(6, 10), rtol=0, atol=5e-6)
+    assert d[0].b_resident and d[0].wpack.shape == (512, 64)
+
+
+def test_discriminator_full_size_macs(exact):
+    torch.manual_seed(3)
+    disc = port.Discriminator(1, 64).eval()
+    progs = nets.discriminator_programs(disc.state_dict())
+    assert sum(p.macs_exact for p in progs) == 5730688
+    x = torch.tanh(torch.randn(2, 1, 28, 28, generator=torch.Generator().manual_seed(4)))
+    xp = np.zeros((2, L.IMG_PAD_ROWS, L.IMG_PAD_PITCH), np.float32)
+    xp[:, 1:29, 1:29] = x.numpy().reshape(2, 28, 28)
+    _, score = nets.emulate_chain(progs, xp.reshape(2, -1), round_out=False)
+    with torch.no_grad():
+        ref = disc(x).reshape(2).numpy()
+    np.testing.assert_allclose(score[:, 0], ref, rtol=0, atol=2e-6)
+
+
+def test_g256_geometry_small(exact):
+    torch.manual_seed(5)
+    g = port.G256(z_dim=10, channels_img=1, features_g=4).eval()   # 128..4 channels, 256x256 output
+    port.randomize_bn_stats(g, torch.Generator().manual_seed(6))
+    progs = nets.g256_programs(g.state_dict())
+    z = torch.randn(1, 10, generator=torch.Generator().manual_seed(7))
+    with torch.no_grad():
+        ref = g(z.view(1, 10, 1, 1)).reshape(1, -1).numpy()
+    _, img = nets.emulate_chain(progs, _z_rows(z.numpy(), progs[0].in_pitch), round_out=False)
+    np.testing.assert_allclose(img, ref, rtol=0, atol=5e-6)
+
+
+def test_channel_chunked_jobs(exact):
+    """Cout > 64 with m=1 splits into per-chunk jobs with their own bias rows (G256 widths)."""
+    rng = np.random.RandomState(0)
+    w = rng.randn(64, 128, 4, 4).astype(np.float32) * 0.05
+    b = rng.randn(128).astype(np.float32)
+    pr = L.lower_convt_k4s2p1("t", w, b, L.ACT_RELU, 3, 3, m=1)
+    assert pr.bias.shape[0] == 2 and pr.mma_n == 256
+    x = rng.randn(2, 64, 3, 3).astype(np.float32)
+    ref = torch.relu(torch.nn.functional.conv_transpose2d(torch.from_numpy(x), torch.from_numpy(w),
+                                                          torch.from_numpy(b), stride=2, padding=1))
+    xin = np.ascontiguousarray(x.transpose(0, 2, 3, 1)).reshape(2, -1)
+    y, _ = L.emulate(pr, xin, round_out=False)
+    np.testing.assert_allclose(y.reshape(2, 6, 6, 128).transpose(0, 3, 1, 2), ref.numpy(), rtol=0, atol=1e-5)
+
+
+def test_program_tables_are_tma_legal():
+    torch.manual_seed(0)
+    for progs in (nets.generator_programs(port.Generator(100, 1, 64).state_dict()),
+                  nets.discriminator_programs(port.Discriminator(1, 64).state_dict())):
+        for p in progs:
+            assert p.steps[:, 0].min() >= 0 and (p.steps[:, 0] + L.KCHUNK).max() <= p.in_pitch
+            assert (p.steps[:, 0] % 8 == 0).all() and p.in_pitch % 8 == 0
+            assert (p.steps[:, 1] + p.mma_n).max() <= p.wpack.shape[0]
+            assert (p.steps[:, 2] + p.mma_n).max() <= p.nt
+            assert p.nt <= 256 and p.mma_n % 16 == 0
+            first = p.steps[p.jobs[:, 0], 3] & L.STEP_ACCUM
+            assert (first == 0).all(), "first step of every job must overwrite its accumulator"

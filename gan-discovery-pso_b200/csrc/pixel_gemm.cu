@@ -1,0 +1,467 @@
+// Pixel-GEMM engine: executes the layer programs of psob/lowering.py on sm_100a.
+//
+//   one CTA per SM, persistent over work items (particle tile of 128 rows, job)
+//   warp 0      TMA producer   : A tile [128 particles x 64 ch] + B tile [mma_n x 64] per step,
+//                                SWIZZLE_128B, n_stages-deep mbarrier ring
+//   warp 1      MMA issuer     : 4 x tcgen05.mma (K = 16 each) per step into a TMEM accumulator
+//                                (2 accumulator buffers of nt columns), tcgen05.commit frees stages
+//   warps 2..5  epilogue       : tcgen05.ld -> bias + activation -> bf16 / fp32 global stores
+//
+// Replaces the cuDNN calls behind nn.ConvTranspose2d / nn.Conv2d in Generator.forward /
+// Discriminator.forward (src/utils/util_dcgan.py:103-149).  A SIMT interpreter of the same tables
+// is kept for bring-up and tests (PSOB_IMPL_SIMT); the product path is PSOB_IMPL_TCGEN05.
+#include "psob_common.cuh"
+#include "umma.cuh"
+
+#include <cuda.h>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+namespace psob {
+
+constexpr int kMaxStages = 8;
+constexpr int kTileM = 128;
+constexpr int kKChunk = 64;
+constexpr int kATileBytes = kTileM * kKChunk * 2;   // 16 KB
+constexpr int kSmemLimit = 232448;                  // 227 KB per CTA on sm_100
+constexpr int kBarBytes = 256;
+constexpr int kThreads = 192;
+
+struct EngineParams {
+  const int4* steps;
+  const int4* jobs;          // 2 x int4 per job
+  const int* col_map;
+  const int* col_map32;
+  const float* bias;
+  __nv_bfloat16* y;
+  float* y32;
+  long long P;
+  long long n_items;
+  int n_jobs;
+  int mma_n, nt, cc, act, out_pitch, out32_pitch, vec8;
+  int b_resident, n_wrows;
+  int n_stages, stage_bytes, res_off, bar_off;
+  uint32_t idesc, tmem_cols;
+};
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+  switch (act) {
+    case PSOB_ACT_RELU: return fmaxf(v, 0.f);
+    case PSOB_ACT_LEAKY: return v > 0.f ? v : 0.2f * v;
+    case PSOB_ACT_TANH: return tanhf(v);
+    case PSOB_ACT_SIGMOID: return 1.f / (1.f + expf(-v));
+    default: return v;
+  }
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const EngineParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (base - raw);
+  const uint32_t bars = base + p.bar_off;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (kMaxStages + s); };
+  auto tfull_bar = [&](int b) { return bars + 8u * (2 * kMaxStages + b); };
+  auto tempty_bar = [&](int b) { return bars + 8u * (2 * kMaxStages + 2 + b); };
+  const uint32_t res_bar = bars + 8u * (2 * kMaxStages + 4);
+  const uint32_t tmem_slot = bars + 8u * (2 * kMaxStages + 5);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.n_stages; ++s) {
+      ptx::mbar_init(full_bar(s), 1);
+      ptx::mbar_init(empty_bar(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(tfull_bar(b), 1);
+      ptx::mbar_init(tempty_bar(b), 4);
+    }
+    ptx::mbar_init(res_bar, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, p.tmem_cols);
+    ptx::tmem_relinquish();
+  }
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gbase + p.bar_off + 8 * (2 * kMaxStages + 5));
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      if (p.b_resident) {
+        ptx::mbar_arrive_expect_tx(res_bar, (uint32_t)p.n_wrows * 128u);
+        for (int r = 0; r < p.n_wrows; r += p.mma_n)
+          ptx::tma_load_2d(base + p.res_off + (uint32_t)r * 128u, &tmB, 0, r, res_bar);
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (long long item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        const int ptile = (int)(item / p.n_jobs);
+        const int job = (int)(item - (long long)ptile * p.n_jobs);
+        const int4 j0 = __ldg(p.jobs + 2 * job);
+        for (int s = j0.x; s < j0.x + j0.y; ++s) {
+          const int4 st = __ldg(p.steps + s);
+          ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
+          const bool res = (st.w & 2) != 0;
+          ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)p.mma_n * 128u));
+          const uint32_t a_dst = base + (uint32_t)stage * p.stage_bytes;
+          ptx::tma_load_2d(a_dst, &tmA, st.x, ptile * kTileM, full_bar(stage));
+          if (!res) ptx::tma_load_2d(a_dst + kATileBytes, &tmB, 0, st.y, full_bar(stage));
+          if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (p.b_resident) ptx::mbar_wait(res_bar, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t it = 0;
+    for (long long item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
+      const int ptile = (int)(item / p.n_jobs);
+      const int job = (int)(item - (long long)ptile * p.n_jobs);
+      const int4 j0 = __ldg(p.jobs + 2 * job);
+      const uint32_t buf = it & 1u, use = it >> 1;
+      ptx::mbar_wait(tempty_bar(buf), (use & 1u) ^ 1u);
+      ptx::tc_fence_after();
+      for (int s = j0.x; s < j0.x + j0.y; ++s) {
+        const int4 st = __ldg(p.steps + s);
+        ptx::mbar_wait(full_bar(stage), phase);
+        ptx::tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_addr = base + (uint32_t)stage * p.stage_bytes;
+          const uint32_t b_addr = (st.w & 2) ? base + p.res_off + (uint32_t)st.y * 128u : a_addr + kATileBytes;
+          const uint64_t adesc = ptx::smem_desc_sw128(a_addr);
+          const uint64_t bdesc = ptx::smem_desc_sw128(b_addr);
+          const uint32_t d = tmem_base + buf * (uint32_t)p.nt + (uint32_t)st.z;
+#pragma unroll
+          for (int k = 0; k < kKChunk / 16; ++k)   // +32 B per K=16 slice inside the 128 B swizzle row
+            ptx::umma_bf16(d, adesc + 2u * k, bdesc + 2u * k, p.idesc, (uint32_t)((st.w & 1) | (k > 0)));
+          ptx::umma_commit(empty_bar(stage));
+        }
+        __syncwarp();
+        if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
+      }
+      if (lane == 0) ptx::umma_commit(tfull_bar(buf));
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (TMEM lane quadrant = warp % 4)
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    uint32_t it = 0;
+    for (long long item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
+      const int ptile = (int)(item / p.n_jobs);
+      const int job = (int)(item - (long long)ptile * p.n_jobs);
+      const int4 j0 = __ldg(p.jobs + 2 * job);
+      const int4 j1 = __ldg(p.jobs + 2 * job + 1);
+      const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
+      const float* bias = p.bias + (size_t)j1.z * p.nt;
+      const uint32_t buf = it & 1u, use = it >> 1;
+      const long long particle = (long long)ptile * kTileM + row;
+      const bool valid = particle < p.P;
+      __nv_bfloat16* yrow = p.y ? p.y + particle * p.out_pitch + j0.z : nullptr;
+      float* y32row = p.y32 ? p.y32 + particle * p.out32_pitch + j0.w : nullptr;
+      ptx::mbar_wait(tfull_bar(buf), use & 1u);
+      ptx::tc_fence_after();
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.nt;
+      for (int c0 = 0; c0 < p.nt; c0 += 16) {
+        uint32_t v[16];
+        __syncwarp();                       // tcgen05.ld is .sync.aligned: reconverge after the masked stores
+        ptx::tmem_ld_x16(tbase + (uint32_t)c0, v);
+        ptx::tmem_ld_wait();
+        if (!valid) {
+          // rows past P hold zero-filled TMA data: nothing to store
+        } else if (p.vec8) {
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            const int n = c0 + 8 * g;
+            const int pix = n / p.cc;
+            const int cm = __ldg(p.col_map + n);
+            if (cm < 0 || !((mask >> pix) & 1ull)) continue;
+            float f[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = apply_act(__uint_as_float(v[8 * g + i]) + __ldg(bias + n + i), p.act);
+            uint4 o;
+            o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+            o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+            *reinterpret_cast<uint4*>(yrow + cm) = o;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int n = c0 + i;
+            const int pix = n / p.cc;
+            if (pix < 64 && !((mask >> pix) & 1ull)) continue;
+            const float f = apply_act(__uint_as_float(v[i]) + __ldg(bias + n), p.act);
+            if (yrow) { const int cm = __ldg(p.col_map + n); if (cm >= 0) yrow[cm] = __float2bfloat16_rn(f); }
+            if (y32row) { const int cm = __ldg(p.col_map32 + n); if (cm >= 0) y32row[cm] = f; }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(tempty_bar(buf));
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// SIMT interpreter of the same tables (bring-up / tests).  grid = (n_jobs, n_ptiles).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+pixel_gemm_simt_kernel(const __nv_bfloat16* __restrict__ x, long long x_pitch, const __nv_bfloat16* __restrict__ w, const EngineParams p) {
+  const int job = blockIdx.x;
+  const long long ptile = blockIdx.y;
+  const int4 j0 = p.jobs[2 * job];
+  const int4 j1 = p.jobs[2 * job + 1];
+  const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
+  const float* bias = p.bias + (size_t)j1.z * p.nt;
+  for (int idx = threadIdx.x; idx < kTileM * p.nt; idx += 256) {
+    const int row = idx / p.nt, n = idx - row * p.nt;
+    const long long particle = ptile * kTileM + row;
+    if (particle >= p.P) continue;
+    const int pix = n / p.cc;
+    if (pix < 64 && !((mask >> pix) & 1ull)) continue;
+    float acc = 0.f;
+    for (int s = j0.x; s < j0.x + j0.y; ++s) {
+      const int4 st = p.steps[s];
+      if (n < st.z || n >= st.z + p.mma_n) continue;
+      if (!(st.w & 1)) acc = 0.f;
+      const __nv_bfloat16* a = x + particle * x_pitch + st.x;
+      const __nv_bfloat16* b = w + (size_t)(st.y + n - st.z) * kKChunk;
+      for (int k = 0; k < kKChunk; ++k) acc += __bfloat162float(a[k]) * __bfloat162float(b[k]);
+    }
+    const float f = apply_act(acc + bias[n], p.act);
+    if (p.y) { const int cm = p.col_map[n]; if (cm >= 0) p.y[particle * p.out_pitch + j0.z + cm] = __float2bfloat16_rn(f); }
+    if (p.y32) { const int cm = p.col_map32[n]; if (cm >= 0) p.y32[particle * p.out32_pitch + j0.w + cm] = f; }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// bf16 matrix [rows, cols] with row pitch `pitch` elements; box = [box_rows x 64], SWIZZLE_128B
+static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, uint64_t pitch, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return fail(PSOB_E_DEVICE, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {pitch * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kKChunk, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail((int)r, "cuTensorMapEncodeTiled failed with CUresult %d (cols=%llu rows=%llu pitch=%llu box_rows=%u)",
+                                     (int)r, (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)pitch, box_rows);
+  return 0;
+}
+
+}  // namespace psob
+
+using namespace psob;
+
+struct psob_layer {
+  psob_layer_desc d;          // scalar fields only (host pointers are not kept)
+  int4* steps = nullptr;
+  int4* jobs = nullptr;
+  int* col_map = nullptr;
+  int* col_map32 = nullptr;
+  float* bias = nullptr;
+  __nv_bfloat16* wpack = nullptr;
+  CUtensorMap tmB;
+  bool have_tmB = false;
+  int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, smem_bytes = 0;
+  uint32_t tmem_cols = 0;
+  int sm_count = 0;
+  int device = -1;
+};
+
+extern "C" {
+
+int psob_layer_destroy(psob_layer* l) {
+  if (!l) return 0;
+  cudaFree(l->steps); cudaFree(l->jobs); cudaFree(l->col_map); cudaFree(l->col_map32); cudaFree(l->bias); cudaFree(l->wpack);
+  delete l;
+  return 0;
+}
+
+int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
+  if (!d || !out) return fail(PSOB_E_ARG, "psob_layer_create: null argument");
+  *out = nullptr;
+  if (d->mma_n % 16 || d->mma_n < 16 || d->mma_n > 256 || d->nt % 16 || d->nt < d->mma_n || d->nt > 256)
+    return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: need 16 <= mma_n <= nt <= 256, multiples of 16 (mma_n=%d nt=%d)", d->mma_n, d->nt);
+  if (d->n_steps <= 0 || d->n_jobs <= 0 || d->n_wrows <= 0 || d->n_bias_rows <= 0 || d->cc <= 0)
+    return fail(PSOB_E_ARG, "psob_layer_create: empty program");
+  if (!d->wpack || !d->steps || !d->jobs || !d->col_map || !d->col_map32 || !d->bias)
+    return fail(PSOB_E_ARG, "psob_layer_create: null table");
+  if (d->in_pitch % 8 || (d->out_pitch == 0 && d->out32_pitch == 0))
+    return fail(PSOB_E_ARG, "psob_layer_create: in_pitch %% 8 != 0 or no output");
+  if (d->vec8 && (d->out32_pitch != 0 || d->out_pitch % 8 || d->cc % 8))
+    return fail(PSOB_E_ARG, "psob_layer_create: vec8 needs bf16-only output with 16-byte aligned rows");
+  // validate the tables so a bad program can never fault on the device
+  for (int s = 0; s < d->n_steps; ++s) {
+    const int32_t* st = d->steps + 4 * s;
+    if (st[0] < 0 || st[0] % 8 || st[0] + kKChunk > d->in_pitch) return fail(PSOB_E_ARG, "step %d: a_col %d out of range", s, st[0]);
+    if (st[1] < 0 || st[1] % 8 || st[1] + d->mma_n > d->n_wrows) return fail(PSOB_E_ARG, "step %d: b_row %d out of range", s, st[1]);
+    if (st[2] < 0 || st[2] % 16 || st[2] + d->mma_n > d->nt) return fail(PSOB_E_ARG, "step %d: d_col %d out of range", s, st[2]);
+    if (((st[3] & 2) != 0) != (d->b_resident != 0)) return fail(PSOB_E_ARG, "step %d: resident flag disagrees with the layer", s);
+  }
+  long long max_cm = -1, max_cm32 = -1;
+  for (int n = 0; n < d->nt; ++n) {
+    if (d->col_map[n] > max_cm) max_cm = d->col_map[n];
+    if (d->col_map32[n] > max_cm32) max_cm32 = d->col_map32[n];
+    if (d->vec8 && d->col_map[n] >= 0 && n % 8 == 0 && d->col_map[n] % 8) return fail(PSOB_E_ARG, "col_map[%d] not 8-aligned for vec8", n);
+  }
+  for (int j = 0; j < d->n_jobs; ++j) {
+    const int32_t* jb = d->jobs + 8 * j;
+    if (jb[0] < 0 || jb[1] <= 0 || jb[0] + jb[1] > d->n_steps) return fail(PSOB_E_ARG, "job %d: step range out of bounds", j);
+    if (jb[6] < 0 || jb[6] >= d->n_bias_rows) return fail(PSOB_E_ARG, "job %d: bias row out of range", j);
+    if (d->vec8 && jb[2] % 8) return fail(PSOB_E_ARG, "job %d: out_base not 8-aligned for vec8", j);
+    // stores are masked per pixel, so only enabled pixels must stay inside the row
+    const unsigned long long mask = (unsigned long long)(uint32_t)jb[4] | ((unsigned long long)(uint32_t)jb[5] << 32);
+    for (int n = 0; n < d->nt; ++n) {
+      int pix = n / d->cc;
+      if (pix < 64 && !((mask >> pix) & 1ull)) continue;
+      if (d->out_pitch && d->col_map[n] >= 0) {
+        long long o = (long long)jb[2] + d->col_map[n];
+        if (o < 0 || o >= d->out_pitch) return fail(PSOB_E_ARG, "job %d col %d: bf16 store offset %lld outside [0,%d)", j, n, o, d->out_pitch);
+      }
+      if (d->out32_pitch && d->col_map32[n] >= 0) {
+        long long o = (long long)jb[3] + d->col_map32[n];
+        if (o < 0 || o >= d->out32_pitch) return fail(PSOB_E_ARG, "job %d col %d: fp32 store offset %lld outside [0,%d)", j, n, o, d->out32_pitch);
+      }
+    }
+  }
+  (void)max_cm; (void)max_cm32;
+
+  psob_layer* l = new (std::nothrow) psob_layer();
+  if (!l) return fail(PSOB_E_ARG, "psob_layer_create: out of host memory");
+  l->d = *d;
+  l->d.wpack = nullptr; l->d.steps = nullptr; l->d.jobs = nullptr; l->d.col_map = nullptr; l->d.col_map32 = nullptr; l->d.bias = nullptr;
+#define PSOB_CUDA_L(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { psob_layer_destroy(l); \
+    return fail((int)e__, "%s failed: %s", #call, cudaGetErrorString(e__)); } } while (0)
+  PSOB_CUDA_L(cudaGetDevice(&l->device));
+  PSOB_CUDA_L(cudaDeviceGetAttribute(&l->sm_count, cudaDevAttrMultiProcessorCount, l->device));
+  PSOB_CUDA_L(cudaMalloc(&l->steps, sizeof(int4) * d->n_steps));
+  PSOB_CUDA_L(cudaMalloc(&l->jobs, sizeof(int4) * 2 * d->n_jobs));
+  PSOB_CUDA_L(cudaMalloc(&l->col_map, sizeof(int) * d->nt));
+  PSOB_CUDA_L(cudaMalloc(&l->col_map32, sizeof(int) * d->nt));
+  PSOB_CUDA_L(cudaMalloc(&l->bias, sizeof(float) * d->nt * d->n_bias_rows));
+  PSOB_CUDA_L(cudaMalloc(&l->wpack, (size_t)d->n_wrows * kKChunk * 2));
+  PSOB_CUDA_L(cudaMemcpy(l->steps, d->steps, sizeof(int4) * d->n_steps, cudaMemcpyHostToDevice));
+  PSOB_CUDA_L(cudaMemcpy(l->jobs, d->jobs, sizeof(int4) * 2 * d->n_jobs, cudaMemcpyHostToDevice));
+  PSOB_CUDA_L(cudaMemcpy(l->col_map, d->col_map, sizeof(int) * d->nt, cudaMemcpyHostToDevice));
+  PSOB_CUDA_L(cudaMemcpy(l->col_map32, d->col_map32, sizeof(int) * d->nt, cudaMemcpyHostToDevice));
+  PSOB_CUDA_L(cudaMemcpy(l->bias, d->bias, sizeof(float) * d->nt * d->n_bias_rows, cudaMemcpyHostToDevice));
+  PSOB_CUDA_L(cudaMemcpy(l->wpack, d->wpack, (size_t)d->n_wrows * kKChunk * 2, cudaMemcpyHostToDevice));
+#undef PSOB_CUDA_L
+
+  // shared-memory plan
+  const int b_tile = d->mma_n * 128;
+  l->stage_bytes = kATileBytes + (d->b_resident ? 0 : b_tile);
+  const int res_bytes = d->b_resident ? d->n_wrows * 128 : 0;
+  int avail = kSmemLimit - 1024 - kBarBytes - res_bytes;
+  l->n_stages = avail / l->stage_bytes;
+  if (l->n_stages > kMaxStages) l->n_stages = kMaxStages;
+  if (l->n_stages < 2) {
+    psob_layer_destroy(l);
+    return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: resident weights (%d B) leave no room for a 2-stage ring", res_bytes);
+  }
+  l->res_off = l->n_stages * l->stage_bytes;
+  l->bar_off = l->res_off + res_bytes;
+  l->smem_bytes = l->bar_off + kBarBytes + 1024;
+  uint32_t cols = 32;
+  while (cols < (uint32_t)(2 * d->nt)) cols <<= 1;
+  l->tmem_cols = cols;
+  *out = l;
+  return 0;
+}
+
+int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, int32_t impl, psob_stream_t s) {
+  if (!l || !x || P <= 0) return fail(PSOB_E_ARG, "psob_layer_run: bad arguments");
+  const psob_layer_desc& d = l->d;
+  if (x_pitch < d.in_pitch || x_pitch % 8 || !aligned16(x)) return fail(PSOB_E_ARG, "psob_layer_run: x_pitch %lld < in_pitch %d, or misaligned", (long long)x_pitch, d.in_pitch);
+  if ((d.out_pitch && !y && !(d.out32_pitch && y32)) || (!d.out_pitch && !y32)) return fail(PSOB_E_ARG, "psob_layer_run: missing output buffer");
+  if (y && !aligned16(y)) return fail(PSOB_E_ARG, "psob_layer_run: y must be 16-byte aligned");
+  EngineParams p;
+  p.steps = l->steps; p.jobs = l->jobs; p.col_map = l->col_map; p.col_map32 = l->col_map32; p.bias = l->bias;
+  p.y = d.out_pitch ? reinterpret_cast<__nv_bfloat16*>(y) : nullptr;
+  p.y32 = d.out32_pitch ? y32 : nullptr;
+  p.P = P;
+  const long long n_ptiles = (P + kTileM - 1) / kTileM;
+  p.n_items = n_ptiles * d.n_jobs;
+  p.n_jobs = d.n_jobs;
+  p.mma_n = d.mma_n; p.nt = d.nt; p.cc = d.cc; p.act = d.act; p.out_pitch = d.out_pitch; p.out32_pitch = d.out32_pitch;
+  p.vec8 = (d.vec8 && p.y) ? 1 : 0;
+  p.b_resident = d.b_resident; p.n_wrows = d.n_wrows;
+  p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
+  p.idesc = make_idesc_bf16(kTileM, d.mma_n);
+  p.tmem_cols = l->tmem_cols;
+
+  if (impl == PSOB_IMPL_SIMT) {
+    if (n_ptiles > 65535) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: SIMT bring-up path is limited to 65535 particle tiles");
+    dim3 grid((unsigned)d.n_jobs, (unsigned)n_ptiles);
+    pixel_gemm_simt_kernel<<<grid, 256, 0, (cudaStream_t)s>>>(reinterpret_cast<const __nv_bfloat16*>(x), x_pitch, l->wpack, p);
+    PSOB_LAUNCH_CHECK("pixel_gemm_simt_kernel");
+    return 0;
+  }
+  if (impl != PSOB_IMPL_TCGEN05) return fail(PSOB_E_ARG, "psob_layer_run: unknown impl %d", impl);
+
+  if (!l->have_tmB) {
+    int rc = make_tmap(&l->tmB, l->wpack, kKChunk, (uint64_t)d.n_wrows, kKChunk, (uint32_t)d.mma_n);
+    if (rc) return rc;
+    PSOB_CUDA(cudaFuncSetAttribute(pixel_gemm_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    l->have_tmB = true;
+  }
+  CUtensorMap tmA;
+  int rc = make_tmap(&tmA, x, (uint64_t)x_pitch, (uint64_t)P, (uint64_t)x_pitch, kTileM);
+  if (rc) return rc;
+  long long grid = p.n_items < l->sm_count ? p.n_items : l->sm_count;
+  pixel_gemm_umma_kernel<<<(unsigned)grid, kThreads, l->smem_bytes, (cudaStream_t)s>>>(tmA, l->tmB, p);
+  PSOB_LAUNCH_CHECK("pixel_gemm_umma_kernel");
+  return 0;
+}
+
+}  // extern "C"

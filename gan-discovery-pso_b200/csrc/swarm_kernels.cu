@@ -1,0 +1,452 @@
+// PSO state kernels of libpsob.so: velocity/position update with in-kernel Philox, personal
+// best + min-loc, global-best record/apply, fitness transforms.  All HBM-bound elementwise or
+// reduction work on fp32 SoA state [P, D]; see include/psob.h for the reference lines each
+// entry point replaces.
+#include "psob_common.cuh"
+
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+namespace psob {
+thread_local char g_err[512] = "";
+
+// ------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al., SC'11).  counter = (particle, iteration, 0, 0), key = seed.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                              uint32_t k0, uint32_t k1, uint32_t& o0, uint32_t& o1) {
+  constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+    uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += W0; k1 += W1;
+  }
+  o0 = c0; o1 = c1;
+}
+
+struct UpdateParams {
+  float4* pos; float4* vel; float4* pbest;
+  const float4* gbest;
+  const uint8_t* improved;
+  const float* r1; const float* r2;
+  __nv_bfloat16* z;
+  const psob_iter_state* dyn;
+  uint32_t total4, d4;
+  int32_t z_pitch;
+  float w, c_cogn, c_soci, v_max, lo, hi;
+  uint32_t seed_lo, seed_hi, iteration;
+  uint64_t index_offset;
+  int clamp_v, clamp_x;
+};
+
+__device__ __forceinline__ float move1(float x, float v, float pb, float g, float w, float c1, float c2,
+                                       const UpdateParams& a, float& nv_out) {
+  // (w*vel + c_soci*r2*(pbest-pos)) + c_cogn*r1*(gbest-pos) — same association as
+  // src/pso/util_pso.py:44-49; explicit _rn ops keep ptxas from contracting into FMAs so the
+  // result is bit-identical to the fp32 restatement in oracle/port.py.
+  float inertia = __fmul_rn(w, v);
+  float cog = __fmul_rn(c1, __fsub_rn(g, x));
+  float soc = __fmul_rn(c2, __fsub_rn(pb, x));
+  float nv = __fadd_rn(__fadd_rn(inertia, soc), cog);
+  if (a.clamp_v) nv = fminf(fmaxf(nv, -a.v_max), a.v_max);
+  float nx = __fadd_rn(x, nv);
+  if (a.clamp_x) nx = fminf(fmaxf(nx, a.lo), a.hi);
+  nv_out = nv;
+  return nx;
+}
+
+template <bool kPhilox>
+__global__ void __launch_bounds__(256) pso_update_kernel(const UpdateParams a) {
+  uint32_t i = blockIdx.x * 256u + threadIdx.x;
+  if (i >= a.total4) return;
+  uint32_t p = i / a.d4;
+  uint32_t j = i - p * a.d4;
+  const float w = a.dyn ? a.dyn->w : a.w;
+  float r1, r2;
+  if (kPhilox) {
+    uint64_t gidx = a.index_offset + p;
+    uint32_t x0, x1;
+    philox4x32_10((uint32_t)gidx, a.dyn ? a.dyn->iteration : a.iteration, 0u, 0u, a.seed_lo, a.seed_hi, x0, x1);
+    r1 = (float)(x0 >> 8) * 5.9604644775390625e-08f;   // 2^-24
+    r2 = (float)(x1 >> 8) * 5.9604644775390625e-08f;
+  } else {
+    r1 = __ldg(a.r1 + p);
+    r2 = __ldg(a.r2 + p);
+  }
+  float4 x = __ldcs(a.pos + i);
+  float4 v = __ldcs(a.vel + i);
+  float4 g = __ldg(a.gbest + j);
+  float4 pb;
+  if (a.improved != nullptr && a.improved[p]) {
+    pb = x;
+    __stcs(a.pbest + i, x);
+  } else {
+    pb = __ldcs(a.pbest + i);
+  }
+  float c1 = __fmul_rn(a.c_cogn, r1);
+  float c2 = __fmul_rn(a.c_soci, r2);
+  float4 nx, nv;
+  nx.x = move1(x.x, v.x, pb.x, g.x, w, c1, c2, a, nv.x);
+  nx.y = move1(x.y, v.y, pb.y, g.y, w, c1, c2, a, nv.y);
+  nx.z = move1(x.z, v.z, pb.z, g.z, w, c1, c2, a, nv.z);
+  nx.w = move1(x.w, v.w, pb.w, g.w, w, c1, c2, a, nv.w);
+  __stcs(a.vel + i, nv);
+  __stcs(a.pos + i, nx);
+  if (a.z != nullptr) {
+    __nv_bfloat162 lo2 = __floats2bfloat162_rn(nx.x, nx.y);
+    __nv_bfloat162 hi2 = __floats2bfloat162_rn(nx.z, nx.w);
+    uint2 packed;
+    packed.x = *reinterpret_cast<uint32_t*>(&lo2);
+    packed.y = *reinterpret_cast<uint32_t*>(&hi2);
+    *reinterpret_cast<uint2*>(a.z + (size_t)p * a.z_pitch + 4 * j) = packed;
+  }
+}
+
+__global__ void pack_latent_kernel(const float4* pos, uint32_t total4, uint32_t d4, __nv_bfloat16* z, int z_pitch) {
+  uint32_t i = blockIdx.x * 256u + threadIdx.x;
+  if (i >= total4) return;
+  uint32_t p = i / d4, j = i - p * d4;
+  float4 x = __ldcs(pos + i);
+  __nv_bfloat162 lo2 = __floats2bfloat162_rn(x.x, x.y), hi2 = __floats2bfloat162_rn(x.z, x.w);
+  uint2 packed;
+  packed.x = *reinterpret_cast<uint32_t*>(&lo2);
+  packed.y = *reinterpret_cast<uint32_t*>(&hi2);
+  *reinterpret_cast<uint2*>(z + (size_t)p * z_pitch + 4 * j) = packed;
+}
+
+__global__ void pack_latent_scalar_kernel(const float* pos, long long total, int D, __nv_bfloat16* z, int z_pitch) {
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  long long p = i / D;
+  int j = (int)(i - p * D);
+  z[p * z_pitch + j] = __float2bfloat16_rn(pos[i]);
+}
+
+// ------------------------------------------------------------------------------------------
+// personal best + min-loc
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long k) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long other = __shfl_xor_sync(0xffffffffu, k, o);
+    k = other < k ? other : k;
+  }
+  return k;
+}
+
+__global__ void __launch_bounds__(256) pbest_minloc_kernel(const float* __restrict__ fit, float* __restrict__ pbest_val,
+                                                           uint8_t* __restrict__ improved, long long P,
+                                                           unsigned long long index_offset,
+                                                           unsigned long long* __restrict__ key) {
+  __shared__ unsigned long long s_k[8];
+  unsigned long long k = ~0ull;
+  for (long long p = (long long)blockIdx.x * 256 + threadIdx.x; p < P; p += (long long)gridDim.x * 256) {
+    float f = fit[p];
+    float pv = pbest_val[p];
+    bool imp = f < pv;                       // strict; NaN never improves (src/pso/util_pso.py:122)
+    if (imp) { pbest_val[p] = f; pv = f; }
+    improved[p] = imp ? 1 : 0;
+    unsigned long long kk = ((unsigned long long)order_key(pv) << 32) | (unsigned long long)(uint32_t)(index_offset + p);
+    k = kk < k ? kk : k;
+  }
+  k = warp_min_u64(k);
+  if ((threadIdx.x & 31) == 0) s_k[threadIdx.x >> 5] = k;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    k = threadIdx.x < 8 ? s_k[threadIdx.x] : ~0ull;
+    k = warp_min_u64(k);
+    if (threadIdx.x == 0) atomicMin(key, k);
+  }
+}
+
+__global__ void gbest_candidate_kernel(const unsigned long long* key, const float* pos, const float* pbest_pos,
+                                       const uint8_t* improved, const float* pbest_val, long long P,
+                                       unsigned long long index_offset, int D, float* rec) {
+  unsigned long long k = *key;
+  long long local = (long long)(uint32_t)(k & 0xffffffffull) - (long long)(uint32_t)index_offset;
+  bool ok = local >= 0 && local < P;
+  if (threadIdx.x == 0) {
+    reinterpret_cast<uint32_t*>(rec)[0] = (uint32_t)(k & 0xffffffffull);
+    reinterpret_cast<uint32_t*>(rec)[1] = (uint32_t)(k >> 32);
+    rec[2] = ok ? pbest_val[local] : INFINITY;
+    rec[3] = 0.f;
+  }
+  if (ok) {
+    const float* src = (improved != nullptr && improved[local]) ? pos + local * D : pbest_pos + local * D;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) rec[4 + d] = src[d];
+  } else {
+    for (int d = threadIdx.x; d < D; d += blockDim.x) rec[4 + d] = 0.f;
+  }
+}
+
+__global__ void gbest_apply_kernel(const float* recs, int n_rec, int D, float* gbest_val, float* gbest_pos, float* hist,
+                                   int hist_rows, psob_iter_state* dyn, float inertia_decay) {
+  __shared__ int s_best;
+  __shared__ int s_replace;
+  if (threadIdx.x == 0) {
+    unsigned long long best = ~0ull;
+    int bi = 0;
+    for (int r = 0; r < n_rec; ++r) {
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(recs + (size_t)r * (4 + D));
+      unsigned long long k = ((unsigned long long)w[1] << 32) | w[0];
+      if (k < best) { best = k; bi = r; }
+    }
+    float cand = recs[(size_t)bi * (4 + D) + 2];
+    float inc = *gbest_val;
+    bool rep = cand < inc;                    // equal never replaces (src/pso/util_pso.py:144)
+    if (rep) *gbest_val = cand;
+    if (hist != nullptr) {
+      int hrow = dyn ? (int)dyn->iteration : 0;
+      if (hrow >= hist_rows) hrow = hist_rows - 1;
+      hist[2 * hrow] = rep ? cand : inc;
+      hist[2 * hrow + 1] = rep ? 1.f : 0.f;
+    }
+    if (dyn != nullptr) {
+      // `if i > 1 and schedule_inertia: w = 0.99*w` runs after the global best and before the move
+      uint32_t i_now = dyn->iteration + 1;
+      dyn->iteration = i_now;
+      if (i_now > 1 && inertia_decay != 1.0f) dyn->w = inertia_decay * dyn->w;
+    }
+    s_best = bi;
+    s_replace = rep ? 1 : 0;
+  }
+  __syncthreads();
+  if (s_replace) {
+    const float* src = recs + (size_t)s_best * (4 + D) + 4;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) gbest_pos[d] = src[d];
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// fitness transforms
+// ------------------------------------------------------------------------------------------
+__global__ void score_fitness_kernel(const float* score, int stride, long long P, int mode, float thr, float eps, float* fit) {
+  long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  float s = fminf(__fadd_rn(score[p * stride], thr), 1.0f);     // torch.min(p + thr, 1)  (util_discovery.py:76,78)
+  fit[p] = mode == PSOB_MODE_IN_TRAINING ? __fadd_rn(s, eps) : __fadd_rn(__fsub_rn(1.0f, s), eps);
+}
+
+__global__ void softmax_select_kernel(const float* logits, int n_class, int class_idx, long long P, float* prob) {
+  long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const float* l = logits + p * n_class;
+  float m = -INFINITY;
+  for (int c = 0; c < n_class; ++c) m = fmaxf(m, l[c]);
+  float sum = 0.f;
+  for (int c = 0; c < n_class; ++c) sum += expf(l[c] - m);
+  prob[p] = expf(l[class_idx] - m) / sum;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// one group of `tpp` threads (32 or 256) per particle
+template <bool kBf16Target>
+__global__ void __launch_bounds__(256) recon_fitness_kernel(const float* __restrict__ img, const void* __restrict__ target,
+                                                            long long P, int n, int tpp, const float* __restrict__ fit_ass,
+                                                            float w_ass, float w_rec, float eps, float* __restrict__ fit) {
+  __shared__ float s_part[8];
+  int groups = 256 / tpp;
+  long long p = (long long)blockIdx.x * groups + threadIdx.x / tpp;
+  int t = threadIdx.x % tpp;
+  float acc = 0.f;
+  if (p < P) {
+    const float* x = img + p * n;
+    if (kBf16Target) {
+      const __nv_bfloat16* tg = reinterpret_cast<const __nv_bfloat16*>(target) + p * n;
+      for (int i = t; i < n; i += tpp) { float d = __bfloat162float(tg[i]) - x[i]; acc += d * d; }
+    } else {
+      const float* tg = reinterpret_cast<const float*>(target) + p * n;
+      for (int i = t; i < n; i += tpp) { float d = tg[i] - x[i]; acc += d * d; }
+    }
+  }
+  acc = warp_sum(acc);
+  if (tpp == 256) {
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      acc = threadIdx.x < 8 ? s_part[threadIdx.x] : 0.f;
+      acc = warp_sum(acc);
+    }
+  }
+  if (t == 0 && p < P) {
+    float mse = acc / (float)n;
+    float ass = fit_ass != nullptr ? w_ass * fit_ass[p] : 0.f;
+    fit[p] = ass + w_rec * mse + eps;        // util_discovery.py:97-101 (the caller's fit_ass already holds one eps)
+  }
+}
+
+__global__ void __launch_bounds__(256) rescale_minmax_kernel(const float* __restrict__ img, long long P, int n, float* __restrict__ out) {
+  // one warp per image (src/utils/util_data.py:129-135 with batch 1)
+  long long p = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (p >= P) return;
+  int lane = threadIdx.x & 31;
+  const float* x = img + p * n;
+  float lo = INFINITY, hi = -INFINITY;
+  for (int i = lane; i < n; i += 32) { float v = x[i]; lo = fminf(lo, v); hi = fmaxf(hi, v); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  float range = __fsub_rn(hi, lo);
+  float* y = out + p * n;
+  for (int i = lane; i < n; i += 32) y[i] = __fdiv_rn(__fsub_rn(x[i], lo), range);
+}
+
+__global__ void pack_image_kernel(const float* __restrict__ img, long long P, __nv_bfloat16* __restrict__ out) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long total = P * 992;
+  if (i >= total) return;
+  long long p = i / 992;
+  int r = (int)(i - p * 992);
+  int y = r / 32 - 1, x = r % 32 - 1;
+  float v = (y >= 0 && y < 28 && x >= 0 && x < 28) ? img[p * 784 + y * 28 + x] : 0.f;
+  out[i] = __float2bfloat16_rn(v);
+}
+
+}  // namespace psob
+
+using namespace psob;
+
+extern "C" {
+
+int psob_version(void) { return PSOB_VERSION; }
+const char* psob_last_error(void) { return g_err; }
+
+int psob_device_info(int* cc_major, int* cc_minor, int* sm_count) {
+  int dev = 0;
+  PSOB_CUDA(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  PSOB_CUDA(cudaGetDeviceProperties(&prop, dev));
+  if (cc_major) *cc_major = prop.major;
+  if (cc_minor) *cc_minor = prop.minor;
+  if (sm_count) *sm_count = prop.multiProcessorCount;
+  return 0;
+}
+
+int psob_update(const psob_update_args* a, psob_stream_t s) {
+  if (!a || !a->pos || !a->vel || !a->pbest_pos || !a->gbest_pos) return fail(PSOB_E_ARG, "psob_update: null state pointer");
+  if (a->P <= 0 || a->D <= 0 || a->D % 4) return fail(PSOB_E_ARG, "psob_update: need P > 0 and D %% 4 == 0 (D=%d)", a->D);
+  if (!aligned16(a->pos) || !aligned16(a->vel) || !aligned16(a->pbest_pos) || !aligned16(a->gbest_pos))
+    return fail(PSOB_E_ARG, "psob_update: state pointers must be 16-byte aligned");
+  if ((a->r1 == nullptr) != (a->r2 == nullptr)) return fail(PSOB_E_ARG, "psob_update: give both r1 and r2 or neither");
+  unsigned long long total4 = (unsigned long long)a->P * (a->D / 4);
+  if (total4 >= (1ull << 32)) return fail(PSOB_E_UNSUPPORTED, "psob_update: P*D/4 must be < 2^32");
+  if (a->z_bf16 && (a->z_pitch < a->D || a->z_pitch % 4 || (reinterpret_cast<uintptr_t>(a->z_bf16) & 7)))
+    return fail(PSOB_E_ARG, "psob_update: z_pitch must be >= D, a multiple of 4, z 8-byte aligned");
+  UpdateParams u;
+  u.pos = reinterpret_cast<float4*>(a->pos); u.vel = reinterpret_cast<float4*>(a->vel);
+  u.pbest = reinterpret_cast<float4*>(a->pbest_pos); u.gbest = reinterpret_cast<const float4*>(a->gbest_pos);
+  u.improved = a->improved; u.r1 = a->r1; u.r2 = a->r2; u.z = reinterpret_cast<__nv_bfloat16*>(a->z_bf16);
+  u.dyn = a->dyn;
+  u.total4 = (uint32_t)total4; u.d4 = (uint32_t)(a->D / 4); u.z_pitch = a->z_pitch;
+  u.w = a->w; u.c_cogn = a->c_cogn; u.c_soci = a->c_soci; u.v_max = a->v_max; u.lo = a->lo; u.hi = a->hi;
+  u.seed_lo = (uint32_t)(a->seed & 0xffffffffull); u.seed_hi = (uint32_t)(a->seed >> 32); u.iteration = a->iteration;
+  u.index_offset = a->index_offset;
+  u.clamp_v = std::isfinite(a->v_max) ? 1 : 0;
+  u.clamp_x = (std::isfinite(a->lo) || std::isfinite(a->hi)) ? 1 : 0;
+  unsigned blocks = (unsigned)((total4 + 255) / 256);
+  if (a->r1) pso_update_kernel<false><<<blocks, 256, 0, (cudaStream_t)s>>>(u);
+  else       pso_update_kernel<true><<<blocks, 256, 0, (cudaStream_t)s>>>(u);
+  PSOB_LAUNCH_CHECK("pso_update_kernel");
+  return 0;
+}
+
+int psob_pack_latent(const float* pos, int64_t P, int32_t D, void* z, int32_t z_pitch, psob_stream_t s) {
+  if (!pos || !z || P <= 0 || D <= 0 || z_pitch < D) return fail(PSOB_E_ARG, "psob_pack_latent: bad arguments");
+  if (D % 4 || z_pitch % 4 || !aligned16(pos) || (reinterpret_cast<uintptr_t>(z) & 7)) {
+    long long total = (long long)P * D;
+    pack_latent_scalar_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)s>>>(pos, total, D, reinterpret_cast<__nv_bfloat16*>(z), z_pitch);
+    PSOB_LAUNCH_CHECK("pack_latent_scalar_kernel");
+    return 0;
+  }
+  unsigned long long total4 = (unsigned long long)P * (D / 4);
+  if (total4 >= (1ull << 32)) return fail(PSOB_E_UNSUPPORTED, "psob_pack_latent: too large");
+  pack_latent_kernel<<<(unsigned)((total4 + 255) / 256), 256, 0, (cudaStream_t)s>>>(
+      reinterpret_cast<const float4*>(pos), (uint32_t)total4, (uint32_t)(D / 4), reinterpret_cast<__nv_bfloat16*>(z), z_pitch);
+  PSOB_LAUNCH_CHECK("pack_latent_kernel");
+  return 0;
+}
+
+int psob_pbest_minloc(const float* fit, float* pbest_val, uint8_t* improved, int64_t P, uint64_t index_offset,
+                      uint64_t* key, psob_stream_t s) {
+  if (!fit || !pbest_val || !improved || !key || P <= 0) return fail(PSOB_E_ARG, "psob_pbest_minloc: bad arguments");
+  if (index_offset + (uint64_t)P > (1ull << 32)) return fail(PSOB_E_UNSUPPORTED, "psob_pbest_minloc: global index must fit 32 bits");
+  PSOB_CUDA(cudaMemsetAsync(key, 0xFF, sizeof(uint64_t), (cudaStream_t)s));
+  long long blocks = (P + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  pbest_minloc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)s>>>(fit, pbest_val, improved, P, index_offset,
+                                                                    reinterpret_cast<unsigned long long*>(key));
+  PSOB_LAUNCH_CHECK("pbest_minloc_kernel");
+  return 0;
+}
+
+int psob_gbest_candidate(const uint64_t* key, const float* pos, const float* pbest_pos, const uint8_t* improved,
+                         const float* pbest_val, int64_t P, uint64_t index_offset, int32_t D, float* rec, psob_stream_t s) {
+  if (!key || !pos || !pbest_pos || !pbest_val || !rec || P <= 0 || D <= 0) return fail(PSOB_E_ARG, "psob_gbest_candidate: bad arguments");
+  gbest_candidate_kernel<<<1, 128, 0, (cudaStream_t)s>>>(reinterpret_cast<const unsigned long long*>(key), pos, pbest_pos,
+                                                        improved, pbest_val, P, index_offset, D, rec);
+  PSOB_LAUNCH_CHECK("gbest_candidate_kernel");
+  return 0;
+}
+
+int psob_gbest_apply(const float* recs, int32_t n_rec, int32_t D, float* gbest_val, float* gbest_pos, float* hist,
+                     int32_t hist_rows, psob_iter_state* dyn, float inertia_decay, psob_stream_t s) {
+  if (!recs || !gbest_val || !gbest_pos || n_rec <= 0 || D <= 0 || (hist && hist_rows <= 0)) return fail(PSOB_E_ARG, "psob_gbest_apply: bad arguments");
+  gbest_apply_kernel<<<1, 128, 0, (cudaStream_t)s>>>(recs, n_rec, D, gbest_val, gbest_pos, hist, hist_rows, dyn, inertia_decay);
+  PSOB_LAUNCH_CHECK("gbest_apply_kernel");
+  return 0;
+}
+
+int psob_score_fitness(const float* score, int32_t stride, int64_t P, int32_t mode, float thr, float eps, float* fit, psob_stream_t s) {
+  if (!score || !fit || P <= 0 || stride <= 0) return fail(PSOB_E_ARG, "psob_score_fitness: bad arguments");
+  if (mode != PSOB_MODE_IN_TRAINING && mode != PSOB_MODE_OUT_TRAINING) return fail(PSOB_E_ARG, "psob_score_fitness: unknown mode %d", mode);
+  score_fitness_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)s>>>(score, stride, P, mode, thr, eps, fit);
+  PSOB_LAUNCH_CHECK("score_fitness_kernel");
+  return 0;
+}
+
+int psob_softmax_select(const float* logits, int32_t n_class, int32_t class_idx, int64_t P, float* prob, psob_stream_t s) {
+  if (!logits || !prob || P <= 0 || n_class <= 0 || class_idx < 0 || class_idx >= n_class) return fail(PSOB_E_ARG, "psob_softmax_select: bad arguments");
+  softmax_select_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)s>>>(logits, n_class, class_idx, P, prob);
+  PSOB_LAUNCH_CHECK("softmax_select_kernel");
+  return 0;
+}
+
+int psob_recon_fitness(const float* img, const void* target, int32_t target_is_bf16, int64_t P, int32_t n, const float* fit_ass,
+                       float w_ass, float w_rec, float eps, float* fit, psob_stream_t s) {
+  if (!img || !target || !fit || P <= 0 || n <= 0) return fail(PSOB_E_ARG, "psob_recon_fitness: bad arguments");
+  int tpp = n >= 4096 ? 256 : 32;
+  long long groups = 256 / tpp;
+  unsigned blocks = (unsigned)((P + groups - 1) / groups);
+  if (target_is_bf16) recon_fitness_kernel<true><<<blocks, 256, 0, (cudaStream_t)s>>>(img, target, P, n, tpp, fit_ass, w_ass, w_rec, eps, fit);
+  else                recon_fitness_kernel<false><<<blocks, 256, 0, (cudaStream_t)s>>>(img, target, P, n, tpp, fit_ass, w_ass, w_rec, eps, fit);
+  PSOB_LAUNCH_CHECK("recon_fitness_kernel");
+  return 0;
+}
+
+int psob_rescale_minmax(const float* img, int64_t P, int32_t n, float* out, psob_stream_t s) {
+  if (!img || !out || P <= 0 || n <= 0) return fail(PSOB_E_ARG, "psob_rescale_minmax: bad arguments");
+  rescale_minmax_kernel<<<(unsigned)((P + 7) / 8), 256, 0, (cudaStream_t)s>>>(img, P, n, out);
+  PSOB_LAUNCH_CHECK("rescale_minmax_kernel");
+  return 0;
+}
+
+int psob_pack_image(const float* img, int64_t P, void* out_bf16, psob_stream_t s) {
+  if (!img || !out_bf16 || P <= 0) return fail(PSOB_E_ARG, "psob_pack_image: bad arguments");
+  long long total = P * 992;
+  pack_image_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)s>>>(img, P, reinterpret_cast<__nv_bfloat16*>(out_bf16));
+  PSOB_LAUNCH_CHECK("pack_image_kernel");
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,430 @@
+"""Device-side swarm engine: SoA PSO state in HBM, pixel-GEMM networks, one CUDA graph per
+iteration.  PyTorch is used for device memory, streams and (multi-GPU) torch.distributed only;
+all arithmetic of the hot path runs in libpsob.so kernels through the C ABI (`_ffi`).
+
+Iteration (mirrors Swarm.optimize, src/pso/util_pso.py:167-193, batched over the swarm):
+
+    img          = G(z)                       generator layers (tcgen05 pixel-GEMM)
+    fit          = fitness(img)               D-score | reconstruction | assessor callable
+    improved,key = pbest/min-loc(fit)
+    gbest        = apply(all_gather(candidate record))
+    pos,vel,z    = update(...)                Philox r1/r2 in-kernel (or injected)
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Callable, List, Optional
+
+import numpy as np
+import torch
+
+from . import _ffi, lowering as L, nets
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise _ffi.PsobError("psob needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+
+
+class Layer:
+    """One pixel-GEMM layer program resident on the current device."""
+
+    def __init__(self, prog: L.LayerProgram):
+        require_cuda()
+        self.prog = prog
+        wbits = np.ascontiguousarray(L.bf16_bits(prog.wpack))
+        steps = np.ascontiguousarray(prog.steps, dtype=np.int32)
+        jobs = np.ascontiguousarray(prog.jobs, dtype=np.int32)
+        cm = np.ascontiguousarray(prog.col_map, dtype=np.int32)
+        cm32 = np.ascontiguousarray(prog.col_map32, dtype=np.int32)
+        bias = np.ascontiguousarray(prog.bias, dtype=np.float32)
+        d = _ffi.LayerDesc(
+            mma_n=prog.mma_n, nt=prog.nt, cc=prog.cc, act=prog.act, in_pitch=prog.in_pitch,
+            out_pitch=prog.out_pitch, out32_pitch=prog.out32_pitch, b_resident=int(prog.b_resident),
+            vec8=int(prog.vec8), n_steps=prog.n_steps, n_jobs=prog.n_jobs, n_wrows=wbits.shape[0],
+            n_bias_rows=bias.shape[0], wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
+            col_map=cm.ctypes.data, col_map32=cm32.ctypes.data, bias=bias.ctypes.data)
+        h = C.c_void_p()
+        _ffi.check(_ffi.lib().psob_layer_create(C.byref(d), C.byref(h)), f"psob_layer_create({prog.name})")
+        self.handle = h
+
+    def run(self, x: torch.Tensor, P: int, y: Optional[torch.Tensor], y32: Optional[torch.Tensor], impl=_ffi.IMPL_TCGEN05):
+        assert x.dtype == torch.bfloat16 and x.is_cuda and x.dim() == 2 and x.stride(1) == 1
+        _ffi.check(_ffi.lib().psob_layer_run(self.handle, x.data_ptr(), x.stride(0), P, _ptr(y), _ptr(y32), impl, _stream()),
+                   f"psob_layer_run({self.prog.name})")
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                _ffi.lib().psob_layer_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+class Network:
+    """A stack of layers with its activation workspace for a fixed swarm size."""
+
+    def __init__(self, programs: List[L.LayerProgram], P: int, device=None, impl=_ffi.IMPL_TCGEN05):
+        require_cuda()
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.P = P
+        self.impl = impl
+        self.programs = programs
+        with torch.cuda.device(self.device):
+            self.layers = [Layer(p) for p in programs]
+            # zero-initialised so that channel padding and image borders that no job writes stay 0
+            self.acts = [torch.zeros(P, p.out_pitch, dtype=torch.bfloat16, device=self.device) if p.out_pitch else None
+                         for p in programs]
+            self.acts32 = [torch.zeros(P, p.out32_pitch, dtype=torch.float32, device=self.device) if p.out32_pitch else None
+                           for p in programs]
+
+    @property
+    def in_pitch(self) -> int:
+        return self.programs[0].in_pitch
+
+    def forward(self, x: torch.Tensor):
+        """x: bf16 [P, >= in_pitch].  Returns (last bf16 activation or None, last fp32 output or None)."""
+        cur = x
+        for layer, y, y32 in zip(self.layers, self.acts, self.acts32):
+            layer.run(cur, self.P, y, y32, self.impl)
+            cur = y
+        return self.acts[-1], self.acts32[-1]
+
+    @property
+    def macs_exact(self) -> int:
+        return sum(p.macs_exact for p in self.programs)
+
+    @property
+    def macs_issued(self) -> int:
+        return sum(p.macs_issued for p in self.programs)
+
+
+def _sd_numpy(sd):
+    return {k: (v.detach().cpu().numpy() if hasattr(v, "detach") else np.asarray(v)) for k, v in sd.items()}
+
+
+class GeneratorNet(Network):
+    """28x28 DCGAN generator / VQ-VAE-GAN decoder (src/utils/util_dcgan.py:128-149)."""
+
+    def __init__(self, state_dict, P, prefix="gen", device=None, impl=_ffi.IMPL_TCGEN05, m_last=2):
+        sd = _sd_numpy(state_dict)
+        if prefix is None:
+            prefix = "gen" if any(k.startswith("gen.") for k in sd) else "decoder"
+        self.z_dim = int(sd[f"{prefix}.0.0.weight"].shape[0])
+        if f"{prefix}.3.0.weight" in sd:
+            progs = nets.g256_programs(sd, prefix)
+        else:
+            progs = nets.generator_programs(sd, prefix, m_last=m_last)
+        super().__init__(progs, P, device, impl)
+        self.image_elems = progs[-1].out32_pitch
+
+    def image(self) -> torch.Tensor:
+        return self.acts32[-1]
+
+    def image_padded_bf16(self) -> Optional[torch.Tensor]:
+        return self.acts[-1]
+
+
+class DiscriminatorNet(Network):
+    """DCGAN discriminator on the padded bf16 image (src/utils/util_dcgan.py:103-125) -> sigmoid score fp32 [P,1]."""
+
+    def __init__(self, state_dict, P, prefix="disc", device=None, impl=_ffi.IMPL_TCGEN05):
+        super().__init__(nets.discriminator_programs(_sd_numpy(state_dict), prefix), P, device, impl)
+
+
+class EncoderNet(Network):
+    """Inverter encoder (src/inverter/utils_ae/util_inverter.py:164-184) -> latent fp32 [P, enc_dim]."""
+
+    def __init__(self, state_dict, P, prefix="enc", device=None, impl=_ffi.IMPL_TCGEN05):
+        super().__init__(nets.encoder_programs(_sd_numpy(state_dict), prefix), P, device, impl)
+
+
+# ----------------------------------------------------------------------------------------------
+# thin functional wrappers over the elementwise entry points (used by the engine and the tests)
+# ----------------------------------------------------------------------------------------------
+
+def pack_latent(pos: torch.Tensor, z: torch.Tensor):
+    P, D = pos.shape
+    _ffi.check(_ffi.lib().psob_pack_latent(pos.data_ptr(), P, D, z.data_ptr(), z.stride(0), _stream()), "psob_pack_latent")
+
+
+def pack_image(img: torch.Tensor, out: torch.Tensor):
+    _ffi.check(_ffi.lib().psob_pack_image(img.data_ptr(), img.shape[0], out.data_ptr(), _stream()), "psob_pack_image")
+
+
+def rescale_minmax(img: torch.Tensor, out: torch.Tensor):
+    P = img.shape[0]
+    _ffi.check(_ffi.lib().psob_rescale_minmax(img.data_ptr(), P, img.numel() // P, out.data_ptr(), _stream()), "psob_rescale_minmax")
+
+
+def score_fitness(score: torch.Tensor, fit: torch.Tensor, mode: str, thr=0.0, eps=0.1):
+    if mode not in ("optimize_in_training", "optimize_out_training"):
+        raise ValueError(mode)                                  # same error as src/pso/util_discovery.py:80
+    m = _ffi.MODE_IN_TRAINING if mode == "optimize_in_training" else _ffi.MODE_OUT_TRAINING
+    stride = score.stride(0) if score.dim() > 1 else 1
+    _ffi.check(_ffi.lib().psob_score_fitness(score.data_ptr(), stride, score.shape[0], m, thr, eps, fit.data_ptr(), _stream()),
+               "psob_score_fitness")
+
+
+def softmax_select(logits: torch.Tensor, class_idx: int, prob: torch.Tensor):
+    P, n = logits.shape
+    _ffi.check(_ffi.lib().psob_softmax_select(logits.data_ptr(), n, class_idx, P, prob.data_ptr(), _stream()), "psob_softmax_select")
+
+
+def recon_fitness(img: torch.Tensor, target: torch.Tensor, fit: torch.Tensor, fit_ass=None, w_ass=1.0, w_rec=1.0, eps=0.1):
+    P = img.shape[0]
+    n = img.numel() // P
+    assert target.numel() == img.numel() and target.dtype in (torch.float32, torch.bfloat16)
+    _ffi.check(_ffi.lib().psob_recon_fitness(img.data_ptr(), target.data_ptr(), int(target.dtype == torch.bfloat16), P, n,
+                                             _ptr(fit_ass), w_ass, w_rec, eps, fit.data_ptr(), _stream()), "psob_recon_fitness")
+
+
+def pso_update(pos, vel, pbest_pos, gbest_pos, *, improved=None, r1=None, r2=None, z=None, dyn=None, w=0.5, c_cogn=0.8,
+               c_soci=0.9, v_max=math.inf, lo=-math.inf, hi=math.inf, seed=0, index_offset=0, iteration=0):
+    P, D = pos.shape
+    a = _ffi.UpdateArgs(pos=pos.data_ptr(), vel=vel.data_ptr(), pbest_pos=pbest_pos.data_ptr(), gbest_pos=gbest_pos.data_ptr(),
+                        improved=_ptr(improved), r1=_ptr(r1), r2=_ptr(r2), z_bf16=_ptr(z), dyn=_ptr(dyn), P=P, D=D,
+                        z_pitch=0 if z is None else z.stride(0), w=w, c_cogn=c_cogn, c_soci=c_soci, v_max=v_max, lo=lo, hi=hi,
+                        seed=seed, index_offset=index_offset, iteration=iteration, reserved=0)
+    _ffi.check(_ffi.lib().psob_update(C.byref(a), _stream()), "psob_update")
+
+
+def pbest_minloc(fit, pbest_val, improved, key, index_offset=0):
+    _ffi.check(_ffi.lib().psob_pbest_minloc(fit.data_ptr(), pbest_val.data_ptr(), improved.data_ptr(), fit.shape[0],
+                                            index_offset, key.data_ptr(), _stream()), "psob_pbest_minloc")
+
+
+def gbest_candidate(key, pos, pbest_pos, improved, pbest_val, rec, index_offset=0):
+    P, D = pos.shape
+    _ffi.check(_ffi.lib().psob_gbest_candidate(key.data_ptr(), pos.data_ptr(), pbest_pos.data_ptr(), _ptr(improved),
+                                               pbest_val.data_ptr(), P, index_offset, D, rec.data_ptr(), _stream()),
+               "psob_gbest_candidate")
+
+
+def gbest_apply(recs, n_rec, D, gbest_val, gbest_pos, hist=None, dyn=None, inertia_decay=1.0):
+    rows = 0 if hist is None else hist.shape[0]
+    _ffi.check(_ffi.lib().psob_gbest_apply(recs.data_ptr(), n_rec, D, gbest_val.data_ptr(), gbest_pos.data_ptr(), _ptr(hist),
+                                           rows, _ptr(dyn), inertia_decay, _stream()), "psob_gbest_apply")
+
+
+# ----------------------------------------------------------------------------------------------
+# fitness stages
+# ----------------------------------------------------------------------------------------------
+
+class DScoreFitness:
+    """EXTENSION discriminator-score fitness: p = D(G(z)) on the raw image, then the
+    clamp/affine of src/pso/util_discovery.py:75-80."""
+
+    def __init__(self, disc: DiscriminatorNet, mode="optimize_out_training", thr=0.0, eps=0.1):
+        if mode not in ("optimize_in_training", "optimize_out_training"):
+            raise ValueError(mode)
+        self.disc, self.mode, self.thr, self.eps = disc, mode, thr, eps
+        self.needs_padded_image = True
+
+    def __call__(self, gen: GeneratorNet, fit: torch.Tensor):
+        _, score = self.disc.forward(gen.image_padded_bf16())
+        score_fitness(score, fit, self.mode, self.thr, self.eps)
+
+
+class ReconFitness:
+    """Reconstruction / inverter-loss fitness (src/pso/util_discovery.py:84-101):
+    w_ass * fitness(pos) + w_rec * mean((target - G(pos))^2) + eps."""
+
+    def __init__(self, target: torch.Tensor, w_rec=1.0, eps=0.1, assessor=None, w_ass=1.0):
+        self.target = target.reshape(target.shape[0], -1).contiguous()
+        self.w_rec, self.eps, self.assessor, self.w_ass = w_rec, eps, assessor, w_ass
+        self.fit_ass = None
+        if assessor is not None:
+            self.fit_ass = torch.empty(target.shape[0], dtype=torch.float32, device=target.device)
+
+    def __call__(self, gen: GeneratorNet, fit: torch.Tensor):
+        if self.assessor is not None:
+            self.assessor(gen, self.fit_ass)
+        recon_fitness(gen.image(), self.target, fit, self.fit_ass, self.w_ass if self.assessor is not None else 0.0,
+                      self.w_rec, self.eps)
+
+
+class AssessorFitness:
+    """The reference's own objective (src/pso/util_discovery.py:52-82) with the assessor CNN as a
+    torch callable on the per-image min-max rescaled batch: logits -> softmax pick -> clamp/affine."""
+
+    def __init__(self, model_cnn: Callable, class_index: Optional[int], mode="optimize_out_training", thr=0.0, eps=0.1,
+                 image_shape=(1, 28, 28)):
+        if mode not in ("optimize_in_training", "optimize_out_training"):
+            raise ValueError(mode)
+        self.model_cnn, self.class_index, self.mode, self.thr, self.eps = model_cnn, class_index, mode, thr, eps
+        self.image_shape = image_shape
+        self.rescaled = None
+        self.prob = None
+
+    def __call__(self, gen: GeneratorNet, fit: torch.Tensor):
+        img = gen.image()
+        if self.rescaled is None:
+            self.rescaled = torch.empty_like(img)
+            self.prob = torch.empty(img.shape[0], dtype=torch.float32, device=img.device)
+        rescale_minmax(img, self.rescaled)
+        with torch.no_grad():
+            logits = self.model_cnn(self.rescaled.view(-1, *self.image_shape)).float().contiguous()
+        n_class = logits.shape[1]
+        idx = self.class_index if n_class > 2 else 1            # src/pso/util_discovery.py:71-74
+        softmax_select(logits, idx, self.prob)
+        score_fitness(self.prob, fit, self.mode, self.thr, self.eps)
+
+
+# ----------------------------------------------------------------------------------------------
+# the swarm
+# ----------------------------------------------------------------------------------------------
+
+class SwarmEngine:
+    """Batched swarm living in HBM.  `fitness(gen, fit_out)` fills fit[P] from the generator's
+    outputs; `objective(pos, fit_out)` (generic-objective swarms, src/hands_on/pso.py) may be
+    given instead of a generator."""
+
+    def __init__(self, P: int, D: int, *, generator: Optional[GeneratorNet] = None, fitness=None, objective=None,
+                 w_inertia=0.5, w_cogn=0.8, w_soci=0.9, v_max=math.inf, lo=-math.inf, hi=math.inf, seed=42,
+                 index_offset=0, max_iterations=1024, group=None, device=None):
+        require_cuda()
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.P, self.D_logical = P, D
+        D = (D + 3) // 4 * 4          # rows are float4-aligned; padding dimensions stay exactly 0 forever
+        self.D = D
+        self.gen, self.fitness, self.objective = generator, fitness, objective
+        self.w0, self.c_cogn, self.c_soci = float(w_inertia), float(w_cogn), float(w_soci)
+        self.v_max, self.lo, self.hi = v_max, lo, hi
+        self.seed, self.index_offset = int(seed), int(index_offset)
+        self.group = group
+        self.world = 1
+        if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
+            self.world = torch.distributed.get_world_size(group)
+        dev = self.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.pos = torch.zeros(P, D, **f32)
+        self.vel = torch.zeros(P, D, **f32)
+        self.pbest_pos = torch.zeros(P, D, **f32)
+        self.pbest_val = torch.full((P,), math.inf, **f32)
+        self.fit = torch.zeros(P, **f32)
+        self.improved = torch.zeros(P, dtype=torch.uint8, device=dev)
+        self.key = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.rec = torch.zeros(4 + D, **f32)
+        self.recs = torch.zeros(self.world, 4 + D, **f32) if self.world > 1 else self.rec.view(1, -1)
+        self.gbest_val = torch.full((1,), math.inf, **f32)
+        self.gbest_pos = torch.zeros(D, **f32)
+        self.hist = torch.zeros(max_iterations + 1, 2, **f32)
+        self.dyn = torch.zeros(2, dtype=torch.int32, device=dev)     # psob_iter_state {iteration, w}
+        self.z = None
+        if generator is not None:
+            self.z = torch.zeros(P, generator.in_pitch, dtype=torch.bfloat16, device=dev)
+        self.r1 = self.r2 = None
+        self.inertia_decay = 1.0
+        self._graph = None
+        self.reset_iteration()
+
+    # -- state ---------------------------------------------------------------------------------
+    def reset_iteration(self):
+        st = np.zeros(1, dtype=[("i", np.uint32), ("w", np.float32)])
+        st["w"] = self.w0
+        self.dyn.copy_(torch.from_numpy(st.view(np.int32).copy()).to(self.device))
+
+    def iteration_state(self):
+        raw = self.dyn.cpu().numpy().view(np.uint32)
+        return int(raw[0]), float(raw[1:2].view(np.float32)[0])
+
+    def init_particles(self, pos=None, vel=None, generator: Optional[torch.Generator] = None):
+        """pos ~ N(0,1), vel = (N(0,1) - 0.5)/10 (src/pso/util_pso.py:25-37) unless given."""
+        Dl = self.D_logical
+        if pos is None:
+            pos = torch.randn(self.P, Dl, generator=generator, device=self.device, dtype=torch.float32)
+        if vel is None:
+            vel = (torch.randn(self.P, Dl, generator=generator, device=self.device, dtype=torch.float32) - 0.5) / 10
+        pos = torch.as_tensor(pos, dtype=torch.float32).to(self.device)
+        vel = torch.as_tensor(vel, dtype=torch.float32).to(self.device)
+        self.pos.zero_()
+        self.vel.zero_()
+        self.pos[:, :pos.shape[1]].copy_(pos)
+        self.vel[:, :vel.shape[1]].copy_(vel)
+        self.pbest_pos.copy_(self.pos)
+        self.pbest_val.fill_(math.inf)
+        self.gbest_val.fill_(math.inf)
+        self.gbest_pos.zero_()
+        self.improved.zero_()
+        self.hist.zero_()
+        self.reset_iteration()
+        if self.z is not None:
+            pack_latent(self.pos, self.z)
+
+    def inject_r(self, r1: Optional[torch.Tensor], r2: Optional[torch.Tensor]):
+        """Teacher-forced r1/r2 (parity runs); None restores the in-kernel Philox draws."""
+        self.r1 = None if r1 is None else r1.to(self.device, torch.float32).contiguous()
+        self.r2 = None if r2 is None else r2.to(self.device, torch.float32).contiguous()
+
+    # -- one iteration -------------------------------------------------------------------------
+    def evaluate(self):
+        if self.gen is not None:
+            self.gen.forward(self.z)
+            self.fitness(self.gen, self.fit)
+        else:
+            self.objective(self.pos, self.fit)
+
+    def personal_and_global_best(self):
+        pbest_minloc(self.fit, self.pbest_val, self.improved, self.key, self.index_offset)
+        gbest_candidate(self.key, self.pos, self.pbest_pos, self.improved, self.pbest_val, self.rec, self.index_offset)
+        if self.world > 1:
+            torch.distributed.all_gather_into_tensor(self.recs.view(-1), self.rec, group=self.group)
+        gbest_apply(self.recs, self.world, self.D, self.gbest_val, self.gbest_pos, self.hist, self.dyn, self.inertia_decay)
+
+    def move(self):
+        pso_update(self.pos, self.vel, self.pbest_pos, self.gbest_pos, improved=self.improved, r1=self.r1, r2=self.r2,
+                   z=self.z, dyn=self.dyn, c_cogn=self.c_cogn, c_soci=self.c_soci, v_max=self.v_max, lo=self.lo, hi=self.hi,
+                   seed=self.seed, index_offset=self.index_offset)
+
+    def step(self):
+        self.evaluate()
+        self.personal_and_global_best()
+        self.move()
+
+    # -- graph ---------------------------------------------------------------------------------
+    def capture(self):
+        """Capture one iteration in a CUDA graph (launch-bound at small P)."""
+        it, w = self.iteration_state()
+        snap = [t.clone() for t in (self.pos, self.vel, self.pbest_pos, self.pbest_val, self.gbest_val, self.gbest_pos,
+                                     self.hist, self.dyn, self.improved)] + ([self.z.clone()] if self.z is not None else [])
+        s = torch.cuda.Stream(device=self.device)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self.step()                                    # warm-up: tensor maps, function attributes
+        torch.cuda.current_stream().wait_stream(s)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.step()
+        self._graph = g
+        torch.cuda.synchronize(self.device)
+        targets = [self.pos, self.vel, self.pbest_pos, self.pbest_val, self.gbest_val, self.gbest_pos, self.hist, self.dyn,
+                   self.improved] + ([self.z] if self.z is not None else [])
+        for t, v in zip(targets, snap):
+            t.copy_(v)
+        return g
+
+    def run(self, n_iterations: int, use_graph=True):
+        if use_graph and self._graph is None and self.r1 is None:
+            self.capture()
+        for _ in range(n_iterations):
+            if use_graph and self._graph is not None:
+                self._graph.replay()
+            else:
+                self.step()
+
+    def history(self):
+        """(g_best_val_dummy, replaced flags) for the iterations run so far."""
+        it, _ = self.iteration_state()
+        h = self.hist[:it].cpu().numpy()
+        return h[:, 0].copy(), h[:, 1] > 0.5

@@ -1,0 +1,183 @@
+/*
+ * psob.h — C ABI of libpsob.so: the B200 (sm_100a) swarm-evaluation hot path of
+ * ltronchin/Gan-discovery-PSO.
+ *
+ * The reference is pure Python/PyTorch and has no FFI; the interface each entry point
+ * replaces is therefore a *method body* of the reference, cited as file:line relative to
+ * the reference root.  The Python host (`gan-discovery-pso_b200/psob/_ffi.py`) binds these
+ * symbols with ctypes; INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - return 0 on success; negative = argument error (PSOB_E_*); positive = cudaError_t /
+ *     CUresult of the failing call.  psob_last_error() returns a thread-local message.
+ *   - no C++ exception crosses the boundary; the caller owns every buffer; nothing is
+ *     allocated per call (layer handles own their device tables, created once).
+ *   - all work is enqueued on the caller's stream, no internal synchronisation: every
+ *     call is CUDA-graph capturable.  Handles are immutable after creation.
+ *   - pointers are DEVICE pointers unless the parameter is documented as host.
+ *   - one process per GPU; `index_offset` carries the rank's first global particle index.
+ */
+#ifndef PSOB_H
+#define PSOB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PSOB_VERSION 100
+
+#define PSOB_E_ARG        (-1)   /* bad argument (null pointer, misaligned, size) */
+#define PSOB_E_UNSUPPORTED (-2)  /* shape outside what the kernels implement */
+#define PSOB_E_DEVICE     (-3)   /* not an sm_100 device / driver entry point missing */
+
+typedef void* psob_stream_t;     /* cudaStream_t */
+
+int         psob_version(void);
+const char* psob_last_error(void);
+/* compute capability and SM count of the current device */
+int         psob_device_info(int* cc_major, int* cc_minor, int* sm_count);
+
+/* ------------------------------------------------------------------------------------------
+ * PSO state update — replaces Particle.update_velocity + Particle.update_position driven by
+ * Swarm.move_particles (src/pso/util_pso.py:39-50, 153-157), fused with the deferred
+ * personal-best position copy of Swarm.update_personal_best (src/pso/util_pso.py:122-124):
+ *
+ *   if improved[p]: pbest_pos[p,:] = pos[p,:]
+ *   vel = (w*vel + c_soci*r2[p]*(pbest_pos - pos)) + c_cogn*r1[p]*(gbest_pos - pos)
+ *   vel = clamp(vel, -v_max, v_max)            (extension; off when v_max = +inf)
+ *   pos = clamp(pos + vel, lo, hi)             (extension; off when lo/hi = -/+inf)
+ *
+ * NB the reference's naming: c_cogn scales the pull to the GLOBAL best, c_soci the pull to
+ * the PERSONAL best (src/pso/util_pso.py:46,48).  r1/r2 are one scalar per particle; when
+ * both pointers are NULL they are drawn in-kernel: Philox4x32-10, key = seed,
+ * counter = (index_offset + p, iteration, 0, 0), r1 = (x0>>8)*2^-24, r2 = (x1>>8)*2^-24.
+ * Optionally emits the new position as a zero-padded bf16 row (generator input).
+ * State is fp32 [P, D] row-major, D % 4 == 0, pointers 16-byte aligned.
+ * ---------------------------------------------------------------------------------------- */
+/* Device-resident iteration state, so that a captured CUDA graph replays correctly:
+ * psob_gbest_apply advances it, psob_update reads it. */
+typedef struct {
+  uint32_t iteration;   /* 1-based index of the iteration whose move is about to run */
+  float    w;           /* current inertia weight */
+} psob_iter_state;
+
+typedef struct {
+  float*         pos;
+  float*         vel;
+  float*         pbest_pos;
+  const float*   gbest_pos;     /* [D] */
+  const uint8_t* improved;      /* [P] or NULL */
+  const float*   r1;            /* [P] or NULL (Philox) */
+  const float*   r2;            /* [P] or NULL (Philox) */
+  void*          z_bf16;        /* [P, z_pitch] bf16 or NULL; columns D..z_pitch-1 untouched */
+  const psob_iter_state* dyn;   /* device, or NULL; when set, overrides `w` and `iteration` below */
+  int64_t        P;
+  int32_t        D;
+  int32_t        z_pitch;
+  float          w, c_cogn, c_soci;
+  float          v_max, lo, hi;
+  uint64_t       seed;
+  uint64_t       index_offset;
+  uint32_t       iteration;
+  uint32_t       reserved;
+} psob_update_args;
+
+int psob_update(const psob_update_args* a, psob_stream_t s);
+
+/* fp32 [P, D] -> zero-padded bf16 [P, z_pitch] (initial generator input) */
+int psob_pack_latent(const float* pos, int64_t P, int32_t D, void* z_bf16, int32_t z_pitch, psob_stream_t s);
+
+/* ------------------------------------------------------------------------------------------
+ * Personal best + local min-loc — replaces the compare in Swarm.update_personal_best
+ * (src/pso/util_pso.py:122-124) and the scan of Swarm.update_global_best (:139-143):
+ *   improved[p] = fit[p] < pbest_val[p]  (strict; NaN never improves);  pbest_val[p] = min
+ *   *key = min over p of (order_key(pbest_val[p]) << 32 | index_offset + p)
+ * order_key is the order-preserving float->uint map, so the lowest global index wins ties
+ * exactly like the reference's in-order scan.  *key is reset by this call.
+ * ---------------------------------------------------------------------------------------- */
+int psob_pbest_minloc(const float* fit, float* pbest_val, uint8_t* improved, int64_t P,
+                      uint64_t index_offset, uint64_t* key, psob_stream_t s);
+
+/* Candidate record of this rank: rec = { key_lo, key_hi, value_bits, 0, pos[D] } (4+D words),
+ * pos = the winner's personal-best position (its current pos when improved this iteration). */
+int psob_gbest_candidate(const uint64_t* key, const float* pos, const float* pbest_pos,
+                         const uint8_t* improved, const float* pbest_val, int64_t P,
+                         uint64_t index_offset, int32_t D, float* rec, psob_stream_t s);
+
+/* Global best — replaces the tail of Swarm.update_global_best (src/pso/util_pso.py:144-151)
+ * and the inertia schedule of Swarm.optimize (:72-74, 178-179): picks the minimum key among
+ * n_rec records (all-gathered over ranks) and replaces the incumbent only on a strict
+ * improvement.  hist (device [hist_rows, 2], may be NULL): row dyn->iteration (row 0 without
+ * dyn) gets { gbest value after the call, 1.0 if replaced else 0.0 }.  Then, when dyn is
+ * given: dyn->iteration += 1 and, if the new value is > 1, dyn->w *= inertia_decay. */
+int psob_gbest_apply(const float* recs, int32_t n_rec, int32_t D, float* gbest_val,
+                     float* gbest_pos, float* hist, int32_t hist_rows, psob_iter_state* dyn,
+                     float inertia_decay, psob_stream_t s);
+
+/* ------------------------------------------------------------------------------------------
+ * Fitness transforms — replace Discovery.fitness / fitness_pso_inverter arithmetic
+ * (src/pso/util_discovery.py:70-80, 97-101) and util_data.rescale_torch (src/utils/util_data.py:129-135)
+ * ---------------------------------------------------------------------------------------- */
+#define PSOB_MODE_IN_TRAINING  0  /* fit = min(p+thr,1) + eps      */
+#define PSOB_MODE_OUT_TRAINING 1  /* fit = 1 - min(p+thr,1) + eps  */
+
+/* score[p*stride] is the assessor probability */
+int psob_score_fitness(const float* score, int32_t stride, int64_t P, int32_t mode, float thr,
+                       float eps, float* fit, psob_stream_t s);
+/* logits [P, n_class] -> softmax(dim 1)[class_idx] */
+int psob_softmax_select(const float* logits, int32_t n_class, int32_t class_idx, int64_t P,
+                        float* prob, psob_stream_t s);
+/* fit[p] = w_ass*fit_ass[p] + w_rec*mean((target[p,:]-img[p,:])^2) + eps ; fit_ass may be NULL (0);
+ * target is fp32 or bf16 [P, n] */
+int psob_recon_fitness(const float* img, const void* target, int32_t target_is_bf16, int64_t P,
+                       int32_t n, const float* fit_ass, float w_ass, float w_rec, float eps,
+                       float* fit, psob_stream_t s);
+/* per-image (img-min)/(max-min), fp32 [P, n] */
+int psob_rescale_minmax(const float* img, int64_t P, int32_t n, float* out, psob_stream_t s);
+/* fp32 [P, 784] image -> padded bf16 [P, 31*32] (real (y,x) at (y+1,x+1), zeros elsewhere) */
+int psob_pack_image(const float* img, int64_t P, void* out_bf16, psob_stream_t s);
+
+/* ------------------------------------------------------------------------------------------
+ * Pixel-GEMM layers — replace Generator.forward / Discriminator.forward / Encoder.forward
+ * (src/utils/util_dcgan.py:103-149, src/inverter/utils_ae/util_inverter.py:164-184): every
+ * ConvTranspose2d / Conv2d (+ folded BatchNorm + activation) is a table of tcgen05 MMA
+ * chains over 128-particle x 64-channel TMA tiles (see psob/lowering.py for the tables).
+ * ---------------------------------------------------------------------------------------- */
+#define PSOB_ACT_NONE 0
+#define PSOB_ACT_RELU 1
+#define PSOB_ACT_LEAKY 2   /* slope 0.2 */
+#define PSOB_ACT_TANH 3
+#define PSOB_ACT_SIGMOID 4
+
+#define PSOB_IMPL_TCGEN05 0   /* product path */
+#define PSOB_IMPL_SIMT    1   /* bring-up interpreter of the same tables (tests only) */
+
+typedef struct {
+  int32_t mma_n, nt, cc, act;
+  int32_t in_pitch, out_pitch, out32_pitch;
+  int32_t b_resident, vec8;
+  int32_t n_steps, n_jobs, n_wrows, n_bias_rows;
+  const uint16_t* wpack;     /* HOST bf16 bits [n_wrows, 64] */
+  const int32_t*  steps;     /* HOST [n_steps, 4]: a_col, b_row, d_col, flags */
+  const int32_t*  jobs;      /* HOST [n_jobs, 8]: step_begin, step_count, out_base, out32_base, mask_lo, mask_hi, bias_row, 0 */
+  const int32_t*  col_map;   /* HOST [nt] */
+  const int32_t*  col_map32; /* HOST [nt] */
+  const float*    bias;      /* HOST [n_bias_rows, nt] */
+} psob_layer_desc;
+
+typedef struct psob_layer psob_layer;
+
+int psob_layer_create(const psob_layer_desc* d, psob_layer** out);
+int psob_layer_destroy(psob_layer* l);
+/* x: bf16 [P, x_pitch] (x_pitch >= in_pitch, x_pitch % 8 == 0, 16-byte aligned);
+ * y: bf16 [P, out_pitch] or NULL; y32: fp32 [P, out32_pitch] or NULL */
+int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32,
+                   int32_t impl, psob_stream_t s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PSOB_H */

@@ -1,0 +1,165 @@
+"""GPU (-m gpu): tcgen05 pixel-GEMM layers vs the CPU emulation of the same tables, the SIMT
+bring-up interpreter, and the reference's fp32 images / scores (golden vectors + oracle)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import port
+from conftest import load_sd
+
+pytestmark = pytest.mark.gpu
+
+IMG_TOL = 2e-2        # north_star: generator images max-abs <= 2e-2 on [-1,1] outputs (bf16 path)
+REL_TOL = 5e-3        # relative L2 gate, needed because ref-init images are nearly constant
+
+
+@pytest.fixture(scope="module")
+def mods():
+    from psob import engine, lowering, nets, _ffi
+    engine.require_cuda()
+    return engine, lowering, nets, _ffi
+
+
+def _rows(z, pitch):
+    x = torch.zeros(z.shape[0], pitch, dtype=torch.bfloat16, device="cuda")
+    x[:, :z.shape[1]] = torch.as_tensor(z).cuda().bfloat16()
+    return x
+
+
+def _run_layers(engine, progs, x, impl):
+    net = engine.Network(progs, x.shape[0], impl=impl)
+    outs = []
+    cur = x
+    for layer, y, y32 in zip(net.layers, net.acts, net.acts32):
+        layer.run(cur, x.shape[0], y, y32, impl)
+        outs.append((None if y is None else y.float().cpu().numpy(), None if y32 is None else y32.cpu().numpy()))
+        cur = y
+    torch.cuda.synchronize()
+    return outs
+
+
+@pytest.mark.parametrize("P", [6, 128, 300])
+def test_each_layer_matches_table_emulation(mods, golden, P):
+    """Layer by layer, teacher-forced: every layer gets the emulation's (bf16-exact) input."""
+    engine, L, nets, ffi = mods
+    sd = load_sd(golden, "gsmall_trained")
+    progs = nets.generator_programs(sd)
+    rng = np.random.RandomState(P)
+    z = L.to_bf16_f32(rng.randn(P, 10).astype(np.float32))
+    x = np.zeros((P, progs[0].in_pitch), np.float32)
+    x[:, :10] = z
+    for prog in progs:
+        y_ref, y32_ref = L.emulate(prog, x)
+        xin = torch.from_numpy(x).cuda().bfloat16()
+        for impl in (ffi.IMPL_SIMT, ffi.IMPL_TCGEN05):
+            net = engine.Network([prog], P, impl=impl)
+            y, y32 = net.forward(xin)
+            torch.cuda.synchronize()
+            if y_ref is not None:
+                got = y.float().cpu().numpy()
+                # fp32 accumulation order differs (tensor core vs numpy): allow one bf16 ulp
+                np.testing.assert_allclose(got, y_ref, rtol=1.0 / 128, atol=1e-3, err_msg=f"{prog.name} impl={impl}")
+            if y32_ref is not None:
+                np.testing.assert_allclose(y32.cpu().numpy(), y32_ref, rtol=1e-3, atol=2e-4, err_msg=f"{prog.name} impl={impl}")
+        x = y_ref
+
+
+@pytest.mark.parametrize("regime", ["refinit", "default", "trained"])
+def test_small_generator_vs_reference_images(mods, golden, regime):
+    engine, L, nets, ffi = mods
+    sd = load_sd(golden, f"gsmall_{regime}")
+    z = golden["gsmall/z"].reshape(6, 10)
+    ref = golden[f"gsmall_{regime}/out"].reshape(6, 784)
+    for impl in (ffi.IMPL_SIMT, ffi.IMPL_TCGEN05):
+        net = engine.GeneratorNet(sd, 6, impl=impl)
+        _, img = net.forward(_rows(z, net.in_pitch))
+        got = img.cpu().numpy()
+        assert np.abs(got - ref).max() <= IMG_TOL
+        assert np.linalg.norm(got - ref) / np.linalg.norm(ref) <= REL_TOL
+        pad = net.image_padded_bf16().float().cpu().numpy().reshape(6, 31, 32)
+        assert np.array_equal(pad[:, 1:29, 1:29].reshape(6, 784), torch.from_numpy(got).bfloat16().float().numpy())
+        pad[:, 1:29, 1:29] = 0
+        assert np.abs(pad).max() == 0
+
+
+def test_full_size_generator_and_discriminator_vs_reference(mods, golden):
+    """Generator(100,1,64) / Discriminator(1,64): weights regenerated from the fixture's seeds."""
+    engine, L, nets, ffi = mods
+    torch.manual_seed(11)
+    gen = port.Generator(100, 1, 64)
+    port.randomize_bn_stats(gen, torch.Generator().manual_seed(12))
+    gen.eval()
+    torch.manual_seed(13)
+    disc = port.Discriminator(1, 64).eval()
+    wsum = sum(float(v.double().sum()) for v in gen.state_dict().values())
+    z = golden["gfull/z"].reshape(8, 100)
+    with torch.no_grad():
+        ref_img = gen(torch.from_numpy(z).view(8, 100, 1, 1))
+        ref_score = disc(ref_img).reshape(8).numpy()
+    ref_img = ref_img.reshape(8, 784).numpy()
+    if abs(wsum - float(golden["gfull/wsum"])) <= 1e-6 * abs(wsum):
+        np.testing.assert_allclose(ref_img, golden["gfull/out"].reshape(8, 784), atol=1e-6, rtol=0)
+    gnet = engine.GeneratorNet(gen.state_dict(), 8)
+    dnet = engine.DiscriminatorNet(disc.state_dict(), 8)
+    _, img = gnet.forward(_rows(z, gnet.in_pitch))
+    _, score = dnet.forward(gnet.image_padded_bf16())
+    got = img.cpu().numpy()
+    assert np.abs(got - ref_img).max() <= IMG_TOL
+    assert np.linalg.norm(got - ref_img) / np.linalg.norm(ref_img) <= REL_TOL
+    np.testing.assert_allclose(score.cpu().numpy()[:, 0], ref_score, atol=5e-3, rtol=0)
+
+
+@pytest.mark.parametrize("P", [1, 129, 4096])
+def test_full_size_ragged_batches_tcgen05_vs_simt(mods, P):
+    engine, L, nets, ffi = mods
+    torch.manual_seed(0)
+    gen = port.Generator(100, 1, 64)
+    port.initialize_weights(gen)
+    disc = port.Discriminator(1, 64)
+    z = torch.randn(P, 100, generator=torch.Generator().manual_seed(P))
+    res = {}
+    for impl in (ffi.IMPL_SIMT, ffi.IMPL_TCGEN05):
+        gnet = engine.GeneratorNet(gen.state_dict(), P, impl=impl)
+        dnet = engine.DiscriminatorNet(disc.state_dict(), P, impl=impl)
+        _, img = gnet.forward(_rows(z.numpy(), gnet.in_pitch))
+        _, score = dnet.forward(gnet.image_padded_bf16())
+        res[impl] = (img.cpu().numpy(), score.cpu().numpy())
+    np.testing.assert_allclose(res[0][0], res[1][0], atol=2e-3, rtol=0)
+    np.testing.assert_allclose(res[0][1], res[1][1], atol=2e-3, rtol=0)
+    with torch.no_grad():
+        ref = gen.eval()(z.view(P, 100, 1, 1)).reshape(P, 784).numpy()
+    assert np.abs(res[0][0] - ref).max() <= IMG_TOL
+    assert np.linalg.norm(res[0][0] - ref) / np.linalg.norm(ref) <= REL_TOL
+
+
+def test_discriminator_encoder_vqdecoder_small(mods, golden):
+    engine, L, nets, ffi = mods
+    x = torch.from_numpy(golden["dsmall/x"]).reshape(6, 784).cuda()
+    xp = torch.empty(6, 31 * 32, dtype=torch.bfloat16, device="cuda")
+    engine.pack_image(x.contiguous(), xp)
+    d = engine.DiscriminatorNet(load_sd(golden, "dsmall"), 6)
+    _, score = d.forward(xp)
+    np.testing.assert_allclose(score.cpu().numpy()[:, 0], golden["dsmall/out"].reshape(6), atol=5e-3, rtol=0)
+    e = engine.EncoderNet(load_sd(golden, "esmall"), 6)
+    _, lat = e.forward(xp)
+    ref = golden["esmall/out"].reshape(6, 10)
+    assert np.abs(lat.cpu().numpy() - ref).max() <= 2e-2 * max(1.0, np.abs(ref).max())
+    v = engine.GeneratorNet(load_sd(golden, "vqdec"), 6, prefix="decoder")
+    _, img = v.forward(_rows(golden["gsmall/z"].reshape(6, 10), v.in_pitch))
+    ref = golden["vqdec/out"].reshape(6, 784)
+    assert np.abs(img.cpu().numpy() - ref).max() <= IMG_TOL
+    assert np.linalg.norm(img.cpu().numpy() - ref) / np.linalg.norm(ref) <= REL_TOL
+
+
+def test_layer_create_rejects_bad_tables(mods, golden):
+    engine, L, nets, ffi = mods
+    import copy
+    prog = nets.generator_programs(load_sd(golden, "gsmall_trained"))[1]
+    bad = copy.deepcopy(prog)
+    bad.steps[0, 0] = prog.in_pitch          # a_col beyond the activation row
+    with pytest.raises(ffi.PsobError):
+        engine.Layer(bad)
+    bad = copy.deepcopy(prog)
+    bad.jobs[0, 2] = prog.out_pitch          # store offset beyond the output row
+    with pytest.raises(ffi.PsobError):
+        engine.Layer(bad)

@@ -41,8 +41,12 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Bounded spin: a protocol bug traps (cudaErrorLaunchFailure) instead of hanging the GPU.  try_wait
+// suspends the thread for a HW-defined interval, so 2^28 failed polls is many seconds.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
+    if (++spins == (1u << 28)) __trap();
   }
 }
 

@@ -26,6 +26,8 @@ constexpr int kKChunk = 64;
 constexpr int kATileBytes = kTileM * kKChunk * 2;   // 16 KB
 constexpr int kSmemLimit = 232448;                  // 227 KB per CTA on sm_100
 constexpr int kBarBytes = 256;
+constexpr int kMaxBiasRowsSmem = 8;
+constexpr int kTabBytes = 256 * 4 * 2 + 256 + kMaxBiasRowsSmem * 256 * 4;   // col_map, col_map32, pix, bias rows
 constexpr int kThreads = 192;
 
 struct EngineParams {
@@ -40,7 +42,7 @@ struct EngineParams {
   long long n_items;
   int n_jobs;
   int mma_n, nt, cc, act, out_pitch, out32_pitch, vec8;
-  int b_resident, n_wrows;
+  int b_resident, n_wrows, n_bias_rows;
   int n_stages, stage_bytes, res_off, bar_off;
   uint32_t idesc, tmem_cols;
 };
@@ -97,6 +99,22 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
   }
+  // Epilogue tables live in shared memory: with ~220 KB of the SM's L1/SMEM carved out for the
+  // ring, every __ldg would be an L2 round trip to the SAME few lines from all 148 SMs (measured:
+  // ~4k cycles per 16-column epilogue iteration before this staging).
+  int* s_cm = reinterpret_cast<int*>(gbase + p.bar_off + kBarBytes);
+  int* s_cm32 = s_cm + 256;
+  uint8_t* s_pix = reinterpret_cast<uint8_t*>(s_cm32 + 256);
+  float* s_bias = reinterpret_cast<float*>(s_pix + 256);
+  const bool bias_in_smem = p.n_bias_rows <= kMaxBiasRowsSmem;
+  for (int i = threadIdx.x; i < p.nt; i += kThreads) {
+    s_cm[i] = p.col_map[i];
+    s_cm32[i] = p.col_map32[i];
+    int px = i / p.cc;
+    s_pix[i] = (uint8_t)(px < 64 ? px : 64);
+  }
+  if (bias_in_smem)
+    for (int i = threadIdx.x; i < p.n_bias_rows * p.nt; i += kThreads) s_bias[i] = p.bias[i];
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -116,8 +134,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const int ptile = (int)(item / p.n_jobs);
         const int job = (int)(item - (long long)ptile * p.n_jobs);
         const int4 j0 = __ldg(p.jobs + 2 * job);
+        int4 st_next = __ldg(p.steps + j0.x);
         for (int s = j0.x; s < j0.x + j0.y; ++s) {
-          const int4 st = __ldg(p.steps + s);
+          const int4 st = st_next;
+          if (s + 1 < j0.x + j0.y) st_next = __ldg(p.steps + s + 1);     // descriptor fetch overlaps the wait
           ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
           const bool res = (st.w & 2) != 0;
           ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)p.mma_n * 128u));
@@ -139,10 +159,12 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const int job = (int)(item - (long long)ptile * p.n_jobs);
       const int4 j0 = __ldg(p.jobs + 2 * job);
       const uint32_t buf = it & 1u, use = it >> 1;
+      int4 st_next = __ldg(p.steps + j0.x);
       ptx::mbar_wait(tempty_bar(buf), (use & 1u) ^ 1u);
       ptx::tc_fence_after();
       for (int s = j0.x; s < j0.x + j0.y; ++s) {
-        const int4 st = __ldg(p.steps + s);
+        const int4 st = st_next;
+        if (s + 1 < j0.x + j0.y) st_next = __ldg(p.steps + s + 1);
         ptx::mbar_wait(full_bar(stage), phase);
         ptx::tc_fence_after();
         if (lane == 0) {
@@ -173,7 +195,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const int4 j0 = __ldg(p.jobs + 2 * job);
       const int4 j1 = __ldg(p.jobs + 2 * job + 1);
       const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
-      const float* bias = p.bias + (size_t)j1.z * p.nt;
+      const float* bias = bias_in_smem ? s_bias + j1.z * p.nt : p.bias + (size_t)j1.z * p.nt;
       const uint32_t buf = it & 1u, use = it >> 1;
       const long long particle = (long long)ptile * kTileM + row;
       const bool valid = particle < p.P;
@@ -193,12 +215,15 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 #pragma unroll
           for (int g = 0; g < 2; ++g) {
             const int n = c0 + 8 * g;
-            const int pix = n / p.cc;
-            const int cm = __ldg(p.col_map + n);
+            const int pix = s_pix[n];
+            const int cm = s_cm[n];
             if (cm < 0 || !((mask >> pix) & 1ull)) continue;
+            const float4 b0 = *reinterpret_cast<const float4*>(bias + n);
+            const float4 b1 = *reinterpret_cast<const float4*>(bias + n + 4);
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
             float f[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = apply_act(__uint_as_float(v[8 * g + i]) + __ldg(bias + n + i), p.act);
+            for (int i = 0; i < 8; ++i) f[i] = apply_act(__uint_as_float(v[8 * g + i]) + bb[i], p.act);
             uint4 o;
             o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
             o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
@@ -208,11 +233,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const int n = c0 + i;
-            const int pix = n / p.cc;
+            const int pix = s_pix[n];
             if (pix < 64 && !((mask >> pix) & 1ull)) continue;
-            const float f = apply_act(__uint_as_float(v[i]) + __ldg(bias + n), p.act);
-            if (yrow) { const int cm = __ldg(p.col_map + n); if (cm >= 0) yrow[cm] = __float2bfloat16_rn(f); }
-            if (y32row) { const int cm = __ldg(p.col_map32 + n); if (cm >= 0) y32row[cm] = f; }
+            const float f = apply_act(__uint_as_float(v[i]) + bias[n], p.act);
+            if (yrow) { const int cm = s_cm[n]; if (cm >= 0) yrow[cm] = __float2bfloat16_rn(f); }
+            if (y32row) { const int cm = s_cm32[n]; if (cm >= 0) y32row[cm] = f; }
           }
         }
       }
@@ -402,7 +427,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   const int b_tile = d->mma_n * 128;
   l->stage_bytes = kATileBytes + (d->b_resident ? 0 : b_tile);
   const int res_bytes = d->b_resident ? d->n_wrows * 128 : 0;
-  int avail = kSmemLimit - 1024 - kBarBytes - res_bytes;
+  int avail = kSmemLimit - 1024 - kBarBytes - kTabBytes - res_bytes;
   l->n_stages = avail / l->stage_bytes;
   if (l->n_stages > kMaxStages) l->n_stages = kMaxStages;
   if (l->n_stages < 2) {
@@ -411,7 +436,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   }
   l->res_off = l->n_stages * l->stage_bytes;
   l->bar_off = l->res_off + res_bytes;
-  l->smem_bytes = l->bar_off + kBarBytes + 1024;
+  l->smem_bytes = l->bar_off + kBarBytes + kTabBytes + 1024;
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * d->nt)) cols <<= 1;
   l->tmem_cols = cols;
@@ -435,7 +460,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.n_jobs = d.n_jobs;
   p.mma_n = d.mma_n; p.nt = d.nt; p.cc = d.cc; p.act = d.act; p.out_pitch = d.out_pitch; p.out32_pitch = d.out32_pitch;
   p.vec8 = (d.vec8 && p.y) ? 1 : 0;
-  p.b_resident = d.b_resident; p.n_wrows = d.n_wrows;
+  p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
   p.tmem_cols = l->tmem_cols;

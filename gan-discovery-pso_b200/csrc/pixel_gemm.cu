@@ -28,7 +28,7 @@ constexpr int kSmemLimit = 232448;                  // 227 KB per CTA on sm_100
 constexpr int kBarBytes = 256;
 constexpr int kMaxBiasRowsSmem = 8;
 constexpr int kTabBytes = 256 * 4 * 2 + 256 + kMaxBiasRowsSmem * 256 * 4;   // col_map, col_map32, pix, bias rows
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;                     // TMA warp + MMA warp + 2 epilogue groups of 4 warps
 
 struct EngineParams {
   const int4* steps;
@@ -43,7 +43,8 @@ struct EngineParams {
   int n_jobs;
   int mma_n, nt, cc, act, out_pitch, out32_pitch, vec8;
   int b_resident, n_wrows, n_bias_rows;
-  int n_stages, stage_bytes, res_off, bar_off;
+  int n_stages, stage_bytes, res_off, bar_off, stg_off;
+  int vec4;
   uint32_t idesc, tmem_cols;
 };
 
@@ -62,8 +63,22 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
+template <int kAct>
+__device__ __forceinline__ float act_fn(float v) {
+  if (kAct == PSOB_ACT_RELU) return fmaxf(v, 0.f);
+  if (kAct == PSOB_ACT_LEAKY) return fmaxf(v, 0.2f * v);      // max(v, 0.2v) == leaky_relu(v, 0.2)
+  if (kAct == PSOB_ACT_TANH) return tanhf(v);
+  if (kAct == PSOB_ACT_SIGMOID) return 1.f / (1.f + expf(-v));
+  return v;
+}
+
+// kTmaStore: bf16 NHWC outputs whose 64-column chunks are contiguous 128-byte rows leave through a
+// swizzled shared-memory tile and one TMA store per chunk (two epilogue groups alternate chunks);
+// otherwise (image / score outputs, nt = 16..64) group 0 stores directly from registers.
+template <int kAct, bool kTmaStore>
 __global__ void __launch_bounds__(kThreads, 1)
-pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const EngineParams p) {
+pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ CUtensorMap tmY, const EngineParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -86,7 +101,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(tfull_bar(b), 1);
-      ptx::mbar_init(tempty_bar(b), 4);
+      ptx::mbar_init(tempty_bar(b), kTmaStore ? 8 : 4);
     }
     ptx::mbar_init(res_bar, 1);
     ptx::fence_barrier_init();
@@ -98,6 +113,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
+    if (kTmaStore) ptx::prefetch_tmap(&tmY);
   }
   // Epilogue tables live in shared memory: with ~220 KB of the SM's L1/SMEM carved out for the
   // ring, every __ldg would be an L2 round trip to the SAME few lines from all 148 SMs (measured:
@@ -185,65 +201,127 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       __syncwarp();
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (TMEM lane quadrant = warp % 4)
+    // ------------------------------------------------------------------ epilogue
+    // 8 warps = 2 groups x 4 TMEM lane quadrants (quadrant = warp % 4, the hardware's access rule)
     const int q = warp & 3;
+    const int grp = (warp - 2) >> 2;
     const int row = q * 32 + lane;
+    const bool issuer = ((warp - 2) & 3) == 0 && lane == 0;
+    const uint32_t sbuf = base + p.stg_off + (uint32_t)grp * kATileBytes;
+    const uint32_t srow = sbuf + (uint32_t)row * 128u;
+    const uint32_t sw = (uint32_t)(row & 7);
     uint32_t it = 0;
-    for (long long item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
-      const int ptile = (int)(item / p.n_jobs);
-      const int job = (int)(item - (long long)ptile * p.n_jobs);
-      const int4 j0 = __ldg(p.jobs + 2 * job);
-      const int4 j1 = __ldg(p.jobs + 2 * job + 1);
-      const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
-      const float* bias = bias_in_smem ? s_bias + j1.z * p.nt : p.bias + (size_t)j1.z * p.nt;
-      const uint32_t buf = it & 1u, use = it >> 1;
-      const long long particle = (long long)ptile * kTileM + row;
-      const bool valid = particle < p.P;
-      __nv_bfloat16* yrow = p.y ? p.y + particle * p.out_pitch + j0.z : nullptr;
-      float* y32row = p.y32 ? p.y32 + particle * p.out32_pitch + j0.w : nullptr;
-      ptx::mbar_wait(tfull_bar(buf), use & 1u);
-      ptx::tc_fence_after();
-      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.nt;
-      for (int c0 = 0; c0 < p.nt; c0 += 16) {
-        uint32_t v[16];
-        __syncwarp();                       // tcgen05.ld is .sync.aligned: reconverge after the masked stores
-        ptx::tmem_ld_x16(tbase + (uint32_t)c0, v);
-        ptx::tmem_ld_wait();
-        if (!valid) {
-          // rows past P hold zero-filled TMA data: nothing to store
-        } else if (p.vec8) {
+    if (kTmaStore || grp == 0) {
+      for (long long item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
+        const int ptile = (int)(item / p.n_jobs);
+        const int job = (int)(item - (long long)ptile * p.n_jobs);
+        const int4 j0 = __ldg(p.jobs + 2 * job);
+        const int4 j1 = __ldg(p.jobs + 2 * job + 1);
+        const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
+        const float* bias = bias_in_smem ? s_bias + j1.z * p.nt : p.bias + (size_t)j1.z * p.nt;
+        const uint32_t buf = it & 1u, use = it >> 1;
+        ptx::mbar_wait(tfull_bar(buf), use & 1u);
+        ptx::tc_fence_after();
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.nt;
+        if (kTmaStore) {
+          const int n_chunks = p.nt >> 6;
+          int last = -1;                      // last chunk this group will read: release TMEM right after it
+          for (int ch = grp; ch < n_chunks; ch += 2)
+            if (s_cm[ch << 6] >= 0 && ((mask >> s_pix[ch << 6]) & 1ull)) last = ch;
+          if (last < 0) {
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(tempty_bar(buf));
+          }
+          for (int ch = grp; ch < n_chunks; ch += 2) {
+            const int n0 = ch << 6;
+            const int cm = s_cm[n0];
+            if (cm < 0 || !((mask >> s_pix[n0]) & 1ull)) continue;       // uniform over the group
+            uint32_t v[64];
+            __syncwarp();
+            ptx::tmem_ld_x16(tbase + (uint32_t)n0, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+            ptx::tmem_ld_x16(tbase + (uint32_t)n0 + 16u, *reinterpret_cast<uint32_t(*)[16]>(&v[16]));
+            ptx::tmem_ld_x16(tbase + (uint32_t)n0 + 32u, *reinterpret_cast<uint32_t(*)[16]>(&v[32]));
+            ptx::tmem_ld_x16(tbase + (uint32_t)n0 + 48u, *reinterpret_cast<uint32_t(*)[16]>(&v[48]));
+            ptx::tmem_ld_wait();
+            if (ch == last) {
+              ptx::tc_fence_before();
+              __syncwarp();
+              if (lane == 0) ptx::mbar_arrive(tempty_bar(buf));
+            }
+            if (issuer) ptx::bulk_wait_read0();           // the previous TMA store has drained the staging tile
+            ptx::named_bar_sync(1 + grp, 128);
 #pragma unroll
-          for (int g = 0; g < 2; ++g) {
-            const int n = c0 + 8 * g;
-            const int pix = s_pix[n];
-            const int cm = s_cm[n];
-            if (cm < 0 || !((mask >> pix) & 1ull)) continue;
-            const float4 b0 = *reinterpret_cast<const float4*>(bias + n);
-            const float4 b1 = *reinterpret_cast<const float4*>(bias + n + 4);
-            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-            float f[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = apply_act(__uint_as_float(v[8 * g + i]) + bb[i], p.act);
-            uint4 o;
-            o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-            o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-            *reinterpret_cast<uint4*>(yrow + cm) = o;
+            for (int j = 0; j < 8; ++j) {
+              const float4 b0 = *reinterpret_cast<const float4*>(bias + n0 + 8 * j);
+              const float4 b1 = *reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4);
+              uint4 o;
+              o.x = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 0]) + b0.x), act_fn<kAct>(__uint_as_float(v[8 * j + 1]) + b0.y));
+              o.y = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 2]) + b0.z), act_fn<kAct>(__uint_as_float(v[8 * j + 3]) + b0.w));
+              o.z = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 4]) + b1.x), act_fn<kAct>(__uint_as_float(v[8 * j + 5]) + b1.y));
+              o.w = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 6]) + b1.z), act_fn<kAct>(__uint_as_float(v[8 * j + 7]) + b1.w));
+              ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);   // SWIZZLE_128B: 16-byte slot j of row r lives at j ^ (r % 8)
+            }
+            ptx::fence_proxy_async();                    // generic-proxy writes -> visible to the TMA (async proxy)
+            ptx::named_bar_sync(1 + grp, 128);
+            if (issuer) {
+              ptx::tma_store_2d(&tmY, sbuf, j0.z + cm, ptile * kTileM);   // rows >= P are clipped by the tensor map
+              ptx::bulk_commit();
+            }
           }
         } else {
+          const long long particle = (long long)ptile * kTileM + row;
+          const bool valid = particle < p.P;
+          __nv_bfloat16* yrow = p.y ? p.y + particle * p.out_pitch + j0.z : nullptr;
+          float* y32row = p.y32 ? p.y32 + particle * p.out32_pitch + j0.w : nullptr;
+          for (int c0 = 0; c0 < p.nt; c0 += 16) {
+            uint32_t v[16];
+            __syncwarp();                       // tcgen05.ld is .sync.aligned: reconverge after the masked stores
+            ptx::tmem_ld_x16(tbase + (uint32_t)c0, v);
+            ptx::tmem_ld_wait();
+            if (!valid) continue;               // rows past P hold zero-filled TMA data: nothing to store
+            if (p.vec4 && yrow) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int n = c0 + i;
-            const int pix = s_pix[n];
-            if (pix < 64 && !((mask >> pix) & 1ull)) continue;
-            const float f = apply_act(__uint_as_float(v[i]) + bias[n], p.act);
-            if (yrow) { const int cm = s_cm[n]; if (cm >= 0) yrow[cm] = __float2bfloat16_rn(f); }
-            if (y32row) { const int cm = s_cm32[n]; if (cm >= 0) y32row[cm] = f; }
+              for (int g = 0; g < 4; ++g) {     // cc == 1: 4 consecutive pixels -> one 8-byte store
+                const int n = c0 + 4 * g;
+                const int cm = s_cm[n];
+                const uint32_t m4 = n < 64 ? (uint32_t)((mask >> n) & 0xFull) : 0u;
+                if (cm < 0 || m4 == 0u) continue;
+                float f[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) f[i] = act_fn<kAct>(__uint_as_float(v[4 * g + i]) + bias[n + i]);
+                if (m4 == 0xFu) {
+                  uint2 o;
+                  o.x = pack_bf16x2(f[0], f[1]);
+                  o.y = pack_bf16x2(f[2], f[3]);
+                  *reinterpret_cast<uint2*>(yrow + cm) = o;
+                } else {
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) if ((m4 >> i) & 1u) yrow[cm + i] = __float2bfloat16_rn(f[i]);
+                }
+                if (y32row) {
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) { const int c32 = s_cm32[n + i]; if (c32 >= 0 && ((m4 >> i) & 1u)) y32row[c32] = f[i]; }
+                }
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const int n = c0 + i;
+                const int pix = s_pix[n];
+                if (pix < 64 && !((mask >> pix) & 1ull)) continue;
+                const float f = act_fn<kAct>(__uint_as_float(v[i]) + bias[n]);
+                if (yrow) { const int cm = s_cm[n]; if (cm >= 0) yrow[cm] = __float2bfloat16_rn(f); }
+                if (y32row) { const int cm = s_cm32[n]; if (cm >= 0) y32row[cm] = f; }
+              }
+            }
           }
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(tempty_bar(buf));
         }
       }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(tempty_bar(buf));
+      if (kTmaStore && issuer) ptx::bulk_wait_all0();      // staging tiles must outlive their TMA stores
     }
   }
 
@@ -253,6 +331,16 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, p.tmem_cols);
   }
+}
+
+typedef void (*UmmaKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const EngineParams);
+static UmmaKernelFn umma_kernel_for(int act, bool tma_store) {
+  switch (act) {
+#define PSOB_K(A) case A: return tma_store ? pixel_gemm_umma_kernel<A, true> : pixel_gemm_umma_kernel<A, false>;
+    PSOB_K(PSOB_ACT_NONE) PSOB_K(PSOB_ACT_RELU) PSOB_K(PSOB_ACT_LEAKY) PSOB_K(PSOB_ACT_TANH) PSOB_K(PSOB_ACT_SIGMOID)
+#undef PSOB_K
+  }
+  return nullptr;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -337,7 +425,8 @@ struct psob_layer {
   __nv_bfloat16* wpack = nullptr;
   CUtensorMap tmB;
   bool have_tmB = false;
-  int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, smem_bytes = 0;
+  bool tma_store = false, vec4 = false;
+  int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, stg_off = 0, smem_bytes = 0;
   uint32_t tmem_cols = 0;
   int sm_count = 0;
   int device = -1;
@@ -423,11 +512,26 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   PSOB_CUDA_L(cudaMemcpy(l->wpack, d->wpack, (size_t)d->n_wrows * kKChunk * 2, cudaMemcpyHostToDevice));
 #undef PSOB_CUDA_L
 
+  // epilogue flavour: TMA store when every 64-column chunk is one contiguous, 16-byte aligned 128-byte row
+  l->tma_store = d->vec8 && d->nt % 64 == 0 && d->cc % 64 == 0 && d->out32_pitch == 0;
+  for (int c = 0; c < d->nt && l->tma_store; c += 64)
+    for (int i = 1; i < 64; ++i)
+      if ((d->col_map[c] >= 0) != (d->col_map[c + i] >= 0) || (d->col_map[c] >= 0 && d->col_map[c + i] != d->col_map[c] + i)) l->tma_store = false;
+  // direct epilogue: 4 single-pixel columns -> one 8-byte bf16 store
+  l->vec4 = !d->vec8 && d->cc == 1 && d->out_pitch > 0 && d->nt <= 64;
+  for (int c = 0; c < d->nt && l->vec4; c += 4) {
+    for (int i = 1; i < 4; ++i)
+      if ((d->col_map[c] >= 0) != (d->col_map[c + i] >= 0) || (d->col_map[c] >= 0 && d->col_map[c + i] != d->col_map[c] + i)) l->vec4 = false;
+    for (int j = 0; j < d->n_jobs && l->vec4 && d->col_map[c] >= 0; ++j)
+      if ((d->jobs[8 * j + 2] + d->col_map[c]) % 4) l->vec4 = false;
+  }
+
   // shared-memory plan
   const int b_tile = d->mma_n * 128;
   l->stage_bytes = kATileBytes + (d->b_resident ? 0 : b_tile);
   const int res_bytes = d->b_resident ? d->n_wrows * 128 : 0;
-  int avail = kSmemLimit - 1024 - kBarBytes - kTabBytes - res_bytes;
+  const int stg_bytes = l->tma_store ? 2 * kATileBytes : 0;
+  int avail = kSmemLimit - 1024 - kBarBytes - kTabBytes - res_bytes - stg_bytes;
   l->n_stages = avail / l->stage_bytes;
   if (l->n_stages > kMaxStages) l->n_stages = kMaxStages;
   if (l->n_stages < 2) {
@@ -435,7 +539,8 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: resident weights (%d B) leave no room for a 2-stage ring", res_bytes);
   }
   l->res_off = l->n_stages * l->stage_bytes;
-  l->bar_off = l->res_off + res_bytes;
+  l->stg_off = l->res_off + res_bytes;
+  l->bar_off = l->stg_off + stg_bytes;
   l->smem_bytes = l->bar_off + kBarBytes + kTabBytes + 1024;
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * d->nt)) cols <<= 1;
@@ -462,6 +567,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.vec8 = (d.vec8 && p.y) ? 1 : 0;
   p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
+  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
   p.tmem_cols = l->tmem_cols;
 
@@ -474,17 +580,26 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   }
   if (impl != PSOB_IMPL_TCGEN05) return fail(PSOB_E_ARG, "psob_layer_run: unknown impl %d", impl);
 
+  const bool tma_store = l->tma_store && p.y != nullptr;
+  UmmaKernelFn fn = umma_kernel_for(d.act, tma_store);
+  if (!fn) return fail(PSOB_E_ARG, "psob_layer_run: unknown activation %d", d.act);
   if (!l->have_tmB) {
     int rc = make_tmap(&l->tmB, l->wpack, kKChunk, (uint64_t)d.n_wrows, kKChunk, (uint32_t)d.mma_n);
     if (rc) return rc;
-    PSOB_CUDA(cudaFuncSetAttribute(pixel_gemm_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    PSOB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     l->have_tmB = true;
   }
-  CUtensorMap tmA;
+  CUtensorMap tmA, tmY;
   int rc = make_tmap(&tmA, x, (uint64_t)x_pitch, (uint64_t)P, (uint64_t)x_pitch, kTileM);
   if (rc) return rc;
+  if (tma_store) {
+    rc = make_tmap(&tmY, y, (uint64_t)d.out_pitch, (uint64_t)P, (uint64_t)d.out_pitch, kTileM);
+    if (rc) return rc;
+  } else {
+    tmY = tmA;
+  }
   long long grid = p.n_items < l->sm_count ? p.n_items : l->sm_count;
-  pixel_gemm_umma_kernel<<<(unsigned)grid, kThreads, l->smem_bytes, (cudaStream_t)s>>>(tmA, l->tmB, p);
+  fn<<<(unsigned)grid, kThreads, l->smem_bytes, (cudaStream_t)s>>>(tmA, l->tmB, tmY, p);
   PSOB_LAUNCH_CHECK("pixel_gemm_umma_kernel");
   return 0;
 }

@@ -158,7 +158,7 @@ def run_psob(args):
     gnet = engine.GeneratorNet(gen.state_dict(), P, device=dev)
     dnet = engine.DiscriminatorNet(disc.state_dict(), P, device=dev)
     sw = engine.SwarmEngine(P, D_LATENT, generator=gnet, fitness=engine.DScoreFitness(dnet), w_inertia=0.73, w_cogn=1.496,
-                            w_soci=1.496, seed=42, index_offset=first, max_iterations=4096, device=dev)
+                            w_soci=1.496, seed=42, index_offset=first, max_iterations=4096, device=dev, need_image_f32=False)
     g = torch.Generator(device=dev).manual_seed(42 + rank)
     sw.init_particles(generator=g)
     use_graph = (world == 1) and not args.no_graph

@@ -79,6 +79,7 @@ class Network:
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.P = P
         self.impl = impl
+        self.skip_f32 = False
         self.programs = programs
         with torch.cuda.device(self.device):
             self.layers = [Layer(p) for p in programs]
@@ -95,7 +96,10 @@ class Network:
     def forward(self, x: torch.Tensor):
         """x: bf16 [P, >= in_pitch].  Returns (last bf16 activation or None, last fp32 output or None)."""
         cur = x
-        for layer, y, y32 in zip(self.layers, self.acts, self.acts32):
+        last = len(self.layers) - 1
+        for i, (layer, y, y32) in enumerate(zip(self.layers, self.acts, self.acts32)):
+            if i == last and self.skip_f32 and y is not None:
+                y32 = None                      # e.g. D-score fitness only consumes the padded bf16 image
             layer.run(cur, self.P, y, y32, self.impl)
             cur = y
         return self.acts[-1], self.acts32[-1]
@@ -292,13 +296,15 @@ class SwarmEngine:
 
     def __init__(self, P: int, D: int, *, generator: Optional[GeneratorNet] = None, fitness=None, objective=None,
                  w_inertia=0.5, w_cogn=0.8, w_soci=0.9, v_max=math.inf, lo=-math.inf, hi=math.inf, seed=42,
-                 index_offset=0, max_iterations=1024, group=None, device=None):
+                 index_offset=0, max_iterations=1024, group=None, device=None, need_image_f32=True):
         require_cuda()
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.P, self.D_logical = P, D
         D = (D + 3) // 4 * 4          # rows are float4-aligned; padding dimensions stay exactly 0 forever
         self.D = D
         self.gen, self.fitness, self.objective = generator, fitness, objective
+        if generator is not None:
+            generator.skip_f32 = (not need_image_f32) and isinstance(fitness, DScoreFitness)
         self.w0, self.c_cogn, self.c_soci = float(w_inertia), float(w_cogn), float(w_soci)
         self.v_max, self.lo, self.hi = v_max, lo, hi
         self.seed, self.index_offset = int(seed), int(index_offset)

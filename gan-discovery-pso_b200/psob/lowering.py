@@ -239,6 +239,8 @@ def lower_convt_k4s2p1(name, w, b, act, h, wd, *, m=1, image_out=False, in_cp=No
         out_pitch = ho * wo * cpo
         out32_pitch = 0
 
+    # small weight packs (the Cout = 1 image layer: 9 tiles x 2 KB) stay in shared memory for the CTA's lifetime
+    resident = len(tiles) * nt * KCHUNK * 2 <= 32 * 1024
     steps, jobs = [], []
     for bq in range(-1, h, m):
         for br in range(-1, wd, m):
@@ -254,7 +256,7 @@ def lower_convt_k4s2p1(name, w, b, act, h, wd, *, m=1, image_out=False, in_cp=No
                             continue
                         for kc in range(nkc):
                             steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, tile_of[(a, bb, kc, ch)] * nt, 0,
-                                          STEP_ACCUM if len(steps) > sb else 0))
+                                          (STEP_ACCUM if len(steps) > sb else 0) | (STEP_B_RESIDENT if resident else 0)))
                 oy0, ox0 = 2 * bq + 1, 2 * br + 1
                 bits = [0 <= oy0 + u < ho and 0 <= ox0 + v < wo for u in range(2 * m) for v in range(2 * m)]
                 if not any(bits):
@@ -290,7 +292,7 @@ def lower_convt_k4s2p1(name, w, b, act, h, wd, *, m=1, image_out=False, in_cp=No
             num = ox + 1 - kx
             if num % 2 == 0 and 0 <= num // 2 < wd:
                 conn_x += 1
-    return _finish(name, nt, nt, cc, act, h * wd * cpi, out_pitch, out32_pitch, tiles, False, steps, jobs,
+    return _finish(name, nt, nt, cc, act, h * wd * cpi, out_pitch, out32_pitch, tiles, resident, steps, jobs,
                    col_map, col_map32, bias, macs_exact=conn * conn_x * cin * cout, meta=meta)
 
 

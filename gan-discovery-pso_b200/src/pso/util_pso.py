@@ -121,7 +121,8 @@ class Swarm:
             self.engine = _engine.SwarmEngine(P, D, generator=gen, fitness=fit, w_inertia=self.w_inertia, w_cogn=self.w_cogn,
                                               w_soci=self.w_soci, v_max=self.v_max, lo=self.bounds[0], hi=self.bounds[1],
                                               seed=self.seed, index_offset=self.index_offset,
-                                              max_iterations=max(self.n_iterations, 1), group=self.group, device=self.device)
+                                              max_iterations=max(self.n_iterations, 1), group=self.group, device=self.device,
+                                              need_image_f32=bool(self.log_images_every))
         self.engine.inertia_decay = self._inertia_decay
         self.swarm = [Particle(D, _owner=self, _index=i) for i in range(P)]
         if self.record_history:

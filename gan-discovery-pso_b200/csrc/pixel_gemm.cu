@@ -45,6 +45,7 @@ struct EngineParams {
   int b_resident, n_wrows, n_bias_rows;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4;
+  unsigned long long* prof;   // optional [gridDim][8] role wait-cycle counters (debug)
   uint32_t idesc, tmem_cols;
 };
 
@@ -61,6 +62,14 @@ __device__ __forceinline__ float apply_act(float v, int act) {
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&t);
+}
+
+// timed mbarrier wait: adds the cycles spent waiting to `acc` when role profiling is on
+__device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity, bool prof, unsigned long long& acc) {
+  if (!prof) { ptx::mbar_wait(bar, parity); return; }
+  long long t0 = clock64();
+  ptx::mbar_wait(bar, parity);
+  acc += (unsigned long long)(clock64() - t0);
 }
 
 template <int kAct>
@@ -93,6 +102,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  // Contiguous item ranges: a CTA walks the jobs of one particle tile in order, so the input pixels
+  // shared by neighbouring jobs (2.25x - 4x re-reads) are re-read from L2 moments later, not from DRAM.
+  const long long per_cta = (p.n_items + gridDim.x - 1) / gridDim.x;
+  const long long item_begin = per_cta * blockIdx.x;
+  const long long item_end = item_begin + per_cta < p.n_items ? item_begin + per_cta : p.n_items;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.n_stages; ++s) {
@@ -146,7 +160,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       }
       int stage = 0;
       uint32_t phase = 0;
-      for (long long item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+      const bool prof = p.prof != nullptr;
+      unsigned long long w_empty = 0;
+      const long long t_start = clock64();
+      for (long long item = item_begin; item < item_end; ++item) {
         const int ptile = (int)(item / p.n_jobs);
         const int job = (int)(item - (long long)ptile * p.n_jobs);
         const int4 j0 = __ldg(p.jobs + 2 * job);
@@ -154,7 +171,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         for (int s = j0.x; s < j0.x + j0.y; ++s) {
           const int4 st = st_next;
           if (s + 1 < j0.x + j0.y) st_next = __ldg(p.steps + s + 1);     // descriptor fetch overlaps the wait
-          ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
+          mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
           const bool res = (st.w & 2) != 0;
           ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)p.mma_n * 128u));
           const uint32_t a_dst = base + (uint32_t)stage * p.stage_bytes;
@@ -163,6 +180,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
         }
       }
+      if (prof) { p.prof[blockIdx.x * 8 + 0] = w_empty; p.prof[blockIdx.x * 8 + 1] = (unsigned long long)(clock64() - t_start); }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
@@ -170,18 +188,21 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     int stage = 0;
     uint32_t phase = 0;
     uint32_t it = 0;
-    for (long long item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
+    const bool prof = p.prof != nullptr;
+    unsigned long long w_full = 0, w_tempty = 0;
+    const long long t_start = clock64();
+    for (long long item = item_begin; item < item_end; ++item, ++it) {
       const int ptile = (int)(item / p.n_jobs);
       const int job = (int)(item - (long long)ptile * p.n_jobs);
       const int4 j0 = __ldg(p.jobs + 2 * job);
       const uint32_t buf = it & 1u, use = it >> 1;
       int4 st_next = __ldg(p.steps + j0.x);
-      ptx::mbar_wait(tempty_bar(buf), (use & 1u) ^ 1u);
+      mbar_wait_t(tempty_bar(buf), (use & 1u) ^ 1u, prof, w_tempty);
       ptx::tc_fence_after();
       for (int s = j0.x; s < j0.x + j0.y; ++s) {
         const int4 st = st_next;
         if (s + 1 < j0.x + j0.y) st_next = __ldg(p.steps + s + 1);
-        ptx::mbar_wait(full_bar(stage), phase);
+        mbar_wait_t(full_bar(stage), phase, prof, w_full);
         ptx::tc_fence_after();
         if (lane == 0) {
           const uint32_t a_addr = base + (uint32_t)stage * p.stage_bytes;
@@ -200,6 +221,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       if (lane == 0) ptx::umma_commit(tfull_bar(buf));
       __syncwarp();
     }
+    if (prof && lane == 0) {
+      p.prof[blockIdx.x * 8 + 2] = w_full; p.prof[blockIdx.x * 8 + 3] = w_tempty;
+      p.prof[blockIdx.x * 8 + 4] = (unsigned long long)(clock64() - t_start);
+    }
   } else {
     // ------------------------------------------------------------------ epilogue
     // 8 warps = 2 groups x 4 TMEM lane quadrants (quadrant = warp % 4, the hardware's access rule)
@@ -211,8 +236,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const uint32_t srow = sbuf + (uint32_t)row * 128u;
     const uint32_t sw = (uint32_t)(row & 7);
     uint32_t it = 0;
+    const bool prof = p.prof != nullptr;
+    unsigned long long w_tfull = 0;
+    const long long t_start = clock64();
     if (kTmaStore || grp == 0) {
-      for (long long item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
+      for (long long item = item_begin; item < item_end; ++item, ++it) {
         const int ptile = (int)(item / p.n_jobs);
         const int job = (int)(item - (long long)ptile * p.n_jobs);
         const int4 j0 = __ldg(p.jobs + 2 * job);
@@ -220,7 +248,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
         const float* bias = bias_in_smem ? s_bias + j1.z * p.nt : p.bias + (size_t)j1.z * p.nt;
         const uint32_t buf = it & 1u, use = it >> 1;
-        ptx::mbar_wait(tfull_bar(buf), use & 1u);
+        mbar_wait_t(tfull_bar(buf), use & 1u, prof, w_tfull);
         ptx::tc_fence_after();
         const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.nt;
         if (kTmaStore) {
@@ -322,6 +350,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         }
       }
       if (kTmaStore && issuer) ptx::bulk_wait_all0();      // staging tiles must outlive their TMA stores
+      if (prof && warp == 2 && lane == 0) {
+        p.prof[blockIdx.x * 8 + 5] = w_tfull; p.prof[blockIdx.x * 8 + 6] = (unsigned long long)(clock64() - t_start);
+        p.prof[blockIdx.x * 8 + 7] = (unsigned long long)(item_end - item_begin);
+      }
     }
   }
 
@@ -426,6 +458,7 @@ struct psob_layer {
   CUtensorMap tmB;
   bool have_tmB = false;
   bool tma_store = false, vec4 = false;
+  unsigned long long* prof = nullptr;
   int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, stg_off = 0, smem_bytes = 0;
   uint32_t tmem_cols = 0;
   int sm_count = 0;
@@ -549,6 +582,12 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   return 0;
 }
 
+int psob_layer_profile(psob_layer* l, void* counters) {
+  if (!l) return fail(PSOB_E_ARG, "psob_layer_profile: null layer");
+  l->prof = reinterpret_cast<unsigned long long*>(counters);
+  return 0;
+}
+
 int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, int32_t impl, psob_stream_t s) {
   if (!l || !x || P <= 0) return fail(PSOB_E_ARG, "psob_layer_run: bad arguments");
   const psob_layer_desc& d = l->d;
@@ -567,7 +606,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.vec8 = (d.vec8 && p.y) ? 1 : 0;
   p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
-  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0;
+  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
   p.tmem_cols = l->tmem_cols;
 

@@ -14,7 +14,7 @@ EXPORTS = [
     "psob_version", "psob_last_error", "psob_device_info", "psob_update", "psob_pack_latent",
     "psob_pbest_minloc", "psob_gbest_candidate", "psob_gbest_apply", "psob_score_fitness",
     "psob_softmax_select", "psob_recon_fitness", "psob_rescale_minmax", "psob_pack_image",
-    "psob_layer_create", "psob_layer_destroy", "psob_layer_run",
+    "psob_layer_create", "psob_layer_destroy", "psob_layer_run", "psob_layer_profile",
 ]
 
 MODE_IN_TRAINING, MODE_OUT_TRAINING = 0, 1
@@ -83,6 +83,7 @@ def lib():
         "psob_layer_create": ([C.POINTER(LayerDesc), C.POINTER(vp)], C.c_int),
         "psob_layer_destroy": ([vp], C.c_int),
         "psob_layer_run": ([vp, vp, i64, i64, vp, vp, i32, vp], C.c_int),
+        "psob_layer_profile": ([vp, vp], C.c_int),
     }
     for name, (args, res) in sig.items():
         fn = getattr(l, name)

@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 from typing import Callable, List, Optional
 
 import numpy as np
@@ -120,8 +121,10 @@ def _sd_numpy(sd):
 class GeneratorNet(Network):
     """28x28 DCGAN generator / VQ-VAE-GAN decoder (src/utils/util_dcgan.py:128-149)."""
 
-    def __init__(self, state_dict, P, prefix="gen", device=None, impl=_ffi.IMPL_TCGEN05, m_last=2):
+    def __init__(self, state_dict, P, prefix="gen", device=None, impl=_ffi.IMPL_TCGEN05, m_last=None):
         sd = _sd_numpy(state_dict)
+        if m_last is None:
+            m_last = int(os.environ.get("PSOB_M_LAST", "2"))      # image-layer block size (tuning knob)
         if prefix is None:
             prefix = "gen" if any(k.startswith("gen.") for k in sd) else "decoder"
         self.z_dim = int(sd[f"{prefix}.0.0.weight"].shape[0])

@@ -27,7 +27,8 @@ constexpr int kATileBytes = kTileM * kKChunk * 2;   // 16 KB
 constexpr int kSmemLimit = 232448;                  // 227 KB per CTA on sm_100
 constexpr int kBarBytes = 256;
 constexpr int kMaxBiasRowsSmem = 8;
-constexpr int kTabBytes = 256 * 4 * 2 + 256 + kMaxBiasRowsSmem * 256 * 4;   // col_map, col_map32, pix, bias rows
+constexpr int kMaxStepsSmem = 1024;                // step descriptors staged in SMEM (16 B each)
+constexpr int kMaxJobsSmem = 256;                  // job descriptors staged in SMEM (32 B each)
 constexpr int kThreads = 320;                     // TMA warp + MMA warp + 2 epilogue groups of 4 warps
 
 struct EngineParams {
@@ -42,9 +43,10 @@ struct EngineParams {
   long long n_items;
   int n_jobs;
   int mma_n, nt, cc, act, out_pitch, out32_pitch, vec8;
-  int b_resident, n_wrows, n_bias_rows;
+  int b_resident, n_wrows, n_bias_rows, n_steps;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4;
+  int bias_off, steps_off, jobs_off, stg_bufs;   // SMEM table offsets from the table base (-1: stays in global)
   unsigned long long* prof;   // optional [gridDim][8] role wait-cycle counters (debug)
   uint32_t idesc, tmem_cols;
 };
@@ -132,11 +134,20 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   // Epilogue tables live in shared memory: with ~220 KB of the SM's L1/SMEM carved out for the
   // ring, every __ldg would be an L2 round trip to the SAME few lines from all 148 SMs (measured:
   // ~4k cycles per 16-column epilogue iteration before this staging).
-  int* s_cm = reinterpret_cast<int*>(gbase + p.bar_off + kBarBytes);
+  uint8_t* tab = gbase + p.bar_off + kBarBytes;
+  int* s_cm = reinterpret_cast<int*>(tab);
   int* s_cm32 = s_cm + 256;
   uint8_t* s_pix = reinterpret_cast<uint8_t*>(s_cm32 + 256);
-  float* s_bias = reinterpret_cast<float*>(s_pix + 256);
-  const bool bias_in_smem = p.n_bias_rows <= kMaxBiasRowsSmem;
+  float* s_bias = reinterpret_cast<float*>(tab + (p.bias_off >= 0 ? p.bias_off : 0));
+  const bool bias_in_smem = p.bias_off >= 0;
+  // Step / job descriptors too: a __ldg per step is an L2 round trip (~700-1000 cycles under load) that a
+  // one-step prefetch cannot hide — it was the per-step floor of every layer (profiles/r01_roles_v3c.log).
+  const int4* steps = p.steps_off >= 0 ? reinterpret_cast<const int4*>(tab + p.steps_off) : p.steps;
+  const int4* jobs = p.jobs_off >= 0 ? reinterpret_cast<const int4*>(tab + p.jobs_off) : p.jobs;
+  if (p.steps_off >= 0)
+    for (int i = threadIdx.x; i < p.n_steps; i += kThreads) reinterpret_cast<int4*>(tab + p.steps_off)[i] = p.steps[i];
+  if (p.jobs_off >= 0)
+    for (int i = threadIdx.x; i < 2 * p.n_jobs; i += kThreads) reinterpret_cast<int4*>(tab + p.jobs_off)[i] = p.jobs[i];
   for (int i = threadIdx.x; i < p.nt; i += kThreads) {
     s_cm[i] = p.col_map[i];
     s_cm32[i] = p.col_map32[i];
@@ -166,11 +177,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       for (long long item = item_begin; item < item_end; ++item) {
         const int ptile = (int)(item / p.n_jobs);
         const int job = (int)(item - (long long)ptile * p.n_jobs);
-        const int4 j0 = __ldg(p.jobs + 2 * job);
-        int4 st_next = __ldg(p.steps + j0.x);
+        const int4 j0 = jobs[2 * job];
+        int4 st_next = steps[j0.x];
         for (int s = j0.x; s < j0.x + j0.y; ++s) {
           const int4 st = st_next;
-          if (s + 1 < j0.x + j0.y) st_next = __ldg(p.steps + s + 1);     // descriptor fetch overlaps the wait
+          if (s + 1 < j0.x + j0.y) st_next = steps[s + 1];     // descriptor fetch overlaps the wait
           mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
           const bool res = (st.w & 2) != 0;
           ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)p.mma_n * 128u));
@@ -194,14 +205,14 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     for (long long item = item_begin; item < item_end; ++item, ++it) {
       const int ptile = (int)(item / p.n_jobs);
       const int job = (int)(item - (long long)ptile * p.n_jobs);
-      const int4 j0 = __ldg(p.jobs + 2 * job);
+      const int4 j0 = jobs[2 * job];
       const uint32_t buf = it & 1u, use = it >> 1;
-      int4 st_next = __ldg(p.steps + j0.x);
+      int4 st_next = steps[j0.x];
       mbar_wait_t(tempty_bar(buf), (use & 1u) ^ 1u, prof, w_tempty);
       ptx::tc_fence_after();
       for (int s = j0.x; s < j0.x + j0.y; ++s) {
         const int4 st = st_next;
-        if (s + 1 < j0.x + j0.y) st_next = __ldg(p.steps + s + 1);
+        if (s + 1 < j0.x + j0.y) st_next = steps[s + 1];
         mbar_wait_t(full_bar(stage), phase, prof, w_full);
         ptx::tc_fence_after();
         if (lane == 0) {
@@ -232,8 +243,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const int grp = (warp - 2) >> 2;
     const int row = q * 32 + lane;
     const bool issuer = ((warp - 2) & 3) == 0 && lane == 0;
-    const uint32_t sbuf = base + p.stg_off + (uint32_t)grp * kATileBytes;
-    const uint32_t srow = sbuf + (uint32_t)row * 128u;
+    const uint32_t sbuf0 = base + p.stg_off + (uint32_t)(grp * p.stg_bufs) * kATileBytes;
+    uint32_t sflip = 0;                       // staging tile in use (double-buffered when stg_bufs == 2)
     const uint32_t sw = (uint32_t)(row & 7);
     uint32_t it = 0;
     const bool prof = p.prof != nullptr;
@@ -243,8 +254,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       for (long long item = item_begin; item < item_end; ++item, ++it) {
         const int ptile = (int)(item / p.n_jobs);
         const int job = (int)(item - (long long)ptile * p.n_jobs);
-        const int4 j0 = __ldg(p.jobs + 2 * job);
-        const int4 j1 = __ldg(p.jobs + 2 * job + 1);
+        const int4 j0 = jobs[2 * job];
+        const int4 j1 = jobs[2 * job + 1];
         const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
         const float* bias = bias_in_smem ? s_bias + j1.z * p.nt : p.bias + (size_t)j1.z * p.nt;
         const uint32_t buf = it & 1u, use = it >> 1;
@@ -277,7 +288,9 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               __syncwarp();
               if (lane == 0) ptx::mbar_arrive(tempty_bar(buf));
             }
-            if (issuer) ptx::bulk_wait_read0();           // the previous TMA store has drained the staging tile
+            const uint32_t sbuf = sbuf0 + sflip * kATileBytes;
+            const uint32_t srow = sbuf + (uint32_t)row * 128u;
+            if (issuer) { if (p.stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }   // the store that last used this tile has drained it
             ptx::named_bar_sync(1 + grp, 128);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -296,6 +309,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               ptx::tma_store_2d(&tmY, sbuf, j0.z + cm, ptile * kTileM);   // rows >= P are clipped by the tensor map
               ptx::bulk_commit();
             }
+            if (p.stg_bufs == 2) sflip ^= 1u;
           }
         } else {
           const long long particle = (long long)ptile * kTileM + row;
@@ -459,6 +473,7 @@ struct psob_layer {
   bool have_tmB = false;
   bool tma_store = false, vec4 = false;
   unsigned long long* prof = nullptr;
+  int bias_off = -1, steps_off = -1, jobs_off = -1, tab_bytes = 0, stg_bufs = 0;
   int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, stg_off = 0, smem_bytes = 0;
   uint32_t tmem_cols = 0;
   int sm_count = 0;
@@ -563,8 +578,22 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   const int b_tile = d->mma_n * 128;
   l->stage_bytes = kATileBytes + (d->b_resident ? 0 : b_tile);
   const int res_bytes = d->b_resident ? d->n_wrows * 128 : 0;
-  const int stg_bytes = l->tma_store ? 2 * kATileBytes : 0;
-  int avail = kSmemLimit - 1024 - kBarBytes - kTabBytes - res_bytes - stg_bytes;
+  // table area: col_map + col_map32 + pix (fixed 2304 B), then optional bias rows, steps, jobs
+  int tab = 256 * 4 * 2 + 256;
+  l->bias_off = l->steps_off = l->jobs_off = -1;
+  if (d->n_bias_rows <= kMaxBiasRowsSmem) { l->bias_off = tab; tab += d->n_bias_rows * d->nt * 4; }
+  tab = (tab + 15) & ~15;
+  if (d->n_steps <= kMaxStepsSmem) { l->steps_off = tab; tab += d->n_steps * 16; }
+  if (d->n_jobs <= kMaxJobsSmem) { l->jobs_off = tab; tab += d->n_jobs * 32; }
+  l->tab_bytes = (tab + 127) & ~127;
+  // staging tiles for the TMA-store epilogue: 2 per group if that still leaves a 3-stage ring
+  l->stg_bufs = 0;
+  if (l->tma_store) {
+    const int room = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes;
+    l->stg_bufs = (room - 4 * kATileBytes) / l->stage_bytes >= 3 ? 2 : 1;
+  }
+  const int stg_bytes = 2 * l->stg_bufs * kATileBytes;
+  int avail = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes - stg_bytes;
   l->n_stages = avail / l->stage_bytes;
   if (l->n_stages > kMaxStages) l->n_stages = kMaxStages;
   if (l->n_stages < 2) {
@@ -574,7 +603,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->res_off = l->n_stages * l->stage_bytes;
   l->stg_off = l->res_off + res_bytes;
   l->bar_off = l->stg_off + stg_bytes;
-  l->smem_bytes = l->bar_off + kBarBytes + kTabBytes + 1024;
+  l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * d->nt)) cols <<= 1;
   l->tmem_cols = cols;
@@ -607,6 +636,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
   p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof;
+  p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
   p.tmem_cols = l->tmem_cols;
 

@@ -14,6 +14,15 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// One elected lane of a CONVERGED warp.  Unlike `if (lane == 0)`, this tells ptxas the warp is converged,
+// so operands of the single-thread instructions (UTCHMMA / UTMALDG / UTCBAR) are moved to uniform
+// registers with plain R2UR instead of a per-instruction ELECT/R2UR/BRA.U.ANY waterfall loop.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
@@ -99,6 +108,28 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// One K-chunk (64 bf16 = 4 MMAs of K=16) plus the commit that frees the ring stage, as ONE asm block:
+// the operands are not provably warp-uniform for nvcc (they come from the step table), so every
+// separate tcgen05 statement costs an ELECT/R2UR "waterfall" (~100+ cycles of scalar latency, measured
+// ~140 cycles per MMA regardless of N).  Inside one block the +32-byte descriptor advances stay in the
+// uniform datapath and the waterfall is paid once per step.
+__device__ __forceinline__ void umma_bf16_k64_commit(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                                     uint32_t accumulate, uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred p, t;\n\t.reg .b64 a1, b1, a2, b2, a3, b3;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.eq.u32 t, 0, 0;\n\t"
+      "add.u64 a1, %1, 2;\n\tadd.u64 b1, %2, 2;\n\t"
+      "add.u64 a2, %1, 4;\n\tadd.u64 b2, %2, 4;\n\t"
+      "add.u64 a3, %1, 6;\n\tadd.u64 b3, %2, 6;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, t;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a2, b2, %3, t;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a3, b3, %3, t;\n\t"
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%5];\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(bar)
       : "memory");
 }
 // arrive on an mbarrier when all previously issued tcgen05.mma of this thread have completed

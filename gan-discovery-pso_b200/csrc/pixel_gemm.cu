@@ -14,6 +14,7 @@
 #include "umma.cuh"
 
 #include <cuda.h>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -28,7 +29,9 @@ constexpr int kSmemLimit = 232448;                  // 227 KB per CTA on sm_100
 constexpr int kBarBytes = 256;
 constexpr int kMaxBiasRowsSmem = 8;
 constexpr int kMaxStepsSmem = 1024;                // step descriptors staged in SMEM (16 B each)
-constexpr int kMaxJobsSmem = 256;                  // job descriptors staged in SMEM (32 B each)
+constexpr int kMaxJobsSmem = 256;
+constexpr int kMaxSoloResident = 96 * 1024;       // resident weights of one CTA before the pair mode takes over
+constexpr int kMaxPairResident = 128 * 1024;      // per CTA of a pair                  // job descriptors staged in SMEM (32 B each)
 constexpr int kThreads = 320;                     // 2 epilogue groups of 4 warps + TMA warp + MMA warp
 // The SMSP arbiter favours the highest warp id: the two single-thread roles that must never wait for
 // an issue slot (TMA producer, MMA issuer) get the top ids; epilogue warps 0..7 map to TMEM quadrant w % 4.
@@ -49,9 +52,10 @@ struct EngineParams {
   int mma_n, nt, cc, act, out_pitch, out32_pitch, vec8;
   int b_resident, n_wrows, n_bias_rows, n_steps;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
-  int vec4;
+  int vec4, strided;
+  int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
   int bias_off, steps_off, jobs_off, stg_bufs;   // SMEM table offsets from the table base (-1: stays in global)
-  unsigned long long* prof;   // optional [gridDim][8] role wait-cycle counters (debug)
+  unsigned long long* prof;   // optional [gridDim][16] role wait-cycle counters (debug)
   uint32_t idesc, tmem_cols;
 };
 
@@ -90,7 +94,14 @@ __device__ __forceinline__ float act_fn(float v) {
 // kTmaStore: bf16 NHWC outputs whose 64-column chunks are contiguous 128-byte rows leave through a
 // swizzled shared-memory tile and one TMA store per chunk (two epilogue groups alternate chunks);
 // otherwise (image / score outputs, nt = 16..64) group 0 stores directly from registers.
-template <int kAct, bool kTmaStore>
+//
+// kPair: the CTA is one half of a cluster of two (tcgen05 cta_group::2).  The pair works on 256 particles
+// (rank r owns rows [r*128, r*128+128) of the pair tile and the matching 128 TMEM lanes); every weight
+// tile is split by rows between the two CTAs and stays RESIDENT in shared memory, so the only per-step
+// L2 traffic is each CTA's own 16 KB A tile (the L2 slices deliver ~42 B/clk/SM with all SMs pulling:
+// streaming a 32 KB B tile per 512-cycle step had every heavy layer L2-bound at ~45 % of the MMA rate).
+// The leader (rank 0) issues all MMAs; its commits arrive on the barriers of both CTAs.
+template <int kAct, bool kTmaStore, bool kPair>
 __global__ void __launch_bounds__(kThreads, 1)
 pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmY, const EngineParams p) {
@@ -108,11 +119,30 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  // Contiguous item ranges: a CTA walks the jobs of one particle tile in order, so the input pixels
-  // shared by neighbouring jobs (2.25x - 4x re-reads) are re-read from L2 moments later, not from DRAM.
-  const long long per_cta = (p.n_items + gridDim.x - 1) / gridDim.x;
-  const long long item_begin = per_cta * blockIdx.x;
-  const long long item_end = item_begin + per_cta < p.n_items ? item_begin + per_cta : p.n_items;
+  const uint32_t crank = kPair ? ptx::cluster_ctarank() : 0u;
+  const bool leader = crank == 0u;
+  // Contiguous item ranges: a CTA (or CTA pair) walks the jobs of one particle tile in order, so the input
+  // pixels shared by neighbouring jobs (2.25x - 4x re-reads) are re-read from L2 moments later, not from DRAM.
+  const long long n_workers = kPair ? (gridDim.x >> 1) : gridDim.x;
+  const long long worker = kPair ? (blockIdx.x >> 1) : blockIdx.x;
+  // Item order.  strided: worker w takes items w, w + W, w + 2W, ... so that at any moment all workers sit on
+  // neighbouring jobs of the same one or two particle tiles (re-reads of shared input pixels hit L2);
+  // contiguous: every worker walks its own particle tiles (no sharing between workers).
+  const long long per_cta = (p.n_items + n_workers - 1) / n_workers;
+  const long long item_begin = p.strided ? worker : (per_cta * worker < p.n_items ? per_cta * worker : p.n_items);
+  const long long item_end = p.strided ? p.n_items : (item_begin + per_cta < p.n_items ? item_begin + per_cta : p.n_items);
+  const long long item_step = p.strided ? n_workers : 1;
+  const uint32_t n_jobs_u = (uint32_t)p.n_jobs;
+  // particle-tile index of this CTA for TMA coordinates: pair tile t covers tiles 2t (leader) and 2t+1
+  auto tile_idx = [&](int ptile) { return kPair ? 2 * ptile + (int)crank : ptile; };
+  auto tile_row = [&](int ptile) { return tile_idx(ptile) * kTileM; };
+  // TMA coordinates of the 64-column chunk starting at column `col` of particle tile `ptile`.  Tile-major
+  // activations keep every [128 particles x 64 channels] operand tile in ONE contiguous 16 KB block (whole
+  // DRAM pages per access); in the row-major layout the same tile is 128 rows of 128 B, one DRAM page each.
+  auto in_c0 = [&](int col) { return p.in_tiled ? 0 : col; };
+  auto in_c1 = [&](int ptile, int col) { return p.in_tiled ? (tile_idx(ptile) * p.n_in_chunks + (col >> 6)) * kTileM : tile_row(ptile); };
+  auto out_c0 = [&](int col) { return p.out_tiled ? 0 : col; };
+  auto out_c1 = [&](int ptile, int col) { return p.out_tiled ? (tile_idx(ptile) * p.n_out_chunks + (col >> 6)) * kTileM : tile_row(ptile); };
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.n_stages; ++s) {
@@ -121,14 +151,14 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(tfull_bar(b), 1);
-      ptx::mbar_init(tempty_bar(b), kTmaStore ? 8 : 4);
+      ptx::mbar_init(tempty_bar(b), kPair ? 16 : (kTmaStore ? 8 : 4));   // pair: both CTAs' epilogue warps
     }
     ptx::mbar_init(res_bar, 1);
     ptx::fence_barrier_init();
   }
   if (warp == kMmaWarp) {
-    ptx::tmem_alloc(tmem_slot, p.tmem_cols);
-    ptx::tmem_relinquish();
+    if (kPair) { ptx::tmem_alloc_pair(tmem_slot, p.tmem_cols); ptx::tmem_relinquish_pair(); }
+    else { ptx::tmem_alloc(tmem_slot, p.tmem_cols); ptx::tmem_relinquish(); }
   }
   if (warp == kTmaWarp && lane == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -161,27 +191,44 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   if (bias_in_smem)
     for (int i = threadIdx.x; i < p.n_bias_rows * p.nt; i += kThreads) s_bias[i] = p.bias[i];
   ptx::tc_fence_before();
-  __syncthreads();
+  if (kPair) ptx::cluster_sync_all(); else __syncthreads();     // pair: the peer's barriers are initialised too
   ptx::tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gbase + p.bar_off + 8 * (2 * kMaxStages + 5));
+
+  if (kPair) {
+    // each CTA loads ITS half of every weight tile (rows [crank*mma_n/2, +mma_n/2) of the tile); the leader's
+    // MMAs read both halves, so nobody starts before both CTAs have seen their loads complete
+    if (warp == kTmaWarp) {
+      if (ptx::elect_one()) {
+        const int half = p.mma_n >> 1;
+        ptx::mbar_arrive_expect_tx(res_bar, (uint32_t)p.n_wrows * 64u);
+        for (int r = 0; r < p.n_wrows; r += p.mma_n)
+          ptx::tma_load_2d(base + p.res_off + (uint32_t)r * 64u, &tmB, 0, r + (int)crank * half, res_bar);
+      }
+      __syncwarp();
+    }
+    ptx::mbar_wait(res_bar, 0);
+    ptx::cluster_sync_all();
+  }
 
   if (warp == kTmaWarp) {
     // ------------------------------------------------------------------ TMA producer
     {
-      if (p.b_resident && ptx::elect_one()) {
+      if (!kPair && p.b_resident && ptx::elect_one()) {
         ptx::mbar_arrive_expect_tx(res_bar, (uint32_t)p.n_wrows * 128u);
         for (int r = 0; r < p.n_wrows; r += p.mma_n)
           ptx::tma_load_2d(base + p.res_off + (uint32_t)r * 128u, &tmB, 0, r, res_bar);
       }
       __syncwarp();
+      const uint32_t full0_leader = kPair ? ptx::map_to_cta(full_bar(0), 0u) : 0u;
       int stage = 0;
       uint32_t phase = 0;
       const bool prof = p.prof != nullptr;
       unsigned long long w_empty = 0;
       const long long t_start = clock64();
-      for (long long item = item_begin; item < item_end; ++item) {
-        const int ptile = (int)(item / p.n_jobs);
-        const int job = (int)(item - (long long)ptile * p.n_jobs);
+      for (long long item = item_begin; item < item_end; item += item_step) {
+        const int ptile = (int)((uint32_t)item / n_jobs_u);          // 32-bit: n_items < 2^31 (checked on the host)
+        const int job = (int)((uint32_t)item - (uint32_t)ptile * n_jobs_u);
         const int4 j0 = jobs[2 * job];
         int4 st_next = steps[j0.x];
         for (int s = j0.x; s < j0.x + j0.y; ++s) {
@@ -190,33 +237,39 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
           const bool res = (st.w & 2) != 0;
           if (ptx::elect_one()) {
-            ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)p.mma_n * 128u));
             const uint32_t a_dst = base + (uint32_t)stage * p.stage_bytes;
-            ptx::tma_load_2d(a_dst, &tmA, st.x, ptile * kTileM, full_bar(stage));
-            if (!res) ptx::tma_load_2d(a_dst + kATileBytes, &tmB, 0, st.y, full_bar(stage));
+            if (kPair) {
+              // both CTAs' A tiles are counted on the leader's barrier (the leader issues the pair MMA)
+              if (leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2u * (uint32_t)kATileBytes);
+              ptx::tma_load_2d_pair(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full0_leader + 8u * (uint32_t)stage);
+            } else {
+              ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)p.mma_n * 128u));
+              ptx::tma_load_2d(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full_bar(stage));
+              if (!res) ptx::tma_load_2d(a_dst + kATileBytes, &tmB, 0, st.y, full_bar(stage));
+            }
           }
           __syncwarp();
           if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
         }
       }
-      if (prof && lane == 0) { p.prof[blockIdx.x * 8 + 0] = w_empty; p.prof[blockIdx.x * 8 + 1] = (unsigned long long)(clock64() - t_start); }
+      if (prof && lane == 0) { p.prof[blockIdx.x * 16 + 0] = w_empty; p.prof[blockIdx.x * 16 + 1] = (unsigned long long)(clock64() - t_start); }
     }
-  } else if (warp == kMmaWarp) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (p.b_resident) ptx::mbar_wait(res_bar, 0);
+  } else if (warp == kMmaWarp && leader) {
+    // ------------------------------------------------------------------ MMA issuer (pair: leader CTA only)
+    if (!kPair && p.b_resident) ptx::mbar_wait(res_bar, 0);
     int stage = 0;
     uint32_t phase = 0;
     uint32_t it = 0;
     const bool prof = p.prof != nullptr;
     unsigned long long w_full = 0, w_tempty = 0;
     const long long t_start = clock64();
-    for (long long item = item_begin; item < item_end; ++item, ++it) {
-      const int ptile = (int)(item / p.n_jobs);
-      const int job = (int)(item - (long long)ptile * p.n_jobs);
+    for (long long item = item_begin; item < item_end; item += item_step, ++it) {
+      const int job = (int)((uint32_t)item % n_jobs_u);
       const int4 j0 = jobs[2 * job];
       const uint32_t buf = it & 1u, use = it >> 1;
       int4 st_next = steps[j0.x];
-      mbar_wait_t(tempty_bar(buf), (use & 1u) ^ 1u, prof, w_tempty);
+      if (kPair) ptx::mbar_wait_cluster(tempty_bar(buf), (use & 1u) ^ 1u);     // arrivals come from both CTAs
+      else mbar_wait_t(tempty_bar(buf), (use & 1u) ^ 1u, prof, w_tempty);
       ptx::tc_fence_after();
       for (int s = j0.x; s < j0.x + j0.y; ++s) {
         const int4 st = st_next;
@@ -225,26 +278,32 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           const uint32_t a_addr = base + (uint32_t)stage * p.stage_bytes;
-          const uint32_t b_addr = (st.w & 2) ? base + p.res_off + (uint32_t)st.y * 128u : a_addr + kATileBytes;
+          const uint32_t b_addr = kPair ? base + p.res_off + (uint32_t)st.y * 64u
+                                        : ((st.w & 2) ? base + p.res_off + (uint32_t)st.y * 128u : a_addr + kATileBytes);
           const uint64_t adesc = ptx::smem_desc_sw128(a_addr);
           const uint64_t bdesc = ptx::smem_desc_sw128(b_addr);
           const uint32_t d = tmem_base + buf * (uint32_t)p.nt + (uint32_t)st.z;
           // 4 x (K = 16) with +32 B descriptor advances inside the 128 B swizzle row, then commit -> stage free
-          ptx::umma_bf16_k64_commit(d, adesc, bdesc, p.idesc, (uint32_t)(st.w & 1), empty_bar(stage));
+          if (kPair) ptx::umma_bf16_k64_commit_pair(d, adesc, bdesc, p.idesc, (uint32_t)(st.w & 1), empty_bar(stage));
+          else ptx::umma_bf16_k64_commit(d, adesc, bdesc, p.idesc, (uint32_t)(st.w & 1), empty_bar(stage));
         }
         __syncwarp();
         if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
       }
-      if (ptx::elect_one()) ptx::umma_commit(tfull_bar(buf));
+      if (ptx::elect_one()) { if (kPair) ptx::umma_commit_pair(tfull_bar(buf)); else ptx::umma_commit(tfull_bar(buf)); }
       __syncwarp();
     }
     if (prof && lane == 0) {
-      p.prof[blockIdx.x * 8 + 2] = w_full; p.prof[blockIdx.x * 8 + 3] = w_tempty;
-      p.prof[blockIdx.x * 8 + 4] = (unsigned long long)(clock64() - t_start);
+      p.prof[blockIdx.x * 16 + 2] = w_full; p.prof[blockIdx.x * 16 + 3] = w_tempty;
+      p.prof[blockIdx.x * 16 + 4] = (unsigned long long)(clock64() - t_start);
     }
-  } else {
+  } else if (warp < 8) {
     // ------------------------------------------------------------------ epilogue
     // 8 warps = 2 groups x 4 TMEM lane quadrants (quadrant = warp % 4, the hardware's access rule)
+    const uint32_t tempty0_leader = kPair ? ptx::map_to_cta(tempty_bar(0), 0u) : 0u;
+    auto release_tmem = [&](uint32_t buf) {
+      if (kPair) ptx::mbar_arrive_cluster(tempty0_leader + 8u * buf); else ptx::mbar_arrive(tempty_bar(buf));
+    };
     const int q = warp & 3;
     const int grp = warp >> 2;
     const int row = q * 32 + lane;
@@ -254,12 +313,13 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const uint32_t sw = (uint32_t)(row & 7);
     uint32_t it = 0;
     const bool prof = p.prof != nullptr;
-    unsigned long long w_tfull = 0;
+    unsigned long long w_tfull = 0, e_ld = 0, e_free = 0, e_math = 0, e_pub = 0;
+    long long tq = 0;
     const long long t_start = clock64();
     if (kTmaStore || grp == 0) {
-      for (long long item = item_begin; item < item_end; ++item, ++it) {
-        const int ptile = (int)(item / p.n_jobs);
-        const int job = (int)(item - (long long)ptile * p.n_jobs);
+      for (long long item = item_begin; item < item_end; item += item_step, ++it) {
+        const int ptile = (int)((uint32_t)item / n_jobs_u);
+        const int job = (int)((uint32_t)item - (uint32_t)ptile * n_jobs_u);
         const int4 j0 = jobs[2 * job];
         const int4 j1 = jobs[2 * job + 1];
         const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
@@ -276,7 +336,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           if (last < 0) {
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(tempty_bar(buf));
+            if (lane == 0) release_tmem(buf);
           }
           for (int ch = grp; ch < n_chunks; ch += 2) {
             const int n0 = ch << 6;
@@ -284,15 +344,17 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             if (cm < 0 || !((mask >> s_pix[n0]) & 1ull)) continue;       // uniform over the group
             uint32_t v[64];
             __syncwarp();
+            if (prof) tq = clock64();
             ptx::tmem_ld_x16(tbase + (uint32_t)n0, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
             ptx::tmem_ld_x16(tbase + (uint32_t)n0 + 16u, *reinterpret_cast<uint32_t(*)[16]>(&v[16]));
             ptx::tmem_ld_x16(tbase + (uint32_t)n0 + 32u, *reinterpret_cast<uint32_t(*)[16]>(&v[32]));
             ptx::tmem_ld_x16(tbase + (uint32_t)n0 + 48u, *reinterpret_cast<uint32_t(*)[16]>(&v[48]));
             ptx::tmem_ld_wait();
+            if (prof) { const long long t = clock64(); e_ld += (unsigned long long)(t - tq); tq = t; }
             if (ch == last) {
               ptx::tc_fence_before();
               __syncwarp();
-              if (lane == 0) ptx::mbar_arrive(tempty_bar(buf));
+              if (lane == 0) release_tmem(buf);
             }
             const uint32_t sbuf = sbuf0 + sflip * kATileBytes;
             const uint32_t srow = sbuf + (uint32_t)row * 128u;
@@ -301,6 +363,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               __syncwarp();
             }   // the store that last used this tile has drained it
             ptx::named_bar_sync(1 + grp, 128);
+            if (prof) { const long long t = clock64(); e_free += (unsigned long long)(t - tq); tq = t; }
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float4 b0 = *reinterpret_cast<const float4*>(bias + n0 + 8 * j);
@@ -312,19 +375,21 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               o.w = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 6]) + b1.z), act_fn<kAct>(__uint_as_float(v[8 * j + 7]) + b1.w));
               ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);   // SWIZZLE_128B: 16-byte slot j of row r lives at j ^ (r % 8)
             }
+            if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
             ptx::fence_proxy_async();                    // generic-proxy writes -> visible to the TMA (async proxy)
             ptx::named_bar_sync(1 + grp, 128);
             if (issuer_warp) {
               if (ptx::elect_one()) {
-                ptx::tma_store_2d(&tmY, sbuf, j0.z + cm, ptile * kTileM);   // rows >= P are clipped by the tensor map
+                ptx::tma_store_2d(&tmY, sbuf, out_c0(j0.z + cm), out_c1(ptile, j0.z + cm));   // row-major: rows >= P are clipped by the tensor map
                 ptx::bulk_commit();
               }
               __syncwarp();
             }
             if (p.stg_bufs == 2) sflip ^= 1u;
+            if (prof) { const long long t = clock64(); e_pub += (unsigned long long)(t - tq); tq = t; }
           }
         } else {
-          const long long particle = (long long)ptile * kTileM + row;
+          const long long particle = (long long)tile_row(ptile) + row;
           const bool valid = particle < p.P;
           __nv_bfloat16* yrow = p.y ? p.y + particle * p.out_pitch + j0.z : nullptr;
           float* y32row = p.y32 ? p.y32 + particle * p.out32_pitch + j0.w : nullptr;
@@ -372,29 +437,39 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           }
           ptx::tc_fence_before();
           __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(tempty_bar(buf));
+          if (lane == 0) release_tmem(buf);
         }
       }
       if (kTmaStore && issuer_warp && ptx::elect_one()) ptx::bulk_wait_all0();      // staging tiles must outlive their TMA stores
       if (prof && warp == 0 && lane == 0) {
-        p.prof[blockIdx.x * 8 + 5] = w_tfull; p.prof[blockIdx.x * 8 + 6] = (unsigned long long)(clock64() - t_start);
-        p.prof[blockIdx.x * 8 + 7] = (unsigned long long)(item_end - item_begin);
+        p.prof[blockIdx.x * 16 + 5] = w_tfull; p.prof[blockIdx.x * 16 + 6] = (unsigned long long)(clock64() - t_start);
+        p.prof[blockIdx.x * 16 + 7] = (unsigned long long)it;
+        p.prof[blockIdx.x * 16 + 8] = e_ld; p.prof[blockIdx.x * 16 + 9] = e_free;
+        p.prof[blockIdx.x * 16 + 10] = e_math; p.prof[blockIdx.x * 16 + 11] = e_pub;
       }
     }
   }
 
   ptx::tc_fence_before();
-  __syncthreads();
+  if (kPair) ptx::cluster_sync_all(); else __syncthreads();     // pair: the peer's TMEM / barriers are in use until both are done
   if (warp == kMmaWarp) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, p.tmem_cols);
+    if (kPair) ptx::tmem_dealloc_pair(tmem_base, p.tmem_cols); else ptx::tmem_dealloc(tmem_base, p.tmem_cols);
   }
 }
 
 typedef void (*UmmaKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const EngineParams);
-static UmmaKernelFn umma_kernel_for(int act, bool tma_store) {
+static UmmaKernelFn umma_kernel_for(int act, bool tma_store, bool pair) {
+  if (pair) {           // pair mode exists for the hidden conv layers only (TMA-store epilogue, ReLU / LeakyReLU / none)
+    switch (act) {
+      case PSOB_ACT_NONE: return pixel_gemm_umma_kernel<PSOB_ACT_NONE, true, true>;
+      case PSOB_ACT_RELU: return pixel_gemm_umma_kernel<PSOB_ACT_RELU, true, true>;
+      case PSOB_ACT_LEAKY: return pixel_gemm_umma_kernel<PSOB_ACT_LEAKY, true, true>;
+    }
+    return nullptr;
+  }
   switch (act) {
-#define PSOB_K(A) case A: return tma_store ? pixel_gemm_umma_kernel<A, true> : pixel_gemm_umma_kernel<A, false>;
+#define PSOB_K(A) case A: return tma_store ? pixel_gemm_umma_kernel<A, true, false> : pixel_gemm_umma_kernel<A, false, false>;
     PSOB_K(PSOB_ACT_NONE) PSOB_K(PSOB_ACT_RELU) PSOB_K(PSOB_ACT_LEAKY) PSOB_K(PSOB_ACT_TANH) PSOB_K(PSOB_ACT_SIGMOID)
 #undef PSOB_K
   }
@@ -423,12 +498,21 @@ pixel_gemm_simt_kernel(const __nv_bfloat16* __restrict__ x, long long x_pitch, c
       const int4 st = p.steps[s];
       if (n < st.z || n >= st.z + p.mma_n) continue;
       if (!(st.w & 1)) acc = 0.f;
-      const __nv_bfloat16* a = x + particle * x_pitch + st.x;
+      const __nv_bfloat16* a = p.in_tiled ? x + (((size_t)ptile * p.n_in_chunks + (st.x >> 6)) * kTileM + row) * kKChunk
+                                          : x + particle * x_pitch + st.x;
       const __nv_bfloat16* b = w + (size_t)(st.y + n - st.z) * kKChunk;
       for (int k = 0; k < kKChunk; ++k) acc += __bfloat162float(a[k]) * __bfloat162float(b[k]);
     }
     const float f = apply_act(acc + bias[n], p.act);
-    if (p.y) { const int cm = p.col_map[n]; if (cm >= 0) p.y[particle * p.out_pitch + j0.z + cm] = __float2bfloat16_rn(f); }
+    if (p.y) {
+      const int cm = p.col_map[n];
+      if (cm >= 0) {
+        const int col = j0.z + cm;
+        const size_t o = p.out_tiled ? (((size_t)ptile * p.n_out_chunks + (col >> 6)) * kTileM + row) * kKChunk + (col & 63)
+                                     : (size_t)particle * p.out_pitch + col;
+        p.y[o] = __float2bfloat16_rn(f);
+      }
+    }
     if (p.y32) { const int cm = p.col_map32[n]; if (cm >= 0) p.y32[particle * p.out32_pitch + j0.w + cm] = f; }
   }
 }
@@ -483,7 +567,7 @@ struct psob_layer {
   __nv_bfloat16* wpack = nullptr;
   CUtensorMap tmB;
   bool have_tmB = false;
-  bool tma_store = false, vec4 = false;
+  bool tma_store = false, vec4 = false, pair = false, strided = false;
   unsigned long long* prof = nullptr;
   int bias_off = -1, steps_off = -1, jobs_off = -1, tab_bytes = 0, stg_bufs = 0;
   int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, stg_off = 0, smem_bytes = 0;
@@ -512,14 +596,17 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     return fail(PSOB_E_ARG, "psob_layer_create: null table");
   if (d->in_pitch % 8 || (d->out_pitch == 0 && d->out32_pitch == 0))
     return fail(PSOB_E_ARG, "psob_layer_create: in_pitch %% 8 != 0 or no output");
+  if (d->in_tiled && d->in_pitch % kKChunk) return fail(PSOB_E_ARG, "psob_layer_create: tile-major input needs in_pitch %% 64 == 0");
+  if (d->out_tiled && (d->out_pitch % kKChunk || d->out32_pitch)) return fail(PSOB_E_ARG, "psob_layer_create: tile-major output needs a bf16-only output with out_pitch %% 64 == 0");
   if (d->vec8 && (d->out32_pitch != 0 || d->out_pitch % 8 || d->cc % 8))
     return fail(PSOB_E_ARG, "psob_layer_create: vec8 needs bf16-only output with 16-byte aligned rows");
   // validate the tables so a bad program can never fault on the device
   for (int s = 0; s < d->n_steps; ++s) {
     const int32_t* st = d->steps + 4 * s;
-    if (st[0] < 0 || st[0] % 8 || st[0] + kKChunk > d->in_pitch) return fail(PSOB_E_ARG, "step %d: a_col %d out of range", s, st[0]);
+    if (st[0] < 0 || st[0] % 8 || st[0] + kKChunk > d->in_pitch || (d->in_tiled && st[0] % kKChunk))
+      return fail(PSOB_E_ARG, "step %d: a_col %d out of range (or not chunk-aligned for a tile-major input)", s, st[0]);
     if (st[1] < 0 || st[1] % 8 || st[1] + d->mma_n > d->n_wrows) return fail(PSOB_E_ARG, "step %d: b_row %d out of range", s, st[1]);
-    if (st[2] < 0 || st[2] % 16 || st[2] + d->mma_n > d->nt) return fail(PSOB_E_ARG, "step %d: d_col %d out of range", s, st[2]);
+    if (st[2] < 0 || st[2] % 2 || st[2] + d->mma_n > d->nt) return fail(PSOB_E_ARG, "step %d: d_col %d out of range", s, st[2]);
     if (((st[3] & 2) != 0) != (d->b_resident != 0)) return fail(PSOB_E_ARG, "step %d: resident flag disagrees with the layer", s);
   }
   long long max_cm = -1, max_cm32 = -1;
@@ -577,6 +664,13 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   for (int c = 0; c < d->nt && l->tma_store; c += 64)
     for (int i = 1; i < 64; ++i)
       if ((d->col_map[c] >= 0) != (d->col_map[c + i] >= 0) || (d->col_map[c] >= 0 && d->col_map[c + i] != d->col_map[c] + i)) l->tma_store = false;
+  if (d->out_tiled) {
+    bool ok = l->tma_store;
+    for (int j = 0; j < d->n_jobs && ok; ++j)
+      for (int c = 0; c < d->nt && ok; c += 64)
+        if (d->col_map[c] >= 0 && (d->jobs[8 * j + 2] + d->col_map[c]) % kKChunk) ok = false;
+    if (!ok) { psob_layer_destroy(l); return fail(PSOB_E_ARG, "psob_layer_create: tile-major output needs chunk-aligned TMA-store jobs"); }
+  }
   // direct epilogue: 4 single-pixel columns -> one 8-byte bf16 store
   l->vec4 = !d->vec8 && d->cc == 1 && d->out_pitch > 0 && d->nt <= 64;
   for (int c = 0; c < d->nt && l->vec4; c += 4) {
@@ -586,10 +680,18 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
       if ((d->jobs[8 * j + 2] + d->col_map[c]) % 4) l->vec4 = false;
   }
 
-  // shared-memory plan
+  // shared-memory plan.  Resident weights beyond what one CTA can hold next to a useful ring are split over a
+  // CTA pair (cta_group::2): each CTA keeps half of every weight tile.
   const int b_tile = d->mma_n * 128;
   l->stage_bytes = kATileBytes + (d->b_resident ? 0 : b_tile);
-  const int res_bytes = d->b_resident ? d->n_wrows * 128 : 0;
+  const int full_res_bytes = d->b_resident ? d->n_wrows * 128 : 0;
+  l->pair = d->b_resident && full_res_bytes > kMaxSoloResident;
+  if (l->pair && (!l->tma_store || full_res_bytes / 2 > kMaxPairResident || d->mma_n % 32 || d->n_wrows % d->mma_n ||
+                  (d->act != PSOB_ACT_NONE && d->act != PSOB_ACT_RELU && d->act != PSOB_ACT_LEAKY) || l->sm_count < 2)) {
+    psob_layer_destroy(l);
+    return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: %d B of resident weights need the CTA-pair mode, which this layer cannot use", full_res_bytes);
+  }
+  const int res_bytes = l->pair ? full_res_bytes / 2 : full_res_bytes;
   // table area: col_map + col_map32 + pix (fixed 2304 B), then optional bias rows, steps, jobs
   int tab = 256 * 4 * 2 + 256;
   l->bias_off = l->steps_off = l->jobs_off = -1;
@@ -602,7 +704,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->stg_bufs = 0;
   if (l->tma_store) {
     const int room = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes;
-    l->stg_bufs = (room - 4 * kATileBytes) / l->stage_bytes >= 3 ? 2 : 1;
+    l->stg_bufs = (room - 4 * kATileBytes) / l->stage_bytes >= (l->pair ? 4 : 3) ? 2 : 1;
   }
   const int stg_bytes = 2 * l->stg_bufs * kATileBytes;
   int avail = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes - stg_bytes;
@@ -616,6 +718,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->stg_off = l->res_off + res_bytes;
   l->bar_off = l->stg_off + stg_bytes;
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
+  { const char* e = getenv("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }     // tuning knob (default: strided)
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * d->nt)) cols <<= 1;
   l->tmem_cols = cols;
@@ -632,6 +735,7 @@ int psob_layer_profile(psob_layer* l, void* counters) {
 int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, int32_t impl, psob_stream_t s) {
   if (!l || !x || P <= 0) return fail(PSOB_E_ARG, "psob_layer_run: bad arguments");
   const psob_layer_desc& d = l->d;
+  if (d.in_tiled && x_pitch != d.in_pitch) return fail(PSOB_E_ARG, "psob_layer_run: a tile-major input has x_pitch == in_pitch (%d), got %lld", d.in_pitch, (long long)x_pitch);
   if (x_pitch < d.in_pitch || x_pitch % 8 || !aligned16(x)) return fail(PSOB_E_ARG, "psob_layer_run: x_pitch %lld < in_pitch %d, or misaligned", (long long)x_pitch, d.in_pitch);
   if ((d.out_pitch && !y && !(d.out32_pitch && y32)) || (!d.out_pitch && !y32)) return fail(PSOB_E_ARG, "psob_layer_run: missing output buffer");
   if (y && !aligned16(y)) return fail(PSOB_E_ARG, "psob_layer_run: y must be 16-byte aligned");
@@ -647,7 +751,9 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.vec8 = (d.vec8 && p.y) ? 1 : 0;
   p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
-  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof;
+  p.in_tiled = d.in_tiled; p.out_tiled = d.out_tiled; p.n_in_chunks = d.in_pitch / kKChunk; p.n_out_chunks = d.out_pitch / kKChunk;
+  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0;
+  if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
   p.tmem_cols = l->tmem_cols;
@@ -662,22 +768,47 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   if (impl != PSOB_IMPL_TCGEN05) return fail(PSOB_E_ARG, "psob_layer_run: unknown impl %d", impl);
 
   const bool tma_store = l->tma_store && p.y != nullptr;
-  UmmaKernelFn fn = umma_kernel_for(d.act, tma_store);
+  if (d.out_tiled && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a tile-major output needs its bf16 output buffer");
+  if (l->pair && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a CTA-pair layer needs its bf16 output buffer");
+  UmmaKernelFn fn = umma_kernel_for(d.act, tma_store, l->pair);
   if (!fn) return fail(PSOB_E_ARG, "psob_layer_run: unknown activation %d", d.act);
+  if (l->pair) {
+    p.n_items = ((n_ptiles + 1) / 2) * d.n_jobs;                  // items are (pair of particle tiles, job)
+    p.idesc = make_idesc_bf16(2 * kTileM, d.mma_n);
+  }
   if (!l->have_tmB) {
-    int rc = make_tmap(&l->tmB, l->wpack, kKChunk, (uint64_t)d.n_wrows, kKChunk, (uint32_t)d.mma_n);
+    int rc = make_tmap(&l->tmB, l->wpack, kKChunk, (uint64_t)d.n_wrows, kKChunk, (uint32_t)(l->pair ? d.mma_n / 2 : d.mma_n));
     if (rc) return rc;
     PSOB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     l->have_tmB = true;
   }
   CUtensorMap tmA, tmY;
-  int rc = make_tmap(&tmA, x, (uint64_t)x_pitch, (uint64_t)P, (uint64_t)x_pitch, kTileM);
+  // tile-major buffers hold n_ptiles full tiles: [n_ptiles][pitch / 64][128][64] == a [rows, 64] matrix with 128 B rows
+  int rc = d.in_tiled ? make_tmap(&tmA, x, kKChunk, (uint64_t)n_ptiles * (d.in_pitch / kKChunk) * kTileM, kKChunk, kTileM)
+                      : make_tmap(&tmA, x, (uint64_t)x_pitch, (uint64_t)P, (uint64_t)x_pitch, kTileM);
   if (rc) return rc;
   if (tma_store) {
-    rc = make_tmap(&tmY, y, (uint64_t)d.out_pitch, (uint64_t)P, (uint64_t)d.out_pitch, kTileM);
+    rc = d.out_tiled ? make_tmap(&tmY, y, kKChunk, (uint64_t)n_ptiles * (d.out_pitch / kKChunk) * kTileM, kKChunk, kTileM)
+                     : make_tmap(&tmY, y, (uint64_t)d.out_pitch, (uint64_t)P, (uint64_t)d.out_pitch, kTileM);
     if (rc) return rc;
   } else {
     tmY = tmA;
+  }
+  if (l->pair) {
+    const long long pairs = p.n_items < l->sm_count / 2 ? p.n_items : l->sm_count / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * pairs));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = (size_t)l->smem_bytes;
+    cfg.stream = (cudaStream_t)s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, fn, tmA, l->tmB, tmY, p);
+    if (e != cudaSuccess) return fail((int)e, "cluster launch of pixel_gemm_umma_kernel failed: %s", cudaGetErrorString(e));
+    return 0;
   }
   long long grid = p.n_items < l->sm_count ? p.n_items : l->sm_count;
   fn<<<(unsigned)grid, kThreads, l->smem_bytes, (cudaStream_t)s>>>(tmA, l->tmB, tmY, p);

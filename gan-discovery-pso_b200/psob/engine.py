@@ -39,9 +39,10 @@ def require_cuda():
 class Layer:
     """One pixel-GEMM layer program resident on the current device."""
 
-    def __init__(self, prog: L.LayerProgram):
+    def __init__(self, prog: L.LayerProgram, in_tiled: bool = False, out_tiled: bool = False):
         require_cuda()
         self.prog = prog
+        self.in_tiled, self.out_tiled = bool(in_tiled), bool(out_tiled)
         wbits = np.ascontiguousarray(L.bf16_bits(prog.wpack))
         steps = np.ascontiguousarray(prog.steps, dtype=np.int32)
         jobs = np.ascontiguousarray(prog.jobs, dtype=np.int32)
@@ -52,7 +53,7 @@ class Layer:
             mma_n=prog.mma_n, nt=prog.nt, cc=prog.cc, act=prog.act, in_pitch=prog.in_pitch,
             out_pitch=prog.out_pitch, out32_pitch=prog.out32_pitch, b_resident=int(prog.b_resident),
             vec8=int(prog.vec8), n_steps=prog.n_steps, n_jobs=prog.n_jobs, n_wrows=wbits.shape[0],
-            n_bias_rows=bias.shape[0], wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
+            n_bias_rows=bias.shape[0], in_tiled=int(in_tiled), out_tiled=int(out_tiled), wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
             col_map=cm.ctypes.data, col_map32=cm32.ctypes.data, bias=bias.ctypes.data)
         h = C.c_void_p()
         _ffi.check(_ffi.lib().psob_layer_create(C.byref(d), C.byref(h)), f"psob_layer_create({prog.name})")
@@ -82,10 +83,18 @@ class Network:
         self.impl = impl
         self.skip_f32 = False
         self.programs = programs
+        # Internal edges use the tile-major layout [ceil(P/128)][pitch/64][128][64] whenever the producer has the
+        # TMA-store epilogue and the consumer reads whole 64-column chunks; the network's own input and its last
+        # output stay row-major [P, pitch].  PSOB_TILED=0 keeps everything row-major (A/B measurements).
+        tiled_ok = os.environ.get("PSOB_TILED", "1") != "0"
+        self.edge_tiled = [tiled_ok and L.can_store_tiled(a) and L.can_load_tiled(b) for a, b in zip(programs[:-1], programs[1:])]
+        rows = (P + L.TILE_M - 1) // L.TILE_M * L.TILE_M
         with torch.cuda.device(self.device):
-            self.layers = [Layer(p) for p in programs]
-            # zero-initialised so that channel padding and image borders that no job writes stay 0
-            self.acts = [torch.zeros(P, p.out_pitch, dtype=torch.bfloat16, device=self.device) if p.out_pitch else None
+            self.layers = [Layer(p, in_tiled=(i > 0 and self.edge_tiled[i - 1]),
+                                 out_tiled=(i < len(programs) - 1 and self.edge_tiled[i])) for i, p in enumerate(programs)]
+            # zero-initialised so that channel padding and image borders that no job writes stay 0; whole
+            # particle tiles are allocated (tile-major buffers are addressed by tile), row-major users see [:P]
+            self.acts = [torch.zeros(rows, p.out_pitch, dtype=torch.bfloat16, device=self.device)[:P] if p.out_pitch else None
                          for p in programs]
             self.acts32 = [torch.zeros(P, p.out32_pitch, dtype=torch.float32, device=self.device) if p.out32_pitch else None
                            for p in programs]
@@ -105,6 +114,13 @@ class Network:
             cur = y
         return self.acts[-1], self.acts32[-1]
 
+    def activation(self, i: int) -> Optional[torch.Tensor]:
+        """Row-major [P, out_pitch] copy of layer i's bf16 output, whatever layout the edge uses (tests, debugging)."""
+        y = self.acts[i]
+        if y is None or not self.layers[i].out_tiled:
+            return y
+        return untile(y, self.P)
+
     @property
     def macs_exact(self) -> int:
         return sum(p.macs_exact for p in self.programs)
@@ -112,6 +128,15 @@ class Network:
     @property
     def macs_issued(self) -> int:
         return sum(p.macs_issued for p in self.programs)
+
+
+def untile(y: torch.Tensor, P: int) -> torch.Tensor:
+    """Tile-major activation buffer (allocated as [rows, pitch], rows a multiple of 128) -> row-major [P, pitch]."""
+    pitch = y.shape[1]
+    rows = (P + L.TILE_M - 1) // L.TILE_M * L.TILE_M
+    flat = torch.as_strided(y, (rows * pitch,), (1,))
+    t = flat.view(rows // L.TILE_M, pitch // L.KCHUNK, L.TILE_M, L.KCHUNK).permute(0, 2, 1, 3).reshape(rows, pitch)
+    return t[:P].contiguous()
 
 
 def _sd_numpy(sd):

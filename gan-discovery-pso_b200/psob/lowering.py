@@ -20,6 +20,7 @@ GPU ever sees them (tests/test_lowering.py).
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass, field
 from typing import List, Optional, Tuple
 
@@ -32,6 +33,11 @@ MAX_N = 256           # UMMA N limit / TMEM columns per accumulator buffer
 ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3, 4
 STEP_ACCUM, STEP_B_RESIDENT = 1, 2
 ROUND_WEIGHTS = True   # tests switch this off to check the geometry exactly in fp32
+# Weight packs up to RESIDENT_SOLO bytes stay in one CTA's shared memory for its lifetime; packs up to
+# RESIDENT_PAIR are split over a CTA pair (tcgen05 cta_group::2, csrc/pixel_gemm.cu) when the layer has the
+# TMA-store epilogue (64-channel NHWC chunks).  PSOB_PAIR=0 falls back to streaming the weights per step.
+RESIDENT_SOLO = 32 * 1024
+RESIDENT_PAIR = 256 * 1024 if os.environ.get("PSOB_PAIR", "1") != "0" else 0
 
 # image layouts
 IMG_PAD_ROWS, IMG_PAD_PITCH = 31, 32          # bf16 padded 28x28 image: real (y,x) at (y+1,x+1)
@@ -88,6 +94,29 @@ class LayerProgram:
     @property
     def n_steps(self) -> int:
         return int(self.steps.shape[0])
+
+
+def can_store_tiled(prog: "LayerProgram") -> bool:
+    """The layer's epilogue writes whole, 64-aligned, 64-column bf16 chunks (the TMA-store epilogue of
+    csrc/pixel_gemm.cu), so its output can use the tile-major layout."""
+    if not (prog.vec8 and prog.nt % KCHUNK == 0 and prog.cc % KCHUNK == 0 and prog.out32_pitch == 0
+            and prog.out_pitch % KCHUNK == 0):
+        return False
+    cm = prog.col_map
+    for c in range(0, prog.nt, KCHUNK):
+        blk = cm[c:c + KCHUNK]
+        if blk[0] < 0:
+            if np.any(blk >= 0):
+                return False
+            continue
+        if np.any(np.diff(blk) != 1) or np.any((prog.jobs[:, 2].astype(np.int64) + int(blk[0])) % KCHUNK):
+            return False
+    return True
+
+
+def can_load_tiled(prog: "LayerProgram") -> bool:
+    """Every step reads a whole 64-column chunk of the input row."""
+    return prog.in_pitch % KCHUNK == 0 and bool(np.all(prog.steps[:, 0] % KCHUNK == 0))
 
 
 def _finish(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, tiles, b_resident, steps, jobs,
@@ -240,7 +269,8 @@ def lower_convt_k4s2p1(name, w, b, act, h, wd, *, m=1, image_out=False, in_cp=No
         out32_pitch = 0
 
     # small weight packs (the Cout = 1 image layer: 9 tiles x 2 KB) stay in shared memory for the CTA's lifetime
-    resident = len(tiles) * nt * KCHUNK * 2 <= 32 * 1024
+    wbytes = len(tiles) * nt * KCHUNK * 2
+    resident = wbytes <= RESIDENT_SOLO or (wbytes <= RESIDENT_PAIR and not image_out and cc % 64 == 0 and nt % 64 == 0)
     steps, jobs = [], []
     for bq in range(-1, h, m):
         for br in range(-1, wd, m):
@@ -321,6 +351,8 @@ def lower_conv_k4s2p1(name, w, b, act, h, wd, in_cp=None) -> LayerProgram:
             for kc in range(nkc):
                 tile_of[(ky, kx, kc)] = len(tiles)
                 tiles.append(wp[:, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
+    wbytes = len(tiles) * cpo * KCHUNK * 2
+    resident = RESIDENT_SOLO < wbytes <= RESIDENT_PAIR and cpo % 64 == 0       # CTA-pair mode only (small packs stream fine)
     steps, jobs = [], []
     macs = 0
     for oy in range(ho):
@@ -342,13 +374,13 @@ def lower_conv_k4s2p1(name, w, b, act, h, wd, in_cp=None) -> LayerProgram:
                         macs += cin * cout
                         for kc in range(nkc):
                             steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, tile_of[(ky, kx, kc)] * cpo, j * cpo,
-                                          0 if first else STEP_ACCUM))
+                                          (0 if first else STEP_ACCUM) | (STEP_B_RESIDENT if resident else 0)))
                             first = False
             lo, hi = _mask_words([ox0 + j < wo for j in range(g)])
             jobs.append((sb, len(steps) - sb, (oy * wo + ox0) * cpo, 0, lo, hi, 0, 0))
     col_map = list(range(nt))
     bias = [bp[n % cpo] for n in range(nt)]
-    return _finish(name, cpo, nt, cpo, act, h * wd * cpi, ho * wo * cpo, 0, tiles, False, steps, jobs, col_map,
+    return _finish(name, cpo, nt, cpo, act, h * wd * cpi, ho * wo * cpo, 0, tiles, resident, steps, jobs, col_map,
                    [-1] * nt, bias, macs_exact=macs, meta=dict(kind="conv_k4s2p1", out_hw=(ho, wo), out_c=cout, out_cp=cpo))
 
 

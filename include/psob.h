@@ -160,6 +160,8 @@ typedef struct {
   int32_t in_pitch, out_pitch, out32_pitch;
   int32_t b_resident, vec8;
   int32_t n_steps, n_jobs, n_wrows, n_bias_rows;
+  int32_t in_tiled, out_tiled; /* tile-major bf16 activations: [ceil(P/128)][pitch/64][128][64] (each 128-particle x
+                                * 64-column operand tile is one contiguous 16 KB block); 0 = row-major [P, pitch] */
   const uint16_t* wpack;     /* HOST bf16 bits [n_wrows, 64] */
   const int32_t*  steps;     /* HOST [n_steps, 4]: a_col, b_row, d_col, flags */
   const int32_t*  jobs;      /* HOST [n_jobs, 8]: step_begin, step_count, out_base, out32_base, mask_lo, mask_hi, bias_row, 0 */
@@ -177,9 +179,11 @@ int psob_layer_destroy(psob_layer* l);
 int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32,
                    int32_t impl, psob_stream_t s);
 
-/* Debug: when `counters` (device, u64 [n_SMs][8]) is non-NULL, later runs of the layer record per CTA
+/* Debug: when `counters` (device, u64 [n_SMs][16]) is non-NULL, later runs of the layer record per CTA
  * { producer wait-empty, producer total, mma wait-full, mma wait-tmem-empty, mma total,
- *   epilogue wait-tmem-full, epilogue total, items } in SM cycles.  NULL switches it off. */
+ *   epilogue wait-tmem-full, epilogue total, items, epilogue tmem-load, staging-free wait,
+ *   bias/activation/st.shared, publish (fence + barrier + TMA store issue), 4 spare } in SM cycles.
+ *   NULL switches it off. */
 int psob_layer_profile(psob_layer* l, void* counters);
 
 #ifdef __cplusplus

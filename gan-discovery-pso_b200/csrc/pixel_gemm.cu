@@ -32,11 +32,11 @@ constexpr int kMaxStepsSmem = 1024;                // step descriptors staged in
 constexpr int kMaxJobsSmem = 256;
 constexpr int kMaxSoloResident = 96 * 1024;       // resident weights of one CTA before the pair mode takes over
 constexpr int kMaxPairResident = 128 * 1024;      // per CTA of a pair                  // job descriptors staged in SMEM (32 B each)
-constexpr int kThreads = 320;                     // 2 epilogue groups of 4 warps + TMA warp + MMA warp
+constexpr int kMaxEpiGroups = 3;                  // epilogue groups of 4 warps (one per TMEM lane quadrant)
+constexpr int kMaxThreads = 32 * (4 * kMaxEpiGroups + 2);   // + TMA warp + MMA warp; blockDim = 32 * (4 * epi_groups + 2)
 // The SMSP arbiter favours the highest warp id: the two single-thread roles that must never wait for
 // an issue slot (TMA producer, MMA issuer) get the top ids; epilogue warps 0..7 map to TMEM quadrant w % 4.
-constexpr int kTmaWarp = 8;
-constexpr int kMmaWarp = 9;
+// (warp ids 4 * epi_groups and 4 * epi_groups + 1, see kTmaWarp / kMmaWarp in the kernel)
 
 struct EngineParams {
   const int4* steps;
@@ -52,7 +52,8 @@ struct EngineParams {
   int mma_n, nt, cc, act, out_pitch, out32_pitch, vec8;
   int b_resident, n_wrows, n_bias_rows, n_steps;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
-  int vec4, strided;
+  int vec4, strided, pf_dist;
+  int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
   int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
   int bias_off, steps_off, jobs_off, stg_bufs;   // SMEM table offsets from the table base (-1: stays in global)
   unsigned long long* prof;   // optional [gridDim][16] role wait-cycle counters (debug)
@@ -102,7 +103,7 @@ __device__ __forceinline__ float act_fn(float v) {
 // streaming a 32 KB B tile per 512-cycle step had every heavy layer L2-bound at ~45 % of the MMA rate).
 // The leader (rank 0) issues all MMAs; its commits arrive on the barriers of both CTAs.
 template <int kAct, bool kTmaStore, bool kPair>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kMaxThreads, 1)
 pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmY, const EngineParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -119,6 +120,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int kThreads = (int)blockDim.x;
+  const int kTmaWarp = 4 * p.epi_groups, kMmaWarp = kTmaWarp + 1;
   const uint32_t crank = kPair ? ptx::cluster_ctarank() : 0u;
   const bool leader = crank == 0u;
   // Contiguous item ranges: a CTA (or CTA pair) walks the jobs of one particle tile in order, so the input
@@ -151,7 +154,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(tfull_bar(b), 1);
-      ptx::mbar_init(tempty_bar(b), kPair ? 16 : (kTmaStore ? 8 : 4));   // pair: both CTAs' epilogue warps
+      ptx::mbar_init(tempty_bar(b), (kTmaStore ? 4 * p.epi_groups : 4) * (kPair ? 2 : 1));   // pair: both CTAs' epilogue warps
     }
     ptx::mbar_init(res_bar, 1);
     ptx::fence_barrier_init();
@@ -174,6 +177,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   uint8_t* s_pix = reinterpret_cast<uint8_t*>(s_cm32 + 256);
   float* s_bias = reinterpret_cast<float*>(tab + (p.bias_off >= 0 ? p.bias_off : 0));
   const bool bias_in_smem = p.bias_off >= 0;
+  const uint32_t s_bias_addr = base + p.bar_off + kBarBytes + (uint32_t)(p.bias_off >= 0 ? p.bias_off : 0);
   // Step / job descriptors too: a __ldg per step is an L2 round trip (~700-1000 cycles under load) that a
   // one-step prefetch cannot hide — it was the per-step floor of every layer (profiles/r01_roles_v3c.log).
   const int4* steps = p.steps_off >= 0 ? reinterpret_cast<const int4*>(tab + p.steps_off) : p.steps;
@@ -226,6 +230,17 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const bool prof = p.prof != nullptr;
       unsigned long long w_empty = 0;
       const long long t_start = clock64();
+      // L2 prefetch cursor: runs p.pf_dist steps ahead of the loads (across job and item boundaries), so the ring
+      // (3 stages next to 128 KB of resident weights) only has to cover the L2 latency, not the DRAM latency.
+      long long pf_item = item_begin;
+      int pf_ptile = 0, pf_s = 0, pf_end = 0, pf_ahead = 0;
+      bool pf_valid = p.pf_dist > 0 && item_begin < item_end;
+      auto pf_load_job = [&]() {
+        pf_ptile = (int)((uint32_t)pf_item / n_jobs_u);
+        const int4 q = jobs[2 * (int)((uint32_t)pf_item - (uint32_t)pf_ptile * n_jobs_u)];
+        pf_s = q.x; pf_end = q.x + q.y;
+      };
+      if (pf_valid) pf_load_job();
       for (long long item = item_begin; item < item_end; item += item_step) {
         const int ptile = (int)((uint32_t)item / n_jobs_u);          // 32-bit: n_items < 2^31 (checked on the host)
         const int job = (int)((uint32_t)item - (uint32_t)ptile * n_jobs_u);
@@ -234,6 +249,17 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         for (int s = j0.x; s < j0.x + j0.y; ++s) {
           const int4 st = st_next;
           if (s + 1 < j0.x + j0.y) st_next = steps[s + 1];     // descriptor fetch overlaps the wait
+          while (pf_valid && pf_ahead < p.pf_dist) {
+            const int a_col = steps[pf_s].x;
+            if (ptx::elect_one()) ptx::tma_prefetch_2d(&tmA, in_c0(a_col), in_c1(pf_ptile, a_col));
+            __syncwarp();
+            ++pf_ahead;
+            if (++pf_s == pf_end) {
+              pf_item += item_step;
+              if (pf_item < item_end) pf_load_job(); else pf_valid = false;
+            }
+          }
+          --pf_ahead;
           mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
           const bool res = (st.w & 2) != 0;
           if (ptx::elect_one()) {
@@ -268,7 +294,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const int4 j0 = jobs[2 * job];
       const uint32_t buf = it & 1u, use = it >> 1;
       int4 st_next = steps[j0.x];
-      if (kPair) ptx::mbar_wait_cluster(tempty_bar(buf), (use & 1u) ^ 1u);     // arrivals come from both CTAs
+      if (kPair) {                                                              // arrivals come from both CTAs
+        const long long t0 = prof ? clock64() : 0;
+        ptx::mbar_wait_cluster(tempty_bar(buf), (use & 1u) ^ 1u);
+        if (prof) w_tempty += (unsigned long long)(clock64() - t0);
+      }
       else mbar_wait_t(tempty_bar(buf), (use & 1u) ^ 1u, prof, w_tempty);
       ptx::tc_fence_after();
       for (int s = j0.x; s < j0.x + j0.y; ++s) {
@@ -297,7 +327,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       p.prof[blockIdx.x * 16 + 2] = w_full; p.prof[blockIdx.x * 16 + 3] = w_tempty;
       p.prof[blockIdx.x * 16 + 4] = (unsigned long long)(clock64() - t_start);
     }
-  } else if (warp < 8) {
+  } else if (warp < kTmaWarp) {
     // ------------------------------------------------------------------ epilogue
     // 8 warps = 2 groups x 4 TMEM lane quadrants (quadrant = warp % 4, the hardware's access rule)
     const uint32_t tempty0_leader = kPair ? ptx::map_to_cta(tempty_bar(0), 0u) : 0u;
@@ -316,7 +346,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     unsigned long long w_tfull = 0, e_ld = 0, e_free = 0, e_math = 0, e_pub = 0;
     long long tq = 0;
     const long long t_start = clock64();
-    if (kTmaStore || grp == 0) {
+    if (kTmaStore ? grp < p.epi_groups : grp == 0) {
       for (long long item = item_begin; item < item_end; item += item_step, ++it) {
         const int ptile = (int)((uint32_t)item / n_jobs_u);
         const int job = (int)((uint32_t)item - (uint32_t)ptile * n_jobs_u);
@@ -331,14 +361,14 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         if (kTmaStore) {
           const int n_chunks = p.nt >> 6;
           int last = -1;                      // last chunk this group will read: release TMEM right after it
-          for (int ch = grp; ch < n_chunks; ch += 2)
+          for (int ch = grp; ch < n_chunks; ch += p.epi_groups)
             if (s_cm[ch << 6] >= 0 && ((mask >> s_pix[ch << 6]) & 1ull)) last = ch;
           if (last < 0) {
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) release_tmem(buf);
           }
-          for (int ch = grp; ch < n_chunks; ch += 2) {
+          for (int ch = grp; ch < n_chunks; ch += p.epi_groups) {
             const int n0 = ch << 6;
             const int cm = s_cm[n0];
             if (cm < 0 || !((mask >> s_pix[n0]) & 1ull)) continue;       // uniform over the group
@@ -364,16 +394,29 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             }   // the store that last used this tile has drained it
             ptx::named_bar_sync(1 + grp, 128);
             if (prof) { const long long t = clock64(); e_free += (unsigned long long)(t - tq); tq = t; }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 b0 = *reinterpret_cast<const float4*>(bias + n0 + 8 * j);
-              const float4 b1 = *reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4);
+            auto emit_slot = [&](int j, const float4& b0, const float4& b1) {
               uint4 o;
               o.x = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 0]) + b0.x), act_fn<kAct>(__uint_as_float(v[8 * j + 1]) + b0.y));
               o.y = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 2]) + b0.z), act_fn<kAct>(__uint_as_float(v[8 * j + 3]) + b0.w));
               o.z = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 4]) + b1.x), act_fn<kAct>(__uint_as_float(v[8 * j + 5]) + b1.y));
               o.w = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 6]) + b1.z), act_fn<kAct>(__uint_as_float(v[8 * j + 7]) + b1.w));
               ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);   // SWIZZLE_128B: 16-byte slot j of row r lives at j ^ (r % 8)
+            };
+            if (bias_in_smem) {
+              // explicit ld.shared, software-pipelined one slot ahead: through a generic pointer every slot was a
+              // dependent LD -> math -> STS chain of ~110 cycles (the epilogue's largest single cost)
+              const uint32_t baddr = s_bias_addr + (uint32_t)(j1.z * p.nt + n0) * 4u;
+              float4 b0 = ptx::ld_shared_f4(baddr), b1 = ptx::ld_shared_f4(baddr + 16u);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                float4 c0 = b0, c1 = b1;
+                if (j < 7) { b0 = ptx::ld_shared_f4(baddr + 32u * (j + 1)); b1 = ptx::ld_shared_f4(baddr + 32u * (j + 1) + 16u); }
+                emit_slot(j, c0, c1);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                emit_slot(j, __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j)), __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4)));
             }
             if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
             ptx::fence_proxy_async();                    // generic-proxy writes -> visible to the TMA (async proxy)
@@ -568,6 +611,7 @@ struct psob_layer {
   CUtensorMap tmB;
   bool have_tmB = false;
   bool tma_store = false, vec4 = false, pair = false, strided = false;
+  int pf_dist = 0, epi_groups = 2;
   unsigned long long* prof = nullptr;
   int bias_off = -1, steps_off = -1, jobs_off = -1, tab_bytes = 0, stg_bufs = 0;
   int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, stg_off = 0, smem_bytes = 0;
@@ -702,11 +746,18 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->tab_bytes = (tab + 127) & ~127;
   // staging tiles for the TMA-store epilogue: 2 per group if that still leaves a 3-stage ring
   l->stg_bufs = 0;
+  // a CTA-pair layer with long MMA chains per item (>= ~6000 tensor cycles) keeps one epilogue group busy at most
+  // half of the time: give the second group's staging tile to the A ring (3 -> 4 stages next to 128 KB of weights)
+  // layers with short chains (K = 128 per 256 output columns) are bound by the epilogue's latency chain
+  // (TMEM load -> bias/activation -> swizzled st.shared -> TMA store): a third group hides more of it
+  l->epi_groups = (l->pair && (long long)d->n_steps * 2 * d->mma_n >= 6000ll * d->n_jobs) ? 1 : 2;   // a third group measured no faster (TMA-bound)
+  { const char* e = getenv("PSOB_EPI_GROUPS"); if (e && atoi(e) >= 1 && atoi(e) <= kMaxEpiGroups) l->epi_groups = atoi(e); }
+  if (!l->tma_store) l->epi_groups = 2;             // the direct-store epilogue uses group 0 only (thread layout of 2 groups)
   if (l->tma_store) {
     const int room = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes;
-    l->stg_bufs = (room - 4 * kATileBytes) / l->stage_bytes >= (l->pair ? 4 : 3) ? 2 : 1;
+    l->stg_bufs = (room - 2 * l->epi_groups * kATileBytes) / l->stage_bytes >= (l->pair ? 4 : 3) ? 2 : 1;
   }
-  const int stg_bytes = 2 * l->stg_bufs * kATileBytes;
+  const int stg_bytes = l->epi_groups * l->stg_bufs * kATileBytes;
   int avail = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes - stg_bytes;
   l->n_stages = avail / l->stage_bytes;
   if (l->n_stages > kMaxStages) l->n_stages = kMaxStages;
@@ -719,6 +770,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->bar_off = l->stg_off + stg_bytes;
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
   { const char* e = getenv("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }     // tuning knob (default: strided)
+  { const char* e = getenv("PSOB_PF"); l->pf_dist = e ? atoi(e) : 0; if (l->pf_dist < 0) l->pf_dist = 0; }   // L2 prefetch distance in steps
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * d->nt)) cols <<= 1;
   l->tmem_cols = cols;
@@ -752,7 +804,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
   p.in_tiled = d.in_tiled; p.out_tiled = d.out_tiled; p.n_in_chunks = d.in_pitch / kKChunk; p.n_out_chunks = d.out_pitch / kKChunk;
-  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0;
+  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.pf_dist = l->pf_dist; p.epi_groups = l->epi_groups;
   if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
@@ -798,7 +850,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
     const long long pairs = p.n_items < l->sm_count / 2 ? p.n_items : l->sm_count / 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(2 * pairs));
-    cfg.blockDim = dim3(kThreads);
+    cfg.blockDim = dim3(32 * (4 * l->epi_groups + 2));
     cfg.dynamicSmemBytes = (size_t)l->smem_bytes;
     cfg.stream = (cudaStream_t)s;
     cudaLaunchAttribute attr[1];
@@ -811,7 +863,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
     return 0;
   }
   long long grid = p.n_items < l->sm_count ? p.n_items : l->sm_count;
-  fn<<<(unsigned)grid, kThreads, l->smem_bytes, (cudaStream_t)s>>>(tmA, l->tmB, tmY, p);
+  fn<<<(unsigned)grid, 32 * (4 * l->epi_groups + 2), l->smem_bytes, (cudaStream_t)s>>>(tmA, l->tmB, tmY, p);
   PSOB_LAUNCH_CHECK("pixel_gemm_umma_kernel");
   return 0;
 }

@@ -31,7 +31,14 @@ constexpr int kMaxBiasRowsSmem = 8;
 constexpr int kMaxStepsSmem = 1024;                // step descriptors staged in SMEM (16 B each)
 constexpr int kMaxJobsSmem = 256;
 constexpr int kMaxSoloResident = 96 * 1024;       // resident weights of one CTA before the pair mode takes over
-constexpr int kMaxPairResident = 128 * 1024;      // per CTA of a pair                  // job descriptors staged in SMEM (32 B each)
+constexpr int kMaxPairResident = 128 * 1024;      // per CTA of a pair
+// step word 1 (meta): bits 0-2 number of MMA ops (1..4), bit 3 weights resident, bit 4 some op targets the NEXT job
+constexpr int kMetaOpsMask = 7, kMetaResident = 8, kMetaHasNext = 16;
+// op word: bits 0-15 weight row / 16, bits 16-23 accumulator column / 2, bit 24 NEXT job's buffer, bit 25 accumulate
+__host__ __device__ __forceinline__ int op_b_row(int op) { return (op & 0xFFFF) << 4; }
+__host__ __device__ __forceinline__ int op_d_col(int op) { return ((op >> 16) & 0xFF) << 1; }
+__host__ __device__ __forceinline__ int op_next(int op) { return (op >> 24) & 1; }
+__host__ __device__ __forceinline__ int op_acc(int op) { return (op >> 25) & 1; }                  // job descriptors staged in SMEM (32 B each)
 constexpr int kMaxEpiGroups = 3;                  // epilogue groups of 4 warps (one per TMEM lane quadrant)
 constexpr int kMaxThreads = 32 * (4 * kMaxEpiGroups + 2);   // + TMA warp + MMA warp; blockDim = 32 * (4 * epi_groups + 2)
 // The SMSP arbiter favours the highest warp id: the two single-thread roles that must never wait for
@@ -39,8 +46,9 @@ constexpr int kMaxThreads = 32 * (4 * kMaxEpiGroups + 2);   // + TMA warp + MMA 
 // (warp ids 4 * epi_groups and 4 * epi_groups + 1, see kTmaWarp / kMmaWarp in the kernel)
 
 struct EngineParams {
-  const int4* steps;
+  const int4* steps;         // 2 x int4 per step: {a_col, meta, op0, op1} {op2, op3, 0, 0}
   const int4* jobs;          // 2 x int4 per job
+  const int2* chains;        // {first job, job count}: jobs of a chain run back to back on one CTA (pair)
   const int* col_map;
   const int* col_map32;
   const float* bias;
@@ -48,14 +56,14 @@ struct EngineParams {
   float* y32;
   long long P;
   long long n_items;
-  int n_jobs;
+  int n_jobs, n_chains;
   int mma_n, nt, cc, act, out_pitch, out32_pitch, vec8;
   int b_resident, n_wrows, n_bias_rows, n_steps;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4, strided, pf_dist;
   int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
   int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
-  int bias_off, steps_off, jobs_off, stg_bufs;   // SMEM table offsets from the table base (-1: stays in global)
+  int bias_off, steps_off, jobs_off, chains_off, stg_bufs;   // SMEM table offsets from the table base (-1: stays in global)
   unsigned long long* prof;   // optional [gridDim][16] role wait-cycle counters (debug)
   uint32_t idesc, tmem_cols;
 };
@@ -135,7 +143,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const long long item_begin = p.strided ? worker : (per_cta * worker < p.n_items ? per_cta * worker : p.n_items);
   const long long item_end = p.strided ? p.n_items : (item_begin + per_cta < p.n_items ? item_begin + per_cta : p.n_items);
   const long long item_step = p.strided ? n_workers : 1;
-  const uint32_t n_jobs_u = (uint32_t)p.n_jobs;
+  const uint32_t n_chains_u = (uint32_t)p.n_chains;
   // particle-tile index of this CTA for TMA coordinates: pair tile t covers tiles 2t (leader) and 2t+1
   auto tile_idx = [&](int ptile) { return kPair ? 2 * ptile + (int)crank : ptile; };
   auto tile_row = [&](int ptile) { return tile_idx(ptile) * kTileM; };
@@ -182,8 +190,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   // one-step prefetch cannot hide — it was the per-step floor of every layer (profiles/r01_roles_v3c.log).
   const int4* steps = p.steps_off >= 0 ? reinterpret_cast<const int4*>(tab + p.steps_off) : p.steps;
   const int4* jobs = p.jobs_off >= 0 ? reinterpret_cast<const int4*>(tab + p.jobs_off) : p.jobs;
+  const int2* chains = p.chains_off >= 0 ? reinterpret_cast<const int2*>(tab + p.chains_off) : p.chains;
+  if (p.chains_off >= 0)
+    for (int i = threadIdx.x; i < p.n_chains; i += kThreads) reinterpret_cast<int2*>(tab + p.chains_off)[i] = p.chains[i];
   if (p.steps_off >= 0)
-    for (int i = threadIdx.x; i < p.n_steps; i += kThreads) reinterpret_cast<int4*>(tab + p.steps_off)[i] = p.steps[i];
+    for (int i = threadIdx.x; i < 2 * p.n_steps; i += kThreads) reinterpret_cast<int4*>(tab + p.steps_off)[i] = p.steps[i];
   if (p.jobs_off >= 0)
     for (int i = threadIdx.x; i < 2 * p.n_jobs; i += kThreads) reinterpret_cast<int4*>(tab + p.jobs_off)[i] = p.jobs[i];
   for (int i = threadIdx.x; i < p.nt; i += kThreads) {
@@ -230,52 +241,32 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const bool prof = p.prof != nullptr;
       unsigned long long w_empty = 0;
       const long long t_start = clock64();
-      // L2 prefetch cursor: runs p.pf_dist steps ahead of the loads (across job and item boundaries), so the ring
-      // (3 stages next to 128 KB of resident weights) only has to cover the L2 latency, not the DRAM latency.
-      long long pf_item = item_begin;
-      int pf_ptile = 0, pf_s = 0, pf_end = 0, pf_ahead = 0;
-      bool pf_valid = p.pf_dist > 0 && item_begin < item_end;
-      auto pf_load_job = [&]() {
-        pf_ptile = (int)((uint32_t)pf_item / n_jobs_u);
-        const int4 q = jobs[2 * (int)((uint32_t)pf_item - (uint32_t)pf_ptile * n_jobs_u)];
-        pf_s = q.x; pf_end = q.x + q.y;
-      };
-      if (pf_valid) pf_load_job();
       for (long long item = item_begin; item < item_end; item += item_step) {
-        const int ptile = (int)((uint32_t)item / n_jobs_u);          // 32-bit: n_items < 2^31 (checked on the host)
-        const int job = (int)((uint32_t)item - (uint32_t)ptile * n_jobs_u);
-        const int4 j0 = jobs[2 * job];
-        int4 st_next = steps[j0.x];
-        for (int s = j0.x; s < j0.x + j0.y; ++s) {
-          const int4 st = st_next;
-          if (s + 1 < j0.x + j0.y) st_next = steps[s + 1];     // descriptor fetch overlaps the wait
-          while (pf_valid && pf_ahead < p.pf_dist) {
-            const int a_col = steps[pf_s].x;
-            if (ptx::elect_one()) ptx::tma_prefetch_2d(&tmA, in_c0(a_col), in_c1(pf_ptile, a_col));
+        const int ptile = (int)((uint32_t)item / n_chains_u);        // 32-bit: n_items < 2^31 (checked on the host)
+        const int2 ch = chains[(uint32_t)item - (uint32_t)ptile * n_chains_u];
+        for (int job = ch.x; job < ch.x + ch.y; ++job) {
+          const int4 j0 = jobs[2 * job];
+          int4 st_next = steps[2 * j0.x];
+          for (int s = j0.x; s < j0.x + j0.y; ++s) {
+            const int4 st = st_next;
+            if (s + 1 < j0.x + j0.y) st_next = steps[2 * (s + 1)];     // descriptor fetch overlaps the wait
+            mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
+            const bool res = (st.y & kMetaResident) != 0;
+            if (ptx::elect_one()) {
+              const uint32_t a_dst = base + (uint32_t)stage * p.stage_bytes;
+              if (kPair) {
+                // both CTAs' A tiles are counted on the leader's barrier (the leader issues the pair MMA)
+                if (leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2u * (uint32_t)kATileBytes);
+                ptx::tma_load_2d_pair(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full0_leader + 8u * (uint32_t)stage);
+              } else {
+                ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)p.mma_n * 128u));
+                ptx::tma_load_2d(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full_bar(stage));
+                if (!res) ptx::tma_load_2d(a_dst + kATileBytes, &tmB, 0, op_b_row(st.z), full_bar(stage));
+              }
+            }
             __syncwarp();
-            ++pf_ahead;
-            if (++pf_s == pf_end) {
-              pf_item += item_step;
-              if (pf_item < item_end) pf_load_job(); else pf_valid = false;
-            }
+            if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
           }
-          --pf_ahead;
-          mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
-          const bool res = (st.w & 2) != 0;
-          if (ptx::elect_one()) {
-            const uint32_t a_dst = base + (uint32_t)stage * p.stage_bytes;
-            if (kPair) {
-              // both CTAs' A tiles are counted on the leader's barrier (the leader issues the pair MMA)
-              if (leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2u * (uint32_t)kATileBytes);
-              ptx::tma_load_2d_pair(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full0_leader + 8u * (uint32_t)stage);
-            } else {
-              ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)p.mma_n * 128u));
-              ptx::tma_load_2d(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full_bar(stage));
-              if (!res) ptx::tma_load_2d(a_dst + kATileBytes, &tmB, 0, st.y, full_bar(stage));
-            }
-          }
-          __syncwarp();
-          if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
         }
       }
       if (prof && lane == 0) { p.prof[blockIdx.x * 16 + 0] = w_empty; p.prof[blockIdx.x * 16 + 1] = (unsigned long long)(clock64() - t_start); }
@@ -289,39 +280,72 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const bool prof = p.prof != nullptr;
     unsigned long long w_full = 0, w_tempty = 0;
     const long long t_start = clock64();
-    for (long long item = item_begin; item < item_end; item += item_step, ++it) {
-      const int job = (int)((uint32_t)item % n_jobs_u);
-      const int4 j0 = jobs[2 * job];
-      const uint32_t buf = it & 1u, use = it >> 1;
-      int4 st_next = steps[j0.x];
-      if (kPair) {                                                              // arrivals come from both CTAs
-        const long long t0 = prof ? clock64() : 0;
-        ptx::mbar_wait_cluster(tempty_bar(buf), (use & 1u) ^ 1u);
-        if (prof) w_tempty += (unsigned long long)(clock64() - t0);
-      }
-      else mbar_wait_t(tempty_bar(buf), (use & 1u) ^ 1u, prof, w_tempty);
-      ptx::tc_fence_after();
-      for (int s = j0.x; s < j0.x + j0.y; ++s) {
-        const int4 st = st_next;
-        if (s + 1 < j0.x + j0.y) st_next = steps[s + 1];
-        mbar_wait_t(full_bar(stage), phase, prof, w_full);
-        ptx::tc_fence_after();
-        if (ptx::elect_one()) {
-          const uint32_t a_addr = base + (uint32_t)stage * p.stage_bytes;
-          const uint32_t b_addr = kPair ? base + p.res_off + (uint32_t)st.y * 64u
-                                        : ((st.w & 2) ? base + p.res_off + (uint32_t)st.y * 128u : a_addr + kATileBytes);
-          const uint64_t adesc = ptx::smem_desc_sw128(a_addr);
-          const uint64_t bdesc = ptx::smem_desc_sw128(b_addr);
-          const uint32_t d = tmem_base + buf * (uint32_t)p.nt + (uint32_t)st.z;
-          // 4 x (K = 16) with +32 B descriptor advances inside the 128 B swizzle row, then commit -> stage free
-          if (kPair) ptx::umma_bf16_k64_commit_pair(d, adesc, bdesc, p.idesc, (uint32_t)(st.w & 1), empty_bar(stage));
-          else ptx::umma_bf16_k64_commit(d, adesc, bdesc, p.idesc, (uint32_t)(st.w & 1), empty_bar(stage));
+    bool next_acquired = false;          // the next job's accumulator buffer was already acquired by a NEXT op
+    for (long long item = item_begin; item < item_end; item += item_step) {
+      const int2 ch = chains[(uint32_t)item % n_chains_u];
+      for (int job = ch.x; job < ch.x + ch.y; ++job, ++it) {
+        const int4 j0 = jobs[2 * job];
+        const uint32_t buf = it & 1u, use = it >> 1;
+        int4 st_next = steps[2 * j0.x];
+        if (!next_acquired) {
+          if (kPair) {                                                              // arrivals come from both CTAs
+            const long long t0 = prof ? clock64() : 0;
+            ptx::mbar_wait_cluster(tempty_bar(buf), (use & 1u) ^ 1u);
+            if (prof) w_tempty += (unsigned long long)(clock64() - t0);
+          } else {
+            mbar_wait_t(tempty_bar(buf), (use & 1u) ^ 1u, prof, w_tempty);
+          }
         }
+        next_acquired = false;
+        ptx::tc_fence_after();
+        for (int s = j0.x; s < j0.x + j0.y; ++s) {
+          const int4 st = st_next;
+          const int n_ops = st.y & kMetaOpsMask;
+          int4 st2 = make_int4(0, 0, 0, 0);
+          if (n_ops > 2) st2 = steps[2 * s + 1];
+          if (s + 1 < j0.x + j0.y) st_next = steps[2 * (s + 1)];
+          if ((st.y & kMetaHasNext) && !next_acquired) {
+            // this A tile also feeds the NEXT job of the chain: its accumulator buffer (the other one) must be drained
+            const uint32_t nuse = (it + 1u) >> 1;
+            if (kPair) ptx::mbar_wait_cluster(tempty_bar(buf ^ 1u), (nuse & 1u) ^ 1u);
+            else ptx::mbar_wait(tempty_bar(buf ^ 1u), (nuse & 1u) ^ 1u);
+            next_acquired = true;
+          }
+          mbar_wait_t(full_bar(stage), phase, prof, w_full);
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+            const uint32_t a_addr = base + (uint32_t)stage * p.stage_bytes;
+            const uint64_t adesc = ptx::smem_desc_sw128(a_addr);
+            const bool res = (st.y & kMetaResident) != 0;
+            auto b_addr_of = [&](int op) {
+              return kPair ? base + p.res_off + (uint32_t)op_b_row(op) * 64u
+                           : (res ? base + p.res_off + (uint32_t)op_b_row(op) * 128u : a_addr + kATileBytes);
+            };
+            auto d_of = [&](int op) { return tmem_base + (buf ^ (uint32_t)op_next(op)) * (uint32_t)p.nt + (uint32_t)op_d_col(op); };
+            if (n_ops == 1) {
+              // 4 x (K = 16) with +32 B descriptor advances inside the 128 B swizzle row, then commit -> stage free
+              const uint64_t bdesc = ptx::smem_desc_sw128(b_addr_of(st.z));
+              if (kPair) ptx::umma_bf16_k64_commit_pair(d_of(st.z), adesc, bdesc, p.idesc, (uint32_t)op_acc(st.z), empty_bar(stage));
+              else ptx::umma_bf16_k64_commit(d_of(st.z), adesc, bdesc, p.idesc, (uint32_t)op_acc(st.z), empty_bar(stage));
+            } else {
+              // one A tile, several weight tiles: own / next job's accumulators (resident weights only)
+              const int ops[4] = {st.z, n_ops > 1 ? st.w : st.z, n_ops > 2 ? st2.x : st.z, n_ops > 3 ? st2.y : st.z};
+              uint32_t dd[4], aa[4];
+              uint64_t bb[4];
+#pragma unroll
+              for (int o = 0; o < 4; ++o) {
+                dd[o] = d_of(ops[o]); aa[o] = (uint32_t)op_acc(ops[o]); bb[o] = ptx::smem_desc_sw128(b_addr_of(ops[o]));
+              }
+              if (kPair) ptx::umma_bf16_k64x4_commit_pair(dd, adesc, bb, p.idesc, aa, n_ops, empty_bar(stage));
+              else ptx::umma_bf16_k64x4_commit(dd, adesc, bb, p.idesc, aa, n_ops, empty_bar(stage));
+            }
+          }
+          __syncwarp();
+          if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
+        }
+        if (ptx::elect_one()) { if (kPair) ptx::umma_commit_pair(tfull_bar(buf)); else ptx::umma_commit(tfull_bar(buf)); }
         __syncwarp();
-        if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
       }
-      if (ptx::elect_one()) { if (kPair) ptx::umma_commit_pair(tfull_bar(buf)); else ptx::umma_commit(tfull_bar(buf)); }
-      __syncwarp();
     }
     if (prof && lane == 0) {
       p.prof[blockIdx.x * 16 + 2] = w_full; p.prof[blockIdx.x * 16 + 3] = w_tempty;
@@ -347,9 +371,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     long long tq = 0;
     const long long t_start = clock64();
     if (kTmaStore ? grp < p.epi_groups : grp == 0) {
-      for (long long item = item_begin; item < item_end; item += item_step, ++it) {
-        const int ptile = (int)((uint32_t)item / n_jobs_u);
-        const int job = (int)((uint32_t)item - (uint32_t)ptile * n_jobs_u);
+      for (long long item = item_begin; item < item_end; item += item_step) {
+        const int ptile = (int)((uint32_t)item / n_chains_u);
+        const int2 chn = chains[(uint32_t)item - (uint32_t)ptile * n_chains_u];
+        for (int job = chn.x; job < chn.x + chn.y; ++job, ++it) {
         const int4 j0 = jobs[2 * job];
         const int4 j1 = jobs[2 * job + 1];
         const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
@@ -482,6 +507,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           __syncwarp();
           if (lane == 0) release_tmem(buf);
         }
+        }   // jobs of the chain
       }
       if (kTmaStore && issuer_warp && ptx::elect_one()) ptx::bulk_wait_all0();      // staging tiles must outlive their TMA stores
       if (prof && warp == 0 && lane == 0) {
@@ -537,14 +563,25 @@ pixel_gemm_simt_kernel(const __nv_bfloat16* __restrict__ x, long long x_pitch, c
     const int pix = n / p.cc;
     if (pix < 64 && !((mask >> pix) & 1ull)) continue;
     float acc = 0.f;
-    for (int s = j0.x; s < j0.x + j0.y; ++s) {
-      const int4 st = p.steps[s];
-      if (n < st.z || n >= st.z + p.mma_n) continue;
-      if (!(st.w & 1)) acc = 0.f;
-      const __nv_bfloat16* a = p.in_tiled ? x + (((size_t)ptile * p.n_in_chunks + (st.x >> 6)) * kTileM + row) * kKChunk
-                                          : x + particle * x_pitch + st.x;
-      const __nv_bfloat16* b = w + (size_t)(st.y + n - st.z) * kKChunk;
-      for (int k = 0; k < kKChunk; ++k) acc += __bfloat162float(a[k]) * __bfloat162float(b[k]);
+    // pass 0: the previous job of the chain (its NEXT ops accumulate into this job), pass 1: this job's own ops
+    for (int pass = (j1.w ? 0 : 1); pass < 2; ++pass) {
+      const int4 js = pass == 0 ? p.jobs[2 * (job - 1)] : j0;
+      for (int s = js.x; s < js.x + js.y; ++s) {
+        const int4 st = p.steps[2 * s];
+        const int4 st2 = p.steps[2 * s + 1];
+        const int ops[4] = {st.z, st.w, st2.x, st2.y};
+        const __nv_bfloat16* a = p.in_tiled ? x + (((size_t)ptile * p.n_in_chunks + (st.x >> 6)) * kTileM + row) * kKChunk
+                                            : x + particle * x_pitch + st.x;
+        for (int o = 0; o < (st.y & kMetaOpsMask); ++o) {
+          const int op = ops[o];
+          if (op_next(op) != (pass == 0)) continue;
+          const int dc = op_d_col(op);
+          if (n < dc || n >= dc + p.mma_n) continue;
+          if (!op_acc(op)) acc = 0.f;
+          const __nv_bfloat16* b = w + (size_t)(op_b_row(op) + n - dc) * kKChunk;
+          for (int k = 0; k < kKChunk; ++k) acc += __bfloat162float(a[k]) * __bfloat162float(b[k]);
+        }
+      }
     }
     const float f = apply_act(acc + bias[n], p.act);
     if (p.y) {
@@ -604,6 +641,7 @@ struct psob_layer {
   psob_layer_desc d;          // scalar fields only (host pointers are not kept)
   int4* steps = nullptr;
   int4* jobs = nullptr;
+  int2* chains = nullptr;
   int* col_map = nullptr;
   int* col_map32 = nullptr;
   float* bias = nullptr;
@@ -613,7 +651,7 @@ struct psob_layer {
   bool tma_store = false, vec4 = false, pair = false, strided = false;
   int pf_dist = 0, epi_groups = 2;
   unsigned long long* prof = nullptr;
-  int bias_off = -1, steps_off = -1, jobs_off = -1, tab_bytes = 0, stg_bufs = 0;
+  int bias_off = -1, steps_off = -1, jobs_off = -1, chains_off = -1, tab_bytes = 0, stg_bufs = 0;
   int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, stg_off = 0, smem_bytes = 0;
   uint32_t tmem_cols = 0;
   int sm_count = 0;
@@ -624,7 +662,7 @@ extern "C" {
 
 int psob_layer_destroy(psob_layer* l) {
   if (!l) return 0;
-  cudaFree(l->steps); cudaFree(l->jobs); cudaFree(l->col_map); cudaFree(l->col_map32); cudaFree(l->bias); cudaFree(l->wpack);
+  cudaFree(l->steps); cudaFree(l->jobs); cudaFree(l->chains); cudaFree(l->col_map); cudaFree(l->col_map32); cudaFree(l->bias); cudaFree(l->wpack);
   delete l;
   return 0;
 }
@@ -645,13 +683,42 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   if (d->vec8 && (d->out32_pitch != 0 || d->out_pitch % 8 || d->cc % 8))
     return fail(PSOB_E_ARG, "psob_layer_create: vec8 needs bf16-only output with 16-byte aligned rows");
   // validate the tables so a bad program can never fault on the device
+  if (d->n_chains <= 0 || !d->chains) return fail(PSOB_E_ARG, "psob_layer_create: no chains");
   for (int s = 0; s < d->n_steps; ++s) {
-    const int32_t* st = d->steps + 4 * s;
+    const int32_t* st = d->steps + 8 * s;
     if (st[0] < 0 || st[0] % 8 || st[0] + kKChunk > d->in_pitch || (d->in_tiled && st[0] % kKChunk))
       return fail(PSOB_E_ARG, "step %d: a_col %d out of range (or not chunk-aligned for a tile-major input)", s, st[0]);
-    if (st[1] < 0 || st[1] % 8 || st[1] + d->mma_n > d->n_wrows) return fail(PSOB_E_ARG, "step %d: b_row %d out of range", s, st[1]);
-    if (st[2] < 0 || st[2] % 2 || st[2] + d->mma_n > d->nt) return fail(PSOB_E_ARG, "step %d: d_col %d out of range", s, st[2]);
-    if (((st[3] & 2) != 0) != (d->b_resident != 0)) return fail(PSOB_E_ARG, "step %d: resident flag disagrees with the layer", s);
+    const int n_ops = st[1] & kMetaOpsMask;
+    if (n_ops < 1 || n_ops > 4) return fail(PSOB_E_ARG, "step %d: %d ops", s, n_ops);
+    if (((st[1] & kMetaResident) != 0) != (d->b_resident != 0)) return fail(PSOB_E_ARG, "step %d: resident flag disagrees with the layer", s);
+    if (n_ops > 1 && !d->b_resident) return fail(PSOB_E_ARG, "step %d: several ops per A tile need resident weights", s);
+    bool has_next = false;
+    const int32_t ops[4] = {st[2], st[3], st[4], st[5]};
+    for (int o = 0; o < n_ops; ++o) {
+      const int br = op_b_row(ops[o]), dc = op_d_col(ops[o]);
+      if (br % 8 || br + d->mma_n > d->n_wrows) return fail(PSOB_E_ARG, "step %d op %d: b_row %d out of range", s, o, br);
+      if (dc + d->mma_n > d->nt) return fail(PSOB_E_ARG, "step %d op %d: d_col %d out of range", s, o, dc);
+      has_next = has_next || op_next(ops[o]);
+    }
+    if (has_next != ((st[1] & kMetaHasNext) != 0)) return fail(PSOB_E_ARG, "step %d: NEXT flag disagrees with its ops", s);
+  }
+  {
+    // chains partition the jobs in order; only the last job of a chain may not use NEXT ops
+    int expect = 0;
+    for (int c = 0; c < d->n_chains; ++c) {
+      const int jb = d->chains[2 * c], jc = d->chains[2 * c + 1];
+      if (jb != expect || jc <= 0) return fail(PSOB_E_ARG, "chain %d: jobs must be consecutive and non-empty", c);
+      expect = jb + jc;
+      for (int j = jb; j < jb + jc; ++j) {
+        if ((d->jobs[8 * j + 7] != 0) != (j > jb)) return fail(PSOB_E_ARG, "job %d: chain-predecessor flag is wrong", j);
+        if (j == jb + jc - 1) {
+          const int sb = d->jobs[8 * j], sc = d->jobs[8 * j + 1];
+          for (int s = sb; s >= 0 && s < sb + sc && s < d->n_steps; ++s)
+            if (d->steps[8 * s + 1] & kMetaHasNext) return fail(PSOB_E_ARG, "job %d ends a chain but has NEXT ops", j);
+        }
+      }
+    }
+    if (expect != d->n_jobs) return fail(PSOB_E_ARG, "chains cover %d of %d jobs", expect, d->n_jobs);
   }
   long long max_cm = -1, max_cm32 = -1;
   for (int n = 0; n < d->nt; ++n) {
@@ -684,18 +751,20 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   psob_layer* l = new (std::nothrow) psob_layer();
   if (!l) return fail(PSOB_E_ARG, "psob_layer_create: out of host memory");
   l->d = *d;
-  l->d.wpack = nullptr; l->d.steps = nullptr; l->d.jobs = nullptr; l->d.col_map = nullptr; l->d.col_map32 = nullptr; l->d.bias = nullptr;
+  l->d.wpack = nullptr; l->d.steps = nullptr; l->d.jobs = nullptr; l->d.chains = nullptr; l->d.col_map = nullptr; l->d.col_map32 = nullptr; l->d.bias = nullptr;
 #define PSOB_CUDA_L(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { psob_layer_destroy(l); \
     return fail((int)e__, "%s failed: %s", #call, cudaGetErrorString(e__)); } } while (0)
   PSOB_CUDA_L(cudaGetDevice(&l->device));
   PSOB_CUDA_L(cudaDeviceGetAttribute(&l->sm_count, cudaDevAttrMultiProcessorCount, l->device));
-  PSOB_CUDA_L(cudaMalloc(&l->steps, sizeof(int4) * d->n_steps));
+  PSOB_CUDA_L(cudaMalloc(&l->steps, sizeof(int4) * 2 * d->n_steps));
+  PSOB_CUDA_L(cudaMalloc(&l->chains, sizeof(int2) * d->n_chains));
+  PSOB_CUDA_L(cudaMemcpy(l->chains, d->chains, sizeof(int2) * d->n_chains, cudaMemcpyHostToDevice));
   PSOB_CUDA_L(cudaMalloc(&l->jobs, sizeof(int4) * 2 * d->n_jobs));
   PSOB_CUDA_L(cudaMalloc(&l->col_map, sizeof(int) * d->nt));
   PSOB_CUDA_L(cudaMalloc(&l->col_map32, sizeof(int) * d->nt));
   PSOB_CUDA_L(cudaMalloc(&l->bias, sizeof(float) * d->nt * d->n_bias_rows));
   PSOB_CUDA_L(cudaMalloc(&l->wpack, (size_t)d->n_wrows * kKChunk * 2));
-  PSOB_CUDA_L(cudaMemcpy(l->steps, d->steps, sizeof(int4) * d->n_steps, cudaMemcpyHostToDevice));
+  PSOB_CUDA_L(cudaMemcpy(l->steps, d->steps, sizeof(int4) * 2 * d->n_steps, cudaMemcpyHostToDevice));
   PSOB_CUDA_L(cudaMemcpy(l->jobs, d->jobs, sizeof(int4) * 2 * d->n_jobs, cudaMemcpyHostToDevice));
   PSOB_CUDA_L(cudaMemcpy(l->col_map, d->col_map, sizeof(int) * d->nt, cudaMemcpyHostToDevice));
   PSOB_CUDA_L(cudaMemcpy(l->col_map32, d->col_map32, sizeof(int) * d->nt, cudaMemcpyHostToDevice));
@@ -741,7 +810,8 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->bias_off = l->steps_off = l->jobs_off = -1;
   if (d->n_bias_rows <= kMaxBiasRowsSmem) { l->bias_off = tab; tab += d->n_bias_rows * d->nt * 4; }
   tab = (tab + 15) & ~15;
-  if (d->n_steps <= kMaxStepsSmem) { l->steps_off = tab; tab += d->n_steps * 16; }
+  if (d->n_chains <= kMaxJobsSmem) { l->chains_off = tab; tab += (d->n_chains * 8 + 15) & ~15; }
+  if (d->n_steps <= kMaxStepsSmem) { l->steps_off = tab; tab += d->n_steps * 32; }
   if (d->n_jobs <= kMaxJobsSmem) { l->jobs_off = tab; tab += d->n_jobs * 32; }
   l->tab_bytes = (tab + 127) & ~127;
   // staging tiles for the TMA-store epilogue: 2 per group if that still leaves a 3-stage ring
@@ -792,12 +862,12 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   if ((d.out_pitch && !y && !(d.out32_pitch && y32)) || (!d.out_pitch && !y32)) return fail(PSOB_E_ARG, "psob_layer_run: missing output buffer");
   if (y && !aligned16(y)) return fail(PSOB_E_ARG, "psob_layer_run: y must be 16-byte aligned");
   EngineParams p;
-  p.steps = l->steps; p.jobs = l->jobs; p.col_map = l->col_map; p.col_map32 = l->col_map32; p.bias = l->bias;
+  p.steps = l->steps; p.jobs = l->jobs; p.chains = l->chains; p.n_chains = d.n_chains; p.chains_off = l->chains_off; p.col_map = l->col_map; p.col_map32 = l->col_map32; p.bias = l->bias;
   p.y = d.out_pitch ? reinterpret_cast<__nv_bfloat16*>(y) : nullptr;
   p.y32 = d.out32_pitch ? y32 : nullptr;
   p.P = P;
   const long long n_ptiles = (P + kTileM - 1) / kTileM;
-  p.n_items = n_ptiles * d.n_jobs;
+  p.n_items = n_ptiles * d.n_chains;
   p.n_jobs = d.n_jobs;
   p.mma_n = d.mma_n; p.nt = d.nt; p.cc = d.cc; p.act = d.act; p.out_pitch = d.out_pitch; p.out32_pitch = d.out32_pitch;
   p.vec8 = (d.vec8 && p.y) ? 1 : 0;
@@ -825,7 +895,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   UmmaKernelFn fn = umma_kernel_for(d.act, tma_store, l->pair);
   if (!fn) return fail(PSOB_E_ARG, "psob_layer_run: unknown activation %d", d.act);
   if (l->pair) {
-    p.n_items = ((n_ptiles + 1) / 2) * d.n_jobs;                  // items are (pair of particle tiles, job)
+    p.n_items = ((n_ptiles + 1) / 2) * d.n_chains;                // items are (pair of particle tiles, chain of jobs)
     p.idesc = make_idesc_bf16(2 * kTileM, d.mma_n);
   }
   if (!l->have_tmB) {

@@ -202,6 +202,72 @@ __device__ __forceinline__ void umma_bf16_k64_commit(uint32_t d_tmem, uint64_t a
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(bar)
       : "memory");
 }
+// The same K-chunk without the commit (steps that feed several weight tiles commit once after the last one).
+#define PSOB_UMMA_K64_BODY(GROUP)                                                                        \
+  asm volatile(                                                                                          \
+      "{\n\t.reg .pred p, t;\n\t.reg .b64 a1, b1, a2, b2, a3, b3;\n\t"                                   \
+      "setp.ne.b32 p, %4, 0;\n\t"                                                                        \
+      "setp.eq.u32 t, 0, 0;\n\t"                                                                         \
+      "add.u64 a1, %1, 2;\n\tadd.u64 b1, %2, 2;\n\t"                                                    \
+      "add.u64 a2, %1, 4;\n\tadd.u64 b2, %2, 4;\n\t"                                                    \
+      "add.u64 a3, %1, 6;\n\tadd.u64 b3, %2, 6;\n\t"                                                    \
+      "tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], %1, %2, %3, p;\n\t"                               \
+      "tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], a1, b1, %3, t;\n\t"                               \
+      "tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], a2, b2, %3, t;\n\t"                               \
+      "tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], a3, b3, %3, t;\n\t}"                              \
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)                               \
+      : "memory")
+__device__ __forceinline__ void umma_bf16_k64(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  PSOB_UMMA_K64_BODY("1");
+}
+__device__ __forceinline__ void umma_bf16_k64_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  PSOB_UMMA_K64_BODY("2");
+}
+#undef PSOB_UMMA_K64_BODY
+// One A tile against up to four weight tiles (ops 1..3 enabled by en1..en3) and the stage-freeing commit, as ONE
+// asm block: each separate tcgen05 statement costs a uniform-register "waterfall", which made multi-op steps
+// issue-bound when every op was its own block.
+#define PSOB_UMMA_K64X4_BODY(GROUP, COMMIT)                                                              \
+  asm volatile(                                                                                          \
+      "{\n\t.reg .pred p0, p1, p2, p3, e1, e2, e3, t;\n\t.reg .b64 a1, a2, a3, x1, x2, x3;\n\t"           \
+      "setp.ne.b32 p0, %10, 0;\n\tsetp.ne.b32 p1, %11, 0;\n\tsetp.ne.b32 p2, %12, 0;\n\tsetp.ne.b32 p3, %13, 0;\n\t" \
+      "setp.ne.b32 e1, %14, 0;\n\tsetp.ne.b32 e2, %15, 0;\n\tsetp.ne.b32 e3, %16, 0;\n\t"                \
+      "setp.eq.u32 t, 0, 0;\n\t"                                                                         \
+      "add.u64 a1, %4, 2;\n\tadd.u64 a2, %4, 4;\n\tadd.u64 a3, %4, 6;\n\t"                              \
+      "add.u64 x1, %5, 2;\n\tadd.u64 x2, %5, 4;\n\tadd.u64 x3, %5, 6;\n\t"                              \
+      "tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], %4, %5, %9, p0;\n\t"                              \
+      "tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], a1, x1, %9, t;\n\t"                               \
+      "tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], a2, x2, %9, t;\n\t"                               \
+      "tcgen05.mma.cta_group::" GROUP ".kind::f16 [%0], a3, x3, %9, t;\n\t"                               \
+      "add.u64 x1, %6, 2;\n\tadd.u64 x2, %6, 4;\n\tadd.u64 x3, %6, 6;\n\t"                              \
+      "@e1 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%1], %4, %6, %9, p1;\n\t"                          \
+      "@e1 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%1], a1, x1, %9, t;\n\t"                           \
+      "@e1 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%1], a2, x2, %9, t;\n\t"                           \
+      "@e1 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%1], a3, x3, %9, t;\n\t"                           \
+      "add.u64 x1, %7, 2;\n\tadd.u64 x2, %7, 4;\n\tadd.u64 x3, %7, 6;\n\t"                              \
+      "@e2 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%2], %4, %7, %9, p2;\n\t"                          \
+      "@e2 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%2], a1, x1, %9, t;\n\t"                           \
+      "@e2 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%2], a2, x2, %9, t;\n\t"                           \
+      "@e2 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%2], a3, x3, %9, t;\n\t"                           \
+      "add.u64 x1, %8, 2;\n\tadd.u64 x2, %8, 4;\n\tadd.u64 x3, %8, 6;\n\t"                              \
+      "@e3 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%3], %4, %8, %9, p3;\n\t"                          \
+      "@e3 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%3], a1, x1, %9, t;\n\t"                           \
+      "@e3 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%3], a2, x2, %9, t;\n\t"                           \
+      "@e3 tcgen05.mma.cta_group::" GROUP ".kind::f16 [%3], a3, x3, %9, t;\n\t"                           \
+      COMMIT "\n\t}"                                                                                     \
+      ::"r"(d[0]), "r"(d[1]), "r"(d[2]), "r"(d[3]), "l"(a_desc), "l"(b[0]), "l"(b[1]), "l"(b[2]), "l"(b[3]),   \
+        "r"(idesc), "r"(acc[0]), "r"(acc[1]), "r"(acc[2]), "r"(acc[3]), "r"((uint32_t)(n_ops > 1)),          \
+        "r"((uint32_t)(n_ops > 2)), "r"((uint32_t)(n_ops > 3)), "r"(bar), "h"((uint16_t)3)                  \
+      : "memory")
+__device__ __forceinline__ void umma_bf16_k64x4_commit(const uint32_t (&d)[4], uint64_t a_desc, const uint64_t (&b)[4], uint32_t idesc,
+                                                       const uint32_t (&acc)[4], int n_ops, uint32_t bar) {
+  PSOB_UMMA_K64X4_BODY("1", "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%17];");
+}
+__device__ __forceinline__ void umma_bf16_k64x4_commit_pair(const uint32_t (&d)[4], uint64_t a_desc, const uint64_t (&b)[4], uint32_t idesc,
+                                                            const uint32_t (&acc)[4], int n_ops, uint32_t bar) {
+  PSOB_UMMA_K64X4_BODY("2", "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%17], %18;");
+}
+#undef PSOB_UMMA_K64X4_BODY
 // CTA-pair form (issued by the pair leader only): M = 256 over both CTAs' A tiles, each CTA supplies half
 // of the B rows from the same shared-memory offset; the commit arrives on `bar` in BOTH CTAs.
 __device__ __forceinline__ void umma_bf16_k64_commit_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,

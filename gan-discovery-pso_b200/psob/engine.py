@@ -44,8 +44,9 @@ class Layer:
         self.prog = prog
         self.in_tiled, self.out_tiled = bool(in_tiled), bool(out_tiled)
         wbits = np.ascontiguousarray(L.bf16_bits(prog.wpack))
-        steps = np.ascontiguousarray(prog.steps, dtype=np.int32)
-        jobs = np.ascontiguousarray(prog.jobs, dtype=np.int32)
+        steps = np.ascontiguousarray(L.pack_steps(prog), dtype=np.int32)
+        jobs = np.ascontiguousarray(L.pack_jobs(prog), dtype=np.int32)
+        chains = np.ascontiguousarray(prog.chains, dtype=np.int32)
         cm = np.ascontiguousarray(prog.col_map, dtype=np.int32)
         cm32 = np.ascontiguousarray(prog.col_map32, dtype=np.int32)
         bias = np.ascontiguousarray(prog.bias, dtype=np.float32)
@@ -53,7 +54,7 @@ class Layer:
             mma_n=prog.mma_n, nt=prog.nt, cc=prog.cc, act=prog.act, in_pitch=prog.in_pitch,
             out_pitch=prog.out_pitch, out32_pitch=prog.out32_pitch, b_resident=int(prog.b_resident),
             vec8=int(prog.vec8), n_steps=prog.n_steps, n_jobs=prog.n_jobs, n_wrows=wbits.shape[0],
-            n_bias_rows=bias.shape[0], in_tiled=int(in_tiled), out_tiled=int(out_tiled), wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
+            n_bias_rows=bias.shape[0], n_chains=chains.shape[0], chains=chains.ctypes.data, in_tiled=int(in_tiled), out_tiled=int(out_tiled), wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
             col_map=cm.ctypes.data, col_map32=cm32.ctypes.data, bias=bias.ctypes.data)
         h = C.c_void_p()
         _ffi.check(_ffi.lib().psob_layer_create(C.byref(d), C.byref(h)), f"psob_layer_create({prog.name})")

@@ -31,13 +31,14 @@ TILE_M = 128          # particles per tile (UMMA M)
 MAX_N = 256           # UMMA N limit / TMEM columns per accumulator buffer
 
 ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3, 4
-STEP_ACCUM, STEP_B_RESIDENT = 1, 2
+STEP_ACCUM, STEP_B_RESIDENT, STEP_NEXT = 1, 2, 4     # NEXT: the op accumulates into the next job of the chain
 ROUND_WEIGHTS = True   # tests switch this off to check the geometry exactly in fp32
 # Weight packs up to RESIDENT_SOLO bytes stay in one CTA's shared memory for its lifetime; packs up to
 # RESIDENT_PAIR are split over a CTA pair (tcgen05 cta_group::2, csrc/pixel_gemm.cu) when the layer has the
 # TMA-store epilogue (64-channel NHWC chunks).  PSOB_PAIR=0 falls back to streaming the weights per step.
 RESIDENT_SOLO = 32 * 1024
 RESIDENT_PAIR = 256 * 1024 if os.environ.get("PSOB_PAIR", "1") != "0" else 0
+CHAIN_ROWS = os.environ.get("PSOB_CHAIN", "1") != "0"      # share input rows between vertically adjacent jobs (resident layers)
 
 # image layouts
 IMG_PAD_ROWS, IMG_PAD_PITCH = 31, 32          # bf16 padded 28x28 image: real (y,x) at (y+1,x+1)
@@ -83,6 +84,8 @@ class LayerProgram:
     col_map32: np.ndarray         # int32 [nt] relative fp32 offsets (-1: not stored)
     bias: np.ndarray              # float32 [n_bias_rows, nt]; jobs[:, 6] selects the row
     vec8: bool                    # col_map is contiguous in aligned groups of 8 (16-byte stores)
+    xops: dict = field(default_factory=dict)    # step index -> [(b_row, d_col, flags), ...]: further MMA ops fed by the same A tile
+    chains: Optional[np.ndarray] = None          # int32 [n_chains, 2]: first job, job count (default: one job per chain)
     macs_exact: int = 0           # border-aware MACs per particle (reference arithmetic)
     macs_issued: int = 0          # MACs per particle the MMA chain actually executes
     meta: dict = field(default_factory=dict)
@@ -119,8 +122,36 @@ def can_load_tiled(prog: "LayerProgram") -> bool:
     return prog.in_pitch % KCHUNK == 0 and bool(np.all(prog.steps[:, 0] % KCHUNK == 0))
 
 
+def pack_steps(prog: "LayerProgram") -> np.ndarray:
+    """Engine step records int32 [n_steps, 8]: a_col, meta, op0..op3, 0, 0 (include/psob.h)."""
+    out = np.zeros((prog.n_steps, 8), np.int32)
+
+    def enc(b_row, d_col, flags):
+        assert b_row % 16 == 0 and b_row // 16 < 65536 and d_col % 2 == 0 and d_col // 2 < 256
+        return (b_row // 16) | ((d_col // 2) << 16) | ((1 << 24) if flags & STEP_NEXT else 0) | ((1 << 25) if flags & STEP_ACCUM else 0)
+
+    for i, (a_col, b_row, d_col, flags) in enumerate(prog.steps):
+        ops = [(int(b_row), int(d_col), int(flags))] + [tuple(map(int, o)) for o in prog.xops.get(i, [])]
+        assert len(ops) <= 4
+        has_next = any(f & STEP_NEXT for _, _, f in ops)
+        out[i, 0] = a_col
+        out[i, 1] = len(ops) | (8 if flags & STEP_B_RESIDENT else 0) | (16 if has_next else 0)
+        for k, o in enumerate(ops):
+            out[i, 2 + k] = enc(*o)
+    return out
+
+
+def pack_jobs(prog: "LayerProgram") -> np.ndarray:
+    """Job records with the chain-predecessor flag in word 7."""
+    jobs = prog.jobs.copy()
+    jobs[:, 7] = 0
+    for jb, jc in prog.chains:
+        jobs[jb + 1:jb + jc, 7] = 1
+    return jobs
+
+
 def _finish(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, tiles, b_resident, steps, jobs,
-            col_map, col_map32, bias, macs_exact, meta=None) -> LayerProgram:
+            col_map, col_map32, bias, macs_exact, meta=None, xops=None, chains=None) -> LayerProgram:
     assert mma_n % 16 == 0 and 16 <= mma_n <= MAX_N and nt <= MAX_N and nt % 16 == 0
     wpack = np.concatenate(tiles, axis=0).astype(np.float32) if tiles else np.zeros((0, KCHUNK), np.float32)
     if ROUND_WEIGHTS:
@@ -137,9 +168,14 @@ def _finish(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, tiles, b
         np.all(col_map[g:g + 8] < 0) for g in range(0, nt, 8)) and cc % 8 == 0)
     bias = np.asarray(bias, dtype=np.float32).reshape(-1, nt)
     assert jobs[:, 6].max(initial=0) < bias.shape[0]
+    xops = dict(xops or {})
+    if chains is None:
+        chains = np.stack([np.arange(jobs.shape[0]), np.ones(jobs.shape[0], np.int64)], axis=1)
+    chains = np.asarray(chains, dtype=np.int32).reshape(-1, 2)
+    n_ops = int(steps.shape[0]) + sum(len(v) for v in xops.values())
     return LayerProgram(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, wpack, b_resident, steps, jobs,
-                        col_map, col_map32, bias, vec8, int(macs_exact),
-                        int(steps.shape[0]) * KCHUNK * mma_n, meta or {})
+                        col_map, col_map32, bias, vec8, xops, chains, int(macs_exact),
+                        n_ops * KCHUNK * mma_n, meta or {})
 
 
 def _mask_words(bits: List[bool]) -> Tuple[int, int]:
@@ -272,7 +308,46 @@ def lower_convt_k4s2p1(name, w, b, act, h, wd, *, m=1, image_out=False, in_cp=No
     wbytes = len(tiles) * nt * KCHUNK * 2
     resident = wbytes <= RESIDENT_SOLO or (wbytes <= RESIDENT_PAIR and not image_out and cc % 64 == 0 and nt % 64 == 0)
     steps, jobs = [], []
-    for bq in range(-1, h, m):
+    xops, chains = {}, None
+    chained = resident and CHAIN_ROWS and m == 1 and wbytes > RESIDENT_SOLO and h >= 2
+    if chained:
+        # Vertically adjacent blocks share an input row (block bq reads rows bq and bq+1): the blocks of one block
+        # column form a chain; every input row is loaded once per chain and feeds this block with the a = 1 taps and,
+        # with STEP_NEXT, the next block with the a = 0 taps (half the A-tile loads; MMA work unchanged).
+        chains = []
+        for br in range(-1, wd):
+            for ch in range(nco):
+                chain_begin = len(jobs)
+                init = False
+                for bq in range(-1, h):
+                    sb = len(steps)
+                    init_next = False
+                    rows = []                       # (input row, a for this job, feeds next job)
+                    if bq == h - 1:
+                        rows.append((bq, 0, False))                 # the last block re-loads its only row itself
+                    if bq + 1 < h:
+                        rows.append((bq + 1, 1, bq + 1 < h - 1))
+                    for iy, a, dual in rows:
+                        for bb in range(2):
+                            ix = br + bb
+                            if not 0 <= ix < wd:
+                                continue
+                            for kc in range(nkc):
+                                fl = (STEP_ACCUM if init else 0) | STEP_B_RESIDENT
+                                init = True
+                                if dual:
+                                    xops[len(steps)] = [(tile_of[(0, bb, kc, ch)] * nt, 0, STEP_NEXT | (STEP_ACCUM if init_next else 0))]
+                                    init_next = True
+                                steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, tile_of[(a, bb, kc, ch)] * nt, 0, fl))
+                    assert len(steps) > sb and init
+                    oy0, ox0 = 2 * bq + 1, 2 * br + 1
+                    bits = [0 <= oy0 + u < ho and 0 <= ox0 + v < wo for u in range(2) for v in range(2)]
+                    assert any(bits)
+                    lo, hi = _mask_words(bits)
+                    jobs.append((sb, len(steps) - sb, base_p + oy0 * row_p + ox0 * pix_p + ch * cc, 0, lo, hi, ch, 0))
+                    init = init_next
+                chains.append((chain_begin, len(jobs) - chain_begin))
+    for bq in ([] if chained else range(-1, h, m)):
         for br in range(-1, wd, m):
             for ch in range(nco):
                 sb = len(steps)
@@ -323,7 +398,7 @@ def lower_convt_k4s2p1(name, w, b, act, h, wd, *, m=1, image_out=False, in_cp=No
             if num % 2 == 0 and 0 <= num // 2 < wd:
                 conn_x += 1
     return _finish(name, nt, nt, cc, act, h * wd * cpi, out_pitch, out32_pitch, tiles, resident, steps, jobs,
-                   col_map, col_map32, bias, macs_exact=conn * conn_x * cin * cout, meta=meta)
+                   col_map, col_map32, bias, macs_exact=conn * conn_x * cin * cout, meta=meta, xops=xops, chains=chains)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -353,6 +428,8 @@ def lower_conv_k4s2p1(name, w, b, act, h, wd, in_cp=None) -> LayerProgram:
                 tiles.append(wp[:, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
     wbytes = len(tiles) * cpo * KCHUNK * 2
     resident = RESIDENT_SOLO < wbytes <= RESIDENT_PAIR and cpo % 64 == 0       # CTA-pair mode only (small packs stream fine)
+    if resident and CHAIN_ROWS:
+        return _lower_conv_k4s2p1_chained(name, wp, bp, act, h, wd, cin, cout, cpi, cpo, g, nt, nkc, tiles, tile_of)
     steps, jobs = [], []
     macs = 0
     for oy in range(ho):
@@ -382,6 +459,63 @@ def lower_conv_k4s2p1(name, w, b, act, h, wd, in_cp=None) -> LayerProgram:
     bias = [bp[n % cpo] for n in range(nt)]
     return _finish(name, cpo, nt, cpo, act, h * wd * cpi, ho * wo * cpo, 0, tiles, resident, steps, jobs, col_map,
                    [-1] * nt, bias, macs_exact=macs, meta=dict(kind="conv_k4s2p1", out_hw=(ho, wo), out_c=cout, out_cp=cpo))
+
+
+def _lower_conv_k4s2p1_chained(name, wp, bp, act, h, wd, cin, cout, cpi, cpo, g, nt, nkc, tiles, tile_of) -> LayerProgram:
+    """Resident-weight form of (c): the jobs of one output-column group (g pixels wide) form a CHAIN over the
+    output rows.  Output rows oy and oy+1 share input rows 2oy+1 and 2oy+2, and the g pixels of a job share input
+    columns, so every A tile (one input pixel, one K-chunk) is loaded ONCE per chain and feeds up to 2g MMA ops:
+    the taps of this job's pixels and, with STEP_NEXT, the taps (ky - 2) of the next job's pixels.  A tile loads per
+    output pixel drop from ~14 to ~6 for the 14x14 -> 7x7 layer; the MMA work is unchanged."""
+    ho, wo = h // 2, wd // 2
+    steps, jobs, chains, xops = [], [], [], {}
+    macs = 0
+    for ox0 in range(0, wo, g):
+        pix = [ox0 + j for j in range(g) if ox0 + j < wo]
+        chain_begin = len(jobs)
+        init = [False] * g                 # this job's accumulators already written by the previous job's NEXT ops
+        for oy in range(ho):
+            sb = len(steps)
+            init_next = [False] * g
+            kys = [ky for ky in range(4) if (oy == 0 or ky >= 2)]      # rows with ky < 2 came from job oy - 1
+            for ky in kys:
+                iy = 2 * oy - 1 + ky
+                if not 0 <= iy < h:
+                    continue
+                dual = ky >= 2 and oy + 1 < ho
+                for ix in range(2 * pix[0] - 1, 2 * pix[-1] + 3):
+                    if not 0 <= ix < wd:
+                        continue
+                    for kc in range(nkc):
+                        ops = []
+                        for j, ox in enumerate(pix):
+                            kx = ix - (2 * ox - 1)
+                            if not 0 <= kx < 4:
+                                continue
+                            ops.append((tile_of[(ky, kx, kc)] * cpo, j * cpo, STEP_ACCUM if init[j] else 0))
+                            init[j] = True
+                            if dual:
+                                ops.append((tile_of[(ky - 2, kx, kc)] * cpo, j * cpo, STEP_NEXT | (STEP_ACCUM if init_next[j] else 0)))
+                                init_next[j] = True
+                        assert ops
+                        b_row, d_col, fl = ops[0]
+                        if len(ops) > 1:
+                            xops[len(steps)] = ops[1:]
+                        steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, b_row, d_col, fl | STEP_B_RESIDENT))
+            assert len(steps) > sb and all(init[j] for j in range(len(pix)))
+            lo, hi = _mask_words([ox0 + j < wo for j in range(g)])
+            jobs.append((sb, len(steps) - sb, (oy * wo + ox0) * cpo, 0, lo, hi, 0, 0))
+            init = init_next
+        chains.append((chain_begin, len(jobs) - chain_begin))
+    for oy in range(ho):
+        for ox in range(wo):
+            macs += cin * cout * sum(1 for ky in range(4) for kx in range(4)
+                                     if 0 <= 2 * oy - 1 + ky < h and 0 <= 2 * ox - 1 + kx < wd)
+    col_map = list(range(nt))
+    bias = [bp[n % cpo] for n in range(nt)]
+    return _finish(name, cpo, nt, cpo, act, h * wd * cpi, ho * wo * cpo, 0, tiles, True, steps, jobs, col_map,
+                   [-1] * nt, bias, macs_exact=macs, xops=xops, chains=chains,
+                   meta=dict(kind="conv_k4s2p1_chained", out_hw=(ho, wo), out_c=cout, out_cp=cpo))
 
 
 # ----------------------------------------------------------------------------------------------
@@ -482,26 +616,41 @@ def emulate(prog: LayerProgram, x: np.ndarray, round_out=True):
     assert x.shape[1] >= prog.in_pitch
     y = np.zeros((p, prog.out_pitch), np.float32) if prog.out_pitch else None
     y32 = np.zeros((p, prog.out32_pitch), np.float32) if prog.out32_pitch else None
-    for job in prog.jobs:
-        sb, sc, base, base32 = int(job[0]), int(job[1]), int(job[2]), int(job[3])
-        mask = (int(np.uint32(job[4])) | (int(np.uint32(job[5])) << 32))
-        acc = np.zeros((p, prog.nt), np.float32)
-        for a_col, b_row, d_col, flags in prog.steps[sb:sb + sc]:
-            a = x[:, a_col:a_col + KCHUNK]
-            bt = prog.wpack[b_row:b_row + prog.mma_n]
-            contrib = a.astype(np.float32) @ bt.T.astype(np.float32)
-            if flags & STEP_ACCUM:
-                acc[:, d_col:d_col + prog.mma_n] += contrib
-            else:
-                acc[:, d_col:d_col + prog.mma_n] = contrib
-        bias = prog.bias[int(job[6])]
-        v = _act(acc + bias[None, :], prog.act).astype(np.float32)
-        for n in range(prog.nt):
-            pix = n // prog.cc
-            if pix < 64 and not (mask >> pix) & 1:
-                continue
-            if y is not None and prog.col_map[n] >= 0:
-                y[:, base + prog.col_map[n]] = to_bf16_f32(v[:, n]) if round_out else v[:, n]
-            if y32 is not None and prog.col_map32[n] >= 0:
-                y32[:, base32 + prog.col_map32[n]] = v[:, n]
+
+    def apply(acc, a, b_row, d_col, flags):
+        contrib = a.astype(np.float32) @ prog.wpack[b_row:b_row + prog.mma_n].T.astype(np.float32)
+        if flags & STEP_ACCUM:
+            acc[:, d_col:d_col + prog.mma_n] += contrib
+        else:
+            acc[:, d_col:d_col + prog.mma_n] = contrib
+
+    for jb, jc in prog.chains:
+        nxt = None
+        for ji in range(jb, jb + jc):
+            job = prog.jobs[ji]
+            sb, sc, base, base32 = int(job[0]), int(job[1]), int(job[2]), int(job[3])
+            mask = (int(np.uint32(job[4])) | (int(np.uint32(job[5])) << 32))
+            acc = nxt if nxt is not None else np.zeros((p, prog.nt), np.float32)     # NEXT ops of the previous job landed here
+            nxt = None
+            for si in range(sb, sb + sc):
+                a_col, b_row, d_col, flags = (int(v) for v in prog.steps[si])
+                a = x[:, a_col:a_col + KCHUNK]
+                for (br, dc, fl) in [(b_row, d_col, flags)] + [tuple(int(v) for v in o) for o in prog.xops.get(si, [])]:
+                    if fl & STEP_NEXT:
+                        assert ji + 1 < jb + jc, "NEXT op in the last job of a chain"
+                        if nxt is None:
+                            nxt = np.zeros((p, prog.nt), np.float32)
+                        apply(nxt, a, br, dc, fl)
+                    else:
+                        apply(acc, a, br, dc, fl)
+            bias = prog.bias[int(job[6])]
+            v = _act(acc + bias[None, :], prog.act).astype(np.float32)
+            for n in range(prog.nt):
+                pix = n // prog.cc
+                if pix < 64 and not (mask >> pix) & 1:
+                    continue
+                if y is not None and prog.col_map[n] >= 0:
+                    y[:, base + prog.col_map[n]] = to_bf16_f32(v[:, n]) if round_out else v[:, n]
+                if y32 is not None and prog.col_map32[n] >= 0:
+                    y32[:, base32 + prog.col_map32[n]] = v[:, n]
     return y, y32

@@ -159,12 +159,17 @@ typedef struct {
   int32_t mma_n, nt, cc, act;
   int32_t in_pitch, out_pitch, out32_pitch;
   int32_t b_resident, vec8;
-  int32_t n_steps, n_jobs, n_wrows, n_bias_rows;
+  int32_t n_steps, n_jobs, n_wrows, n_bias_rows, n_chains;
   int32_t in_tiled, out_tiled; /* tile-major bf16 activations: [ceil(P/128)][pitch/64][128][64] (each 128-particle x
                                 * 64-column operand tile is one contiguous 16 KB block); 0 = row-major [P, pitch] */
   const uint16_t* wpack;     /* HOST bf16 bits [n_wrows, 64] */
-  const int32_t*  steps;     /* HOST [n_steps, 4]: a_col, b_row, d_col, flags */
-  const int32_t*  jobs;      /* HOST [n_jobs, 8]: step_begin, step_count, out_base, out32_base, mask_lo, mask_hi, bias_row, 0 */
+  const int32_t*  steps;     /* HOST [n_steps, 8]: a_col, meta, op0, op1, op2, op3, 0, 0.  One A tile (TMA load) feeds 1..4 MMA ops.
+                              * meta: bits 0-2 op count, bit 3 weights resident, bit 4 some op targets the NEXT job of the chain.
+                              * op:   bits 0-15 weight row / 16, bits 16-23 accumulator column / 2, bit 24 NEXT job, bit 25 accumulate */
+  const int32_t*  jobs;      /* HOST [n_jobs, 8]: step_begin, step_count, out_base, out32_base, mask_lo, mask_hi, bias_row,
+                              * has_chain_predecessor */
+  const int32_t*  chains;    /* HOST [n_chains, 2]: first job, job count.  The jobs of a chain run back to back on one CTA, so an
+                              * A tile loaded by job j may also accumulate into job j+1 (input rows shared by neighbouring outputs) */
   const int32_t*  col_map;   /* HOST [nt] */
   const int32_t*  col_map32; /* HOST [nt] */
   const float*    bias;      /* HOST [n_bias_rows, nt] */

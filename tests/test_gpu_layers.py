@@ -168,7 +168,8 @@ def test_layer_create_rejects_bad_tables(mods, golden):
 @pytest.mark.parametrize("P", [129, 700])
 def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
     """Tile-major vs row-major activations, CTA-pair (cta_group::2, resident weights) vs streamed weights, strided
-    vs contiguous item order: same MMA chains, same accumulation order -> every hidden activation, the image and
+    vs contiguous item order, chained jobs (one A tile feeding this and the next job's accumulators) vs independent
+    jobs: same MMA sequence per accumulator, same accumulation order -> every hidden activation, the image and
     the score must be identical to the last bit.  P = 129 leaves the pair's second particle tile almost empty,
     P = 700 ends on an odd tile count (the last pair has no second tile at all)."""
     engine, L, nets, ffi = mods
@@ -179,10 +180,11 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
     disc = port.Discriminator(1, 64)
     z = torch.randn(P, 100, generator=torch.Generator().manual_seed(P))
     results = {}
-    for tiled, pair, strided in ((1, 1, 1), (0, 1, 1), (1, 0, 1), (1, 1, 0), (0, 0, 0)):
+    for tiled, pair, strided, chain in ((1, 1, 1, 1), (1, 1, 1, 0), (0, 1, 1, 1), (1, 0, 1, 1), (1, 1, 0, 1), (0, 0, 0, 0)):
         monkeypatch.setenv("PSOB_TILED", str(tiled))
         monkeypatch.setenv("PSOB_STRIDED", str(strided))
         monkeypatch.setattr(L, "RESIDENT_PAIR", 256 * 1024 if pair else 0)
+        monkeypatch.setattr(L, "CHAIN_ROWS", bool(chain))
         gnet = engine.GeneratorNet(gen.state_dict(), P)
         dnet = engine.DiscriminatorNet(disc.state_dict(), P)
         assert any(l.out_tiled for l in gnet.layers) == bool(tiled)
@@ -190,9 +192,10 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
         _, img = gnet.forward(_rows(z.numpy(), gnet.in_pitch))
         _, score = dnet.forward(gnet.image_padded_bf16())
         torch.cuda.synchronize()
-        results[(tiled, pair, strided)] = [gnet.activation(i).cpu() for i in range(3)] + \
+        assert (len(dnet.programs[1].chains) < dnet.programs[1].n_jobs) == bool(pair and chain)
+        results[(tiled, pair, strided, chain)] = [gnet.activation(i).cpu() for i in range(3)] + \
             [dnet.activation(i).cpu() for i in range(2)] + [img.cpu(), score.cpu()]
-    base = results[(0, 0, 0)]
+    base = results[(0, 0, 0, 0)]
     for key, got in results.items():
         for i, (a, b) in enumerate(zip(base, got)):
-            assert torch.equal(a, b), f"mode (tiled, pair, strided)={key}: tensor {i} differs"
+            assert torch.equal(a, b), f"mode (tiled, pair, strided, chain)={key}: tensor {i} differs"

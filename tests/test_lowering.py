@@ -132,5 +132,8 @@ def test_program_tables_are_tma_legal():
             assert (p.steps[:, 1] + p.mma_n).max() <= p.wpack.shape[0]
             assert (p.steps[:, 2] + p.mma_n).max() <= p.nt
             assert p.nt <= 256 and p.mma_n % 16 == 0
-            first = p.steps[p.jobs[:, 0], 3] & L.STEP_ACCUM
-            assert (first == 0).all(), "first step of every job must overwrite its accumulator"
+            first = p.steps[p.jobs[p.chains[:, 0], 0], 3] & L.STEP_ACCUM
+            assert (first == 0).all(), "the first step of every chain must overwrite its accumulator"
+            assert p.chains[:, 1].sum() == p.n_jobs and (p.chains[1:, 0] == p.chains[:-1, 0] + p.chains[:-1, 1]).all()
+            packed = L.pack_steps(p)
+            assert ((packed[:, 1] & 7) >= 1).all() and ((packed[:, 1] & 7) <= 4).all()

@@ -32,6 +32,7 @@ constexpr int kMaxStepsSmem = 1024;                // step descriptors staged in
 constexpr int kMaxJobsSmem = 256;
 constexpr int kMaxSoloResident = 96 * 1024;       // resident weights of one CTA before the pair mode takes over
 constexpr int kMaxPairResident = 128 * 1024;      // per CTA of a pair
+constexpr int kBandPitch = 30;                    // accumulator columns per padded image row of an image band (psob/lowering.py)
 // step word 1 (meta): bits 0-2 number of MMA ops (1..4), bit 3 weights resident, bit 4 some op targets the NEXT job
 constexpr int kMetaOpsMask = 7, kMetaResident = 8, kMetaHasNext = 16;
 // op word: bits 0-15 weight row / 16, bits 16-23 accumulator column / 2, bit 24 NEXT job's buffer, bit 25 accumulate
@@ -39,7 +40,7 @@ __host__ __device__ __forceinline__ int op_b_row(int op) { return (op & 0xFFFF) 
 __host__ __device__ __forceinline__ int op_d_col(int op) { return ((op >> 16) & 0xFF) << 1; }
 __host__ __device__ __forceinline__ int op_next(int op) { return (op >> 24) & 1; }
 __host__ __device__ __forceinline__ int op_acc(int op) { return (op >> 25) & 1; }                  // job descriptors staged in SMEM (32 B each)
-constexpr int kMaxEpiGroups = 3;                  // epilogue groups of 4 warps (one per TMEM lane quadrant)
+constexpr int kMaxEpiGroups = 2;                  // epilogue groups of 4 warps (one per TMEM lane quadrant)
 constexpr int kMaxThreads = 32 * (4 * kMaxEpiGroups + 2);   // + TMA warp + MMA warp; blockDim = 32 * (4 * epi_groups + 2)
 // The SMSP arbiter favours the highest warp id: the two single-thread roles that must never wait for
 // an issue slot (TMA producer, MMA issuer) get the top ids; epilogue warps 0..7 map to TMEM quadrant w % 4.
@@ -61,6 +62,7 @@ struct EngineParams {
   int b_resident, n_wrows, n_bias_rows, n_steps;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4, strided, pf_dist;
+  int band;                  // image-band epilogue (lower_convt_image_band): 4 chunks of two padded image rows each
   int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
   int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
   int bias_off, steps_off, jobs_off, chains_off, stg_bufs;   // SMEM table offsets from the table base (-1: stays in global)
@@ -387,16 +389,17 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           const int n_chunks = p.nt >> 6;
           int last = -1;                      // last chunk this group will read: release TMEM right after it
           for (int ch = grp; ch < n_chunks; ch += p.epi_groups)
-            if (s_cm[ch << 6] >= 0 && ((mask >> s_pix[ch << 6]) & 1ull)) last = ch;
+            if (p.band || (s_cm[ch << 6] >= 0 && ((mask >> s_pix[ch << 6]) & 1ull))) last = ch;
           if (last < 0) {
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) release_tmem(buf);
           }
           for (int ch = grp; ch < n_chunks; ch += p.epi_groups) {
-            const int n0 = ch << 6;
-            const int cm = s_cm[n0];
-            if (cm < 0 || !((mask >> s_pix[n0]) & 1ull)) continue;       // uniform over the group
+            // image band: chunk ch = padded image rows 2ch, 2ch+1 of the band = accumulator columns [60 ch, 60 ch + 60)
+            const int n0 = p.band ? ch * 2 * kBandPitch : ch << 6;
+            const int cm = p.band ? ch << 6 : s_cm[n0];
+            if (!p.band && (cm < 0 || !((mask >> s_pix[n0]) & 1ull))) continue;       // uniform over the group
             uint32_t v[64];
             __syncwarp();
             if (prof) tq = clock64();
@@ -427,7 +430,28 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               o.w = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 6]) + b1.z), act_fn<kAct>(__uint_as_float(v[8 * j + 7]) + b1.w));
               ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);   // SWIZZLE_128B: 16-byte slot j of row r lives at j ^ (r % 8)
             };
-            if (bias_in_smem) {
+            if (p.band) {
+              // out element e = 32 * rr + px of the 128-byte row <- column rr * 30 + px; the padding columns and the
+              // padding rows of the image (mask) are written as zeros
+              const float bz = bias_in_smem ? s_bias[0] : __ldg(p.bias);
+              const long long particle = (long long)tile_row(ptile) + row;
+              float* y32row = (p.y32 && particle < p.P) ? p.y32 + particle * p.out32_pitch + j0.w + ch * 2 * 28 : nullptr;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const int rr = j >> 2;
+                const bool rowok = ((mask >> (2 * ch + rr)) & 1ull) != 0;
+                float f[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  const int px = (8 * j + i) & 31;
+                  f[i] = (px >= 1 && px <= 28 && rowok) ? act_fn<kAct>(__uint_as_float(v[(rr * kBandPitch + px) & 63]) + bz) : 0.f;
+                  if (px >= 1 && px <= 28 && rowok && y32row) y32row[rr * 28 + px - 1] = f[i];
+                }
+                uint4 o;
+                o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]); o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+                ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);
+              }
+            } else if (bias_in_smem) {
               // explicit ld.shared, software-pipelined one slot ahead: through a generic pointer every slot was a
               // dependent LD -> math -> STS chain of ~110 cycles (the epilogue's largest single cost)
               const uint32_t baddr = s_bias_addr + (uint32_t)(j1.z * p.nt + n0) * 4u;
@@ -650,6 +674,7 @@ struct psob_layer {
   bool have_tmB = false;
   bool tma_store = false, vec4 = false, pair = false, strided = false;
   int pf_dist = 0, epi_groups = 2;
+  bool band = false;
   unsigned long long* prof = nullptr;
   int bias_off = -1, steps_off = -1, jobs_off = -1, chains_off = -1, tab_bytes = 0, stg_bufs = 0;
   int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, stg_off = 0, smem_bytes = 0;
@@ -773,8 +798,13 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
 #undef PSOB_CUDA_L
 
   // epilogue flavour: TMA store when every 64-column chunk is one contiguous, 16-byte aligned 128-byte row
-  l->tma_store = d->vec8 && d->nt % 64 == 0 && d->cc % 64 == 0 && d->out32_pitch == 0;
-  for (int c = 0; c < d->nt && l->tma_store; c += 64)
+  l->band = d->band_pitch != 0;
+  if (l->band && (d->band_pitch != kBandPitch || d->nt != 256 || d->cc != kBandPitch || d->out_pitch % 8 || d->in_tiled < 0 || d->out_tiled)) {
+    psob_layer_destroy(l);
+    return fail(PSOB_E_ARG, "psob_layer_create: an image-band layer has nt = 256, cc = band_pitch = %d and a row-major output", kBandPitch);
+  }
+  l->tma_store = l->band || (d->vec8 && d->nt % 64 == 0 && d->cc % 64 == 0 && d->out32_pitch == 0);
+  for (int c = 0; c < d->nt && l->tma_store && !l->band; c += 64)
     for (int i = 1; i < 64; ++i)
       if ((d->col_map[c] >= 0) != (d->col_map[c + i] >= 0) || (d->col_map[c] >= 0 && d->col_map[c + i] != d->col_map[c] + i)) l->tma_store = false;
   if (d->out_tiled) {
@@ -874,7 +904,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
   p.in_tiled = d.in_tiled; p.out_tiled = d.out_tiled; p.n_in_chunks = d.in_pitch / kKChunk; p.n_out_chunks = d.out_pitch / kKChunk;
-  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.pf_dist = l->pf_dist; p.epi_groups = l->epi_groups;
+  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.pf_dist = l->pf_dist; p.epi_groups = l->epi_groups; p.band = (l->band && p.y != nullptr) ? 1 : 0;
   if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);

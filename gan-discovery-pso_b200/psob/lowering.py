@@ -38,6 +38,7 @@ ROUND_WEIGHTS = True   # tests switch this off to check the geometry exactly in 
 # TMA-store epilogue (64-channel NHWC chunks).  PSOB_PAIR=0 falls back to streaming the weights per step.
 RESIDENT_SOLO = 32 * 1024
 RESIDENT_PAIR = 256 * 1024 if os.environ.get("PSOB_PAIR", "1") != "0" else 0
+IMAGE_BAND = os.environ.get("PSOB_BAND", "1") != "0"       # band form of the 14x14 -> 28x28 image layer
 CHAIN_ROWS = os.environ.get("PSOB_CHAIN", "1") != "0"      # share input rows between vertically adjacent jobs (resident layers)
 
 # image layouts
@@ -399,6 +400,92 @@ def lower_convt_k4s2p1(name, w, b, act, h, wd, *, m=1, image_out=False, in_cp=No
                 conn_x += 1
     return _finish(name, nt, nt, cc, act, h * wd * cpi, out_pitch, out32_pitch, tiles, resident, steps, jobs,
                    col_map, col_map32, bias, macs_exact=conn * conn_x * cin * cout, meta=meta, xops=xops, chains=chains)
+
+
+# ----------------------------------------------------------------------------------------------
+# (b') ConvTranspose2d(Cin <= 64 -> 1, k=4, s=2, p=1): 14 x 14 -> the 28 x 28 image, "band" form
+#      (last generator block, src/utils/util_dcgan.py:137-138).
+#
+#      One output channel makes N tiny (16 taps per input pixel) while every A tile still costs 16 KB of
+#      shared-memory ingest, so the 2x2-block form (b) is bound by re-reading input pixels (2.25x) and by 8-byte
+#      scattered image stores.  Here a job owns a BAND of 8 padded image rows as 8 x 30 accumulator columns
+#      (column = band_row * 30 + padded_x): the 4x4 output patch of an input pixel is a strided set of columns,
+#      so ONE MMA with a zero-padded, position-independent weight tile (N = 96: rows ky * 30 + kx carry
+#      w[:, ky, kx]) scatter-adds the whole patch -- the tensor core does the col2im overlap-add in TMEM.
+#      Every input pixel is loaded once per band it touches (238 loads instead of 441) and the band leaves as four
+#      128-byte-per-particle TMA stores (two padded image rows each).
+# ----------------------------------------------------------------------------------------------
+
+BAND_ROWS, BAND_PITCH, BAND_N = 8, 30, 96
+
+
+def lower_convt_image_band(name, w, b, act, in_cp=None) -> LayerProgram:
+    """w: [Cin, 1, 4, 4], b: [1].  Input NHWC [14, 14, Cp_in] -> bf16 padded image (IMG_PAD layout) and fp32 [784]."""
+    cin, cout = w.shape[0], w.shape[1]
+    assert cout == 1 and tuple(w.shape[2:]) == (4, 4)
+    h = wd = 14
+    cpi = in_cp or cpitch(cin)
+    nkc = rup(cin, KCHUNK) // KCHUNK
+    wp = np.zeros((nkc * KCHUNK, 4, 4), np.float32)
+    wp[:cin] = w[:, 0]
+    nt = 256
+    # weight tiles per K-chunk: full patch, top-cut (ky = 2, 3 land on band rows 0, 1), bottom-cut (ky = 0, 1 land on
+    # band rows 6, 7; stored two rows lower so that the 96-column window stays inside the band), and zeros
+    tiles, tile_of = [], {}
+    for kc in range(nkc):
+        wk = wp[kc * KCHUNK:(kc + 1) * KCHUNK]
+        full = np.zeros((BAND_N, KCHUNK), np.float32)
+        top = np.zeros((BAND_N, KCHUNK), np.float32)
+        bot = np.zeros((BAND_N, KCHUNK), np.float32)
+        for ky in range(4):
+            for kx in range(4):
+                full[ky * BAND_PITCH + kx] = wk[:, ky, kx]
+                if ky >= 2:
+                    top[(ky - 2) * BAND_PITCH + kx] = wk[:, ky, kx]
+                else:
+                    bot[(ky + 2) * BAND_PITCH + kx] = wk[:, ky, kx]
+        for key, t in (("full", full), ("top", top), ("bot", bot)):
+            tile_of[(key, kc)] = len(tiles)
+            tiles.append(t)
+    zero_row = len(tiles) * BAND_N
+    tiles.append(np.zeros((BAND_N, KCHUNK), np.float32))
+    steps, jobs, xops = [], [], {}
+    for band in range(4):
+        sb = len(steps)
+        for iy in range(4 * band - 1, 4 * band + 4):
+            if not 0 <= iy < h:
+                continue
+            r0 = 2 * iy - BAND_ROWS * band                  # band row of the patch's first row: -2, 0, 2, 4, 6
+            for ix in range(wd):
+                for kc in range(nkc):
+                    if r0 < 0:
+                        key, d_col = "top", 2 * ix
+                    elif r0 + 3 < BAND_ROWS:
+                        key, d_col = "full", r0 * BAND_PITCH + 2 * ix
+                    else:
+                        key, d_col = "bot", (r0 - 2) * BAND_PITCH + 2 * ix
+                    assert d_col + BAND_N <= nt
+                    op = (tile_of[(key, kc)] * BAND_N, d_col, STEP_ACCUM)
+                    if len(steps) == sb:
+                        # overlapping windows: no "first touch" per column, so the job's first step clears the band
+                        xops[len(steps)] = [(zero_row, 96, 0), (zero_row, 160, 0), op]
+                        steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, zero_row, 0, STEP_B_RESIDENT))
+                    else:
+                        steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, op[0], op[1], STEP_ACCUM | STEP_B_RESIDENT))
+        py0 = BAND_ROWS * band
+        lo, hi = _mask_words([1 <= py0 + r <= 28 for r in range(BAND_ROWS)])
+        jobs.append((sb, len(steps) - sb, py0 * IMG_PAD_PITCH, (py0 - 1) * 28, lo, hi, 0, 0))
+    col_map, col_map32 = [], []
+    for n in range(nt):
+        r, px = divmod(n, BAND_PITCH)
+        ok = r < BAND_ROWS and 1 <= px <= 28
+        col_map.append(r * IMG_PAD_PITCH + px if ok else -1)
+        col_map32.append(r * 28 + px - 1 if ok else -1)
+    bias = np.full(nt, float(np.asarray(b).reshape(-1)[0]), np.float32)
+    conn = sum(1 for o in range(28) for k in range(4) if (o + 1 - k) % 2 == 0 and 0 <= (o + 1 - k) // 2 < 14)
+    return _finish(name, BAND_N, nt, BAND_PITCH, act, h * wd * cpi, IMG_PAD_ROWS * IMG_PAD_PITCH, 28 * 28, tiles, True, steps, jobs,
+                   col_map, col_map32, bias, macs_exact=conn * conn * cin, xops=xops,
+                   meta=dict(kind="convt_image_band", out_hw=(28, 28), out_c=1, out_cp=1, band=(BAND_ROWS, BAND_PITCH)))
 
 
 # ----------------------------------------------------------------------------------------------

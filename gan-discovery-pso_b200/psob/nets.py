@@ -42,7 +42,10 @@ def generator_programs(sd: Dict, prefix: str = "gen", m_last: int = 2) -> List[L
     assert w1.shape[2] == 7 and w2.shape[2] == 4 and w3.shape[1] == 1, "28x28 single-channel generator expected"
     l1 = L.lower_convt_from_1x1("g.l1", w1, b1, L.ACT_RELU)
     l2 = L.lower_convt_k4s2p1("g.l2", w2, b2, L.ACT_RELU, 7, 7, m=1)
-    l3 = L.lower_convt_k4s2p1("g.l3", w3, b3, L.ACT_TANH, 14, 14, m=m_last, image_out=True)
+    if L.IMAGE_BAND and w3.shape[0] <= 64:
+        l3 = L.lower_convt_image_band("g.l3", w3, b3, L.ACT_TANH)
+    else:
+        l3 = L.lower_convt_k4s2p1("g.l3", w3, b3, L.ACT_TANH, 14, 14, m=m_last, image_out=True)
     assert l1.out_pitch == l2.in_pitch and l2.out_pitch == l3.in_pitch
     return [l1, l2, l3]
 

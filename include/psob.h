@@ -162,6 +162,8 @@ typedef struct {
   int32_t n_steps, n_jobs, n_wrows, n_bias_rows, n_chains;
   int32_t in_tiled, out_tiled; /* tile-major bf16 activations: [ceil(P/128)][pitch/64][128][64] (each 128-particle x
                                 * 64-column operand tile is one contiguous 16 KB block); 0 = row-major [P, pitch] */
+  int32_t band_pitch;          /* != 0: image-band layer (psob/lowering.py lower_convt_image_band): the job's accumulator is
+                                * 8 padded image rows x band_pitch columns; stored as four 64-element chunks (2 rows each) */
   const uint16_t* wpack;     /* HOST bf16 bits [n_wrows, 64] */
   const int32_t*  steps;     /* HOST [n_steps, 8]: a_col, meta, op0, op1, op2, op3, 0, 0.  One A tile (TMA load) feeds 1..4 MMA ops.
                               * meta: bits 0-2 op count, bit 3 weights resident, bit 4 some op targets the NEXT job of the chain.

@@ -49,7 +49,7 @@ def test_generator_full_size_geometry_and_macs(exact):
     np.testing.assert_allclose(img, ref, rtol=0, atol=5e-6)
     assert [p.macs_exact for p in progs] == [627200, 5537792, 186624]
     assert progs[1].macs_issued == 6422528                                   # nominal implicit-GEMM count
-    assert progs[1].mma_n == 256 and progs[0].mma_n == 256 and progs[2].mma_n == 16
+    assert progs[1].mma_n == 256 and progs[0].mma_n == 256 and progs[2].mma_n == (L.BAND_N if L.IMAGE_BAND else 16)
 
 
 def test_generator_bf16_pipeline_within_tolerance(golden):

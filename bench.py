@@ -199,7 +199,9 @@ def run_psob(args):
         stage_ms[name] = float(np.median([a.elapsed_time(b) for a, b in evs]))
 
     cur = sw.z
-    for layer, y, y32 in zip(gnet.layers, gnet.acts, gnet.acts32):
+    for i, (layer, y, y32) in enumerate(zip(gnet.layers, gnet.acts, gnet.acts32)):
+        if i == len(gnet.layers) - 1 and gnet.skip_f32 and y is not None:
+            y32 = None                      # exactly what the timed step runs: D-score fitness reads the bf16 image only
         timed(layer.prog.name, lambda l=layer, c=cur, y=y, y32=y32: l.run(c, P, y, y32))
         cur = y
     cur = gnet.image_padded_bf16()
@@ -215,8 +217,13 @@ def run_psob(args):
     pk = peaks()
     flops = 2.0 * progs[top].macs_exact * P
     achieved_tf = flops / (stage_ms[top] * 1e-3) / 1e12
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic_latest.json")       # dram read+write bytes per launch, from `ncu --set full`
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(top)
     roofline = {"kernel": f"pixel_gemm_umma_kernel[{top}]", "bound": "tensor", "achieved": achieved_tf, "peak": pk["tf_sustained"],
-                "unit": "TFLOP/s", "frac": achieved_tf / pk["tf_sustained"], "traffic": None, "peak_source": pk["source"],
+                "unit": "TFLOP/s", "frac": achieved_tf / pk["tf_sustained"], "traffic": traffic, "peak_source": pk["source"],
                 "algorithmic_flops_per_launch": flops, "ms_per_launch": stage_ms[top]}
     upd_bytes = 5.0 * D_LATENT * 4 * P
     upd_gbs = upd_bytes / (stage_ms["pso_update"] * 1e-3) / 1e9

@@ -62,6 +62,7 @@ struct EngineParams {
   int b_resident, n_wrows, n_bias_rows, n_steps;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4, strided, pf_dist;
+  int step_stride;           // int4 words per step in the shared-memory copy of the step table (1 when no step has > 2 ops)
   int band;                  // image-band epilogue (lower_convt_image_band): 4 chunks of two padded image rows each
   int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
   int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
@@ -196,7 +197,9 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   if (p.chains_off >= 0)
     for (int i = threadIdx.x; i < p.n_chains; i += kThreads) reinterpret_cast<int2*>(tab + p.chains_off)[i] = p.chains[i];
   if (p.steps_off >= 0)
-    for (int i = threadIdx.x; i < 2 * p.n_steps; i += kThreads) reinterpret_cast<int4*>(tab + p.steps_off)[i] = p.steps[i];
+    for (int i = threadIdx.x; i < p.step_stride * p.n_steps; i += kThreads)     // <= 2 ops per step: first word only (16 B)
+      reinterpret_cast<int4*>(tab + p.steps_off)[i] = p.step_stride == 2 ? p.steps[i] : p.steps[2 * i];
+  const int ss = p.steps_off >= 0 ? p.step_stride : 2;
   if (p.jobs_off >= 0)
     for (int i = threadIdx.x; i < 2 * p.n_jobs; i += kThreads) reinterpret_cast<int4*>(tab + p.jobs_off)[i] = p.jobs[i];
   for (int i = threadIdx.x; i < p.nt; i += kThreads) {
@@ -248,10 +251,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const int2 ch = chains[(uint32_t)item - (uint32_t)ptile * n_chains_u];
         for (int job = ch.x; job < ch.x + ch.y; ++job) {
           const int4 j0 = jobs[2 * job];
-          int4 st_next = steps[2 * j0.x];
+          int4 st_next = steps[ss * j0.x];
           for (int s = j0.x; s < j0.x + j0.y; ++s) {
             const int4 st = st_next;
-            if (s + 1 < j0.x + j0.y) st_next = steps[2 * (s + 1)];     // descriptor fetch overlaps the wait
+            if (s + 1 < j0.x + j0.y) st_next = steps[ss * (s + 1)];     // descriptor fetch overlaps the wait
             mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
             const bool res = (st.y & kMetaResident) != 0;
             if (ptx::elect_one()) {
@@ -288,7 +291,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       for (int job = ch.x; job < ch.x + ch.y; ++job, ++it) {
         const int4 j0 = jobs[2 * job];
         const uint32_t buf = it & 1u, use = it >> 1;
-        int4 st_next = steps[2 * j0.x];
+        int4 st_next = steps[ss * j0.x];
         if (!next_acquired) {
           if (kPair) {                                                              // arrivals come from both CTAs
             const long long t0 = prof ? clock64() : 0;
@@ -304,8 +307,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           const int4 st = st_next;
           const int n_ops = st.y & kMetaOpsMask;
           int4 st2 = make_int4(0, 0, 0, 0);
-          if (n_ops > 2) st2 = steps[2 * s + 1];
-          if (s + 1 < j0.x + j0.y) st_next = steps[2 * (s + 1)];
+          if (n_ops > 2) st2 = steps[ss * s + 1];
+          if (s + 1 < j0.x + j0.y) st_next = steps[ss * (s + 1)];
           if ((st.y & kMetaHasNext) && !next_acquired) {
             // this A tile also feeds the NEXT job of the chain: its accumulator buffer (the other one) must be drained
             const uint32_t nuse = (it + 1u) >> 1;
@@ -673,7 +676,7 @@ struct psob_layer {
   CUtensorMap tmB;
   bool have_tmB = false;
   bool tma_store = false, vec4 = false, pair = false, strided = false;
-  int pf_dist = 0, epi_groups = 2;
+  int pf_dist = 0, epi_groups = 2, step_stride = 2;
   bool band = false;
   unsigned long long* prof = nullptr;
   int bias_off = -1, steps_off = -1, jobs_off = -1, chains_off = -1, tab_bytes = 0, stg_bufs = 0;
@@ -841,7 +844,9 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   if (d->n_bias_rows <= kMaxBiasRowsSmem) { l->bias_off = tab; tab += d->n_bias_rows * d->nt * 4; }
   tab = (tab + 15) & ~15;
   if (d->n_chains <= kMaxJobsSmem) { l->chains_off = tab; tab += (d->n_chains * 8 + 15) & ~15; }
-  if (d->n_steps <= kMaxStepsSmem) { l->steps_off = tab; tab += d->n_steps * 32; }
+  l->step_stride = 1;
+  for (int s = 0; s < d->n_steps; ++s) if ((d->steps[8 * s + 1] & kMetaOpsMask) > 2) l->step_stride = 2;
+  if (d->n_steps <= kMaxStepsSmem) { l->steps_off = tab; tab += d->n_steps * 16 * l->step_stride; }
   if (d->n_jobs <= kMaxJobsSmem) { l->jobs_off = tab; tab += d->n_jobs * 32; }
   l->tab_bytes = (tab + 127) & ~127;
   // staging tiles for the TMA-store epilogue: 2 per group if that still leaves a 3-stage ring
@@ -904,7 +909,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
   p.in_tiled = d.in_tiled; p.out_tiled = d.out_tiled; p.n_in_chunks = d.in_pitch / kKChunk; p.n_out_chunks = d.out_pitch / kKChunk;
-  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.pf_dist = l->pf_dist; p.epi_groups = l->epi_groups; p.band = (l->band && p.y != nullptr) ? 1 : 0;
+  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.pf_dist = l->pf_dist; p.epi_groups = l->epi_groups; p.step_stride = l->step_stride; p.band = (l->band && p.y != nullptr) ? 1 : 0;
   if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);

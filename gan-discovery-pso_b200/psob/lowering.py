@@ -40,6 +40,7 @@ RESIDENT_SOLO = 32 * 1024
 RESIDENT_PAIR = 256 * 1024 if os.environ.get("PSOB_PAIR", "1") != "0" else 0
 IMAGE_BAND = os.environ.get("PSOB_BAND", "1") != "0"       # band form of the 14x14 -> 28x28 image layer
 CHAIN_ROWS = os.environ.get("PSOB_CHAIN", "1") != "0"      # share input rows between vertically adjacent jobs (resident layers)
+CHAIN_CONVT = os.environ.get("PSOB_CHAIN_CONVT", "0") != "0"   # ... also for the transposed convs (measured slower, see below)
 
 # image layouts
 IMG_PAD_ROWS, IMG_PAD_PITCH = 31, 32          # bf16 padded 28x28 image: real (y,x) at (y+1,x+1)
@@ -310,7 +311,10 @@ def lower_convt_k4s2p1(name, w, b, act, h, wd, *, m=1, image_out=False, in_cp=No
     resident = wbytes <= RESIDENT_SOLO or (wbytes <= RESIDENT_PAIR and not image_out and cc % 64 == 0 and nt % 64 == 0)
     steps, jobs = [], []
     xops, chains = {}, None
-    chained = resident and CHAIN_ROWS and m == 1 and wbytes > RESIDENT_SOLO and h >= 2
+    # measured on B200 (profiles/r01_roles_v4*.log): chaining the 7x7 -> 14x14 layer halves its A loads but costs
+    # 25 % more cycles (two N = 256 ops per step alternate between both accumulator buffers and the epilogue loses
+    # its overlap), so it stays off by default for transposed convs; PSOB_CHAIN_CONVT=1 switches it on
+    chained = resident and CHAIN_ROWS and CHAIN_CONVT and m == 1 and wbytes > RESIDENT_SOLO and h >= 2
     if chained:
         # Vertically adjacent blocks share an input row (block bq reads rows bq and bq+1): the blocks of one block
         # column form a chain; every input row is loaded once per chain and feeds this block with the a = 1 taps and,

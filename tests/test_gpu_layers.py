@@ -185,6 +185,7 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
         monkeypatch.setenv("PSOB_STRIDED", str(strided))
         monkeypatch.setattr(L, "RESIDENT_PAIR", 256 * 1024 if pair else 0)
         monkeypatch.setattr(L, "CHAIN_ROWS", bool(chain))
+        monkeypatch.setattr(L, "CHAIN_CONVT", bool(chain))
         gnet = engine.GeneratorNet(gen.state_dict(), P)
         dnet = engine.DiscriminatorNet(disc.state_dict(), P)
         assert any(l.out_tiled for l in gnet.layers) == bool(tiled)

@@ -133,6 +133,53 @@ mixed_kernel(const __grid_constant__ CUtensorMap tl, const __grid_constant__ CUt
   }
 }
 
+// 1-D bulk copies (no tensor map): contiguous `bytes` per op.  mode 0: loads through an S-stage ring, mode 1: stores, 2 buffers
+__global__ void __launch_bounds__(64, 1)
+bulk1d_kernel(const uint8_t* g, int n_ops, int stages, int bytes, int mode, int same, unsigned long long* cycles) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bars = base + (uint32_t)stages * (uint32_t)bytes;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) { ptx::mbar_init(bars + 8u * s, 1); ptx::mbar_init(bars + 8u * (32 + s), 1); }
+    ptx::fence_barrier_init();
+  }
+  __syncthreads();
+  const long long t0 = clock64();
+  const unsigned long long span = (3ull << 30);
+  if (mode == 0) {
+    if (threadIdx.x == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int k = 0; k < n_ops; ++k) {
+        ptx::mbar_wait(bars + 8u * (32 + stage), phase ^ 1u);
+        ptx::mbar_arrive_expect_tx(bars + 8u * stage, (uint32_t)bytes);
+        const uint8_t* src = g + (same ? 0ull : ((unsigned long long)(blockIdx.x * n_ops + k) * (unsigned long long)bytes) % span);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(base + (uint32_t)stage * (uint32_t)bytes), "l"(src), "r"((uint32_t)bytes), "r"(bars + 8u * stage) : "memory");
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
+      }
+    } else if (threadIdx.x == 32) {
+      int stage = 0; uint32_t phase = 0;
+      for (int k = 0; k < n_ops; ++k) {
+        ptx::mbar_wait(bars + 8u * stage, phase);
+        ptx::mbar_arrive(bars + 8u * (32 + stage));
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
+      }
+      cycles[blockIdx.x] = (unsigned long long)(clock64() - t0);
+    }
+  } else if (threadIdx.x == 0) {
+    for (int k = 0; k < n_ops; ++k) {
+      ptx::bulk_wait_read1();
+      uint8_t* dst = const_cast<uint8_t*>(g) + ((unsigned long long)(blockIdx.x * n_ops + k) * (unsigned long long)bytes) % span;
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                   ::"l"(dst), "r"(base + (uint32_t)(k & 1) * (uint32_t)bytes), "r"((uint32_t)bytes) : "memory");
+      ptx::bulk_commit();
+    }
+    ptx::bulk_wait_all0();
+    cycles[blockIdx.x] = (unsigned long long)(clock64() - t0);
+  }
+}
+
 int main() {
   void* sym = nullptr;
   cudaDriverEntryPointQueryResult q;
@@ -184,6 +231,31 @@ int main() {
       store_kernel<<<sms, 32, smem>>>(t2, n, bufs, box_rows, 2, 98, cyc);
       snprintf(name, sizeof name, "store box %3dx128B bufs %d    DRAM stream, rows 12544 B apart (row-major)", box_rows, bufs); report(name, box_rows);
     }
+  }
+  cudaFuncSetAttribute(bulk1d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+  for (int g : {19, 148}) {
+    for (int kb : {16, 32, 64}) {
+      const int bytes1 = kb * 1024, stages = kb == 64 ? 3 : 4;
+      auto run = [&](int mode, int same, const char* what) {
+        bulk1d_kernel<<<g, 64, stages * bytes1 + 2048>>>((const uint8_t*)buf, n, stages, bytes1, mode, same, cyc);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("bulk1d: %s\n", cudaGetErrorString(e)); exit(1); }
+        cudaMemcpy(h.data(), cyc, sizeof(unsigned long long) * g, cudaMemcpyDeviceToHost);
+        double mean = 0; for (int i = 0; i < g; ++i) mean += (double)h[i]; mean /= g;
+        printf("bulk1d %-28s %2d KB/op %3d CTAs: %7.1f cycles/op %6.1f B/clk/SM\n", what, kb, g, mean / n, (double)n * bytes1 / mean);
+      };
+      run(0, 1, "load, same block (L2 hit)");
+      run(0, 0, "load, DRAM stream");
+      run(1, 0, "store, DRAM stream");
+    }
+  }
+  for (int g : {19, 148}) {
+    CUtensorMap t0 = make_map(buf, 64, 1 << 25, 64, 256);
+    store_kernel<<<g, 32, 2 * 32768 + 2048>>>(t0, n, 2, 256, 1, 1, cyc);
+    cudaDeviceSynchronize();
+    cudaMemcpy(h.data(), cyc, sizeof(unsigned long long) * g, cudaMemcpyDeviceToHost);
+    double mean = 0; for (int i = 0; i < g; ++i) mean += (double)h[i]; mean /= g;
+    printf("tensor store box 256x128B bufs 2, DRAM stream, %3d CTAs: %7.1f cycles/op %6.1f B/clk/SM\n", g, mean / n, (double)n * 32768 / mean);
   }
   // fewer SMs storing: is ~26 B/clk/SM a per-SM limit or the shared HBM limit?
   for (int g : {19, 37, 74, 148}) {

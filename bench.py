@@ -23,6 +23,10 @@ for _p in (ROOT, os.path.join(ROOT, "gan-discovery-pso_b200")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
+# rank 0 prints exactly one JSON line on stdout: keep NCCL's version banner (NCCL_DEBUG=VERSION on some boxes) off it
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
+
 import numpy as np
 import torch
 
@@ -243,22 +247,54 @@ def run_psob(args):
     h_fit = torch.empty(P, dtype=torch.float32).pin_memory()
     h_best = torch.empty(D_LATENT + 1, dtype=torch.float32).pin_memory()
 
-    def e2e_step():
-        sw.pos.copy_(h_pos, non_blocking=True)
-        sw.vel.copy_(h_vel, non_blocking=True)
-        engine.pack_latent(sw.pos, sw.z)
-        sw.step()
-        h_fit.copy_(sw.fit, non_blocking=True)
-        h_best[:D_LATENT].copy_(sw.gbest_pos, non_blocking=True)
-        h_best[D_LATENT:].copy_(sw.gbest_val, non_blocking=True)
+    # Two device staging buffers and a copy stream: the upload of step k+1's inputs and the read-back of step k's
+    # results overlap step k's / k+1's kernels (every step still moves all of its bytes inside the timed region).
+    cs = torch.cuda.Stream(device=dev)
+    stage_pos = [torch.empty_like(sw.pos) for _ in range(2)]
+    stage_vel = [torch.empty_like(sw.vel) for _ in range(2)]
+    ev_h2d = [torch.cuda.Event() for _ in range(2)]
+    ev_free = [torch.cuda.Event() for _ in range(2)]
+    ev_done, ev_d2h = torch.cuda.Event(), torch.cuda.Event()
 
-    for _ in range(max(3, args.warmup)):
-        e2e_step()
+    def upload(k):
+        with torch.cuda.stream(cs):
+            cs.wait_event(ev_free[k % 2])
+            stage_pos[k % 2][:, :D_LATENT].copy_(h_pos, non_blocking=True)
+            stage_vel[k % 2][:, :D_LATENT].copy_(h_vel, non_blocking=True)
+            ev_h2d[k % 2].record(cs)
+
+    def e2e_run(n):
+        main = torch.cuda.current_stream()
+        for e in ev_free:
+            e.record(main)
+        ev_d2h.record(main)
+        upload(0)
+        for k in range(n):
+            main.wait_event(ev_h2d[k % 2])
+            sw.pos.copy_(stage_pos[k % 2])
+            sw.vel.copy_(stage_vel[k % 2])
+            ev_free[k % 2].record(main)
+            if k + 1 < n:
+                upload(k + 1)
+            engine.pack_latent(sw.pos, sw.z)
+            main.wait_event(ev_d2h)                 # the previous step's results have left sw.fit / gbest
+            sw.step()
+            ev_done.record(main)
+            with torch.cuda.stream(cs):
+                cs.wait_event(ev_done)
+                h_fit.copy_(sw.fit, non_blocking=True)
+                h_best[:D_LATENT].copy_(sw.gbest_pos[:D_LATENT], non_blocking=True)
+                h_best[D_LATENT:].copy_(sw.gbest_val, non_blocking=True)
+                ev_d2h.record(cs)
+        main.wait_event(ev_d2h)
+
+    for t in stage_pos + stage_vel:
+        t.zero_()
+    e2e_run(max(3, args.warmup))
     barrier()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    for _ in range(args.steps):
-        e2e_step()
+    e2e_run(args.steps)
     b.record()
     barrier()
     e2e_ms = torch.tensor([a.elapsed_time(b)], device=dev)

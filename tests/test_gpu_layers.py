@@ -200,3 +200,27 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
     for key, got in results.items():
         for i, (a, b) in enumerate(zip(base, got)):
             assert torch.equal(a, b), f"mode (tiled, pair, strided, chain)={key}: tensor {i} differs"
+
+
+def test_g256_generator_small_widths_vs_reference(mods):
+    """EXTENSION generator 1x256x256 (BASELINE config 4 shape; port.G256) at reduced widths (128..4 channels): seven
+    layers, streamed weights, chunked bias rows, fp32 image [P, 65536]; tcgen05 == SIMT interpreter and both within the
+    image tolerance of the fp32 torch module."""
+    engine, L, nets, ffi = mods
+    torch.manual_seed(5)
+    g = port.G256(z_dim=10, channels_img=1, features_g=4).eval()
+    port.randomize_bn_stats(g, torch.Generator().manual_seed(6))
+    P = 130
+    z = torch.randn(P, 10, generator=torch.Generator().manual_seed(7))
+    with torch.no_grad():
+        ref = g(z.view(P, 10, 1, 1)).reshape(P, -1).numpy()
+    res = {}
+    for impl in (ffi.IMPL_SIMT, ffi.IMPL_TCGEN05):
+        net = engine.GeneratorNet(g.state_dict(), P, impl=impl)
+        assert len(net.layers) == 7 and net.image_elems == 256 * 256
+        _, img = net.forward(_rows(z.numpy(), net.in_pitch))
+        res[impl] = img.cpu().numpy()
+    np.testing.assert_allclose(res[ffi.IMPL_SIMT], res[ffi.IMPL_TCGEN05], atol=2e-3, rtol=0)
+    got = res[ffi.IMPL_TCGEN05]
+    assert np.abs(got - ref).max() <= IMG_TOL
+    assert np.linalg.norm(got - ref) / np.linalg.norm(ref) <= REL_TOL

@@ -67,7 +67,7 @@ struct EngineParams {
   int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
   int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
   int bias_off, steps_off, jobs_off, chains_off, stg_bufs;   // SMEM table offsets from the table base (-1: stays in global)
-  unsigned long long* prof;   // optional [gridDim][16] role wait-cycle counters (debug)
+  unsigned long long* prof;   // optional [gridDim][32] role wait-cycle counters (debug)
   uint32_t idesc, tmem_cols;
 };
 
@@ -118,6 +118,31 @@ __global__ void __launch_bounds__(kMaxThreads, 1)
 pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmY, const EngineParams p) {
   extern __shared__ uint8_t smem_raw[];
+  // Hot scalar parameters in registers: the kernel parameters live in constant memory, and every asm volatile with a
+  // "memory" clobber (mbarrier, TMA, tcgen05 wrappers) makes the compiler re-load whatever it needs next from there --
+  // ncu showed LDCU -> short-scoreboard chains of ~400 cycles in the head of every epilogue chunk.
+  const int q_n_stages = p.n_stages;
+  const int q_stage_bytes = p.stage_bytes;
+  const int q_res_off = p.res_off;
+  const int q_nt = p.nt;
+  const int q_mma_n = p.mma_n;
+  const int q_epi_groups = p.epi_groups;
+  const int q_stg_bufs = p.stg_bufs;
+  const int q_band = p.band;
+  const int q_in_tiled = p.in_tiled;
+  const int q_out_tiled = p.out_tiled;
+  const int q_n_in_chunks = p.n_in_chunks;
+  const int q_n_out_chunks = p.n_out_chunks;
+  const uint32_t q_idesc = p.idesc;
+  const int q_strided = p.strided;
+  const int q_n_chains = p.n_chains;
+  const int q_b_resident = p.b_resident;
+  const long long q_P = p.P;
+  const int q_out32_pitch = p.out32_pitch;
+  const int q_out_pitch = p.out_pitch;
+  const int q_vec4 = p.vec4;
+  const int q_cc = p.cc;
+  const long long q_n_items = p.n_items;
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (base - raw);
@@ -132,7 +157,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int kThreads = (int)blockDim.x;
-  const int kTmaWarp = 4 * p.epi_groups, kMmaWarp = kTmaWarp + 1;
+  const int kTmaWarp = 4 * q_epi_groups, kMmaWarp = kTmaWarp + 1;
   const uint32_t crank = kPair ? ptx::cluster_ctarank() : 0u;
   const bool leader = crank == 0u;
   // Contiguous item ranges: a CTA (or CTA pair) walks the jobs of one particle tile in order, so the input
@@ -142,30 +167,30 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   // Item order.  strided: worker w takes items w, w + W, w + 2W, ... so that at any moment all workers sit on
   // neighbouring jobs of the same one or two particle tiles (re-reads of shared input pixels hit L2);
   // contiguous: every worker walks its own particle tiles (no sharing between workers).
-  const long long per_cta = (p.n_items + n_workers - 1) / n_workers;
-  const long long item_begin = p.strided ? worker : (per_cta * worker < p.n_items ? per_cta * worker : p.n_items);
-  const long long item_end = p.strided ? p.n_items : (item_begin + per_cta < p.n_items ? item_begin + per_cta : p.n_items);
-  const long long item_step = p.strided ? n_workers : 1;
-  const uint32_t n_chains_u = (uint32_t)p.n_chains;
+  const long long per_cta = (q_n_items + n_workers - 1) / n_workers;
+  const long long item_begin = q_strided ? worker : (per_cta * worker < q_n_items ? per_cta * worker : q_n_items);
+  const long long item_end = q_strided ? q_n_items : (item_begin + per_cta < q_n_items ? item_begin + per_cta : q_n_items);
+  const long long item_step = q_strided ? n_workers : 1;
+  const uint32_t n_chains_u = (uint32_t)q_n_chains;
   // particle-tile index of this CTA for TMA coordinates: pair tile t covers tiles 2t (leader) and 2t+1
   auto tile_idx = [&](int ptile) { return kPair ? 2 * ptile + (int)crank : ptile; };
   auto tile_row = [&](int ptile) { return tile_idx(ptile) * kTileM; };
   // TMA coordinates of the 64-column chunk starting at column `col` of particle tile `ptile`.  Tile-major
   // activations keep every [128 particles x 64 channels] operand tile in ONE contiguous 16 KB block (whole
   // DRAM pages per access); in the row-major layout the same tile is 128 rows of 128 B, one DRAM page each.
-  auto in_c0 = [&](int col) { return p.in_tiled ? 0 : col; };
-  auto in_c1 = [&](int ptile, int col) { return p.in_tiled ? (tile_idx(ptile) * p.n_in_chunks + (col >> 6)) * kTileM : tile_row(ptile); };
-  auto out_c0 = [&](int col) { return p.out_tiled ? 0 : col; };
-  auto out_c1 = [&](int ptile, int col) { return p.out_tiled ? (tile_idx(ptile) * p.n_out_chunks + (col >> 6)) * kTileM : tile_row(ptile); };
+  auto in_c0 = [&](int col) { return q_in_tiled ? 0 : col; };
+  auto in_c1 = [&](int ptile, int col) { return q_in_tiled ? (tile_idx(ptile) * q_n_in_chunks + (col >> 6)) * kTileM : tile_row(ptile); };
+  auto out_c0 = [&](int col) { return q_out_tiled ? 0 : col; };
+  auto out_c1 = [&](int ptile, int col) { return q_out_tiled ? (tile_idx(ptile) * q_n_out_chunks + (col >> 6)) * kTileM : tile_row(ptile); };
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.n_stages; ++s) {
+    for (int s = 0; s < q_n_stages; ++s) {
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
     }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(tfull_bar(b), 1);
-      ptx::mbar_init(tempty_bar(b), (kTmaStore ? 4 * p.epi_groups : 4) * (kPair ? 2 : 1));   // pair: both CTAs' epilogue warps
+      ptx::mbar_init(tempty_bar(b), (kTmaStore ? 4 * q_epi_groups : 4) * (kPair ? 2 : 1));   // pair: both CTAs' epilogue warps
     }
     ptx::mbar_init(res_bar, 1);
     ptx::fence_barrier_init();
@@ -195,21 +220,21 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const int4* jobs = p.jobs_off >= 0 ? reinterpret_cast<const int4*>(tab + p.jobs_off) : p.jobs;
   const int2* chains = p.chains_off >= 0 ? reinterpret_cast<const int2*>(tab + p.chains_off) : p.chains;
   if (p.chains_off >= 0)
-    for (int i = threadIdx.x; i < p.n_chains; i += kThreads) reinterpret_cast<int2*>(tab + p.chains_off)[i] = p.chains[i];
+    for (int i = threadIdx.x; i < q_n_chains; i += kThreads) reinterpret_cast<int2*>(tab + p.chains_off)[i] = p.chains[i];
   if (p.steps_off >= 0)
     for (int i = threadIdx.x; i < p.step_stride * p.n_steps; i += kThreads)     // <= 2 ops per step: first word only (16 B)
       reinterpret_cast<int4*>(tab + p.steps_off)[i] = p.step_stride == 2 ? p.steps[i] : p.steps[2 * i];
   const int ss = p.steps_off >= 0 ? p.step_stride : 2;
   if (p.jobs_off >= 0)
     for (int i = threadIdx.x; i < 2 * p.n_jobs; i += kThreads) reinterpret_cast<int4*>(tab + p.jobs_off)[i] = p.jobs[i];
-  for (int i = threadIdx.x; i < p.nt; i += kThreads) {
+  for (int i = threadIdx.x; i < q_nt; i += kThreads) {
     s_cm[i] = p.col_map[i];
     s_cm32[i] = p.col_map32[i];
-    int px = i / p.cc;
+    int px = i / q_cc;
     s_pix[i] = (uint8_t)(px < 64 ? px : 64);
   }
   if (bias_in_smem)
-    for (int i = threadIdx.x; i < p.n_bias_rows * p.nt; i += kThreads) s_bias[i] = p.bias[i];
+    for (int i = threadIdx.x; i < p.n_bias_rows * q_nt; i += kThreads) s_bias[i] = p.bias[i];
   ptx::tc_fence_before();
   if (kPair) ptx::cluster_sync_all(); else __syncthreads();     // pair: the peer's barriers are initialised too
   ptx::tc_fence_after();
@@ -220,10 +245,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     // MMAs read both halves, so nobody starts before both CTAs have seen their loads complete
     if (warp == kTmaWarp) {
       if (ptx::elect_one()) {
-        const int half = p.mma_n >> 1;
+        const int half = q_mma_n >> 1;
         ptx::mbar_arrive_expect_tx(res_bar, (uint32_t)p.n_wrows * 64u);
-        for (int r = 0; r < p.n_wrows; r += p.mma_n)
-          ptx::tma_load_2d(base + p.res_off + (uint32_t)r * 64u, &tmB, 0, r + (int)crank * half, res_bar);
+        for (int r = 0; r < p.n_wrows; r += q_mma_n)
+          ptx::tma_load_2d(base + q_res_off + (uint32_t)r * 64u, &tmB, 0, r + (int)crank * half, res_bar);
       }
       __syncwarp();
     }
@@ -234,10 +259,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   if (warp == kTmaWarp) {
     // ------------------------------------------------------------------ TMA producer
     {
-      if (!kPair && p.b_resident && ptx::elect_one()) {
+      if (!kPair && q_b_resident && ptx::elect_one()) {
         ptx::mbar_arrive_expect_tx(res_bar, (uint32_t)p.n_wrows * 128u);
-        for (int r = 0; r < p.n_wrows; r += p.mma_n)
-          ptx::tma_load_2d(base + p.res_off + (uint32_t)r * 128u, &tmB, 0, r, res_bar);
+        for (int r = 0; r < p.n_wrows; r += q_mma_n)
+          ptx::tma_load_2d(base + q_res_off + (uint32_t)r * 128u, &tmB, 0, r, res_bar);
       }
       __syncwarp();
       const uint32_t full0_leader = kPair ? ptx::map_to_cta(full_bar(0), 0u) : 0u;
@@ -258,27 +283,27 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
             const bool res = (st.y & kMetaResident) != 0;
             if (ptx::elect_one()) {
-              const uint32_t a_dst = base + (uint32_t)stage * p.stage_bytes;
+              const uint32_t a_dst = base + (uint32_t)stage * q_stage_bytes;
               if (kPair) {
                 // both CTAs' A tiles are counted on the leader's barrier (the leader issues the pair MMA)
                 if (leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2u * (uint32_t)kATileBytes);
                 ptx::tma_load_2d_pair(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full0_leader + 8u * (uint32_t)stage);
               } else {
-                ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)p.mma_n * 128u));
+                ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)q_mma_n * 128u));
                 ptx::tma_load_2d(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full_bar(stage));
                 if (!res) ptx::tma_load_2d(a_dst + kATileBytes, &tmB, 0, op_b_row(st.z), full_bar(stage));
               }
             }
             __syncwarp();
-            if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
+            if (++stage == q_n_stages) { stage = 0; phase ^= 1u; }
           }
         }
       }
-      if (prof && lane == 0) { p.prof[blockIdx.x * 16 + 0] = w_empty; p.prof[blockIdx.x * 16 + 1] = (unsigned long long)(clock64() - t_start); }
+      if (prof && lane == 0) { p.prof[blockIdx.x * 32 + 0] = w_empty; p.prof[blockIdx.x * 32 + 1] = (unsigned long long)(clock64() - t_start); }
     }
   } else if (warp == kMmaWarp && leader) {
     // ------------------------------------------------------------------ MMA issuer (pair: leader CTA only)
-    if (!kPair && p.b_resident) ptx::mbar_wait(res_bar, 0);
+    if (!kPair && q_b_resident) ptx::mbar_wait(res_bar, 0);
     int stage = 0;
     uint32_t phase = 0;
     uint32_t it = 0;
@@ -319,19 +344,19 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           mbar_wait_t(full_bar(stage), phase, prof, w_full);
           ptx::tc_fence_after();
           if (ptx::elect_one()) {
-            const uint32_t a_addr = base + (uint32_t)stage * p.stage_bytes;
+            const uint32_t a_addr = base + (uint32_t)stage * q_stage_bytes;
             const uint64_t adesc = ptx::smem_desc_sw128(a_addr);
             const bool res = (st.y & kMetaResident) != 0;
             auto b_addr_of = [&](int op) {
-              return kPair ? base + p.res_off + (uint32_t)op_b_row(op) * 64u
-                           : (res ? base + p.res_off + (uint32_t)op_b_row(op) * 128u : a_addr + kATileBytes);
+              return kPair ? base + q_res_off + (uint32_t)op_b_row(op) * 64u
+                           : (res ? base + q_res_off + (uint32_t)op_b_row(op) * 128u : a_addr + kATileBytes);
             };
-            auto d_of = [&](int op) { return tmem_base + (buf ^ (uint32_t)op_next(op)) * (uint32_t)p.nt + (uint32_t)op_d_col(op); };
+            auto d_of = [&](int op) { return tmem_base + (buf ^ (uint32_t)op_next(op)) * (uint32_t)q_nt + (uint32_t)op_d_col(op); };
             if (n_ops == 1) {
               // 4 x (K = 16) with +32 B descriptor advances inside the 128 B swizzle row, then commit -> stage free
               const uint64_t bdesc = ptx::smem_desc_sw128(b_addr_of(st.z));
-              if (kPair) ptx::umma_bf16_k64_commit_pair(d_of(st.z), adesc, bdesc, p.idesc, (uint32_t)op_acc(st.z), empty_bar(stage));
-              else ptx::umma_bf16_k64_commit(d_of(st.z), adesc, bdesc, p.idesc, (uint32_t)op_acc(st.z), empty_bar(stage));
+              if (kPair) ptx::umma_bf16_k64_commit_pair(d_of(st.z), adesc, bdesc, q_idesc, (uint32_t)op_acc(st.z), empty_bar(stage));
+              else ptx::umma_bf16_k64_commit(d_of(st.z), adesc, bdesc, q_idesc, (uint32_t)op_acc(st.z), empty_bar(stage));
             } else {
               // one A tile, several weight tiles: own / next job's accumulators (resident weights only)
               const int ops[4] = {st.z, n_ops > 1 ? st.w : st.z, n_ops > 2 ? st2.x : st.z, n_ops > 3 ? st2.y : st.z};
@@ -341,20 +366,20 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               for (int o = 0; o < 4; ++o) {
                 dd[o] = d_of(ops[o]); aa[o] = (uint32_t)op_acc(ops[o]); bb[o] = ptx::smem_desc_sw128(b_addr_of(ops[o]));
               }
-              if (kPair) ptx::umma_bf16_k64x4_commit_pair(dd, adesc, bb, p.idesc, aa, n_ops, empty_bar(stage));
-              else ptx::umma_bf16_k64x4_commit(dd, adesc, bb, p.idesc, aa, n_ops, empty_bar(stage));
+              if (kPair) ptx::umma_bf16_k64x4_commit_pair(dd, adesc, bb, q_idesc, aa, n_ops, empty_bar(stage));
+              else ptx::umma_bf16_k64x4_commit(dd, adesc, bb, q_idesc, aa, n_ops, empty_bar(stage));
             }
           }
           __syncwarp();
-          if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
+          if (++stage == q_n_stages) { stage = 0; phase ^= 1u; }
         }
         if (ptx::elect_one()) { if (kPair) ptx::umma_commit_pair(tfull_bar(buf)); else ptx::umma_commit(tfull_bar(buf)); }
         __syncwarp();
       }
     }
     if (prof && lane == 0) {
-      p.prof[blockIdx.x * 16 + 2] = w_full; p.prof[blockIdx.x * 16 + 3] = w_tempty;
-      p.prof[blockIdx.x * 16 + 4] = (unsigned long long)(clock64() - t_start);
+      p.prof[blockIdx.x * 32 + 2] = w_full; p.prof[blockIdx.x * 32 + 3] = w_tempty;
+      p.prof[blockIdx.x * 32 + 4] = (unsigned long long)(clock64() - t_start);
     }
   } else if (warp < kTmaWarp) {
     // ------------------------------------------------------------------ epilogue
@@ -367,7 +392,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const int grp = warp >> 2;
     const int row = q * 32 + lane;
     const bool issuer_warp = (warp & 3) == 0;          // its elected lane issues / tracks the group's TMA stores
-    const uint32_t sbuf0 = base + p.stg_off + (uint32_t)(grp * p.stg_bufs) * kATileBytes;
+    const uint32_t sbuf0 = base + p.stg_off + (uint32_t)(grp * q_stg_bufs) * kATileBytes;
     uint32_t sflip = 0;                       // staging tile in use (double-buffered when stg_bufs == 2)
     const uint32_t sw = (uint32_t)(row & 7);
     uint32_t it = 0;
@@ -375,7 +400,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     unsigned long long w_tfull = 0, e_ld = 0, e_free = 0, e_math = 0, e_pub = 0;
     long long tq = 0;
     const long long t_start = clock64();
-    if (kTmaStore ? grp < p.epi_groups : grp == 0) {
+    if (kTmaStore ? grp < q_epi_groups : grp == 0) {
       for (long long item = item_begin; item < item_end; item += item_step) {
         const int ptile = (int)((uint32_t)item / n_chains_u);
         const int2 chn = chains[(uint32_t)item - (uint32_t)ptile * n_chains_u];
@@ -383,26 +408,26 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const int4 j0 = jobs[2 * job];
         const int4 j1 = jobs[2 * job + 1];
         const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
-        const float* bias = bias_in_smem ? s_bias + j1.z * p.nt : p.bias + (size_t)j1.z * p.nt;
+        const float* bias = bias_in_smem ? s_bias + j1.z * q_nt : p.bias + (size_t)j1.z * q_nt;
         const uint32_t buf = it & 1u, use = it >> 1;
         mbar_wait_t(tfull_bar(buf), use & 1u, prof, w_tfull);
         ptx::tc_fence_after();
-        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)p.nt;
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)q_nt;
         if (kTmaStore) {
-          const int n_chunks = p.nt >> 6;
+          const int n_chunks = q_nt >> 6;
           int last = -1;                      // last chunk this group will read: release TMEM right after it
-          for (int ch = grp; ch < n_chunks; ch += p.epi_groups)
-            if (p.band || (s_cm[ch << 6] >= 0 && ((mask >> s_pix[ch << 6]) & 1ull))) last = ch;
+          for (int ch = grp; ch < n_chunks; ch += q_epi_groups)
+            if (q_band || (s_cm[ch << 6] >= 0 && ((mask >> s_pix[ch << 6]) & 1ull))) last = ch;
           if (last < 0) {
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) release_tmem(buf);
           }
-          for (int ch = grp; ch < n_chunks; ch += p.epi_groups) {
+          for (int ch = grp; ch < n_chunks; ch += q_epi_groups) {
             // image band: chunk ch = padded image rows 2ch, 2ch+1 of the band = accumulator columns [60 ch, 60 ch + 60)
-            const int n0 = p.band ? ch * 2 * kBandPitch : ch << 6;
-            const int cm = p.band ? ch << 6 : s_cm[n0];
-            if (!p.band && (cm < 0 || !((mask >> s_pix[n0]) & 1ull))) continue;       // uniform over the group
+            const int n0 = q_band ? ch * 2 * kBandPitch : ch << 6;
+            const int cm = q_band ? ch << 6 : s_cm[n0];
+            if (!q_band && (cm < 0 || !((mask >> s_pix[n0]) & 1ull))) continue;       // uniform over the group
             uint32_t v[64];
             __syncwarp();
             if (prof) tq = clock64();
@@ -420,7 +445,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             const uint32_t sbuf = sbuf0 + sflip * kATileBytes;
             const uint32_t srow = sbuf + (uint32_t)row * 128u;
             if (issuer_warp) {
-              if (ptx::elect_one()) { if (p.stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
+              if (ptx::elect_one()) { if (q_stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
               __syncwarp();
             }   // the store that last used this tile has drained it
             ptx::named_bar_sync(1 + grp, 128);
@@ -433,12 +458,12 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               o.w = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 6]) + b1.z), act_fn<kAct>(__uint_as_float(v[8 * j + 7]) + b1.w));
               ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);   // SWIZZLE_128B: 16-byte slot j of row r lives at j ^ (r % 8)
             };
-            if (p.band) {
+            if (q_band) {
               // out element e = 32 * rr + px of the 128-byte row <- column rr * 30 + px; the padding columns and the
               // padding rows of the image (mask) are written as zeros
               const float bz = bias_in_smem ? s_bias[0] : __ldg(p.bias);
               const long long particle = (long long)tile_row(ptile) + row;
-              float* y32row = (p.y32 && particle < p.P) ? p.y32 + particle * p.out32_pitch + j0.w + ch * 2 * 28 : nullptr;
+              float* y32row = (p.y32 && particle < q_P) ? p.y32 + particle * q_out32_pitch + j0.w + ch * 2 * 28 : nullptr;
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 const int rr = j >> 2;
@@ -456,8 +481,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               }
             } else if (bias_in_smem) {
               // explicit ld.shared, software-pipelined one slot ahead: through a generic pointer every slot was a
-              // dependent LD -> math -> STS chain of ~110 cycles (the epilogue's largest single cost)
-              const uint32_t baddr = s_bias_addr + (uint32_t)(j1.z * p.nt + n0) * 4u;
+              // dependent LD -> math -> STS chain of ~110 cycles
+              const uint32_t baddr = s_bias_addr + (uint32_t)(j1.z * q_nt + n0) * 4u;
               float4 b0 = ptx::ld_shared_f4(baddr), b1 = ptx::ld_shared_f4(baddr + 16u);
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
@@ -480,21 +505,21 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               }
               __syncwarp();
             }
-            if (p.stg_bufs == 2) sflip ^= 1u;
+            if (q_stg_bufs == 2) sflip ^= 1u;
             if (prof) { const long long t = clock64(); e_pub += (unsigned long long)(t - tq); tq = t; }
           }
         } else {
           const long long particle = (long long)tile_row(ptile) + row;
-          const bool valid = particle < p.P;
-          __nv_bfloat16* yrow = p.y ? p.y + particle * p.out_pitch + j0.z : nullptr;
-          float* y32row = p.y32 ? p.y32 + particle * p.out32_pitch + j0.w : nullptr;
-          for (int c0 = 0; c0 < p.nt; c0 += 16) {
+          const bool valid = particle < q_P;
+          __nv_bfloat16* yrow = p.y ? p.y + particle * q_out_pitch + j0.z : nullptr;
+          float* y32row = p.y32 ? p.y32 + particle * q_out32_pitch + j0.w : nullptr;
+          for (int c0 = 0; c0 < q_nt; c0 += 16) {
             uint32_t v[16];
             __syncwarp();                       // tcgen05.ld is .sync.aligned: reconverge after the masked stores
             ptx::tmem_ld_x16(tbase + (uint32_t)c0, v);
             ptx::tmem_ld_wait();
             if (!valid) continue;               // rows past P hold zero-filled TMA data: nothing to store
-            if (p.vec4 && yrow) {
+            if (q_vec4 && yrow) {
 #pragma unroll
               for (int g = 0; g < 4; ++g) {     // cc == 1: 4 consecutive pixels -> one 8-byte store
                 const int n = c0 + 4 * g;
@@ -537,11 +562,15 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         }   // jobs of the chain
       }
       if (kTmaStore && issuer_warp && ptx::elect_one()) ptx::bulk_wait_all0();      // staging tiles must outlive their TMA stores
+      if (prof && warp < 4 && lane == 0) {        // per lane-quadrant warp of group 0: {tmem load, staging/barrier wait, math, publish}
+        unsigned long long* q4 = p.prof + blockIdx.x * 32 + 16 + 4 * warp;
+        q4[0] = e_ld; q4[1] = e_free; q4[2] = e_math; q4[3] = e_pub;
+      }
       if (prof && warp == 0 && lane == 0) {
-        p.prof[blockIdx.x * 16 + 5] = w_tfull; p.prof[blockIdx.x * 16 + 6] = (unsigned long long)(clock64() - t_start);
-        p.prof[blockIdx.x * 16 + 7] = (unsigned long long)it;
-        p.prof[blockIdx.x * 16 + 8] = e_ld; p.prof[blockIdx.x * 16 + 9] = e_free;
-        p.prof[blockIdx.x * 16 + 10] = e_math; p.prof[blockIdx.x * 16 + 11] = e_pub;
+        p.prof[blockIdx.x * 32 + 5] = w_tfull; p.prof[blockIdx.x * 32 + 6] = (unsigned long long)(clock64() - t_start);
+        p.prof[blockIdx.x * 32 + 7] = (unsigned long long)it;
+        p.prof[blockIdx.x * 32 + 8] = e_ld; p.prof[blockIdx.x * 32 + 9] = e_free;
+        p.prof[blockIdx.x * 32 + 10] = e_math; p.prof[blockIdx.x * 32 + 11] = e_pub;
       }
     }
   }

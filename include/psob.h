@@ -186,10 +186,11 @@ int psob_layer_destroy(psob_layer* l);
 int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32,
                    int32_t impl, psob_stream_t s);
 
-/* Debug: when `counters` (device, u64 [n_SMs][16]) is non-NULL, later runs of the layer record per CTA
+/* Debug: when `counters` (device, u64 [n_SMs][32]) is non-NULL, later runs of the layer record per CTA
  * { producer wait-empty, producer total, mma wait-full, mma wait-tmem-empty, mma total,
  *   epilogue wait-tmem-full, epilogue total, items, epilogue tmem-load, staging-free wait,
- *   bias/activation/st.shared, publish (fence + barrier + TMA store issue), 4 spare } in SM cycles.
+ *   bias/activation/st.shared, publish (fence + barrier + TMA store issue), 4 spare, then the last four for each
+ *   of the warps 0..3 (TMEM lane quadrants of epilogue group 0) } in SM cycles.
  *   NULL switches it off. */
 int psob_layer_profile(psob_layer* l, void* counters);
 

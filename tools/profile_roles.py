@@ -15,7 +15,7 @@ engine.pack_latent(torch.randn(P, 100, device="cuda"), z)
 for _ in range(2):
     gnet.forward(z); dnet.forward(gnet.image_padded_bf16())
 torch.cuda.synchronize()
-buf = torch.zeros(148, 16, dtype=torch.int64, device="cuda")
+buf = torch.zeros(148, 32, dtype=torch.int64, device="cuda")
 cur = z
 print("layer        jobs steps | prod: wait_empty/total | mma: wait_full wait_tmem /total | epi: wait_tfull/total | cyc/item cyc/step | epi per chunk: ld free math pub")
 for net, x0 in ((gnet, z), (dnet, gnet.image_padded_bf16())):
@@ -33,5 +33,6 @@ for net, x0 in ((gnet, z), (dnet, gnet.image_padded_bf16())):
         steps_per_item = pr.n_steps / pr.n_jobs
         print(f"{pr.name:10s} {pr.n_jobs:5d} {pr.n_steps:5d} | {m[0]/m[1]:.2f} of {m[1]/1e3:8.0f}k | {m[2]/m[4]:.2f} {m[3]/m[4]:.2f} of {m[4]/1e3:8.0f}k | "
               f"{m[5]/m[6]:.2f} of {m[6]/1e3:8.0f}k | {m[4]/m[7]:8.0f} {m[4]/m[7]/steps_per_item:7.0f} | "
-              f"{m[8]/m[6]:.2f} {m[9]/m[6]:.2f} {m[10]/m[6]:.2f} {m[11]/m[6]:.2f}")
+              f"{m[8]/m[6]:.2f} {m[9]/m[6]:.2f} {m[10]/m[6]:.2f} {m[11]/m[6]:.2f} | warps 0-3 ld/wait/math/pub: " +
+              " ".join("/".join(f"{m[16 + 4 * w + k]/m[6]:.2f}" for k in range(4)) for w in range(4)))
         cur = y

@@ -454,9 +454,19 @@ def lower_convt_image_band(name, w, b, act, in_cp=None) -> LayerProgram:
     zero_row = len(tiles) * BAND_N
     tiles.append(np.zeros((BAND_N, KCHUNK), np.float32))
     steps, jobs, xops = [], [], {}
+    chain = CHAIN_ROWS
+    zero_ops = lambda fl: [(zero_row, 0, fl), (zero_row, 96, fl), (zero_row, 160, fl)]     # three N = 96 clears cover 256 columns
     for band in range(4):
         sb = len(steps)
-        for iy in range(4 * band - 1, 4 * band + 4):
+        # chained (bands 0+1 and 2+3 of a particle tile run back to back on one CTA; chains of all four would leave
+        # 512 items for 148 CTAs): input row 4 band + 3 lands on the last two rows of this band AND on the first two rows
+        # of the next one, so it is loaded once and feeds both (NEXT op); the next band's accumulator is cleared by NEXT
+        # clears on an earlier step of this band.  210 loads instead of 238.
+        feeds_next = chain and band in (0, 2)
+        fed_by_prev = chain and band in (1, 3)
+        rows = range(4 * band if fed_by_prev else 4 * band - 1, 4 * band + 4)
+        cleared_next = False
+        for iy in rows:
             if not 0 <= iy < h:
                 continue
             r0 = 2 * iy - BAND_ROWS * band                  # band row of the patch's first row: -2, 0, 2, 4, 6
@@ -469,16 +479,26 @@ def lower_convt_image_band(name, w, b, act, in_cp=None) -> LayerProgram:
                     else:
                         key, d_col = "bot", (r0 - 2) * BAND_PITCH + 2 * ix
                     assert d_col + BAND_N <= nt
-                    op = (tile_of[(key, kc)] * BAND_N, d_col, STEP_ACCUM)
-                    if len(steps) == sb:
-                        # overlapping windows: no "first touch" per column, so the job's first step clears the band
-                        xops[len(steps)] = [(zero_row, 96, 0), (zero_row, 160, 0), op]
-                        steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, zero_row, 0, STEP_B_RESIDENT))
-                    else:
-                        steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, op[0], op[1], STEP_ACCUM | STEP_B_RESIDENT))
+                    ops = []
+                    if len(steps) == sb and not fed_by_prev:
+                        ops += zero_ops(0)          # overlapping windows: no "first touch" per column, clear the band first
+                    ops.append((tile_of[(key, kc)] * BAND_N, d_col, STEP_ACCUM))
+                    if feeds_next:
+                        if key == "bot":            # shared row: top-cut taps into the next band
+                            ops.append((tile_of[("top", kc)] * BAND_N, 2 * ix, STEP_ACCUM | STEP_NEXT))
+                        elif not cleared_next and len(ops) == 1:
+                            ops += zero_ops(STEP_NEXT)
+                            cleared_next = True
+                    assert len(ops) <= 4
+                    b_row, dc, fl = ops[0]
+                    if len(ops) > 1:
+                        xops[len(steps)] = ops[1:]
+                    steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, b_row, dc, fl | STEP_B_RESIDENT))
+        assert cleared_next == feeds_next
         py0 = BAND_ROWS * band
         lo, hi = _mask_words([1 <= py0 + r <= 28 for r in range(BAND_ROWS)])
         jobs.append((sb, len(steps) - sb, py0 * IMG_PAD_PITCH, (py0 - 1) * 28, lo, hi, 0, 0))
+    chains = [(0, 2), (2, 2)] if chain else None
     col_map, col_map32 = [], []
     for n in range(nt):
         r, px = divmod(n, BAND_PITCH)
@@ -488,7 +508,7 @@ def lower_convt_image_band(name, w, b, act, in_cp=None) -> LayerProgram:
     bias = np.full(nt, float(np.asarray(b).reshape(-1)[0]), np.float32)
     conn = sum(1 for o in range(28) for k in range(4) if (o + 1 - k) % 2 == 0 and 0 <= (o + 1 - k) // 2 < 14)
     return _finish(name, BAND_N, nt, BAND_PITCH, act, h * wd * cpi, IMG_PAD_ROWS * IMG_PAD_PITCH, 28 * 28, tiles, True, steps, jobs,
-                   col_map, col_map32, bias, macs_exact=conn * conn * cin, xops=xops,
+                   col_map, col_map32, bias, macs_exact=conn * conn * cin, xops=xops, chains=chains,
                    meta=dict(kind="convt_image_band", out_hw=(28, 28), out_c=1, out_cp=1, band=(BAND_ROWS, BAND_PITCH)))
 
 

@@ -61,7 +61,7 @@ struct EngineParams {
   int mma_n, nt, cc, act, out_pitch, out32_pitch, vec8;
   int b_resident, n_wrows, n_bias_rows, n_steps;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
-  int vec4, strided, pf_dist;
+  int vec4, strided;
   int step_stride;           // int4 words per step in the shared-memory copy of the step table (1 when no step has > 2 ops)
   int band;                  // image-band epilogue (lower_convt_image_band): 4 chunks of two padded image rows each
   int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
@@ -705,7 +705,7 @@ struct psob_layer {
   CUtensorMap tmB;
   bool have_tmB = false;
   bool tma_store = false, vec4 = false, pair = false, strided = false;
-  int pf_dist = 0, epi_groups = 2, step_stride = 2;
+  int epi_groups = 2, step_stride = 2;
   bool band = false;
   unsigned long long* prof = nullptr;
   int bias_off = -1, steps_off = -1, jobs_off = -1, chains_off = -1, tab_bytes = 0, stg_bufs = 0;
@@ -904,7 +904,6 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->bar_off = l->stg_off + stg_bytes;
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
   { const char* e = getenv("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }     // tuning knob (default: strided)
-  { const char* e = getenv("PSOB_PF"); l->pf_dist = e ? atoi(e) : 0; if (l->pf_dist < 0) l->pf_dist = 0; }   // L2 prefetch distance in steps
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * d->nt)) cols <<= 1;
   l->tmem_cols = cols;
@@ -938,7 +937,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
   p.in_tiled = d.in_tiled; p.out_tiled = d.out_tiled; p.n_in_chunks = d.in_pitch / kKChunk; p.n_out_chunks = d.out_pitch / kKChunk;
-  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.pf_dist = l->pf_dist; p.epi_groups = l->epi_groups; p.step_stride = l->step_stride; p.band = (l->band && p.y != nullptr) ? 1 : 0;
+  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.epi_groups = l->epi_groups; p.step_stride = l->step_stride; p.band = (l->band && p.y != nullptr) ? 1 : 0;
   if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);

@@ -317,6 +317,121 @@ __global__ void pack_image_kernel(const float* __restrict__ img, long long P, __
 
 using namespace psob;
 
+// ------------------------------------------------------------------------------------------
+// Swarm diversity: mean Euclidean distance over all unordered particle pairs -- `Swarm.mse`
+// (src/pso/util_pso.py:76-86; reporting only, O(P^2 D)).  One block per 64 x 64 tile of the upper
+// triangle; both 64-particle slabs sit in shared memory (row pitch D + 1: conflict-free), every
+// thread owns a 4 x 4 patch of pairs.  Differences are squared directly (no Gram-matrix
+// cancellation), distances are summed per block in double and added with one atomicAdd(double).
+// ------------------------------------------------------------------------------------------
+constexpr int kPairTile = 64;
+
+__global__ void __launch_bounds__(256)
+pairwise_distance_sum_kernel(const float* __restrict__ pos, long long P, int D, int pitch, int n_tiles, double* __restrict__ out) {
+  extern __shared__ float sm[];
+  // linear block index -> (ti <= tj) of the upper triangle
+  long long b = blockIdx.x;
+  int ti = 0;
+  while (b >= (long long)(n_tiles - ti)) { b -= (n_tiles - ti); ++ti; }
+  const int tj = ti + (int)b;
+  const int ld = D + 1;
+  float* A = sm;
+  float* B = sm + kPairTile * ld;
+  for (int idx = threadIdx.x; idx < kPairTile * D; idx += 256) {
+    const int r = idx / D, c = idx - r * D;
+    const long long ia = (long long)ti * kPairTile + r, ib = (long long)tj * kPairTile + r;
+    A[r * ld + c] = ia < P ? pos[ia * pitch + c] : 0.f;
+    B[r * ld + c] = ib < P ? pos[ib * pitch + c] : 0.f;
+  }
+  __syncthreads();
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (int c = 0; c < D; ++c) {
+    float a[4], bb[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { a[i] = A[(ty + 16 * i) * ld + c]; bb[i] = B[(tx + 16 * i) * ld + c]; }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { const float d = a[i] - bb[j]; acc[i][j] = fmaf(d, d, acc[i][j]); }
+  }
+  double sum = 0.0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long gi = (long long)ti * kPairTile + ty + 16 * i, gj = (long long)tj * kPairTile + tx + 16 * j;
+      if (gi < gj && gj < P) sum += (double)sqrtf(acc[i][j]);
+    }
+  __shared__ double red[8];
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_down_sync(0xffffffffu, sum, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    atomicAdd(out, t);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Nearest codebook entry -- `vq` (src/inverter/utils_vq_vae/util_function.py:4-23):
+// argmin_k (|c_k|^2 + |x|^2 - 2 x.c_k), lowest k on ties (torch.min).  One warp per input row; the
+// codebook is staged through shared memory in slabs of rows (pitch D + 1), lane l scans entries
+// l, l + 32, ...; the warp reduces (distance, index) lexicographically.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+vq_nearest_kernel(const float* __restrict__ x, long long P, int D, int x_pitch, const float* __restrict__ cb, int K, int slab,
+                  long long* __restrict__ idx_out, float* __restrict__ dist_out) {
+  extern __shared__ float sm[];
+  const int ld = D + 1;
+  float* C = sm;                       // [slab][ld]
+  float* C2 = sm + (size_t)slab * ld;  // [slab]
+  float* X = C2 + slab;                // [8 warps][D]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * 8 + warp;
+  float x2 = 0.f;
+  if (row < P) {
+    for (int c = lane; c < D; c += 32) { const float v = x[row * x_pitch + c]; X[warp * D + c] = v; x2 = fmaf(v, v, x2); }
+  }
+  for (int o = 16; o > 0; o >>= 1) x2 += __shfl_xor_sync(0xffffffffu, x2, o);
+  float best = INFINITY;
+  int best_k = 0x7fffffff;
+  for (int k0 = 0; k0 < K; k0 += slab) {
+    const int n = min(slab, K - k0);
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < n * D; idx += 256) { const int r = idx / D, c = idx - r * D; C[r * ld + c] = cb[(size_t)(k0 + r) * D + c]; }
+    __syncthreads();
+    for (int r = threadIdx.x; r < n; r += 256) {
+      float s2 = 0.f;
+      for (int c = 0; c < D; ++c) s2 = fmaf(C[r * ld + c], C[r * ld + c], s2);
+      C2[r] = s2;
+    }
+    __syncthreads();
+    if (row < P) {
+      for (int r = lane; r < n; r += 32) {
+        float dot = 0.f;
+        for (int c = 0; c < D; ++c) dot = fmaf(X[warp * D + c], C[r * ld + c], dot);
+        const float d = (C2[r] + x2) - 2.f * dot;
+        if (d < best) { best = d; best_k = k0 + r; }      // ascending k per lane: strict < keeps the lowest index
+      }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int ok = __shfl_xor_sync(0xffffffffu, best_k, o);
+    if (ob < best || (ob == best && ok < best_k)) { best = ob; best_k = ok; }
+  }
+  if (row < P && lane == 0) {
+    idx_out[row] = best_k;
+    if (dist_out) dist_out[row] = best;
+  }
+}
+
 extern "C" {
 
 int psob_version(void) { return PSOB_VERSION; }
@@ -446,6 +561,34 @@ int psob_pack_image(const float* img, int64_t P, void* out_bf16, psob_stream_t s
   long long total = P * 992;
   pack_image_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)s>>>(img, P, reinterpret_cast<__nv_bfloat16*>(out_bf16));
   PSOB_LAUNCH_CHECK("pack_image_kernel");
+  return 0;
+}
+
+int psob_pairwise_distance_sum(const float* pos, int64_t P, int32_t D, int32_t pitch, double* sum_out, psob_stream_t s) {
+  if (!pos || !sum_out || P <= 0 || D <= 0 || pitch < D) return fail(PSOB_E_ARG, "psob_pairwise_distance_sum: bad arguments");
+  const long long n_tiles = (P + kPairTile - 1) / kPairTile;
+  const long long n_blocks = n_tiles * (n_tiles + 1) / 2;
+  if (n_blocks >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_pairwise_distance_sum: P = %lld is too large (sub-sample the swarm)", (long long)P);
+  const size_t smem = (size_t)2 * kPairTile * (D + 1) * sizeof(float);
+  if (smem > 200 * 1024) return fail(PSOB_E_UNSUPPORTED, "psob_pairwise_distance_sum: D = %d is too large", D);
+  PSOB_CUDA(cudaFuncSetAttribute(pairwise_distance_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  PSOB_CUDA(cudaMemsetAsync(sum_out, 0, sizeof(double), (cudaStream_t)s));
+  pairwise_distance_sum_kernel<<<(unsigned)n_blocks, 256, smem, (cudaStream_t)s>>>(pos, P, D, pitch, (int)n_tiles, sum_out);
+  PSOB_LAUNCH_CHECK("pairwise_distance_sum_kernel");
+  return 0;
+}
+
+int psob_vq_nearest(const float* x, int64_t P, int32_t D, int32_t x_pitch, const float* codebook, int32_t K,
+                    int64_t* idx_out, float* dist_out, psob_stream_t s) {
+  if (!x || !codebook || !idx_out || P <= 0 || D <= 0 || K <= 0 || x_pitch < D) return fail(PSOB_E_ARG, "psob_vq_nearest: bad arguments");
+  int slab = K;
+  auto bytes = [&](int sl) { return ((size_t)sl * (D + 1) + sl + (size_t)8 * D) * sizeof(float); };
+  while (slab > 32 && bytes(slab) > 160 * 1024) slab = (slab + 1) / 2;
+  if (bytes(slab) > 200 * 1024) return fail(PSOB_E_UNSUPPORTED, "psob_vq_nearest: D = %d is too large", D);
+  PSOB_CUDA(cudaFuncSetAttribute(vq_nearest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes(slab)));
+  vq_nearest_kernel<<<(unsigned)((P + 7) / 8), 256, bytes(slab), (cudaStream_t)s>>>(x, P, D, x_pitch, codebook, K, slab,
+                                                                                  reinterpret_cast<long long*>(idx_out), dist_out);
+  PSOB_LAUNCH_CHECK("vq_nearest_kernel");
   return 0;
 }
 

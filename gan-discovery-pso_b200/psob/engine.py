@@ -201,6 +201,34 @@ def rescale_minmax(img: torch.Tensor, out: torch.Tensor):
     _ffi.check(_ffi.lib().psob_rescale_minmax(img.data_ptr(), P, img.numel() // P, out.data_ptr(), _stream()), "psob_rescale_minmax")
 
 
+def mean_pairwise_distance(pos: torch.Tensor) -> float:
+    """`Swarm.mse` (src/pso/util_pso.py:76-86) on the device: mean |pos_i - pos_j|_2 over unordered pairs."""
+    assert pos.is_cuda and pos.dtype == torch.float32 and pos.dim() == 2 and pos.stride(1) == 1
+    P, D = pos.shape
+    if P < 2:
+        return float("nan")
+    total = torch.empty(1, dtype=torch.float64, device=pos.device)
+    _ffi.check(_ffi.lib().psob_pairwise_distance_sum(pos.data_ptr(), P, D, pos.stride(0), total.data_ptr(), _stream()),
+               "psob_pairwise_distance_sum")
+    return float(total.item()) / (P * (P - 1) / 2)
+
+
+def vq_nearest(x: torch.Tensor, codebook: torch.Tensor, return_distance=False):
+    """`vq` (src/inverter/utils_vq_vae/util_function.py:4-23): index of the nearest codebook row for every row
+    of x (any leading shape), int64, lowest index on ties."""
+    assert x.is_cuda and codebook.is_cuda and x.dtype == torch.float32 and codebook.dtype == torch.float32
+    K, D = codebook.shape
+    flat = x.reshape(-1, D).contiguous()
+    cb = codebook.contiguous()
+    idx = torch.empty(flat.shape[0], dtype=torch.int64, device=x.device)
+    dist = torch.empty(flat.shape[0], dtype=torch.float32, device=x.device) if return_distance else None
+    if flat.shape[0]:
+        _ffi.check(_ffi.lib().psob_vq_nearest(flat.data_ptr(), flat.shape[0], D, flat.stride(0), cb.data_ptr(), K, idx.data_ptr(),
+                                              _ptr(dist), _stream()), "psob_vq_nearest")
+    idx = idx.view(x.shape[:-1])
+    return (idx, dist.view(x.shape[:-1])) if return_distance else idx
+
+
 def score_fitness(score: torch.Tensor, fit: torch.Tensor, mode: str, thr=0.0, eps=0.1):
     if mode not in ("optimize_in_training", "optimize_out_training"):
         raise ValueError(mode)                                  # same error as src/pso/util_discovery.py:80

@@ -147,18 +147,7 @@ class Swarm:
 
     def mse(self):
         """Mean Euclidean distance over all unordered particle pairs (src/pso/util_pso.py:76-86)."""
-        pos = self.engine.pos[:, :self.dim_space].double()
-        P = pos.shape[0]
-        if P < 2:
-            return float("nan")
-        total = torch.zeros((), dtype=torch.float64, device=pos.device)
-        chunk = max(1, min(P, (1 << 24) // P))
-        for s in range(0, P, chunk):
-            d = torch.cdist(pos[s:s + chunk], pos, compute_mode="donot_use_mm_for_euclid_dist")
-            idx = torch.arange(s, min(s + chunk, P), device=pos.device)[:, None]
-            d = torch.where(torch.arange(P, device=pos.device)[None, :] > idx, d, torch.zeros_like(d))
-            total += d.sum()
-        return float(total / (P * (P - 1) / 2))
+        return _engine.mean_pairwise_distance(self.engine.pos[:, :self.dim_space])
 
     def init_particles(self, generator: torch.Generator = None, pos=None, vel=None):
         if self.engine is None:

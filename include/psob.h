@@ -141,6 +141,18 @@ int psob_rescale_minmax(const float* img, int64_t P, int32_t n, float* out, psob
 int psob_pack_image(const float* img, int64_t P, void* out_bf16, psob_stream_t s);
 
 /* ------------------------------------------------------------------------------------------
+ * "Next" rows of the hot-path scope
+ * ---------------------------------------------------------------------------------------- */
+/* Swarm.mse (src/pso/util_pso.py:76-86): *sum_out (device double) = sum over unordered pairs i < j of |pos_i - pos_j|_2;
+ * the caller divides by P (P - 1) / 2.  pos: fp32 [P, pitch], D <= pitch. */
+int psob_pairwise_distance_sum(const float* pos, int64_t P, int32_t D, int32_t pitch, double* sum_out, psob_stream_t s);
+/* vq (src/inverter/utils_vq_vae/util_function.py:4-23): idx_out[p] = argmin_k |x_p - c_k|^2 (lowest k on ties),
+ * computed as (|c_k|^2 + |x_p|^2) - 2 x_p.c_k like the reference; dist_out (optional) receives that minimum.
+ * x: fp32 [P, x_pitch]; codebook: fp32 [K, D] dense; idx_out: int64 [P]. */
+int psob_vq_nearest(const float* x, int64_t P, int32_t D, int32_t x_pitch, const float* codebook, int32_t K,
+                    int64_t* idx_out, float* dist_out, psob_stream_t s);
+
+/* ------------------------------------------------------------------------------------------
  * Pixel-GEMM layers — replace Generator.forward / Discriminator.forward / Encoder.forward
  * (src/utils/util_dcgan.py:103-149, src/inverter/utils_ae/util_inverter.py:164-184): every
  * ConvTranspose2d / Conv2d (+ folded BatchNorm + activation) is a table of tcgen05 MMA

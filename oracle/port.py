@@ -136,6 +136,91 @@ class G256(nn.Module):
         return self.gen(x)
 
 
+class Bottleneck(nn.Module):
+    """`resnet_block` (src/pso/util_cnn.py:160-190): 1x1 (cin -> mid) BN ReLU, 3x3 stride s pad 1 BN ReLU,
+    1x1 (mid -> 4 mid) BN, + shortcut (1x1 stride s conv + BN when the shape changes), ReLU.
+    The stride sits on the 3x3 conv; no conv has a bias."""
+
+    def __init__(self, cin: int, mid: int, stride: int, project: bool):
+        super().__init__()
+        self.conv1 = nn.Conv2d(cin, mid, 1, 1, 0, bias=False)
+        self.bn1 = nn.BatchNorm2d(mid)
+        self.conv2 = nn.Conv2d(mid, mid, 3, stride, 1, bias=False)
+        self.bn2 = nn.BatchNorm2d(mid)
+        self.conv3 = nn.Conv2d(mid, 4 * mid, 1, 1, 0, bias=False)
+        self.bn3 = nn.BatchNorm2d(4 * mid)
+        self.identity_downsample = nn.Sequential(nn.Conv2d(cin, 4 * mid, 1, stride, bias=False),
+                                                 nn.BatchNorm2d(4 * mid)) if project else None
+
+    def forward(self, x):
+        y = F.relu(self.bn1(self.conv1(x)))
+        y = F.relu(self.bn2(self.conv2(y)))
+        y = self.bn3(self.conv3(y))
+        sc = x if self.identity_downsample is None else self.identity_downsample(x)
+        return F.relu(y + sc)
+
+
+class Resnet(nn.Module):
+    """The reference's assessor (src/pso/util_cnn.py:81-133): 7x7 stride-2 pad-3 stem + BN + ReLU,
+    3x3 stride-2 pad-1 max pool, four stages of bottlenecks (widths 64/128/256/512, the first block of
+    stages 2-4 has stride 2), a global MAX pool (the attribute is named `avgpool`, :99) and
+    `fc: 2048 -> n_class`.  `layers = [3, 4, 6, 3]` is ResNet-50.  Same state_dict keys as the reference."""
+
+    def __init__(self, layers: Sequence[int], image_channels: int, iid_classes: Sequence[int], n_class: int = 2):
+        super().__init__()
+        self.conv1 = nn.Conv2d(image_channels, 64, 7, 2, 3, bias=False)
+        self.bn1 = nn.BatchNorm2d(64)
+        self.class_to_idx = {c: i for i, c in enumerate(sorted(iid_classes))}
+        self.idx_to_class = {i: c for c, i in self.class_to_idx.items()}
+        cin = 64
+        for li, (n, mid, stride) in enumerate(zip(layers, (64, 128, 256, 512), (1, 2, 2, 2)), start=1):
+            blocks = []
+            for b in range(n):
+                first = b == 0
+                blocks.append(Bottleneck(cin, mid, stride if first else 1, first and (stride != 1 or cin != 4 * mid)))
+                cin = 4 * mid
+            setattr(self, f"layer{li}", nn.Sequential(*blocks))
+        self.fc = nn.Linear(2048, n_class)
+
+    def forward_avgpool(self, x):
+        x = F.max_pool2d(F.relu(self.bn1(self.conv1(x))), 3, 2, 1)
+        x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
+        return F.adaptive_max_pool2d(x, 1).flatten(1)
+
+    def forward(self, x):
+        return self.fc(self.forward_avgpool(x))
+
+
+def seeded_fill(model: nn.Module, seed: int) -> None:
+    """Deterministic 'trained-like' parameters, independent of module construction order: every
+    state_dict entry is drawn in sorted-key order from one seeded generator.  Conv weights
+    N(0, 2 / fan_in), BN gamma U(0.7, 1.3) (the last BN of a bottleneck U(0.1, 0.4): keeps the residual
+    stream O(1) over 16 blocks), beta / running_mean N(0, 0.1), running_var U(0.5, 1.5), fc so that
+    the logits are O(1).  Used on the reference model by oracle/gen_golden_resnet.py and on the port / the
+    CUDA path by the tests, so that a 94 MB state_dict need not be committed."""
+    gen = torch.Generator().manual_seed(seed)
+    sd = model.state_dict()
+    with torch.no_grad():
+        for k in sorted(sd.keys()):
+            v = sd[k]
+            if k.endswith("num_batches_tracked"):
+                continue
+            if v.dim() == 4:
+                fan_in = v.shape[1] * v.shape[2] * v.shape[3]
+                v.copy_(torch.randn(v.shape, generator=gen) * math.sqrt(2.0 / fan_in))
+            elif k.endswith("running_var"):
+                v.copy_(torch.rand(v.shape, generator=gen) + 0.5)
+            elif k.endswith("running_mean"):
+                v.copy_(torch.randn(v.shape, generator=gen) * 0.1)
+            elif k.startswith("fc."):
+                v.copy_(torch.randn(v.shape, generator=gen) * (0.07 if v.dim() == 2 else 0.1))
+            elif k.endswith(".weight"):       # BN gamma
+                lo, hi = (0.1, 0.4) if ".bn3." in k else (0.7, 1.3)
+                v.copy_(torch.rand(v.shape, generator=gen) * (hi - lo) + lo)
+            else:                             # BN beta
+                v.copy_(torch.randn(v.shape, generator=gen) * 0.1)
+
+
 def initialize_weights(model: nn.Module) -> None:
     """N(0, 0.02) on conv, conv-transpose *and BN gamma* (src/utils/util_dcgan.py:45-48)."""
     for m in model.modules():

@@ -54,6 +54,7 @@ def load():
         import src.inverter.utils_ae.util_inverter as util_inverter
         import src.inverter.utils_vq_vae.util_model as vq_model
         import src.inverter.utils_vq_vae.util_function as vq_function
+        import src.pso.util_cnn as util_cnn
         sys.path.insert(0, os.path.join(REFERENCE_ROOT, "src"))
         try:
             import hands_on.pso as hands_on_pso
@@ -73,5 +74,5 @@ def load():
     ns = types.SimpleNamespace(
         util_pso=util_pso, util_discovery=util_discovery, util_dcgan=util_dcgan,
         util_data=util_data, util_inverter=util_inverter, vq_model=vq_model,
-        vq_function=vq_function, hands_on_pso=hands_on_pso)
+        vq_function=vq_function, hands_on_pso=hands_on_pso, util_cnn=util_cnn)
     return ns

@@ -42,3 +42,11 @@ def load_sd(golden, prefix):
     return {k[len(pre):]: torch.from_numpy(v.copy()) for k, v in golden.items()
             if k.startswith(pre) and not k.endswith("/out") and k[len(pre):].split(".")[0] in
             ("gen", "disc", "enc", "decoder", "0", "1")}
+
+
+@pytest.fixture(scope="session")
+def golden_resnet():
+    """Outputs of the reference's own `Resnet` (src/pso/util_cnn.py) on seeded parameters (oracle/gen_golden_resnet.py)."""
+    path = os.path.join(ROOT, "tests", "golden", "ref_resnet.npz")
+    with np.load(path) as z:
+        return {k: z[k] for k in z.files}

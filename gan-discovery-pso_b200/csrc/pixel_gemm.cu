@@ -55,6 +55,8 @@ struct EngineParams {
   const float* bias;
   __nv_bfloat16* y;
   float* y32;
+  const __nv_bfloat16* res;  // optional residual, same layout as y (TMA-store epilogue): out = act(acc + bias + res)
+  long long res_pitch;
   long long P;
   long long n_items;
   int n_jobs, n_chains;
@@ -113,7 +115,7 @@ __device__ __forceinline__ float act_fn(float v) {
 // L2 traffic is each CTA's own 16 KB A tile (the L2 slices deliver ~42 B/clk/SM with all SMs pulling:
 // streaming a 32 KB B tile per 512-cycle step had every heavy layer L2-bound at ~45 % of the MMA rate).
 // The leader (rank 0) issues all MMAs; its commits arrive on the barriers of both CTAs.
-template <int kAct, bool kTmaStore, bool kPair>
+template <int kAct, bool kTmaStore, bool kPair, bool kRes = false>
 __global__ void __launch_bounds__(kMaxThreads, 1)
 pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmY, const EngineParams p) {
@@ -397,6 +399,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const uint32_t sw = (uint32_t)(row & 7);
     uint32_t it = 0;
     const bool prof = p.prof != nullptr;
+    constexpr bool has_res = kRes;      // residual epilogue: its own instantiation (32 more live registers)
     unsigned long long w_tfull = 0, e_ld = 0, e_free = 0, e_math = 0, e_pub = 0;
     long long tq = 0;
     const long long t_start = clock64();
@@ -429,6 +432,16 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             const int cm = q_band ? ch << 6 : s_cm[n0];
             if (!q_band && (cm < 0 || !((mask >> s_pix[n0]) & 1ull))) continue;       // uniform over the group
             uint32_t v[64];
+            uint4 rres[8];
+            if (has_res) {
+              // residual chunk of this row, issued ahead of the TMEM load so that its latency hides behind it
+              const long long particle = (long long)tile_row(ptile) + row;
+              const int col = j0.z + cm;
+              const __nv_bfloat16* rp = q_out_tiled ? p.res + ((size_t)out_c1(ptile, col) + row) * kKChunk
+                                                    : p.res + particle * p.res_pitch + col;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) rres[j] = particle < q_P ? __ldg(reinterpret_cast<const uint4*>(rp) + j) : make_uint4(0u, 0u, 0u, 0u);
+            }
             __syncwarp();
             if (prof) tq = clock64();
             ptx::tmem_ld_x16(tbase + (uint32_t)n0, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
@@ -451,6 +464,14 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             ptx::named_bar_sync(1 + grp, 128);
             if (prof) { const long long t = clock64(); e_free += (unsigned long long)(t - tq); tq = t; }
             auto emit_slot = [&](int j, const float4& b0, const float4& b1) {
+              if (has_res) {
+                const uint32_t rw[4] = {rres[j].x, rres[j].y, rres[j].z, rres[j].w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {     // bf16 -> fp32 is a 16-bit shift
+                  v[8 * j + 2 * i] = __float_as_uint(__uint_as_float(v[8 * j + 2 * i]) + __uint_as_float(rw[i] << 16));
+                  v[8 * j + 2 * i + 1] = __float_as_uint(__uint_as_float(v[8 * j + 2 * i + 1]) + __uint_as_float(rw[i] & 0xFFFF0000u));
+                }
+              }
               uint4 o;
               o.x = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 0]) + b0.x), act_fn<kAct>(__uint_as_float(v[8 * j + 1]) + b0.y));
               o.y = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 2]) + b0.z), act_fn<kAct>(__uint_as_float(v[8 * j + 3]) + b0.w));
@@ -584,7 +605,13 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 }
 
 typedef void (*UmmaKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const EngineParams);
-static UmmaKernelFn umma_kernel_for(int act, bool tma_store, bool pair) {
+static UmmaKernelFn umma_kernel_for(int act, bool tma_store, bool pair, bool res) {
+  if (res) {            // residual add: solo CTAs, TMA-store epilogue, the bottleneck's ReLU (or none)
+    if (pair || !tma_store) return nullptr;
+    if (act == PSOB_ACT_RELU) return pixel_gemm_umma_kernel<PSOB_ACT_RELU, true, false, true>;
+    if (act == PSOB_ACT_NONE) return pixel_gemm_umma_kernel<PSOB_ACT_NONE, true, false, true>;
+    return nullptr;
+  }
   if (pair) {           // pair mode exists for the hidden conv layers only (TMA-store epilogue, ReLU / LeakyReLU / none)
     switch (act) {
       case PSOB_ACT_NONE: return pixel_gemm_umma_kernel<PSOB_ACT_NONE, true, true>;
@@ -639,7 +666,13 @@ pixel_gemm_simt_kernel(const __nv_bfloat16* __restrict__ x, long long x_pitch, c
         }
       }
     }
-    const float f = apply_act(acc + bias[n], p.act);
+    float pre = acc + bias[n];
+    if (p.res && p.col_map[n] >= 0) {
+      const int col = j0.z + p.col_map[n];
+      pre += __bfloat162float(p.res[p.out_tiled ? (((size_t)ptile * p.n_out_chunks + (col >> 6)) * kTileM + row) * kKChunk + (col & 63)
+                                                : (size_t)particle * p.res_pitch + col]);
+    }
+    const float f = apply_act(pre, p.act);
     if (p.y) {
       const int cm = p.col_map[n];
       if (cm >= 0) {
@@ -704,6 +737,7 @@ struct psob_layer {
   __nv_bfloat16* wpack = nullptr;
   CUtensorMap tmB;
   bool have_tmB = false;
+  const void* attr_fn = nullptr;   // kernel instantiation whose dynamic-SMEM limit has been raised
   bool tma_store = false, vec4 = false, pair = false, strided = false;
   int epi_groups = 2, step_stride = 2;
   bool band = false;
@@ -918,8 +952,18 @@ int psob_layer_profile(psob_layer* l, void* counters) {
 }
 
 int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, int32_t impl, psob_stream_t s) {
+  return psob_layer_run_residual(l, x, x_pitch, P, y, y32, nullptr, 0, impl, s);
+}
+
+int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, const void* res,
+                            int64_t res_pitch, int32_t impl, psob_stream_t s) {
   if (!l || !x || P <= 0) return fail(PSOB_E_ARG, "psob_layer_run: bad arguments");
   const psob_layer_desc& d = l->d;
+  if (res) {
+    if (!l->tma_store || l->band || !y) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_residual: the residual add needs the chunked bf16 (TMA-store) epilogue");
+    if (!aligned16(res) || (d.out_tiled ? res_pitch != d.out_pitch : (res_pitch < d.out_pitch || res_pitch % 8)))
+      return fail(PSOB_E_ARG, "psob_layer_run_residual: res must have the output's layout (pitch %lld vs out_pitch %d) and 16-byte alignment", (long long)res_pitch, d.out_pitch);
+  }
   if (d.in_tiled && x_pitch != d.in_pitch) return fail(PSOB_E_ARG, "psob_layer_run: a tile-major input has x_pitch == in_pitch (%d), got %lld", d.in_pitch, (long long)x_pitch);
   if (x_pitch < d.in_pitch || x_pitch % 8 || !aligned16(x)) return fail(PSOB_E_ARG, "psob_layer_run: x_pitch %lld < in_pitch %d, or misaligned", (long long)x_pitch, d.in_pitch);
   if ((d.out_pitch && !y && !(d.out32_pitch && y32)) || (!d.out_pitch && !y32)) return fail(PSOB_E_ARG, "psob_layer_run: missing output buffer");
@@ -928,6 +972,7 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   p.steps = l->steps; p.jobs = l->jobs; p.chains = l->chains; p.n_chains = d.n_chains; p.chains_off = l->chains_off; p.col_map = l->col_map; p.col_map32 = l->col_map32; p.bias = l->bias;
   p.y = d.out_pitch ? reinterpret_cast<__nv_bfloat16*>(y) : nullptr;
   p.y32 = d.out32_pitch ? y32 : nullptr;
+  p.res = reinterpret_cast<const __nv_bfloat16*>(res); p.res_pitch = res_pitch;
   p.P = P;
   const long long n_ptiles = (P + kTileM - 1) / kTileM;
   p.n_items = n_ptiles * d.n_chains;
@@ -955,8 +1000,8 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   const bool tma_store = l->tma_store && p.y != nullptr;
   if (d.out_tiled && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a tile-major output needs its bf16 output buffer");
   if (l->pair && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a CTA-pair layer needs its bf16 output buffer");
-  UmmaKernelFn fn = umma_kernel_for(d.act, tma_store, l->pair);
-  if (!fn) return fail(PSOB_E_ARG, "psob_layer_run: unknown activation %d", d.act);
+  UmmaKernelFn fn = umma_kernel_for(d.act, tma_store, l->pair, res != nullptr);
+  if (!fn) return fail(PSOB_E_ARG, "psob_layer_run: no kernel for activation %d%s", d.act, res ? " with a residual (solo CTAs, ReLU / none only)" : "");
   if (l->pair) {
     p.n_items = ((n_ptiles + 1) / 2) * d.n_chains;                // items are (pair of particle tiles, chain of jobs)
     p.idesc = make_idesc_bf16(2 * kTileM, d.mma_n);
@@ -964,8 +1009,11 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
   if (!l->have_tmB) {
     int rc = make_tmap(&l->tmB, l->wpack, kKChunk, (uint64_t)d.n_wrows, kKChunk, (uint32_t)(l->pair ? d.mma_n / 2 : d.mma_n));
     if (rc) return rc;
-    PSOB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
     l->have_tmB = true;
+  }
+  if (l->attr_fn != (const void*)fn) {
+    PSOB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+    l->attr_fn = (const void*)fn;
   }
   CUtensorMap tmA, tmY;
   // tile-major buffers hold n_ptiles full tiles: [n_ptiles][pitch / 64][128][64] == a [rows, 64] matrix with 128 B rows

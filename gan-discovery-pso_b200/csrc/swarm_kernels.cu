@@ -432,6 +432,83 @@ vq_nearest_kernel(const float* __restrict__ x, long long P, int D, int x_pitch, 
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Assessor input: fp32 28x28 image -> the stem's bf16 rows (zero padding 3, row pitch 40, 36 rows; see
+// lower_conv_image_k7s2p3), optionally through the per-image min-max rescale of Discovery.particles_to_img
+// (src/pso/util_discovery.py:45 -> src/utils/util_data.py:129-135) in the same pass.  One warp per image.
+// ------------------------------------------------------------------------------------------
+constexpr int kStemPad = 3, kStemPitch = 40, kStemRows = 36;
+
+__global__ void __launch_bounds__(256)
+pack_image_stem_kernel(const float* __restrict__ img, long long P, int rescale, __nv_bfloat16* __restrict__ out, float* __restrict__ out32) {
+  long long p = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (p >= P) return;
+  const int lane = threadIdx.x & 31;
+  const float* x = img + p * 784;
+  float lo = 0.f, range = 1.f;
+  if (rescale) {
+    float mn = INFINITY, mx = -INFINITY;
+    for (int i = lane; i < 784; i += 32) { float v = x[i]; mn = fminf(mn, v); mx = fmaxf(mx, v); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    lo = mn;
+    range = __fsub_rn(mx, mn);
+  }
+  __nv_bfloat16* y = out + p * (kStemRows * kStemPitch);
+  for (int i = lane; i < kStemRows * kStemPitch; i += 32) {
+    const int r = i / kStemPitch - kStemPad, c = i % kStemPitch - kStemPad;
+    float v = 0.f;
+    if (r >= 0 && r < 28 && c >= 0 && c < 28) {
+      v = x[r * 28 + c];
+      if (rescale) v = __fdiv_rn(__fsub_rn(v, lo), range);
+      if (out32) out32[p * 784 + r * 28 + c] = v;
+    }
+    y[i] = __float2bfloat16_rn(v);
+  }
+}
+
+// MaxPool2d(k, stride, pad) on a bf16 NHWC activation [P, h * w * cp] (the assessor's 3x3 stride-2 pool,
+// src/pso/util_cnn.py:88).  One thread per 8 channels of one output pixel; padding never wins (-inf).
+__global__ void __launch_bounds__(256)
+maxpool_nhwc_kernel(const __nv_bfloat16* __restrict__ x, long long P, int h, int w, int cp, int k, int stride, int pad, int ho, int wo,
+                    long long x_pitch, long long y_pitch, __nv_bfloat16* __restrict__ y) {
+  const int c8 = cp >> 3;
+  const long long per = (long long)ho * wo * c8;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P * per) return;
+  const long long p = i / per;
+  int r = (int)(i - p * per);
+  const int c = r % c8; r /= c8;
+  const int ox = r % wo, oy = r / wo;
+  float m[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) m[e] = -INFINITY;
+  for (int ky = 0; ky < k; ++ky) {
+    const int iy = oy * stride - pad + ky;
+    if (iy < 0 || iy >= h) continue;
+    for (int kx = 0; kx < k; ++kx) {
+      const int ix = ox * stride - pad + kx;
+      if (ix < 0 || ix >= w) continue;
+      const uint4 q = __ldg(reinterpret_cast<const uint4*>(x + p * x_pitch + ((long long)iy * w + ix) * cp) + c);
+      const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        m[2 * e] = fmaxf(m[2 * e], __uint_as_float(qw[e] << 16));
+        m[2 * e + 1] = fmaxf(m[2 * e + 1], __uint_as_float(qw[e] & 0xFFFF0000u));
+      }
+    }
+  }
+  uint4 o;      // the maxima are bf16 values already: truncation is exact
+  o.x = (__float_as_uint(m[0]) >> 16) | (__float_as_uint(m[1]) & 0xFFFF0000u);
+  o.y = (__float_as_uint(m[2]) >> 16) | (__float_as_uint(m[3]) & 0xFFFF0000u);
+  o.z = (__float_as_uint(m[4]) >> 16) | (__float_as_uint(m[5]) & 0xFFFF0000u);
+  o.w = (__float_as_uint(m[6]) >> 16) | (__float_as_uint(m[7]) & 0xFFFF0000u);
+  reinterpret_cast<uint4*>(y + p * y_pitch + ((long long)oy * wo + ox) * cp)[c] = o;
+}
+
 extern "C" {
 
 int psob_version(void) { return PSOB_VERSION; }
@@ -589,6 +666,28 @@ int psob_vq_nearest(const float* x, int64_t P, int32_t D, int32_t x_pitch, const
   vq_nearest_kernel<<<(unsigned)((P + 7) / 8), 256, bytes(slab), (cudaStream_t)s>>>(x, P, D, x_pitch, codebook, K, slab,
                                                                                   reinterpret_cast<long long*>(idx_out), dist_out);
   PSOB_LAUNCH_CHECK("vq_nearest_kernel");
+  return 0;
+}
+
+int psob_pack_image_stem(const float* img, int64_t P, int32_t rescale, void* out_bf16, float* out32, psob_stream_t s) {
+  if (!img || !out_bf16 || P <= 0) return fail(PSOB_E_ARG, "psob_pack_image_stem: bad arguments");
+  pack_image_stem_kernel<<<(unsigned)((P + 7) / 8), 256, 0, (cudaStream_t)s>>>(img, P, rescale, reinterpret_cast<__nv_bfloat16*>(out_bf16), out32);
+  PSOB_LAUNCH_CHECK("pack_image_stem_kernel");
+  return 0;
+}
+
+int psob_maxpool_nhwc(const void* x, int64_t x_pitch, int64_t P, int32_t h, int32_t w, int32_t cp, int32_t k, int32_t stride, int32_t pad,
+                      void* y, int64_t y_pitch, psob_stream_t s) {
+  if (!x || !y || P <= 0 || h <= 0 || w <= 0 || cp <= 0 || cp % 8 || k <= 0 || stride <= 0 || pad < 0 || 2 * pad > k)
+    return fail(PSOB_E_ARG, "psob_maxpool_nhwc: bad arguments");
+  const int ho = (h + 2 * pad - k) / stride + 1, wo = (w + 2 * pad - k) / stride + 1;
+  if (ho <= 0 || wo <= 0 || x_pitch < (int64_t)h * w * cp || y_pitch < (int64_t)ho * wo * cp || x_pitch % 8 || y_pitch % 8 ||
+      ((uintptr_t)x & 15) || ((uintptr_t)y & 15))
+    return fail(PSOB_E_ARG, "psob_maxpool_nhwc: pitches must cover the maps and keep 16-byte alignment");
+  const long long total = (long long)P * ho * wo * (cp / 8);
+  maxpool_nhwc_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)s>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), P, h, w, cp, k, stride, pad, ho, wo, x_pitch, y_pitch, reinterpret_cast<__nv_bfloat16*>(y));
+  PSOB_LAUNCH_CHECK("maxpool_nhwc_kernel");
   return 0;
 }
 

@@ -14,8 +14,8 @@ EXPORTS = [
     "psob_version", "psob_last_error", "psob_device_info", "psob_update", "psob_pack_latent",
     "psob_pbest_minloc", "psob_gbest_candidate", "psob_gbest_apply", "psob_score_fitness",
     "psob_softmax_select", "psob_recon_fitness", "psob_rescale_minmax", "psob_pack_image",
-    "psob_pairwise_distance_sum", "psob_vq_nearest",
-    "psob_layer_create", "psob_layer_destroy", "psob_layer_run", "psob_layer_profile",
+    "psob_pairwise_distance_sum", "psob_vq_nearest", "psob_pack_image_stem", "psob_maxpool_nhwc",
+    "psob_layer_create", "psob_layer_destroy", "psob_layer_run", "psob_layer_run_residual", "psob_layer_profile",
 ]
 
 MODE_IN_TRAINING, MODE_OUT_TRAINING = 0, 1
@@ -85,9 +85,12 @@ def lib():
         "psob_pack_image": ([vp, i64, vp, vp], C.c_int),
         "psob_pairwise_distance_sum": ([vp, i64, i32, i32, vp, vp], C.c_int),
         "psob_vq_nearest": ([vp, i64, i32, i32, vp, i32, vp, vp, vp], C.c_int),
+        "psob_pack_image_stem": ([vp, i64, i32, vp, vp, vp], C.c_int),
+        "psob_maxpool_nhwc": ([vp, i64, i64, i32, i32, i32, i32, i32, i32, vp, i64, vp], C.c_int),
         "psob_layer_create": ([C.POINTER(LayerDesc), C.POINTER(vp)], C.c_int),
         "psob_layer_destroy": ([vp], C.c_int),
         "psob_layer_run": ([vp, vp, i64, i64, vp, vp, i32, vp], C.c_int),
+        "psob_layer_run_residual": ([vp, vp, i64, i64, vp, vp, vp, i64, i32, vp], C.c_int),
         "psob_layer_profile": ([vp, vp], C.c_int),
     }
     for name, (args, res) in sig.items():

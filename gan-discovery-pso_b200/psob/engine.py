@@ -183,6 +183,72 @@ class EncoderNet(Network):
         super().__init__(nets.encoder_programs(_sd_numpy(state_dict), prefix), P, device, impl)
 
 
+class AssessorNet:
+    """The reference's ResNet assessor (src/pso/util_cnn.py:81-190, any `layers`) on the pixel-GEMM engine:
+    fp32 [P, 784] image (raw generator output, or already in [0, 1]) -> logits fp32 [P, n_class].
+
+    Graph from `nets.assessor_programs`: stem as a banded GEMM on the zero-padded image, 3x3/2 max pool, per
+    bottleneck three convs (+ the projection shortcut as its own layer) with the shortcut added in the epilogue of
+    the third.  BN folded on the host; activations bf16 NHWC row-major, fp32 accumulation.  The final feature map
+    of a 28x28 input is 1x1, so the global max pool is the identity."""
+
+    def __init__(self, state_dict, P, device=None, impl=_ffi.IMPL_TCGEN05):
+        require_cuda()
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.P, self.impl = P, impl
+        self.ops, sizes = nets.assessor_programs(_sd_numpy(state_dict))
+        self.n_class = sizes["logits"]
+        with torch.cuda.device(self.device):
+            self.layers = [Layer(op.prog) if op.kind == "layer" else None for op in self.ops]
+            # named buffers are reused by feature maps of different sizes: flat storage, viewed per use as [P, pitch]
+            self.flat = {k: torch.zeros(P * n, dtype=torch.bfloat16, device=self.device) for k, n in sizes.items() if k != "logits"}
+            self.logits = torch.zeros(P, self.n_class, dtype=torch.float32, device=self.device)
+            self.rescaled = None
+
+    def _t(self, name, pitch) -> torch.Tensor:
+        return self.flat[name][:self.P * pitch].view(self.P, pitch)
+
+    @property
+    def macs_exact(self) -> int:
+        return sum(op.prog.macs_exact for op in self.ops if op.prog is not None)
+
+    @property
+    def macs_issued(self) -> int:
+        return sum(op.prog.macs_issued for op in self.ops if op.prog is not None)
+
+    def pack(self, img: torch.Tensor, rescale: bool, keep_rescaled=False):
+        """img fp32 [P, 784] -> the stem's padded bf16 rows; rescale = per-image min-max (src/utils/util_data.py:129-135)."""
+        assert img.is_cuda and img.dtype == torch.float32 and img.is_contiguous() and img.numel() == self.P * 784
+        if keep_rescaled and self.rescaled is None:
+            self.rescaled = torch.empty(self.P, 784, dtype=torch.float32, device=self.device)
+        _ffi.check(_ffi.lib().psob_pack_image_stem(img.data_ptr(), self.P, int(bool(rescale)), self.flat["img"].data_ptr(),
+                                                   _ptr(self.rescaled) if keep_rescaled else None, _stream()), "psob_pack_image_stem")
+
+    def run_graph(self):
+        lib = _ffi.lib()
+        for op, layer in zip(self.ops, self.layers):
+            if op.kind == "maxpool":
+                q = op.pool
+                ho, wo = (q["h"] + 2 * q["pad"] - q["k"]) // q["stride"] + 1, (q["w"] + 2 * q["pad"] - q["k"]) // q["stride"] + 1
+                src, dst = self._t(op.src, q["h"] * q["w"] * q["cp"]), self._t(op.dst, ho * wo * q["cp"])
+                _ffi.check(lib.psob_maxpool_nhwc(src.data_ptr(), src.stride(0), self.P, q["h"], q["w"], q["cp"], q["k"], q["stride"],
+                                                 q["pad"], dst.data_ptr(), dst.stride(0), _stream()), "psob_maxpool_nhwc")
+                continue
+            pr = op.prog
+            src = self._t(op.src, pr.in_pitch)
+            dst = self._t(op.dst, pr.out_pitch) if op.dst else None
+            res = self._t(op.res, pr.out_pitch) if op.res else None
+            _ffi.check(lib.psob_layer_run_residual(layer.handle, src.data_ptr(), src.stride(0), self.P, _ptr(dst),
+                                                   _ptr(self.logits if op.dst32 else None), _ptr(res),
+                                                   res.stride(0) if res is not None else 0, self.impl, _stream()),
+                       f"psob_layer_run({pr.name})")
+        return self.logits
+
+    def forward(self, img: torch.Tensor, rescale=False) -> torch.Tensor:
+        self.pack(img, rescale)
+        return self.run_graph()
+
+
 # ----------------------------------------------------------------------------------------------
 # thin functional wrappers over the elementwise entry points (used by the engine and the tests)
 # ----------------------------------------------------------------------------------------------
@@ -339,6 +405,24 @@ class AssessorFitness:
             logits = self.model_cnn(self.rescaled.view(-1, *self.image_shape)).float().contiguous()
         n_class = logits.shape[1]
         idx = self.class_index if n_class > 2 else 1            # src/pso/util_discovery.py:71-74
+        softmax_select(logits, idx, self.prob)
+        score_fitness(self.prob, fit, self.mode, self.thr, self.eps)
+
+
+class ResnetFitness:
+    """`Discovery.fitness` (src/pso/util_discovery.py:52-82) with the reference's ResNet assessor running on the
+    engine (`AssessorNet`): per-image min-max rescale fused into the stem's input pack, logits, softmax pick,
+    clamp / affine.  Same arguments as `AssessorFitness`."""
+
+    def __init__(self, net: AssessorNet, class_index: Optional[int], mode="optimize_out_training", thr=0.0, eps=0.1):
+        if mode not in ("optimize_in_training", "optimize_out_training"):
+            raise ValueError(mode)
+        self.net, self.class_index, self.mode, self.thr, self.eps = net, class_index, mode, thr, eps
+        self.prob = torch.empty(net.P, dtype=torch.float32, device=net.device)
+
+    def __call__(self, gen: GeneratorNet, fit: torch.Tensor):
+        logits = self.net.forward(gen.image(), rescale=True)
+        idx = self.class_index if self.net.n_class > 2 else 1      # src/pso/util_discovery.py:71-74
         softmax_select(logits, idx, self.prob)
         score_fitness(self.prob, fit, self.mode, self.thr, self.eps)
 

@@ -705,6 +705,138 @@ def lower_conv_full(name, w, b, act, in_cp=None) -> LayerProgram:
 
 
 # ----------------------------------------------------------------------------------------------
+# (f) General Conv2d(Cin -> Cout, k, stride, pad) on an NHWC activation -- the assessor's bottleneck convs
+#     (src/pso/util_cnn.py:160-190: 1x1, 3x3 stride 1/2 pad 1, 1x1 stride-2 shortcut).  M = particles, so a
+#     2x2 or 1x1 feature map costs no padding; border taps are simply absent.  Cout >= 256: one job per
+#     (output pixel, 256-channel group), one N = 256 op per (tap, K-chunk).  Cout < 256: 256 / Cout consecutive
+#     output pixels per job, each with its own N = Cout ops.  `residual`: the epilogue adds the bf16 tensor
+#     res[P, same layout as the output] before the activation (x += identity; relu, :185-187).
+# ----------------------------------------------------------------------------------------------
+
+def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False) -> LayerProgram:
+    cout, cin, k, k2 = w.shape
+    assert k == k2
+    cpi = in_cp or cpitch(cin)
+    cpo = cpitch(cout)
+    ho, wo = (h + 2 * pad - k) // stride + 1, (wd + 2 * pad - k) // stride + 1
+    mma_n = cpo if cpo <= MAX_N else max(n for n in (256, 192, 128, 64) if cpo % n == 0)
+    ncg = cpo // mma_n                  # channel groups per output pixel (Cout > 256)
+    g = MAX_N // mma_n                  # output pixels per job (Cout < 256)
+    nt = g * mma_n
+    nkc = rup(cin, KCHUNK) // KCHUNK
+    wp = np.zeros((cpo, nkc * KCHUNK, k, k), np.float32)
+    wp[:cout, :cin] = w
+    bp = np.zeros(cpo, np.float32)
+    bp[:cout] = b
+    tiles, tile_of = [], {}
+    steps, jobs = [], []
+    macs = 0
+    npix = ho * wo
+    for pix0 in range(0, npix, g):
+        for cg in range(ncg):
+            sb = len(steps)
+            for j in range(min(g, npix - pix0)):
+                oy, ox = divmod(pix0 + j, wo)
+                first = True
+                for ky in range(k):
+                    iy = stride * oy - pad + ky
+                    if not 0 <= iy < h:
+                        continue
+                    for kx in range(k):
+                        ix = stride * ox - pad + kx
+                        if not 0 <= ix < wd:
+                            continue
+                        if cg == 0:
+                            macs += cin * cout
+                        for kc in range(nkc):
+                            key = (ky, kx, kc, cg)
+                            if key not in tile_of:
+                                tile_of[key] = len(tiles)
+                                tiles.append(wp[cg * mma_n:(cg + 1) * mma_n, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
+                            steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, tile_of[key] * mma_n, j * mma_n, 0 if first else STEP_ACCUM))
+                            first = False
+                assert not first, "an output pixel without any tap"
+            lo, hi = _mask_words([pix0 + j < npix for j in range(g)])
+            jobs.append((sb, len(steps) - sb, pix0 * cpo + cg * mma_n, 0, lo, hi, cg, 0))
+    bias = [[bp[cg * mma_n + (n % mma_n)] for n in range(nt)] for cg in range(ncg)]
+    return _finish(name, mma_n, nt, mma_n, act, h * wd * cpi, npix * cpo, 0, tiles, False, steps, jobs, list(range(nt)),
+                   [-1] * nt, bias, macs_exact=macs,
+                   meta=dict(kind="conv2d", out_hw=(ho, wo), out_c=cout, out_cp=cpo, residual=bool(residual)))
+
+
+# ----------------------------------------------------------------------------------------------
+# (g) The assessor's stem: Conv2d(1 -> 64, k=7, s=2, p=3) on the 28x28 image (src/pso/util_cnn.py:85) as a
+#     banded GEMM like (d): the image is stored zero-padded by 3 with a 40-element row pitch, a job owns 4
+#     consecutive output pixels of one row and reads ONE contiguous window of 5 x 64 elements (8 padded rows
+#     from (2 oy, 8 g)); the weight tiles are position-independent.
+# ----------------------------------------------------------------------------------------------
+STEM_PAD = 3
+STEM_PITCH = 40
+STEM_ROWS = 36
+
+
+def lower_conv_image_k7s2p3(name, w, b, act) -> LayerProgram:
+    cout = w.shape[0]
+    assert w.shape[1] == 1 and tuple(w.shape[2:]) == (7, 7)
+    cpo = cpitch(cout)
+    gox = MAX_N // cpo
+    assert gox == 4, "window shift must be a multiple of 8 elements (4 output pixels)"
+    nt = gox * cpo
+    ho = wo = 14
+    nk = 5
+    tiles = []
+    for kc in range(nk):
+        t = np.zeros((nt, KCHUNK), np.float32)
+        for kk in range(KCHUNK):
+            r, j = divmod(kc * KCHUNK + kk, STEM_PITCH)
+            if r >= 7:
+                continue
+            for oxl in range(gox):
+                kx = j - 2 * oxl
+                if 0 <= kx < 7:
+                    t[oxl * cpo:oxl * cpo + cout, kk] = w[:, 0, r, kx]
+        tiles.append(t)
+    steps, jobs = [], []
+    for oy in range(ho):
+        for g in range((wo + gox - 1) // gox):
+            sb = len(steps)
+            start = 2 * oy * STEM_PITCH + 2 * gox * g
+            for kc in range(nk):
+                steps.append((start + kc * KCHUNK, kc * nt, 0, STEP_ACCUM if kc else 0))
+            lo, hi = _mask_words([gox * g + j < wo for j in range(gox)])
+            jobs.append((sb, nk, (oy * wo + gox * g) * cpo, 0, lo, hi, 0, 0))
+    assert steps[-1][0] + KCHUNK <= STEM_ROWS * STEM_PITCH
+    bp = np.zeros(cpo, np.float32)
+    bp[:cout] = b
+    taps = sum(1 for o in range(14) for kk in range(7) if 0 <= 2 * o - 3 + kk < 28)
+    return _finish(name, nt, nt, cpo, act, STEM_ROWS * STEM_PITCH, ho * wo * cpo, 0, tiles, False, steps, jobs,
+                   list(range(nt)), [-1] * nt, [bp[n % cpo] for n in range(nt)], macs_exact=taps * taps * cout,
+                   meta=dict(kind="conv_image_k7", out_hw=(ho, wo), out_c=cout, out_cp=cpo))
+
+
+def pad_image_stem(img: np.ndarray) -> np.ndarray:
+    """[P, 28, 28] -> the stem's padded input rows [P, 36 * 40] (host-side twin of psob_pack_image_stem)."""
+    p = img.shape[0]
+    out = np.zeros((p, STEM_ROWS, STEM_PITCH), np.float32)
+    out[:, STEM_PAD:STEM_PAD + 28, STEM_PAD:STEM_PAD + 28] = img.reshape(p, 28, 28)
+    return out.reshape(p, -1)
+
+
+def maxpool_nhwc(x: np.ndarray, h, wd, cp, k, stride, pad) -> np.ndarray:
+    """MaxPool2d(k, stride, pad) on [P, h * wd * cp] (host-side twin of psob_maxpool_nhwc; padding never wins)."""
+    p = x.shape[0]
+    ho, wo = (h + 2 * pad - k) // stride + 1, (wd + 2 * pad - k) // stride + 1
+    xi = x.reshape(p, h, wd, cp)
+    out = np.full((p, ho, wo, cp), -np.inf, np.float32)
+    for oy in range(ho):
+        for ox in range(wo):
+            y0, y1 = max(0, stride * oy - pad), min(h, stride * oy - pad + k)
+            x0, x1 = max(0, stride * ox - pad), min(wd, stride * ox - pad + k)
+            out[:, oy, ox] = xi[:, y0:y1, x0:x1].max(axis=(1, 2))
+    return out.reshape(p, -1)
+
+
+# ----------------------------------------------------------------------------------------------
 # CPU emulation of the engine (numpy): the semantics csrc/pixel_gemm.cuh must reproduce.
 # ----------------------------------------------------------------------------------------------
 
@@ -720,9 +852,10 @@ def _act(x, act):
     return x
 
 
-def emulate(prog: LayerProgram, x: np.ndarray, round_out=True):
-    """x: float32 [P, in_pitch] holding bf16-representable values.  Returns (y_bf16_as_f32 or
-    None, y_f32 or None)."""
+def emulate(prog: LayerProgram, x: np.ndarray, round_out=True, res: Optional[np.ndarray] = None):
+    """x: float32 [P, in_pitch] holding bf16-representable values; res: [P, out_pitch] added before the
+    activation (layers lowered with residual=True).  Returns (y_bf16_as_f32 or None, y_f32 or None)."""
+    assert (res is not None) == bool(prog.meta.get("residual")), "residual operand does not match the layer"
     p = x.shape[0]
     assert x.shape[1] >= prog.in_pitch
     y = np.zeros((p, prog.out_pitch), np.float32) if prog.out_pitch else None
@@ -755,7 +888,12 @@ def emulate(prog: LayerProgram, x: np.ndarray, round_out=True):
                     else:
                         apply(acc, a, br, dc, fl)
             bias = prog.bias[int(job[6])]
-            v = _act(acc + bias[None, :], prog.act).astype(np.float32)
+            pre = acc + bias[None, :]
+            if res is not None:
+                idx = base + prog.col_map.astype(np.int64)
+                ok = (prog.col_map >= 0) & (idx < res.shape[1])
+                pre[:, ok] = pre[:, ok] + res[:, idx[ok]]
+            v = _act(pre, prog.act).astype(np.float32)
             for n in range(prog.nt):
                 pix = n // prog.cc
                 if pix < 64 and not (mask >> pix) & 1:

@@ -103,3 +103,107 @@ def emulate_chain(progs: List[L.LayerProgram], x: np.ndarray, round_out=True):
     for pr in progs:
         y, y32 = L.emulate(pr, y, round_out=round_out)
     return y, y32
+
+
+# ----------------------------------------------------------------------------------------------
+# The reference's assessor: ResNet bottleneck network on the 28x28 image (src/pso/util_cnn.py:81-190)
+# ----------------------------------------------------------------------------------------------
+
+def fold_bn_conv(sd: Dict, conv: str, bn: str):
+    """Bias-free Conv2d weight [Cout, Cin, k, k] followed by an eval-mode BN over Cout."""
+    w = _np(sd[f"{conv}.weight"])
+    g, beta = _np(sd[f"{bn}.weight"]), _np(sd[f"{bn}.bias"])
+    mean, var = _np(sd[f"{bn}.running_mean"]), _np(sd[f"{bn}.running_var"])
+    s = g / np.sqrt(var + BN_EPS)
+    return (w * s[:, None, None, None]).astype(np.float32), (beta - mean * s).astype(np.float32)
+
+
+class AssessorOp:
+    """One node of the assessor graph: `kind` in {"layer", "maxpool"}; buffers are named, `res` is the tensor the
+    epilogue adds before the activation."""
+
+    def __init__(self, kind, src, dst, prog=None, res=None, pool=None, dst32=None):
+        self.kind, self.src, self.dst, self.prog, self.res, self.pool, self.dst32 = kind, src, dst, prog, res, pool, dst32
+
+
+def assessor_programs(sd: Dict):
+    """-> (ops, buffers): ops in execution order over named bf16 buffers {name: elements per particle}.
+    Input buffer "img" = the stem's zero-padded image rows (lowering.pad_image_stem); output "logits" fp32."""
+    sd = {k: v for k, v in sd.items()}
+    ops, bufs = [], {}
+
+    def need(name, n):
+        bufs[name] = max(bufs.get(name, 0), int(n))
+
+    w, b = fold_bn_conv(sd, "conv1", "bn1")
+    stem = L.lower_conv_image_k7s2p3("a.stem", w, b, L.ACT_RELU)
+    need("img", stem.in_pitch)
+    need("stem", stem.out_pitch)
+    ops.append(AssessorOp("layer", "img", "stem", stem))
+    h = wd = 7
+    c = 64
+    need("x0", h * wd * L.cpitch(c))
+    ops.append(AssessorOp("maxpool", "stem", "x0", pool=dict(h=14, w=14, cp=L.cpitch(c), k=3, stride=2, pad=1)))
+    cur, other = "x0", "x1"
+    for li in range(1, 5):
+        bi = 0
+        while f"layer{li}.{bi}.conv1.weight" in sd:
+            pre = f"layer{li}.{bi}"
+            mid = int(_np(sd[f"{pre}.conv1.weight"]).shape[0])
+            stride = 2 if (li > 1 and bi == 0) else 1
+            w1, b1 = fold_bn_conv(sd, f"{pre}.conv1", f"{pre}.bn1")
+            w2, b2 = fold_bn_conv(sd, f"{pre}.conv2", f"{pre}.bn2")
+            w3, b3 = fold_bn_conv(sd, f"{pre}.conv3", f"{pre}.bn3")
+            assert w1.shape[1] == c and w3.shape[0] == 4 * mid
+            p1 = L.lower_conv2d(f"a.{li}.{bi}.c1", w1, b1, L.ACT_RELU, h, wd, 1, 0)
+            p2 = L.lower_conv2d(f"a.{li}.{bi}.c2", w2, b2, L.ACT_RELU, h, wd, stride, 1)
+            ho, wo = p2.meta["out_hw"]
+            p3 = L.lower_conv2d(f"a.{li}.{bi}.c3", w3, b3, L.ACT_RELU, ho, wo, 1, 0, residual=True)
+            need("t1", p1.out_pitch)
+            need("t2", p2.out_pitch)
+            ops.append(AssessorOp("layer", cur, "t1", p1))
+            ops.append(AssessorOp("layer", "t1", "t2", p2))
+            res = cur
+            if f"{pre}.identity_downsample.0.weight" in sd:
+                wd_, bd_ = fold_bn_conv(sd, f"{pre}.identity_downsample.0", f"{pre}.identity_downsample.1")
+                pd = L.lower_conv2d(f"a.{li}.{bi}.ds", wd_, bd_, L.ACT_NONE, h, wd, stride, 0)
+                need("ds", pd.out_pitch)
+                ops.append(AssessorOp("layer", cur, "ds", pd))
+                res = "ds"
+            else:
+                assert stride == 1 and c == 4 * mid, "an identity shortcut needs matching shapes"
+            need(other, p3.out_pitch)
+            ops.append(AssessorOp("layer", "t2", other, p3, res=res))
+            cur, other = other, cur
+            h, wd, c = ho, wo, 4 * mid
+            bi += 1
+    if h != 1 or wd != 1:
+        raise ValueError(f"assessor: final feature map is {h}x{wd}; only inputs that reduce to 1x1 (28x28 images) are supported "
+                         "(the global max pool is then the identity)")
+    wf = _np(sd["fc.weight"]).astype(np.float32)
+    fc = L.lower_conv_full("a.fc", wf.reshape(wf.shape[0], wf.shape[1], 1, 1), _np(sd["fc.bias"]).astype(np.float32), L.ACT_NONE,
+                           in_cp=L.cpitch(c))
+    ops.append(AssessorOp("layer", cur, None, fc, dst32="logits"))
+    bufs["logits"] = fc.out32_pitch
+    return ops, bufs
+
+
+def emulate_assessor(ops, bufs, img: np.ndarray, round_out=True):
+    """img: [P, 28*28] values in the assessor's input range -> logits fp32 [P, n_class] (numpy emulation of the graph)."""
+    p = img.shape[0]
+    x = L.pad_image_stem(L.to_bf16_f32(img) if round_out else img.astype(np.float32))
+    mem = {"img": x}
+    for op in ops:
+        if op.kind == "maxpool":
+            mem[op.dst] = L.maxpool_nhwc(mem[op.src], **{("wd" if k == "w" else k): v for k, v in op.pool.items()})
+            continue
+        src = mem[op.src]
+        if src.shape[1] < op.prog.in_pitch:
+            src = np.concatenate([src, np.zeros((p, op.prog.in_pitch - src.shape[1]), np.float32)], axis=1)
+        res = mem[op.res] if op.res else None
+        y, y32 = L.emulate(op.prog, src, round_out=round_out, res=res)
+        if op.dst:
+            mem[op.dst] = y
+        if op.dst32:
+            mem[op.dst32] = y32
+    return mem["logits"]

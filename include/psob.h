@@ -143,6 +143,13 @@ int psob_pack_image(const float* img, int64_t P, void* out_bf16, psob_stream_t s
 /* ------------------------------------------------------------------------------------------
  * "Next" rows of the hot-path scope
  * ---------------------------------------------------------------------------------------- */
+/* Assessor input (src/pso/util_discovery.py:45,61-66): fp32 [P, 784] image -> bf16 [P, 36 * 40] rows, zero-padded by 3
+ * with a 40-element row pitch (the stem's banded-GEMM input); rescale != 0 applies the per-image min-max rescale
+ * (src/utils/util_data.py:129-135) first; out32 (optional, fp32 [P, 784]) receives the rescaled image. */
+int psob_pack_image_stem(const float* img, int64_t P, int32_t rescale, void* out_bf16, float* out32, psob_stream_t s);
+/* MaxPool2d(k, stride, pad) on a bf16 NHWC activation [P, h * w * cp] (src/pso/util_cnn.py:88), cp % 8 == 0. */
+int psob_maxpool_nhwc(const void* x, int64_t x_pitch, int64_t P, int32_t h, int32_t w, int32_t cp, int32_t k, int32_t stride,
+                      int32_t pad, void* y, int64_t y_pitch, psob_stream_t s);
 /* Swarm.mse (src/pso/util_pso.py:76-86): *sum_out (device double) = sum over unordered pairs i < j of |pos_i - pos_j|_2;
  * the caller divides by P (P - 1) / 2.  pos: fp32 [P, pitch], D <= pitch. */
 int psob_pairwise_distance_sum(const float* pos, int64_t P, int32_t D, int32_t pitch, double* sum_out, psob_stream_t s);
@@ -197,6 +204,11 @@ int psob_layer_destroy(psob_layer* l);
  * y: bf16 [P, out_pitch] or NULL; y32: fp32 [P, out32_pitch] or NULL */
 int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32,
                    int32_t impl, psob_stream_t s);
+/* Same, with a residual operand: out = act(acc + bias + res) -- the bottleneck's `x += identity; relu`
+ * (src/pso/util_cnn.py:185-187).  res: bf16 in the OUTPUT's layout (row-major [P, res_pitch >= out_pitch], or the
+ * same tile-major buffer shape when the layer stores tile-major); only layers with the chunked bf16 epilogue. */
+int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32,
+                            const void* res, int64_t res_pitch, int32_t impl, psob_stream_t s);
 
 /* Debug: when `counters` (device, u64 [n_SMs][32]) is non-NULL, later runs of the layer record per CTA
  * { producer wait-empty, producer total, mma wait-full, mma wait-tmem-empty, mma total,

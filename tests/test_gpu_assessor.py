@@ -1,0 +1,97 @@
+"""GPU (-m gpu): the reference's ResNet assessor (src/pso/util_cnn.py:81-190) on the pixel-GEMM engine, through the
+C-ABI, against the reference's golden logits, the engine's numpy emulation, and `Discovery.fitness`."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import port
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from psob import engine
+    engine.require_cuda()
+    return engine
+
+
+def _model(g, name):
+    *layers, n_class, seed = (int(v) for v in g[f"{name}/meta"])
+    m = port.Resnet(layers, 1, list(range(n_class)) if n_class > 2 else [0, 1], n_class).eval()
+    port.seeded_fill(m, seed)
+    return m
+
+
+@pytest.mark.parametrize("name", ["r1111_c8", "r2121_c3", "r50_c2", "r50_c8"])
+def test_assessor_logits_vs_reference_golden(engine, golden_resnet, name):
+    """bf16 operands / fp32 accumulation over up to 53 layers vs the fp32 reference: |dlogit| <= 3 % of the logit
+    range, softmax probabilities within 3e-2."""
+    g = golden_resnet
+    m = _model(g, name)
+    x = torch.from_numpy(g["x"]).reshape(-1, 784).cuda()
+    net = engine.AssessorNet(m.state_dict(), x.shape[0])
+    got = net.forward(x).cpu().numpy()
+    ref = g[f"{name}/logits"]
+    assert np.abs(got - ref).max() <= 0.03 * np.abs(ref).max()
+    sm = lambda v: torch.softmax(torch.from_numpy(v), 1).numpy()
+    assert np.abs(sm(got) - sm(ref)).max() <= 3e-2
+
+
+def test_assessor_matches_table_emulation_and_simt(engine, golden_resnet):
+    """The tcgen05 path, the SIMT interpreter and the numpy emulation execute the same tables: logits agree to
+    fp32 summation-order noise amplified by bf16 re-rounding (1e-2 of the range), P = 300 crosses particle tiles."""
+    from psob import nets, _ffi
+    g = golden_resnet
+    m = _model(g, "r2121_c3")
+    gen = torch.Generator().manual_seed(3)
+    x = torch.rand(300, 784, generator=gen)
+    x[7] = 0.0                                   # a constant image
+    ops, bufs = nets.assessor_programs(m.state_dict())
+    emu = nets.emulate_assessor(ops, bufs, x.numpy())
+    tc = engine.AssessorNet(m.state_dict(), 300).forward(x.cuda()).cpu().numpy()
+    simt = engine.AssessorNet(m.state_dict(), 300, impl=_ffi.IMPL_SIMT).forward(x.cuda()).cpu().numpy()
+    scale = np.abs(emu).max()
+    assert np.abs(tc - emu).max() <= 1e-2 * scale and np.abs(simt - emu).max() <= 1e-2 * scale
+    with torch.no_grad():
+        ref = m(x.view(-1, 1, 28, 28)).numpy()
+    assert np.abs(tc - ref).max() <= 0.03 * np.abs(ref).max()
+
+
+def test_stem_pack_rescale_and_maxpool_bit_exact(engine):
+    from psob import lowering as L, _ffi
+    gen = torch.Generator().manual_seed(9)
+    img = torch.randn(37, 784, generator=gen)
+    m = port.Resnet([1, 1, 1, 1], 1, [0, 1], 2).eval()
+    net = engine.AssessorNet(m.state_dict(), 37)
+    net.pack(img.cuda(), rescale=True, keep_rescaled=True)
+    ref = port.rescale_minmax_per_image(img.view(37, 1, 28, 28)).view(37, 784)
+    assert torch.equal(net.rescaled.cpu(), ref)                                    # same fp32 operations, bit for bit
+    packed = net._t("img", L.STEM_ROWS * L.STEM_PITCH).float().cpu().numpy()
+    assert np.array_equal(packed, L.pad_image_stem(L.to_bf16_f32(ref.numpy())))
+    # max pool: bf16 in, bf16 out, exact
+    x = torch.randn(37, 14 * 14 * 64, generator=gen).bfloat16()
+    y = torch.zeros(37, 7 * 7 * 64, dtype=torch.bfloat16, device="cuda")
+    xc = x.cuda()
+    _ffi.check(_ffi.lib().psob_maxpool_nhwc(xc.data_ptr(), xc.stride(0), 37, 14, 14, 64, 3, 2, 1, y.data_ptr(), y.stride(0), None), "maxpool")
+    ref = torch.nn.functional.max_pool2d(x.float().view(37, 14, 14, 64).permute(0, 3, 1, 2), 3, 2, 1).permute(0, 2, 3, 1).reshape(37, -1)
+    assert torch.equal(y.float().cpu(), ref)
+
+
+def test_discovery_fitness_with_resnet_assessor_vs_reference(engine, golden_resnet):
+    """Whole fitness (G -> per-image rescale -> ResNet-50 -> softmax pick -> clamp/affine) vs the reference's own
+    `Discovery.fitness` outputs: |dfit| <= 2e-2 (probabilities through 56 bf16 layers)."""
+    g = golden_resnet
+    gen = port.Generator(100, 1, 16).eval()
+    gen.load_state_dict({k[len("fit/gen/"):]: torch.from_numpy(v.copy()) for k, v in g.items() if k.startswith("fit/gen/")})
+    m = _model(g, "r50_c8")
+    pos = torch.from_numpy(g["fit/pos"]).float().cuda()
+    P = pos.shape[0]
+    gnet = engine.GeneratorNet(gen.state_dict(), P)
+    anet = engine.AssessorNet(m.state_dict(), P)
+    for mode in ("optimize_out_training", "optimize_in_training"):
+        sw = engine.SwarmEngine(P, 100, generator=gnet, fitness=engine.ResnetFitness(anet, 2, mode), seed=1)
+        sw.init_particles(pos=pos, vel=torch.zeros_like(pos))
+        sw.step()
+        torch.cuda.synchronize()
+        assert np.abs(sw.fit.cpu().numpy() - g[f"fit/{mode}"]).max() <= 2e-2

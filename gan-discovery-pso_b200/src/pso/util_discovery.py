@@ -6,6 +6,8 @@ batched forms (`*_batch`) are what `Swarm` uses.  Differences that are deliberat
   * min-max rescale is per image (the reference's whole-tensor `rescale_torch`,
     src/utils/util_data.py:129-135, is per image only because its batch is 1);
   * the two range asserts of :63-64 (host syncs per particle) are dropped;
+  * a `src.pso.util_cnn.Resnet` assessor (the reference's own, :52-82) runs on the engine; any other
+    `model_cnn` is called as a torch module on the rescaled batch;
   * passing a `Discriminator` as `model_cnn` selects the discriminator-score fitness
     (extension; in the reference it raises IndexError at :74).
 """
@@ -17,6 +19,7 @@ import torch
 from psob import engine as _engine
 from psob import _ffi
 from src.utils import util_dcgan
+from src.pso import util_cnn
 
 _MODES = ("optimize_in_training", "optimize_out_training")
 
@@ -53,6 +56,8 @@ class Discovery:
             raise ValueError(self.control_pso_fitness)
         if isinstance(self.model_cnn, util_dcgan.Discriminator):
             return _engine.DScoreFitness(self.model_cnn.engine_net(P), self.control_pso_fitness, self.threshold, eps)
+        if isinstance(self.model_cnn, util_cnn.Resnet):       # the reference's assessor, on the engine
+            return _engine.ResnetFitness(self.model_cnn.engine_net(P), self._class_index(), self.control_pso_fitness, self.threshold, eps)
         self.model_cnn.eval()
         return _engine.AssessorFitness(self.model_cnn, self._class_index(), self.control_pso_fitness, self.threshold, eps)
 

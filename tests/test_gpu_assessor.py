@@ -95,3 +95,32 @@ def test_discovery_fitness_with_resnet_assessor_vs_reference(engine, golden_resn
         sw.step()
         torch.cuda.synchronize()
         assert np.abs(sw.fit.cpu().numpy() - g[f"fit/{mode}"]).max() <= 2e-2
+
+
+def test_dropin_discovery_with_mirror_resnet(engine, golden_resnet):
+    """The reference's call sequence (src/training/pso_discovery.py:177-219): get_cnn('ResNet50', ...), load_state_dict,
+    Discovery(...).fitness(dim_space, pos) per particle -> the reference's own fitness values, and a whole Swarm."""
+    import tempfile
+    from src.pso import util_cnn, util_discovery, util_pso
+    from src.utils import util_dcgan
+    g = golden_resnet
+    classes = [0, 2, 3, 4, 6, 7, 8, 9]
+    ref_cnn = _model(g, "r50_c8")
+    cnn = util_cnn.get_cnn("ResNet50", 1, iid_classes=classes, n_class=8).cuda()
+    assert list(cnn.state_dict().keys()) == list(ref_cnn.state_dict().keys())
+    cnn.load_state_dict(ref_cnn.state_dict())
+    gen = util_dcgan.Generator(100, 1, 16).cuda()
+    gen.load_state_dict({k[len("fit/gen/"):]: torch.from_numpy(v.copy()) for k, v in g.items() if k.startswith("fit/gen/")})
+    x = torch.from_numpy(g["x"]).cuda()
+    assert np.abs(cnn(x).cpu().numpy() - g["r50_c8/logits"]).max() <= 0.03 * np.abs(g["r50_c8/logits"]).max()
+    for mode in ("optimize_out_training", "optimize_in_training"):
+        d = util_discovery.Discovery(iid_class=3, model_gan=gen, model_cnn=cnn, device="cuda", control_pso_fitness=mode,
+                                     iid_classes=classes)
+        fit = np.concatenate([d.fitness(100, g["fit/pos"][i])[0] for i in range(g["fit/pos"].shape[0])])
+        assert fit.dtype == np.float32 and np.abs(fit - g[f"fit/{mode}"]).max() <= 2e-2
+    with tempfile.TemporaryDirectory() as td:
+        sw = util_pso.Swarm(td, d, num_particles=64, n_iterations=4, dim_space=100, device="cuda", tolerance=1e-5,
+                            w_inertia=0.73, w_cogn=1.496, w_soci=1.496)
+        history, _, _, it = sw.optimize(schedule_inertia=False, early_stopping=False)
+    assert it == 5 and 0.1 <= float(np.asarray(sw.g_best_val[-1]).reshape(-1)[0]) <= 1.1
+    assert all(b <= a for a, b in zip(sw.g_best_val, sw.g_best_val[1:]))

@@ -98,7 +98,9 @@ def test_full_size_generator_and_discriminator_vs_reference(mods, golden):
         ref_score = disc(ref_img).reshape(8).numpy()
     ref_img = ref_img.reshape(8, 784).numpy()
     if abs(wsum - float(golden["gfull/wsum"])) <= 1e-6 * abs(wsum):
-        np.testing.assert_allclose(ref_img, golden["gfull/out"].reshape(8, 784), atol=1e-6, rtol=0)
+        # fp32 torch on the GPU box's host CPU vs the fixture made in the build container: conv summation order
+        # depends on the CPU's vector ISA (seen once: > 1e-6 on another box), so 2e-5, still far below the 2e-2 gate
+        np.testing.assert_allclose(ref_img, golden["gfull/out"].reshape(8, 784), atol=2e-5, rtol=0)
     gnet = engine.GeneratorNet(gen.state_dict(), 8)
     dnet = engine.DiscriminatorNet(disc.state_dict(), 8)
     _, img = gnet.forward(_rows(z, gnet.in_pitch))

@@ -192,21 +192,17 @@ class AssessorNet:
     the third.  BN folded on the host; activations bf16 NHWC row-major, fp32 accumulation.  The final feature map
     of a 28x28 input is 1x1, so the global max pool is the identity."""
 
-    def __init__(self, state_dict, P, device=None, impl=_ffi.IMPL_TCGEN05):
+    def __init__(self, state_dict, P, device=None, impl=_ffi.IMPL_TCGEN05, shortcut=None):
         require_cuda()
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.P, self.impl = P, impl
-        self.ops, sizes = nets.assessor_programs(_sd_numpy(state_dict))
+        self.ops, sizes = nets.assessor_programs(_sd_numpy(state_dict), shortcut=shortcut)
         self.n_class = sizes["logits"]
         with torch.cuda.device(self.device):
             self.layers = [Layer(op.prog) if op.kind == "layer" else None for op in self.ops]
-            # named buffers are reused by feature maps of different sizes: flat storage, viewed per use as [P, pitch]
-            self.flat = {k: torch.zeros(P * n, dtype=torch.bfloat16, device=self.device) for k, n in sizes.items() if k != "logits"}
+            self.buf = {k: torch.zeros(P, n, dtype=torch.bfloat16, device=self.device) for k, n in sizes.items() if k != "logits"}
             self.logits = torch.zeros(P, self.n_class, dtype=torch.float32, device=self.device)
             self.rescaled = None
-
-    def _t(self, name, pitch) -> torch.Tensor:
-        return self.flat[name][:self.P * pitch].view(self.P, pitch)
 
     @property
     def macs_exact(self) -> int:
@@ -221,23 +217,22 @@ class AssessorNet:
         assert img.is_cuda and img.dtype == torch.float32 and img.is_contiguous() and img.numel() == self.P * 784
         if keep_rescaled and self.rescaled is None:
             self.rescaled = torch.empty(self.P, 784, dtype=torch.float32, device=self.device)
-        _ffi.check(_ffi.lib().psob_pack_image_stem(img.data_ptr(), self.P, int(bool(rescale)), self.flat["img"].data_ptr(),
+        _ffi.check(_ffi.lib().psob_pack_image_stem(img.data_ptr(), self.P, int(bool(rescale)), self.buf["img"].data_ptr(),
                                                    _ptr(self.rescaled) if keep_rescaled else None, _stream()), "psob_pack_image_stem")
 
     def run_graph(self):
         lib = _ffi.lib()
         for op, layer in zip(self.ops, self.layers):
+            src = self.buf[op.src]
+            dst = self.buf[op.dst] if op.dst else None
             if op.kind == "maxpool":
                 q = op.pool
-                ho, wo = (q["h"] + 2 * q["pad"] - q["k"]) // q["stride"] + 1, (q["w"] + 2 * q["pad"] - q["k"]) // q["stride"] + 1
-                src, dst = self._t(op.src, q["h"] * q["w"] * q["cp"]), self._t(op.dst, ho * wo * q["cp"])
                 _ffi.check(lib.psob_maxpool_nhwc(src.data_ptr(), src.stride(0), self.P, q["h"], q["w"], q["cp"], q["k"], q["stride"],
                                                  q["pad"], dst.data_ptr(), dst.stride(0), _stream()), "psob_maxpool_nhwc")
                 continue
             pr = op.prog
-            src = self._t(op.src, pr.in_pitch)
-            dst = self._t(op.dst, pr.out_pitch) if op.dst else None
-            res = self._t(op.res, pr.out_pitch) if op.res else None
+            assert dst is None or dst.stride(0) == pr.out_pitch
+            res = self.buf[op.res] if op.res else None
             _ffi.check(lib.psob_layer_run_residual(layer.handle, src.data_ptr(), src.stride(0), self.P, _ptr(dst),
                                                    _ptr(self.logits if op.dst32 else None), _ptr(res),
                                                    res.stride(0) if res is not None else 0, self.impl, _stream()),

@@ -713,7 +713,14 @@ def lower_conv_full(name, w, b, act, in_cp=None) -> LayerProgram:
 #     res[P, same layout as the output] before the activation (x += identity; relu, :185-187).
 # ----------------------------------------------------------------------------------------------
 
-def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False) -> LayerProgram:
+def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False, in_base=0, out_base=0, out_pitch=None,
+                 shortcut=None) -> LayerProgram:
+    """`in_base` / `out_base`: element offsets of the input map / the output map inside their particle rows (several
+    maps may share one row-major buffer); `out_pitch`: row pitch of the output buffer (default: the map itself).
+    `shortcut` folds the bottleneck's skip connection into the SAME accumulator as further MMA steps, so that its
+    operand arrives through the pipelined TMA ring instead of the epilogue:
+      ("identity", x_base)                      + x[pixel, channel]  (one 64x64 identity block per 64 channels, exact in fp32)
+      ("conv", w_s, b_s, stride_s, x_base, h_x, wd_x, x_cp)   + the 1x1 projection conv of x (identity_downsample)."""
     cout, cin, k, k2 = w.shape
     assert k == k2
     cpi = in_cp or cpitch(cin)
@@ -728,7 +735,30 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
     wp[:cout, :cin] = w
     bp = np.zeros(cpo, np.float32)
     bp[:cout] = b
+    in_need = in_base + h * wd * cpi
+    sc_kind = shortcut[0] if shortcut else None
+    if sc_kind == "identity":
+        x_base = shortcut[1]
+        assert cout == cpo and cpo % KCHUNK == 0
+        in_need = max(in_need, x_base + ho * wo * cpo)
+    elif sc_kind == "conv":
+        _, w_s, b_s, stride_s, x_base, h_x, wd_x, x_cp = shortcut
+        assert w_s.shape[0] == cout and tuple(w_s.shape[2:]) == (1, 1)
+        assert ((h_x - 1) // stride_s + 1, (wd_x - 1) // stride_s + 1) == (ho, wo)
+        cin_s = w_s.shape[1]
+        nkc_s = rup(cin_s, KCHUNK) // KCHUNK
+        ws = np.zeros((cpo, nkc_s * KCHUNK), np.float32)
+        ws[:cout, :cin_s] = w_s[:, :, 0, 0]
+        bp[:cout] += b_s
+        in_need = max(in_need, x_base + h_x * wd_x * x_cp)
     tiles, tile_of = [], {}
+
+    def tile(key, make):
+        if key not in tile_of:
+            tile_of[key] = len(tiles)
+            tiles.append(make())
+        return tile_of[key] * mma_n
+
     steps, jobs = [], []
     macs = 0
     npix = ho * wo
@@ -749,19 +779,32 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
                         if cg == 0:
                             macs += cin * cout
                         for kc in range(nkc):
-                            key = (ky, kx, kc, cg)
-                            if key not in tile_of:
-                                tile_of[key] = len(tiles)
-                                tiles.append(wp[cg * mma_n:(cg + 1) * mma_n, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
-                            steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, tile_of[key] * mma_n, j * mma_n, 0 if first else STEP_ACCUM))
+                            b_row = tile((ky, kx, kc, cg), lambda: wp[cg * mma_n:(cg + 1) * mma_n, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
+                            steps.append((in_base + (iy * wd + ix) * cpi + kc * KCHUNK, b_row, j * mma_n, 0 if first else STEP_ACCUM))
                             first = False
                 assert not first, "an output pixel without any tap"
+                if sc_kind == "identity":
+                    for i in range(mma_n // KCHUNK):      # channels [cg * mma_n + 64 i, + 64) of x feed columns [64 i, 64 i + 64)
+                        def eye(i=i):
+                            t = np.zeros((mma_n, KCHUNK), np.float32)
+                            t[i * KCHUNK + np.arange(KCHUNK), np.arange(KCHUNK)] = 1.0
+                            return t
+                        steps.append((x_base + (pix0 + j) * cpo + cg * mma_n + i * KCHUNK, tile(("eye", i), eye), j * mma_n, STEP_ACCUM))
+                elif sc_kind == "conv":
+                    if cg == 0:
+                        macs += cin_s * cout
+                    for kc in range(nkc_s):
+                        b_row = tile(("sc", kc, cg), lambda: ws[cg * mma_n:(cg + 1) * mma_n, kc * KCHUNK:(kc + 1) * KCHUNK].copy())
+                        steps.append((x_base + ((stride_s * oy) * wd_x + stride_s * ox) * x_cp + kc * KCHUNK, b_row, j * mma_n, STEP_ACCUM))
             lo, hi = _mask_words([pix0 + j < npix for j in range(g)])
-            jobs.append((sb, len(steps) - sb, pix0 * cpo + cg * mma_n, 0, lo, hi, cg, 0))
+            jobs.append((sb, len(steps) - sb, out_base + pix0 * cpo + cg * mma_n, 0, lo, hi, cg, 0))
     bias = [[bp[cg * mma_n + (n % mma_n)] for n in range(nt)] for cg in range(ncg)]
-    return _finish(name, mma_n, nt, mma_n, act, h * wd * cpi, npix * cpo, 0, tiles, False, steps, jobs, list(range(nt)),
+    out_pitch = out_pitch or npix * cpo
+    assert out_pitch >= out_base + npix * cpo
+    return _finish(name, mma_n, nt, mma_n, act, in_need, out_pitch, 0, tiles, False, steps, jobs, list(range(nt)),
                    [-1] * nt, bias, macs_exact=macs,
-                   meta=dict(kind="conv2d", out_hw=(ho, wo), out_c=cout, out_cp=cpo, residual=bool(residual)))
+                   meta=dict(kind="conv2d", out_hw=(ho, wo), out_c=cout, out_cp=cpo, residual=bool(residual), out_base=out_base,
+                             out_elems=npix * cpo, shortcut=sc_kind))
 
 
 # ----------------------------------------------------------------------------------------------

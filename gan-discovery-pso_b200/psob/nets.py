@@ -9,7 +9,9 @@ the preceding ConvTranspose2d: w' = w * g/sqrt(var+eps), b' = (b-mean) * g/sqrt(
 """
 from __future__ import annotations
 
-from typing import Dict, List
+from typing import Dict, List, Optional
+
+import os
 
 import numpy as np
 
@@ -119,70 +121,100 @@ def fold_bn_conv(sd: Dict, conv: str, bn: str):
 
 
 class AssessorOp:
-    """One node of the assessor graph: `kind` in {"layer", "maxpool"}; buffers are named, `res` is the tensor the
-    epilogue adds before the activation."""
+    """One node of the assessor graph: `kind` in {"layer", "maxpool"}; buffers are named row-major bf16 matrices
+    [P, pitch]; a layer reads its whole source row (maps at fixed offsets) and writes `out_elems` elements at
+    `dst_off`; `res` names the buffer the epilogue adds before the activation (shortcut mode "epilogue")."""
 
-    def __init__(self, kind, src, dst, prog=None, res=None, pool=None, dst32=None):
+    def __init__(self, kind, src, dst, prog=None, res=None, pool=None, dst32=None, src_off=0, dst_off=0):
         self.kind, self.src, self.dst, self.prog, self.res, self.pool, self.dst32 = kind, src, dst, prog, res, pool, dst32
+        self.src_off, self.dst_off = src_off, dst_off
 
 
-def assessor_programs(sd: Dict):
-    """-> (ops, buffers): ops in execution order over named bf16 buffers {name: elements per particle}.
-    Input buffer "img" = the stem's zero-padded image rows (lowering.pad_image_stem); output "logits" fp32."""
-    sd = {k: v for k, v in sd.items()}
-    ops, bufs = [], {}
+SHORTCUT_MODE = os.environ.get("PSOB_SHORTCUT", "mma")     # "mma": skip connection as MMA steps; "epilogue": residual add in the epilogue
 
-    def need(name, n):
-        bufs[name] = max(bufs.get(name, 0), int(n))
 
-    w, b = fold_bn_conv(sd, "conv1", "bn1")
-    stem = L.lower_conv_image_k7s2p3("a.stem", w, b, L.ACT_RELU)
-    need("img", stem.in_pitch)
-    need("stem", stem.out_pitch)
-    ops.append(AssessorOp("layer", "img", "stem", stem))
-    h = wd = 7
-    c = 64
-    need("x0", h * wd * L.cpitch(c))
-    ops.append(AssessorOp("maxpool", "stem", "x0", pool=dict(h=14, w=14, cp=L.cpitch(c), k=3, stride=2, pad=1)))
-    cur, other = "x0", "x1"
+def _assessor_geometry(sd):
+    """[(prefix, cin, mid, stride, h_in, h_out, has_projection)] per bottleneck, for a 28x28 input."""
+    out, h, c = [], 7, 64
     for li in range(1, 5):
         bi = 0
         while f"layer{li}.{bi}.conv1.weight" in sd:
             pre = f"layer{li}.{bi}"
-            mid = int(_np(sd[f"{pre}.conv1.weight"]).shape[0])
+            mid = int(np.shape(sd[f"{pre}.conv1.weight"])[0])
             stride = 2 if (li > 1 and bi == 0) else 1
-            w1, b1 = fold_bn_conv(sd, f"{pre}.conv1", f"{pre}.bn1")
-            w2, b2 = fold_bn_conv(sd, f"{pre}.conv2", f"{pre}.bn2")
-            w3, b3 = fold_bn_conv(sd, f"{pre}.conv3", f"{pre}.bn3")
-            assert w1.shape[1] == c and w3.shape[0] == 4 * mid
-            p1 = L.lower_conv2d(f"a.{li}.{bi}.c1", w1, b1, L.ACT_RELU, h, wd, 1, 0)
-            p2 = L.lower_conv2d(f"a.{li}.{bi}.c2", w2, b2, L.ACT_RELU, h, wd, stride, 1)
-            ho, wo = p2.meta["out_hw"]
-            p3 = L.lower_conv2d(f"a.{li}.{bi}.c3", w3, b3, L.ACT_RELU, ho, wo, 1, 0, residual=True)
-            need("t1", p1.out_pitch)
-            need("t2", p2.out_pitch)
-            ops.append(AssessorOp("layer", cur, "t1", p1))
+            ho = (h + 2 - 3) // stride + 1
+            proj = f"{pre}.identity_downsample.0.weight" in sd
+            if not proj:
+                assert stride == 1 and c == 4 * mid, "an identity shortcut needs matching shapes"
+            out.append((pre, c, mid, stride, h, ho, proj))
+            h, c = ho, 4 * mid
+            bi += 1
+    return out, h, c
+
+
+def assessor_programs(sd: Dict, shortcut: Optional[str] = None):
+    """-> (ops, buffers): ops in execution order over named bf16 buffers {name: row pitch in elements}.
+    Input buffer "img" = the stem's zero-padded image rows (lowering.pad_image_stem); output "logits" fp32.
+
+    shortcut == "mma" (default): the block input x and the 3x3 conv's output t2 share one row ("cat0"/"cat1":
+    [x | t2]), and the third conv accumulates the skip connection as extra MMA steps on the same row -- identity
+    blocks for `x += identity`, the projection conv's own weights for `identity_downsample` (src/pso/util_cnn.py:
+    182-187) -- so no operand is fetched in the epilogue and the projection needs no layer of its own.
+    shortcut == "epilogue": the projection is a separate layer and the third conv adds a residual tensor in its
+    epilogue (psob_layer_run_residual)."""
+    mode = shortcut or SHORTCUT_MODE
+    assert mode in ("mma", "epilogue")
+    blocks, h_last, c_last = _assessor_geometry(sd)
+    if h_last != 1:
+        raise ValueError(f"assessor: final feature map is {h_last}x{h_last}; only inputs that reduce to 1x1 (28x28 images) are "
+                         "supported (the global max pool is then the identity)")
+    ops, bufs = [], {}
+    w, b = fold_bn_conv(sd, "conv1", "bn1")
+    stem = L.lower_conv_image_k7s2p3("a.stem", w, b, L.ACT_RELU)
+    bufs["img"], bufs["stem"] = stem.in_pitch, stem.out_pitch
+    ops.append(AssessorOp("layer", "img", "stem", stem))
+    x_max = max([49 * 64] + [ho * ho * 4 * mid for (_, _, mid, _, _, ho, _) in blocks])
+    t2_max = max(ho * ho * mid for (_, _, mid, _, _, ho, _) in blocks)
+    t2_off = x_max if mode == "mma" else 0
+    cat_pitch = x_max + t2_max if mode == "mma" else x_max
+    bufs["cat0"] = bufs["cat1"] = cat_pitch
+    bufs["t1"] = max(h * h * mid for (_, _, mid, _, h, _, _) in blocks)
+    if mode == "epilogue":
+        bufs["t2"] = t2_max
+        if any(bk[6] for bk in blocks):
+            bufs["ds"] = cat_pitch            # a residual operand has the output's row pitch
+    ops.append(AssessorOp("maxpool", "stem", "cat0", pool=dict(h=14, w=14, cp=64, k=3, stride=2, pad=1)))
+    cur, other = "cat0", "cat1"
+    for (pre, c, mid, stride, h, ho, proj) in blocks:
+        tag = "a." + pre[5:]
+        w1, b1 = fold_bn_conv(sd, f"{pre}.conv1", f"{pre}.bn1")
+        w2, b2 = fold_bn_conv(sd, f"{pre}.conv2", f"{pre}.bn2")
+        w3, b3 = fold_bn_conv(sd, f"{pre}.conv3", f"{pre}.bn3")
+        assert w1.shape[1] == c and w3.shape[0] == 4 * mid
+        p1 = L.lower_conv2d(f"{tag}.c1", w1, b1, L.ACT_RELU, h, h, 1, 0, out_pitch=bufs["t1"])
+        ops.append(AssessorOp("layer", cur, "t1", p1))
+        if proj:
+            ws, bs = fold_bn_conv(sd, f"{pre}.identity_downsample.0", f"{pre}.identity_downsample.1")
+        if mode == "mma":
+            p2 = L.lower_conv2d(f"{tag}.c2", w2, b2, L.ACT_RELU, h, h, stride, 1, out_base=t2_off, out_pitch=cat_pitch)
+            ops.append(AssessorOp("layer", "t1", cur, p2))
+            sc = ("conv", ws, bs, stride, 0, h, h, L.cpitch(c)) if proj else ("identity", 0)
+            p3 = L.lower_conv2d(f"{tag}.c3", w3, b3, L.ACT_RELU, ho, ho, 1, 0, in_base=t2_off, out_pitch=cat_pitch, shortcut=sc)
+            ops.append(AssessorOp("layer", cur, other, p3))
+        else:
+            p2 = L.lower_conv2d(f"{tag}.c2", w2, b2, L.ACT_RELU, h, h, stride, 1, out_pitch=bufs["t2"])
             ops.append(AssessorOp("layer", "t1", "t2", p2))
             res = cur
-            if f"{pre}.identity_downsample.0.weight" in sd:
-                wd_, bd_ = fold_bn_conv(sd, f"{pre}.identity_downsample.0", f"{pre}.identity_downsample.1")
-                pd = L.lower_conv2d(f"a.{li}.{bi}.ds", wd_, bd_, L.ACT_NONE, h, wd, stride, 0)
-                need("ds", pd.out_pitch)
+            if proj:
+                pd = L.lower_conv2d(f"{tag}.ds", ws, bs, L.ACT_NONE, h, h, stride, 0, out_pitch=cat_pitch)
                 ops.append(AssessorOp("layer", cur, "ds", pd))
                 res = "ds"
-            else:
-                assert stride == 1 and c == 4 * mid, "an identity shortcut needs matching shapes"
-            need(other, p3.out_pitch)
+            p3 = L.lower_conv2d(f"{tag}.c3", w3, b3, L.ACT_RELU, ho, ho, 1, 0, residual=True, out_pitch=cat_pitch)
             ops.append(AssessorOp("layer", "t2", other, p3, res=res))
-            cur, other = other, cur
-            h, wd, c = ho, wo, 4 * mid
-            bi += 1
-    if h != 1 or wd != 1:
-        raise ValueError(f"assessor: final feature map is {h}x{wd}; only inputs that reduce to 1x1 (28x28 images) are supported "
-                         "(the global max pool is then the identity)")
+        cur, other = other, cur
     wf = _np(sd["fc.weight"]).astype(np.float32)
     fc = L.lower_conv_full("a.fc", wf.reshape(wf.shape[0], wf.shape[1], 1, 1), _np(sd["fc.bias"]).astype(np.float32), L.ACT_NONE,
-                           in_cp=L.cpitch(c))
+                           in_cp=L.cpitch(c_last))
     ops.append(AssessorOp("layer", cur, None, fc, dst32="logits"))
     bufs["logits"] = fc.out32_pitch
     return ops, bufs
@@ -191,19 +223,20 @@ def assessor_programs(sd: Dict):
 def emulate_assessor(ops, bufs, img: np.ndarray, round_out=True):
     """img: [P, 28*28] values in the assessor's input range -> logits fp32 [P, n_class] (numpy emulation of the graph)."""
     p = img.shape[0]
-    x = L.pad_image_stem(L.to_bf16_f32(img) if round_out else img.astype(np.float32))
-    mem = {"img": x}
+    mem = {k: np.zeros((p, n), np.float32) for k, n in bufs.items()}
+    mem["img"] = L.pad_image_stem(L.to_bf16_f32(img) if round_out else img.astype(np.float32))
     for op in ops:
         if op.kind == "maxpool":
-            mem[op.dst] = L.maxpool_nhwc(mem[op.src], **{("wd" if k == "w" else k): v for k, v in op.pool.items()})
+            q = op.pool
+            y = L.maxpool_nhwc(mem[op.src][:, :q["h"] * q["w"] * q["cp"]], q["h"], q["w"], q["cp"], q["k"], q["stride"], q["pad"])
+            mem[op.dst][:, :y.shape[1]] = y
             continue
-        src = mem[op.src]
-        if src.shape[1] < op.prog.in_pitch:
-            src = np.concatenate([src, np.zeros((p, op.prog.in_pitch - src.shape[1]), np.float32)], axis=1)
+        pr = op.prog
         res = mem[op.res] if op.res else None
-        y, y32 = L.emulate(op.prog, src, round_out=round_out, res=res)
+        y, y32 = L.emulate(pr, mem[op.src], round_out=round_out, res=res)
         if op.dst:
-            mem[op.dst] = y
+            b0, n = pr.meta.get("out_base", 0), pr.meta.get("out_elems", pr.out_pitch)
+            mem[op.dst][:, b0:b0 + n] = y[:, b0:b0 + n]
         if op.dst32:
             mem[op.dst32] = y32
     return mem["logits"]

@@ -15,13 +15,14 @@ def _model(golden_resnet, name):
     return m
 
 
+@pytest.mark.parametrize("mode", ["mma", "epilogue"])
 @pytest.mark.parametrize("name", ["r1111_c8", "r2121_c3"])
-def test_assessor_tables_are_the_reference_arithmetic_in_fp32(golden_resnet, name, monkeypatch):
+def test_assessor_tables_are_the_reference_arithmetic_in_fp32(golden_resnet, name, mode, monkeypatch):
     """Without bf16 rounding the tables reproduce the fp32 network to summation-order noise: geometry, BN folding,
     residual wiring, max pool and border handling are exact."""
     monkeypatch.setattr(L, "ROUND_WEIGHTS", False)
     m = _model(golden_resnet, name)
-    ops, bufs = nets.assessor_programs(m.state_dict())
+    ops, bufs = nets.assessor_programs(m.state_dict(), shortcut=mode)
     x = golden_resnet["x"]
     got = nets.emulate_assessor(ops, bufs, x.reshape(x.shape[0], -1), round_out=False)
     ref = golden_resnet[f"{name}/logits"]
@@ -40,7 +41,7 @@ def test_resnet50_tables_bf16_vs_reference_logits(golden_resnet):
     sm = lambda v: torch.softmax(torch.from_numpy(v), 1).numpy()
     assert np.abs(sm(got) - sm(ref)).max() <= 3e-2
     progs = [o.prog for o in ops if o.prog is not None]
-    assert len(progs) == 1 + 16 * 3 + 4 + 1
+    assert len(progs) == 1 + 16 * 3 + 1           # projection shortcuts are folded into the third conv
     # border-aware MACs counted independently with torch: conv(ones, ones) counts the taps inside the map
     macs = 0
     h = 28
@@ -61,7 +62,11 @@ def test_resnet50_tables_bf16_vs_reference_logits(golden_resnet):
             cin, h = 4 * mid, ho
     macs += 2048 * 8
     assert sum(p.macs_exact for p in progs) == macs
-    assert all(p.meta.get("residual", False) == p.name.endswith(".c3") for p in progs)
+    assert all((p.meta.get("shortcut") is not None) == p.name.endswith(".c3") for p in progs)
+    ops_e, _ = nets.assessor_programs(m.state_dict(), shortcut="epilogue")
+    progs_e = [o.prog for o in ops_e if o.prog is not None]
+    assert len(progs_e) == 1 + 16 * 3 + 4 + 1 and sum(p.macs_exact for p in progs_e) == macs
+    assert all(p.meta.get("residual", False) == p.name.endswith(".c3") for p in progs_e)
 
 
 def test_conv2d_lowering_matches_torch_on_odd_shapes(monkeypatch):

@@ -14,7 +14,7 @@ from psob import engine, _ffi  # noqa: E402
 P = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
 m = port.Resnet([3, 4, 6, 3], 1, list(range(8)), 8).eval()
 port.seeded_fill(m, 11)
-net = engine.AssessorNet(m.state_dict(), P)
+net = engine.AssessorNet(m.state_dict(), P, shortcut=os.environ.get("PSOB_SHORTCUT"))
 img = torch.rand(P, 784, device="cuda")
 
 
@@ -40,9 +40,9 @@ for op, layer in zip(net.ops, net.layers):
     if op.kind != "layer":
         continue
     pr = op.prog
-    src = net._t(op.src, pr.in_pitch)
-    dst = net._t(op.dst, pr.out_pitch) if op.dst else None
-    res = net._t(op.res, pr.out_pitch) if op.res else None
+    src = net.buf[op.src]
+    dst = net.buf[op.dst] if op.dst else None
+    res = net.buf[op.res] if op.res else None
     y32 = net.logits if op.dst32 else None
 
     def run():

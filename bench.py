@@ -35,6 +35,9 @@ UNIT = "particle-evals/s"
 D_LATENT = 100
 PARTICLES_PER_GPU = 65536
 WORKLOAD = "DCGAN MNIST swarm=65,536 per GPU, Generator(100,1,64)+Discriminator(1,64) random init, discriminator-score fitness"
+# --workload assessor: the reference's OWN objective (configs[0]: ResNet-50 assessor, src/pso/util_cnn.py) at GPU scale
+WORKLOAD_ASSESSOR = ("DCGAN MNIST swarm=65,536 per GPU, Generator(100,1,64) random init + ResNet-50 assessor (8 classes, seeded "
+                     "trained-like parameters), the reference's Discovery.fitness (rescale, softmax pick, optimize_out_training)")
 
 
 def peaks():
@@ -61,12 +64,22 @@ def make_models(seed=42):
 # CPU baseline: the reference's per-particle loop (oracle port), bounded sample
 # ------------------------------------------------------------------------------------------------
 
-def cpu_reference_rate(n_particles=64, n_iters=2, seed=42):
-    """Times the faithful restatement of Swarm.optimize (python loop over particles, batch-1 G and D,
-    numpy fp64 state) with discriminator-score fitness.  Returns (particle-evals/s, seconds, threads)."""
+def make_assessor(seed=11):
+    from oracle import port
+    m = port.Resnet([3, 4, 6, 3], 1, list(range(8)), 8).eval()
+    port.seeded_fill(m, seed)
+    return m
+
+
+def cpu_reference_rate(n_particles=64, n_iters=2, seed=42, workload="dscore"):
+    """Times the faithful restatement of Swarm.optimize (python loop over particles, batch-1 G and D / assessor,
+    numpy fp64 state).  Returns (particle-evals/s, seconds, threads)."""
     from oracle import port
     gen, disc = make_models(seed)
-    obj = port.make_dscore_objective(gen, disc, D_LATENT)
+    if workload == "assessor":
+        obj = port.make_assessor_objective(gen, make_assessor(), D_LATENT, class_index=0)
+    else:
+        obj = port.make_dscore_objective(gen, disc, D_LATENT)
     sw = port.PortSwarm(obj, num_particles=n_particles, n_iterations=n_iters, dim_space=D_LATENT, tolerance=1e-5,
                         w_inertia=0.73, w_cogn=1.496, w_soci=1.496, compute_diversity=False)
     np.random.seed(seed)
@@ -81,21 +94,23 @@ def run_reference(args):
     if rank != 0:
         return
     torch.set_num_threads(os.cpu_count() or 1)
-    n_particles = 1024
+    n_particles = 1024 if args.workload == "dscore" else 128
     for _ in range(args.warmup):
-        cpu_reference_rate(32, 1)
+        cpu_reference_rate(32 if args.workload == "dscore" else 8, 1, workload=args.workload)
     times = []
     for _ in range(args.steps):
-        rate, dt, threads = cpu_reference_rate(n_particles, 1)
+        rate, dt, threads = cpu_reference_rate(n_particles, 1, workload=args.workload)
         times.append(dt)
     ms = 1e3 * float(np.mean(times))
     value = n_particles / (ms / 1e3)
-    sample = f"{n_particles} particles x 1 PSO iteration per step (per-particle batch-1 G+D forward, numpy fp64 update)"
+    nets_ = "G+D" if args.workload == "dscore" else "G + ResNet-50 assessor"
+    sample = f"{n_particles} particles x 1 PSO iteration per step (per-particle batch-1 {nets_} forward, numpy fp64 update)"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": sample, "host": "oracle/port.py PortSwarm (reference is pure Python; no GPU)"},
+        "config": {"workload": WORKLOAD if args.workload == "dscore" else WORKLOAD_ASSESSOR, "sample": sample,
+                   "host": "oracle/port.py PortSwarm (reference is pure Python; no GPU)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -160,8 +175,15 @@ def run_psob(args):
     first = rank * P
     gen, disc = make_models()
     gnet = engine.GeneratorNet(gen.state_dict(), P, device=dev)
-    dnet = engine.DiscriminatorNet(disc.state_dict(), P, device=dev)
-    sw = engine.SwarmEngine(P, D_LATENT, generator=gnet, fitness=engine.DScoreFitness(dnet), w_inertia=0.73, w_cogn=1.496,
+    assessor = args.workload == "assessor"
+    if assessor:
+        anet = engine.AssessorNet(make_assessor().state_dict(), P, device=dev)
+        fitness = engine.ResnetFitness(anet, 0, "optimize_out_training")
+        dnet = None
+    else:
+        dnet = engine.DiscriminatorNet(disc.state_dict(), P, device=dev)
+        fitness = engine.DScoreFitness(dnet)
+    sw = engine.SwarmEngine(P, D_LATENT, generator=gnet, fitness=fitness, w_inertia=0.73, w_cogn=1.496,
                             w_soci=1.496, seed=42, index_offset=first, max_iterations=4096, device=dev, need_image_f32=False)
     g = torch.Generator(device=dev).manual_seed(42 + rank)
     sw.init_particles(generator=g)
@@ -208,15 +230,35 @@ def run_psob(args):
             y32 = None                      # exactly what the timed step runs: D-score fitness reads the bf16 image only
         timed(layer.prog.name, lambda l=layer, c=cur, y=y, y32=y32: l.run(c, P, y, y32))
         cur = y
-    cur = gnet.image_padded_bf16()
-    for layer, y, y32 in zip(dnet.layers, dnet.acts, dnet.acts32):
-        timed(layer.prog.name, lambda l=layer, c=cur, y=y, y32=y32: l.run(c, P, y, y32))
-        cur = y
-    timed("score_fitness", lambda: engine.score_fitness(dnet.acts32[-1], sw.fit, "optimize_out_training"))
+    if assessor:
+        lib = _ffi.lib()
+        timed("assessor_pack_rescale", lambda: anet.pack(gnet.image(), True))
+        for op, layer in zip(anet.ops, anet.layers):
+            src, dst = anet.buf[op.src], (anet.buf[op.dst] if op.dst else None)
+            if op.kind == "maxpool":
+                q = op.pool
+                timed("a.maxpool", lambda s_=src, d_=dst, q=q: _ffi.check(lib.psob_maxpool_nhwc(
+                    s_.data_ptr(), s_.stride(0), P, q["h"], q["w"], q["cp"], q["k"], q["stride"], q["pad"], d_.data_ptr(), d_.stride(0),
+                    engine._stream()), "maxpool"))
+                continue
+            res = anet.buf[op.res] if op.res else None
+            timed(op.prog.name, lambda l=layer, s_=src, d_=dst, o=op, r=res: _ffi.check(lib.psob_layer_run_residual(
+                l.handle, s_.data_ptr(), s_.stride(0), P, engine._ptr(d_), engine._ptr(anet.logits if o.dst32 else None),
+                engine._ptr(r), r.stride(0) if r is not None else 0, anet.impl, engine._stream()), o.prog.name))
+        timed("softmax_score_fitness", lambda: (engine.softmax_select(anet.logits, 0, fitness.prob),
+                                                engine.score_fitness(fitness.prob, sw.fit, "optimize_out_training")))
+        stage_ms["assessor_total"] = float(sum(v for k, v in stage_ms.items() if k.startswith("a.") or k == "assessor_pack_rescale"))
+    else:
+        cur = gnet.image_padded_bf16()
+        for layer, y, y32 in zip(dnet.layers, dnet.acts, dnet.acts32):
+            timed(layer.prog.name, lambda l=layer, c=cur, y=y, y32=y32: l.run(c, P, y, y32))
+            cur = y
+        timed("score_fitness", lambda: engine.score_fitness(dnet.acts32[-1], sw.fit, "optimize_out_training"))
     timed("pbest_gbest", sw.personal_and_global_best)
     timed("pso_update", sw.move)
 
-    progs = {p.name: p for p in gnet.programs + dnet.programs}
+    fit_programs = [op.prog for op in anet.ops if op.prog is not None] if assessor else dnet.programs
+    progs = {p.name: p for p in gnet.programs + fit_programs}
     top = max((k for k in stage_ms if k in progs), key=lambda k: stage_ms[k])
     pk = peaks()
     flops = 2.0 * progs[top].macs_exact * P
@@ -234,7 +276,7 @@ def run_psob(args):
     roofline_update = {"kernel": "pso_update_kernel", "bound": "hbm", "achieved": upd_gbs, "peak": pk["hbm"], "unit": "GB/s",
                        "frac": upd_gbs / pk["hbm"], "traffic": None, "algorithmic_bytes_per_launch": upd_bytes,
                        "ms_per_launch": stage_ms["pso_update"]}
-    net_flops = 2.0 * (gnet.macs_exact + dnet.macs_exact) * P
+    net_flops = 2.0 * (gnet.macs_exact + (anet if assessor else dnet).macs_exact) * P
     tensor_frac_step = net_flops / (ms_per_step * 1e-3) / 1e12 / pk["tf_sustained"]
 
     # ---- end to end through the public API with HOST buffers -------------------------------------
@@ -306,19 +348,21 @@ def run_psob(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         torch.set_num_threads(os.cpu_count() or 1)
-        cpu_reference_rate(32, 1)
-        rate, dt, threads = cpu_reference_rate(2048, 2)
+        n_cpu = 256 if assessor else 2048
+        cpu_reference_rate(8 if assessor else 32, 1, workload=args.workload)
+        rate, dt, threads = cpu_reference_rate(n_cpu, 2, workload=args.workload)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": f"2048 particles x 2 iterations of the per-particle reference loop (oracle/port.py PortSwarm), {dt:.1f} s"}
+               "sample": f"{n_cpu} particles x 2 iterations of the per-particle reference loop (oracle/port.py PortSwarm), {dt:.1f} s"}
 
     if rank == 0:
-        launches_per_step = len(gnet.layers) + len(dnet.layers) + 1 + 3 + 1     # layers, score, pbest+candidate+apply, update
+        # layers, score, pbest+candidate+apply, update (assessor: + pack, max pool, softmax pick)
+        launches_per_step = len(gnet.layers) + (len(anet.ops) + 2 if assessor else len(dnet.layers)) + 1 + 3 + 1
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "particles_per_gpu": P, "latent_dim": D_LATENT, "parallelism": f"dp{world}",
-                       "l2_policy": "inputs_exceed_l2 (per-step working set ~5 GB)", "cuda_graph": bool(use_graph),
+            "config": {"workload": WORKLOAD_ASSESSOR if assessor else WORKLOAD, "particles_per_gpu": P, "latent_dim": D_LATENT, "parallelism": f"dp{world}",
+                       "l2_policy": "inputs_exceed_l2 (per-step working set %s)" % ("~12 GB" if assessor else "~5 GB"), "cuda_graph": bool(use_graph),
                        "state_dtype": "f32", "rng": "philox4x32-10 in-kernel"},
             "roofline": roofline, "roofline_update": roofline_update,
             "tensor_frac_whole_step": tensor_frac_step,
@@ -342,6 +386,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="psob", choices=["psob", "reference"])
     ap.add_argument("--particles", type=int, default=PARTICLES_PER_GPU, help="particles per GPU")
+    ap.add_argument("--workload", default="dscore", choices=["dscore", "assessor"],
+                    help="dscore: BASELINE configs[1] (headline); assessor: the reference's own ResNet-50 fitness at the same swarm size")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -31,7 +31,7 @@ TILE_M = 128          # particles per tile (UMMA M)
 MAX_N = 256           # UMMA N limit / TMEM columns per accumulator buffer
 
 ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3, 4
-STEP_ACCUM, STEP_B_RESIDENT, STEP_NEXT = 1, 2, 4     # NEXT: the op accumulates into the next job of the chain
+STEP_ACCUM, STEP_B_RESIDENT, STEP_NEXT, STEP_EYE = 1, 2, 4, 8     # NEXT: the op accumulates into the next job of the chain
 ROUND_WEIGHTS = True   # tests switch this off to check the geometry exactly in fp32
 # Weight packs up to RESIDENT_SOLO bytes stay in one CTA's shared memory for its lifetime; packs up to
 # RESIDENT_PAIR are split over a CTA pair (tcgen05 cta_group::2, csrc/pixel_gemm.cu) when the layer has the
@@ -40,6 +40,7 @@ RESIDENT_SOLO = 32 * 1024
 RESIDENT_PAIR = 256 * 1024 if os.environ.get("PSOB_PAIR", "1") != "0" else 0
 IMAGE_BAND = os.environ.get("PSOB_BAND", "1") != "0"       # band form of the 14x14 -> 28x28 image layer
 CHAIN_ROWS = os.environ.get("PSOB_CHAIN", "1") != "0"      # share input rows between vertically adjacent jobs (resident layers)
+EYE_OPS = os.environ.get("PSOB_EYE", "1") != "0"           # identity shortcuts as N = 64 ops on the built-in identity tile
 CHAIN_CONVT = os.environ.get("PSOB_CHAIN_CONVT", "0") != "0"   # ... also for the transposed convs (measured slower, see below)
 
 # image layouts
@@ -130,14 +131,16 @@ def pack_steps(prog: "LayerProgram") -> np.ndarray:
 
     def enc(b_row, d_col, flags):
         assert b_row % 16 == 0 and b_row // 16 < 65536 and d_col % 2 == 0 and d_col // 2 < 256
-        return (b_row // 16) | ((d_col // 2) << 16) | ((1 << 24) if flags & STEP_NEXT else 0) | ((1 << 25) if flags & STEP_ACCUM else 0)
+        return ((b_row // 16) | ((d_col // 2) << 16) | ((1 << 24) if flags & STEP_NEXT else 0) | ((1 << 25) if flags & STEP_ACCUM else 0) |
+                ((1 << 26) if flags & STEP_EYE else 0))
 
     for i, (a_col, b_row, d_col, flags) in enumerate(prog.steps):
         ops = [(int(b_row), int(d_col), int(flags))] + [tuple(map(int, o)) for o in prog.xops.get(i, [])]
         assert len(ops) <= 4
         has_next = any(f & STEP_NEXT for _, _, f in ops)
         out[i, 0] = a_col
-        out[i, 1] = len(ops) | (8 if flags & STEP_B_RESIDENT else 0) | (16 if has_next else 0)
+        assert not any(f & STEP_EYE for _, _, f in ops) or len(ops) == 1, "an identity op is the only op of its step"
+        out[i, 1] = len(ops) | (8 if flags & STEP_B_RESIDENT else 0) | (16 if has_next else 0) | (32 if flags & STEP_EYE else 0)
         for k, o in enumerate(ops):
             out[i, 2 + k] = enc(*o)
     return out
@@ -174,10 +177,11 @@ def _finish(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, tiles, b
     if chains is None:
         chains = np.stack([np.arange(jobs.shape[0]), np.ones(jobs.shape[0], np.int64)], axis=1)
     chains = np.asarray(chains, dtype=np.int32).reshape(-1, 2)
-    n_ops = int(steps.shape[0]) + sum(len(v) for v in xops.values())
+    n_eye = int(np.count_nonzero(steps[:, 3] & STEP_EYE)) if steps.size else 0
+    n_ops = int(steps.shape[0]) - n_eye + sum(len(v) for v in xops.values())
     return LayerProgram(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, wpack, b_resident, steps, jobs,
                         col_map, col_map32, bias, vec8, xops, chains, int(macs_exact),
-                        n_ops * KCHUNK * mma_n, meta or {})
+                        n_ops * KCHUNK * mma_n + n_eye * KCHUNK * KCHUNK, meta or {})
 
 
 def _mask_words(bits: List[bool]) -> Tuple[int, int]:
@@ -785,11 +789,15 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
                 assert not first, "an output pixel without any tap"
                 if sc_kind == "identity":
                     for i in range(mma_n // KCHUNK):      # channels [cg * mma_n + 64 i, + 64) of x feed columns [64 i, 64 i + 64)
+                        a_col = x_base + (pix0 + j) * cpo + cg * mma_n + i * KCHUNK
+                        if EYE_OPS:                       # N = 64 op against the engine's built-in identity tile: no weight traffic
+                            steps.append((a_col, 0, j * mma_n + i * KCHUNK, STEP_ACCUM | STEP_EYE))
+                            continue
                         def eye(i=i):
                             t = np.zeros((mma_n, KCHUNK), np.float32)
                             t[i * KCHUNK + np.arange(KCHUNK), np.arange(KCHUNK)] = 1.0
                             return t
-                        steps.append((x_base + (pix0 + j) * cpo + cg * mma_n + i * KCHUNK, tile(("eye", i), eye), j * mma_n, STEP_ACCUM))
+                        steps.append((a_col, tile(("eye", i), eye), j * mma_n, STEP_ACCUM))
                 elif sc_kind == "conv":
                     if cg == 0:
                         macs += cin_s * cout
@@ -905,6 +913,12 @@ def emulate(prog: LayerProgram, x: np.ndarray, round_out=True, res: Optional[np.
     y32 = np.zeros((p, prog.out32_pitch), np.float32) if prog.out32_pitch else None
 
     def apply(acc, a, b_row, d_col, flags):
+        if flags & STEP_EYE:                 # identity op: 64 columns (+)= the A tile itself
+            if flags & STEP_ACCUM:
+                acc[:, d_col:d_col + KCHUNK] += a.astype(np.float32)
+            else:
+                acc[:, d_col:d_col + KCHUNK] = a.astype(np.float32)
+            return
         contrib = a.astype(np.float32) @ prog.wpack[b_row:b_row + prog.mma_n].T.astype(np.float32)
         if flags & STEP_ACCUM:
             acc[:, d_col:d_col + prog.mma_n] += contrib

@@ -185,8 +185,11 @@ typedef struct {
                                 * 8 padded image rows x band_pitch columns; stored as four 64-element chunks (2 rows each) */
   const uint16_t* wpack;     /* HOST bf16 bits [n_wrows, 64] */
   const int32_t*  steps;     /* HOST [n_steps, 8]: a_col, meta, op0, op1, op2, op3, 0, 0.  One A tile (TMA load) feeds 1..4 MMA ops.
-                              * meta: bits 0-2 op count, bit 3 weights resident, bit 4 some op targets the NEXT job of the chain.
-                              * op:   bits 0-15 weight row / 16, bits 16-23 accumulator column / 2, bit 24 NEXT job, bit 25 accumulate */
+                              * meta: bits 0-2 op count, bit 3 weights resident, bit 4 some op targets the NEXT job of the chain,
+                              *       bit 5 identity step (streamed-weight layers: no weight tile is loaded).
+                              * op:   bits 0-15 weight row / 16, bits 16-23 accumulator column / 2, bit 24 NEXT job, bit 25 accumulate,
+                              *       bit 26 identity: D[:, col : col + 64] (+)= A, an N = 64 MMA against a built-in identity tile
+                              *       (the bottleneck's `x += identity`, src/pso/util_cnn.py:185, through the operand ring) */
   const int32_t*  jobs;      /* HOST [n_jobs, 8]: step_begin, step_count, out_base, out32_base, mask_lo, mask_hi, bias_row,
                               * has_chain_predecessor */
   const int32_t*  chains;    /* HOST [n_chains, 2]: first job, job count.  The jobs of a chain run back to back on one CTA, so an

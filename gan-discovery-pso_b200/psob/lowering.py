@@ -40,6 +40,8 @@ RESIDENT_SOLO = 32 * 1024
 RESIDENT_PAIR = 256 * 1024 if os.environ.get("PSOB_PAIR", "1") != "0" else 0
 IMAGE_BAND = os.environ.get("PSOB_BAND", "1") != "0"       # band form of the 14x14 -> 28x28 image layer
 CHAIN_ROWS = os.environ.get("PSOB_CHAIN", "1") != "0"      # share input rows between vertically adjacent jobs (resident layers)
+CONV2D_RESIDENT = os.environ.get("PSOB_CONV2D_RESIDENT", "1") != "0"   # small general-conv weight packs resident + shared A tiles
+CONV2D_RESIDENT_MAX = 80 * 1024
 EYE_OPS = os.environ.get("PSOB_EYE", "1") != "0"           # identity shortcuts as N = 64 ops on the built-in identity tile
 CHAIN_CONVT = os.environ.get("PSOB_CHAIN_CONVT", "0") != "0"   # ... also for the transposed convs (measured slower, see below)
 
@@ -766,6 +768,44 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
     steps, jobs = [], []
     macs = 0
     npix = ho * wo
+    # Small weight packs stay RESIDENT in shared memory (no per-step weight tile through L2, which is what bounds the
+    # N = 64 / 128 layers), and one A tile then feeds every output pixel of the job it touches (up to 4 ops per step).
+    wbytes = k * k * nkc * cpo * KCHUNK * 2
+    if CONV2D_RESIDENT and shortcut is None and not residual and ncg == 1 and wbytes <= CONV2D_RESIDENT_MAX:
+        xops = {}
+        for pix0 in range(0, npix, g):
+            sb = len(steps)
+            outs = [divmod(pix0 + j, wo) for j in range(min(g, npix - pix0))]
+            feeds = {}                      # input pixel -> [(j, ky, kx)]
+            for j, (oy, ox) in enumerate(outs):
+                for ky in range(k):
+                    for kx in range(k):
+                        iy, ix = stride * oy - pad + ky, stride * ox - pad + kx
+                        if 0 <= iy < h and 0 <= ix < wd:
+                            feeds.setdefault((iy, ix), []).append((j, ky, kx))
+                            macs += cin * cout
+            started = set()
+            for (iy, ix) in sorted(feeds):
+                for kc in range(nkc):
+                    ops = []
+                    for (j, ky, kx) in feeds[(iy, ix)]:
+                        b_row = tile((ky, kx, kc, 0), lambda: wp[:, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
+                        ops.append((b_row, j * mma_n, (STEP_ACCUM if j in started else 0) | STEP_B_RESIDENT))
+                        started.add(j)
+                    for o0 in range(0, len(ops), 4):
+                        grp = ops[o0:o0 + 4]
+                        steps.append(((iy * wd + ix) * cpi + in_base + kc * KCHUNK, grp[0][0], grp[0][1], grp[0][2]))
+                        if len(grp) > 1:
+                            xops[len(steps) - 1] = grp[1:]
+            assert len(started) == len(outs), "an output pixel without any tap"
+            lo, hi = _mask_words([pix0 + j < npix for j in range(g)])
+            jobs.append((sb, len(steps) - sb, out_base + pix0 * cpo, 0, lo, hi, 0, 0))
+        out_pitch = out_pitch or npix * cpo
+        assert out_pitch >= out_base + npix * cpo
+        return _finish(name, mma_n, nt, mma_n, act, in_need, out_pitch, 0, tiles, True, steps, jobs, list(range(nt)),
+                       [-1] * nt, [[bp[n % mma_n] for n in range(nt)]], macs_exact=macs, xops=xops,
+                       meta=dict(kind="conv2d", out_hw=(ho, wo), out_c=cout, out_cp=cpo, residual=False, out_base=out_base,
+                                 out_elems=npix * cpo, shortcut=None, hbm_bytes=2 * (h * wd * cpi + npix * cpo)))
     for pix0 in range(0, npix, g):
         for cg in range(ncg):
             sb = len(steps)
@@ -812,7 +852,10 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
     return _finish(name, mma_n, nt, mma_n, act, in_need, out_pitch, 0, tiles, False, steps, jobs, list(range(nt)),
                    [-1] * nt, bias, macs_exact=macs,
                    meta=dict(kind="conv2d", out_hw=(ho, wo), out_c=cout, out_cp=cpo, residual=bool(residual), out_base=out_base,
-                             out_elems=npix * cpo, shortcut=sc_kind))
+                             out_elems=npix * cpo, shortcut=sc_kind,
+                             # compulsory HBM traffic per particle: every input map once, the output once (bf16)
+                             hbm_bytes=2 * (h * wd * cpi + npix * cpo + (npix * cpo if (sc_kind == "identity" or residual) else 0) +
+                                            (shortcut[5] * shortcut[6] * shortcut[7] if sc_kind == "conv" else 0))))
 
 
 # ----------------------------------------------------------------------------------------------
@@ -822,6 +865,7 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
 #     from (2 oy, 8 g)); the weight tiles are position-independent.
 # ----------------------------------------------------------------------------------------------
 STEM_PAD = 3
+STEM_RESIDENT = os.environ.get("PSOB_STEM_RESIDENT", "0") != "0"     # 160 KB of stem weights resident over a CTA pair: measured no faster (MMA-bound on the zero-padded window)
 STEM_PITCH = 40
 STEM_ROWS = 36
 
@@ -853,16 +897,17 @@ def lower_conv_image_k7s2p3(name, w, b, act) -> LayerProgram:
             sb = len(steps)
             start = 2 * oy * STEM_PITCH + 2 * gox * g
             for kc in range(nk):
-                steps.append((start + kc * KCHUNK, kc * nt, 0, STEP_ACCUM if kc else 0))
+                steps.append((start + kc * KCHUNK, kc * nt, 0, (STEP_ACCUM if kc else 0) | (STEP_B_RESIDENT if STEM_RESIDENT else 0)))
             lo, hi = _mask_words([gox * g + j < wo for j in range(gox)])
             jobs.append((sb, nk, (oy * wo + gox * g) * cpo, 0, lo, hi, 0, 0))
     assert steps[-1][0] + KCHUNK <= STEM_ROWS * STEM_PITCH
     bp = np.zeros(cpo, np.float32)
     bp[:cout] = b
     taps = sum(1 for o in range(14) for kk in range(7) if 0 <= 2 * o - 3 + kk < 28)
-    return _finish(name, nt, nt, cpo, act, STEM_ROWS * STEM_PITCH, ho * wo * cpo, 0, tiles, False, steps, jobs,
+    return _finish(name, nt, nt, cpo, act, STEM_ROWS * STEM_PITCH, ho * wo * cpo, 0, tiles, STEM_RESIDENT, steps, jobs,
                    list(range(nt)), [-1] * nt, [bp[n % cpo] for n in range(nt)], macs_exact=taps * taps * cout,
-                   meta=dict(kind="conv_image_k7", out_hw=(ho, wo), out_c=cout, out_cp=cpo))
+                   meta=dict(kind="conv_image_k7", out_hw=(ho, wo), out_c=cout, out_cp=cpo,
+                             hbm_bytes=2 * (STEM_ROWS * STEM_PITCH + ho * wo * cpo)))
 
 
 def pad_image_stem(img: np.ndarray) -> np.ndarray:

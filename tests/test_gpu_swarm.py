@@ -178,3 +178,55 @@ def test_sphere_known_answer_hands_on_swarm(engine):
     sb = pso.Swarm(obj_fun=lambda p: (p ** 2).sum(dim=1), num_particles=4096, dim_space=3, n_iterations=60, batched=True, tolerance=0.0)
     sb.optimize()
     assert sb.g_best_val[-1] < 1e-4
+
+
+def test_inverter_swarm_and_on_disk_history_format(engine, golden, tmp_path):
+    """`Swarm.optimize(ood_patient=..., encoder=...)` (src/pso/util_pso.py:93-112,167-193): particles start at E(img), the
+    objective is the inverter loss; then the history pickle the PSO scripts write (src/training/pso_inverter.py:342-343)
+    read back the way `upload_pso_particles` does (src/pso/util_pso_analysis.py:16-34)."""
+    import pickle
+    from src.pso import util_pso, util_discovery
+    from src.utils import util_dcgan
+    from src.inverter.utils_ae import util_inverter
+    gen = util_dcgan.Generator(10, 1, 16)
+    gen.load_state_dict(load_sd(golden, "fit/gen"))
+    enc = util_inverter.Encoder(10, 1, 16)
+    enc.load_state_dict(load_sd(golden, "esmall"))
+    cnn = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(784, 8))
+    cnn.load_state_dict(load_sd(golden, "fit_multi/cnn"))
+    gen, enc, cnn = gen.cuda().eval(), enc.cuda().eval(), cnn.cuda().eval()
+    tg = torch.Generator().manual_seed(21)
+    ood_patient = [(torch.tanh(torch.randn(1, 1, 28, 28, generator=tg)), torch.tensor([0])) for _ in range(12)]
+    classes = [0, 2, 3, 4, 6, 7, 8, 9]
+    disc = util_discovery.Discovery(iid_class=3, model_gan=gen, model_cnn=cnn, device="cuda:0", iid_classes=classes)
+    sw = util_pso.Swarm(str(tmp_path), disc, num_particles=8, n_iterations=3, dim_space=10, device="cuda:0",
+                        tolerance=1e-5, w_inertia=0.73, w_cogn=1.496, w_soci=1.496)
+    history, hp, hv, it = sw.optimize(schedule_inertia=False, early_stopping=False, ood_patient=ood_patient, encoder=enc)
+    assert it == 4 and len(hp) == 8 and hp["particle_7"].shape == (4, 10)
+    # row 0 of every particle's history is the encoder's latent of its target image (fp32 oracle, bf16 engine)
+    pe = port.Encoder(10, 1, 16).eval()
+    pe.load_state_dict(load_sd(golden, "esmall"))
+    tgt = torch.cat([im for im, _ in ood_patient[:8]])
+    with torch.no_grad():
+        z0 = pe(tgt).reshape(8, 10).numpy()
+    got0 = np.stack([hp[f"particle_{i}"].values[0] for i in range(8)])
+    assert np.abs(got0 - z0).max() <= 2e-2 * max(1.0, np.abs(z0).max())
+    # the first global best is the minimum of the inverter loss at those positions (oracle evaluated at the engine's z0)
+    pg = port.Generator(10, 1, 16).eval()
+    pg.load_state_dict(load_sd(golden, "fit/gen"))
+    pc = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(784, 8)).eval()
+    pc.load_state_dict(load_sd(golden, "fit_multi/cnn"))
+    ass = np.concatenate([port.fitness_assessor(pg, pc, torch.from_numpy(got0[i]).float(), 10, class_index=2)[0] for i in range(8)])
+    fit_ref, _ = port.fitness_inverter(pg, torch.from_numpy(got0).float(), tgt, 10, assessor_fitness=ass)
+    assert abs(float(np.asarray(sw.g_best_val_dummy[0]).reshape(-1)[0]) - float(fit_ref.min())) <= 3e-2
+    # on-disk format: dict particle_k -> DataFrame[(iterations + 1) x D]; the consumer takes `.iloc[iteration, :]`
+    path = tmp_path / "particles_position_ood_class_0.pkl"
+    with open(path, "wb") as f:
+        pickle.dump(hp, f)
+    with open(path, "rb") as f:
+        back = pickle.load(f)
+    data = np.ones((8, 10), dtype="float32")
+    for particle_idx, p_key in enumerate(back.keys()):
+        data[particle_idx, :] = back[p_key].iloc[-1, :]
+    final = np.stack([p.pos for p in sw.swarm]).astype(np.float32)
+    assert list(back.keys()) == [f"particle_{i}" for i in range(8)] and np.array_equal(data, final)

@@ -441,14 +441,21 @@ constexpr int kStemPad = 3, kStemPitch = 40, kStemRows = 36;
 
 __global__ void __launch_bounds__(256)
 pack_image_stem_kernel(const float* __restrict__ img, long long P, int rescale, __nv_bfloat16* __restrict__ out, float* __restrict__ out32) {
-  long long p = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  // the image goes through shared memory once: float4 loads, min/max from registers, 16-byte bf16 stores
+  __shared__ __align__(16) float simg[8][784];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long p = (long long)blockIdx.x * 8 + w;
   if (p >= P) return;
-  const int lane = threadIdx.x & 31;
-  const float* x = img + p * 784;
+  const float4* x4 = reinterpret_cast<const float4*>(img + p * 784);
+  float mn = INFINITY, mx = -INFINITY;
+  for (int i = lane; i < 196; i += 32) {
+    const float4 v = __ldg(x4 + i);
+    reinterpret_cast<float4*>(simg[w])[i] = v;
+    mn = fminf(fminf(mn, fminf(v.x, v.y)), fminf(v.z, v.w));
+    mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+  }
   float lo = 0.f, range = 1.f;
   if (rescale) {
-    float mn = INFINITY, mx = -INFINITY;
-    for (int i = lane; i < 784; i += 32) { float v = x[i]; mn = fminf(mn, v); mx = fmaxf(mx, v); }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
@@ -457,16 +464,31 @@ pack_image_stem_kernel(const float* __restrict__ img, long long P, int rescale, 
     lo = mn;
     range = __fsub_rn(mx, mn);
   }
-  __nv_bfloat16* y = out + p * (kStemRows * kStemPitch);
-  for (int i = lane; i < kStemRows * kStemPitch; i += 32) {
-    const int r = i / kStemPitch - kStemPad, c = i % kStemPitch - kStemPad;
-    float v = 0.f;
-    if (r >= 0 && r < 28 && c >= 0 && c < 28) {
-      v = x[r * 28 + c];
-      if (rescale) v = __fdiv_rn(__fsub_rn(v, lo), range);
-      if (out32) out32[p * 784 + r * 28 + c] = v;
+  __syncwarp();
+  if (rescale) {
+    for (int i = lane; i < 784; i += 32) simg[w][i] = __fdiv_rn(__fsub_rn(simg[w][i], lo), range);
+    __syncwarp();
+    if (out32)
+      for (int i = lane; i < 196; i += 32) reinterpret_cast<float4*>(out32 + p * 784)[i] = reinterpret_cast<const float4*>(simg[w])[i];
+  } else if (out32) {
+    for (int i = lane; i < 196; i += 32) reinterpret_cast<float4*>(out32 + p * 784)[i] = reinterpret_cast<const float4*>(simg[w])[i];
+  }
+  uint4* y = reinterpret_cast<uint4*>(out + p * (kStemRows * kStemPitch));       // 2880 B per image: 180 x 16 B
+  for (int v = lane; v < kStemRows * kStemPitch / 8; v += 32) {
+    const int r = v / (kStemPitch / 8) - kStemPad, c0 = (v % (kStemPitch / 8)) * 8 - kStemPad;
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = c0 + e;
+      f[e] = (r >= 0 && r < 28 && c >= 0 && c < 28) ? simg[w][r * 28 + c] : 0.f;
     }
-    y[i] = __float2bfloat16_rn(v);
+    uint4 o;
+    __nv_bfloat162 t;
+    t = __floats2bfloat162_rn(f[0], f[1]); o.x = *reinterpret_cast<uint32_t*>(&t);
+    t = __floats2bfloat162_rn(f[2], f[3]); o.y = *reinterpret_cast<uint32_t*>(&t);
+    t = __floats2bfloat162_rn(f[4], f[5]); o.z = *reinterpret_cast<uint32_t*>(&t);
+    t = __floats2bfloat162_rn(f[6], f[7]); o.w = *reinterpret_cast<uint32_t*>(&t);
+    y[v] = o;
   }
 }
 
@@ -717,7 +739,8 @@ int psob_vq_nearest(const float* x, int64_t P, int32_t D, int32_t x_pitch, const
 }
 
 int psob_pack_image_stem(const float* img, int64_t P, int32_t rescale, void* out_bf16, float* out32, psob_stream_t s) {
-  if (!img || !out_bf16 || P <= 0) return fail(PSOB_E_ARG, "psob_pack_image_stem: bad arguments");
+  if (!img || !out_bf16 || P <= 0 || ((uintptr_t)img & 15) || ((uintptr_t)out_bf16 & 15) || ((uintptr_t)out32 & 15))
+    return fail(PSOB_E_ARG, "psob_pack_image_stem: bad arguments (pointers must be 16-byte aligned)");
   pack_image_stem_kernel<<<(unsigned)((P + 7) / 8), 256, 0, (cudaStream_t)s>>>(img, P, rescale, reinterpret_cast<__nv_bfloat16*>(out_bf16), out32);
   PSOB_LAUNCH_CHECK("pack_image_stem_kernel");
   return 0;

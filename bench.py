@@ -239,7 +239,7 @@ def run_psob(args):
                 q = op.pool
                 timed("a.maxpool", lambda s_=src, d_=dst, q=q: _ffi.check(lib.psob_maxpool_nhwc(
                     s_.data_ptr(), s_.stride(0), P, q["h"], q["w"], q["cp"], q["k"], q["stride"], q["pad"], d_.data_ptr(), d_.stride(0),
-                    engine._stream()), "maxpool"))
+                    int(anet.tiled[op.dst]), engine._stream()), "maxpool"))
                 continue
             res = anet.buf[op.res] if op.res else None
             timed(op.prog.name, lambda l=layer, s_=src, d_=dst, o=op, r=res: _ffi.check(lib.psob_layer_run_residual(

@@ -495,10 +495,15 @@ pack_image_stem_kernel(const float* __restrict__ img, long long P, int rescale, 
 // The assessor's own pool (3x3, stride 2, pad 1): one thread per (particle, output row, 8 channels) walks the
 // input columns once -- column maxima over the <= 3 rows (all loads independent), each feeding the one or two
 // windows it belongs to -- 6 loads per output instead of 9, with 3 W loads in flight per thread.
+// element offset of (particle p, column col) in a row-major [P, pitch] or tile-major [P/128][pitch/64][128][64] activation
+__device__ __forceinline__ long long out_offset(long long p, long long col, long long pitch, int tiled) {
+  return tiled ? (((p >> 7) * (pitch >> 6) + (col >> 6)) * 128 + (p & 127)) * 64 + (col & 63) : p * pitch + col;
+}
+
 template <int W>
 __global__ void __launch_bounds__(256)
 maxpool3x3s2_rows_kernel(const __nv_bfloat16* __restrict__ x, long long P, int h, int cp, int ho, long long x_pitch, long long y_pitch,
-                         __nv_bfloat16* __restrict__ y) {
+                         int y_tiled, __nv_bfloat16* __restrict__ y) {
   constexpr int WO = (W + 2 - 3) / 2 + 1;
   const int c8 = cp >> 3;
   const long long per = (long long)ho * c8;
@@ -535,7 +540,8 @@ maxpool3x3s2_rows_kernel(const __nv_bfloat16* __restrict__ x, long long P, int h
       if (2 * ox - 1 >= 0) m[e] = __hmax2(m[e], cm[2 * ox - 1][e]);
       if (2 * ox + 1 < W) m[e] = __hmax2(m[e], cm[2 * ox + 1][e]);
     }
-    reinterpret_cast<uint4*>(y + p * y_pitch + ((long long)oy * WO + ox) * cp)[c] = *reinterpret_cast<const uint4*>(m);
+    const long long col = ((long long)oy * WO + ox) * cp + 8 * c;
+    *reinterpret_cast<uint4*>(y + out_offset(p, col, y_pitch, y_tiled)) = *reinterpret_cast<const uint4*>(m);
   }
 }
 
@@ -543,7 +549,7 @@ maxpool3x3s2_rows_kernel(const __nv_bfloat16* __restrict__ x, long long P, int h
 // src/pso/util_cnn.py:88).  One thread per 8 channels of one output pixel; padding never wins (-inf).
 __global__ void __launch_bounds__(256)
 maxpool_nhwc_kernel(const __nv_bfloat16* __restrict__ x, long long P, int h, int w, int cp, int k, int stride, int pad, int ho, int wo,
-                    long long x_pitch, long long y_pitch, __nv_bfloat16* __restrict__ y) {
+                    long long x_pitch, long long y_pitch, int y_tiled, __nv_bfloat16* __restrict__ y) {
   const int c8 = cp >> 3;
   const long long per = (long long)ho * wo * c8;
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -575,7 +581,7 @@ maxpool_nhwc_kernel(const __nv_bfloat16* __restrict__ x, long long P, int h, int
   o.y = (__float_as_uint(m[2]) >> 16) | (__float_as_uint(m[3]) & 0xFFFF0000u);
   o.z = (__float_as_uint(m[4]) >> 16) | (__float_as_uint(m[5]) & 0xFFFF0000u);
   o.w = (__float_as_uint(m[6]) >> 16) | (__float_as_uint(m[7]) & 0xFFFF0000u);
-  reinterpret_cast<uint4*>(y + p * y_pitch + ((long long)oy * wo + ox) * cp)[c] = o;
+  *reinterpret_cast<uint4*>(y + out_offset(p, ((long long)oy * wo + ox) * cp + 8 * c, y_pitch, y_tiled)) = o;
 }
 
 extern "C" {
@@ -747,23 +753,23 @@ int psob_pack_image_stem(const float* img, int64_t P, int32_t rescale, void* out
 }
 
 int psob_maxpool_nhwc(const void* x, int64_t x_pitch, int64_t P, int32_t h, int32_t w, int32_t cp, int32_t k, int32_t stride, int32_t pad,
-                      void* y, int64_t y_pitch, psob_stream_t s) {
+                      void* y, int64_t y_pitch, int32_t y_tiled, psob_stream_t s) {
   if (!x || !y || P <= 0 || h <= 0 || w <= 0 || cp <= 0 || cp % 8 || k <= 0 || stride <= 0 || pad < 0 || 2 * pad > k)
     return fail(PSOB_E_ARG, "psob_maxpool_nhwc: bad arguments");
   const int ho = (h + 2 * pad - k) / stride + 1, wo = (w + 2 * pad - k) / stride + 1;
   if (ho <= 0 || wo <= 0 || x_pitch < (int64_t)h * w * cp || y_pitch < (int64_t)ho * wo * cp || x_pitch % 8 || y_pitch % 8 ||
-      ((uintptr_t)x & 15) || ((uintptr_t)y & 15))
+      ((uintptr_t)x & 15) || ((uintptr_t)y & 15) || (y_tiled && (y_pitch % 64 || cp % 64)))
     return fail(PSOB_E_ARG, "psob_maxpool_nhwc: pitches must cover the maps and keep 16-byte alignment");
   if (k == 3 && stride == 2 && pad == 1 && w == 14) {
     const long long rows = (long long)P * ho * (cp / 8);
     maxpool3x3s2_rows_kernel<14><<<(unsigned)((rows + 255) / 256), 256, 0, (cudaStream_t)s>>>(
-        reinterpret_cast<const __nv_bfloat16*>(x), P, h, cp, ho, x_pitch, y_pitch, reinterpret_cast<__nv_bfloat16*>(y));
+        reinterpret_cast<const __nv_bfloat16*>(x), P, h, cp, ho, x_pitch, y_pitch, y_tiled, reinterpret_cast<__nv_bfloat16*>(y));
     PSOB_LAUNCH_CHECK("maxpool3x3s2_rows_kernel");
     return 0;
   }
   const long long total = (long long)P * ho * wo * (cp / 8);
   maxpool_nhwc_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)s>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), P, h, w, cp, k, stride, pad, ho, wo, x_pitch, y_pitch, reinterpret_cast<__nv_bfloat16*>(y));
+      reinterpret_cast<const __nv_bfloat16*>(x), P, h, w, cp, k, stride, pad, ho, wo, x_pitch, y_pitch, y_tiled, reinterpret_cast<__nv_bfloat16*>(y));
   PSOB_LAUNCH_CHECK("maxpool_nhwc_kernel");
   return 0;
 }

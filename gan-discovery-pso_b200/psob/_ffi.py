@@ -86,7 +86,7 @@ def lib():
         "psob_pairwise_distance_sum": ([vp, i64, i32, i32, vp, vp], C.c_int),
         "psob_vq_nearest": ([vp, i64, i32, i32, vp, i32, vp, vp, vp], C.c_int),
         "psob_pack_image_stem": ([vp, i64, i32, vp, vp, vp], C.c_int),
-        "psob_maxpool_nhwc": ([vp, i64, i64, i32, i32, i32, i32, i32, i32, vp, i64, vp], C.c_int),
+        "psob_maxpool_nhwc": ([vp, i64, i64, i32, i32, i32, i32, i32, i32, vp, i64, i32, vp], C.c_int),
         "psob_layer_create": ([C.POINTER(LayerDesc), C.POINTER(vp)], C.c_int),
         "psob_layer_destroy": ([vp], C.c_int),
         "psob_layer_run": ([vp, vp, i64, i64, vp, vp, i32, vp], C.c_int),

@@ -198,9 +198,15 @@ class AssessorNet:
         self.P, self.impl = P, impl
         self.ops, sizes = nets.assessor_programs(_sd_numpy(state_dict), shortcut=shortcut)
         self.n_class = sizes["logits"]
+        # Buffers written and read by engine layers only (everything after the max pool) use the tile-major layout
+        # [ceil(P/128)][pitch/64][128][64]: every operand tile and epilogue chunk is one contiguous 16 KB block.
+        tiled_ok = os.environ.get("PSOB_TILED", "1") != "0"
+        self.tiled = {k: tiled_ok and k not in ("img", "stem", "logits") for k in sizes}
+        rows = (P + L.TILE_M - 1) // L.TILE_M * L.TILE_M
         with torch.cuda.device(self.device):
-            self.layers = [Layer(op.prog) if op.kind == "layer" else None for op in self.ops]
-            self.buf = {k: torch.zeros(P, n, dtype=torch.bfloat16, device=self.device) for k, n in sizes.items() if k != "logits"}
+            self.layers = [Layer(op.prog, in_tiled=self.tiled[op.src], out_tiled=bool(op.dst) and self.tiled[op.dst])
+                           if op.kind == "layer" else None for op in self.ops]
+            self.buf = {k: torch.zeros(rows, n, dtype=torch.bfloat16, device=self.device)[:P] for k, n in sizes.items() if k != "logits"}
             self.logits = torch.zeros(P, self.n_class, dtype=torch.float32, device=self.device)
             self.rescaled = None
 
@@ -228,7 +234,8 @@ class AssessorNet:
             if op.kind == "maxpool":
                 q = op.pool
                 _ffi.check(lib.psob_maxpool_nhwc(src.data_ptr(), src.stride(0), self.P, q["h"], q["w"], q["cp"], q["k"], q["stride"],
-                                                 q["pad"], dst.data_ptr(), dst.stride(0), _stream()), "psob_maxpool_nhwc")
+                                                 q["pad"], dst.data_ptr(), dst.stride(0), int(self.tiled[op.dst]), _stream()),
+                           "psob_maxpool_nhwc")
                 continue
             pr = op.prog
             assert dst is None or dst.stride(0) == pr.out_pitch

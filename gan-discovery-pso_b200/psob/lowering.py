@@ -687,7 +687,7 @@ def lower_conv_image_k4s2p1(name, w, b, act) -> LayerProgram:
 #      src/inverter/utils_ae/util_inverter.py:173).  N = Cout padded to 16; fp32 output.
 # ----------------------------------------------------------------------------------------------
 
-def lower_conv_full(name, w, b, act, in_cp=None) -> LayerProgram:
+def lower_conv_full(name, w, b, act, in_cp=None, in_pitch=None) -> LayerProgram:
     cout, cin, k, _ = w.shape
     cpi = in_cp or cpitch(cin)
     nt = rup(cout, 16)
@@ -705,7 +705,7 @@ def lower_conv_full(name, w, b, act, in_cp=None) -> LayerProgram:
     bias = np.zeros(nt, np.float32)
     bias[:cout] = b
     cm32 = [n if n < cout else -1 for n in range(nt)]
-    return _finish(name, nt, nt, nt, act, k * k * cpi, 0, cout, tiles, False,
+    return _finish(name, nt, nt, nt, act, max(k * k * cpi, in_pitch or 0), 0, cout, tiles, False,
                    steps, jobs, [-1] * nt, cm32, bias, macs_exact=cin * cout * k * k,
                    meta=dict(kind="conv_full", out_c=cout))
 
@@ -720,7 +720,7 @@ def lower_conv_full(name, w, b, act, in_cp=None) -> LayerProgram:
 # ----------------------------------------------------------------------------------------------
 
 def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False, in_base=0, out_base=0, out_pitch=None,
-                 shortcut=None) -> LayerProgram:
+                 shortcut=None, in_pitch=None) -> LayerProgram:
     """`in_base` / `out_base`: element offsets of the input map / the output map inside their particle rows (several
     maps may share one row-major buffer); `out_pitch`: row pitch of the output buffer (default: the map itself).
     `shortcut` folds the bottleneck's skip connection into the SAME accumulator as further MMA steps, so that its
@@ -741,7 +741,7 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
     wp[:cout, :cin] = w
     bp = np.zeros(cpo, np.float32)
     bp[:cout] = b
-    in_need = in_base + h * wd * cpi
+    in_need = max(in_base + h * wd * cpi, in_pitch or 0)      # in_pitch: row pitch of the (shared) input buffer
     sc_kind = shortcut[0] if shortcut else None
     if sc_kind == "identity":
         x_base = shortcut[1]

@@ -191,30 +191,32 @@ def assessor_programs(sd: Dict, shortcut: Optional[str] = None):
         w2, b2 = fold_bn_conv(sd, f"{pre}.conv2", f"{pre}.bn2")
         w3, b3 = fold_bn_conv(sd, f"{pre}.conv3", f"{pre}.bn3")
         assert w1.shape[1] == c and w3.shape[0] == 4 * mid
-        p1 = L.lower_conv2d(f"{tag}.c1", w1, b1, L.ACT_RELU, h, h, 1, 0, out_pitch=bufs["t1"])
+        p1 = L.lower_conv2d(f"{tag}.c1", w1, b1, L.ACT_RELU, h, h, 1, 0, out_pitch=bufs["t1"], in_pitch=cat_pitch)
         ops.append(AssessorOp("layer", cur, "t1", p1))
         if proj:
             ws, bs = fold_bn_conv(sd, f"{pre}.identity_downsample.0", f"{pre}.identity_downsample.1")
         if mode == "mma":
-            p2 = L.lower_conv2d(f"{tag}.c2", w2, b2, L.ACT_RELU, h, h, stride, 1, out_base=t2_off, out_pitch=cat_pitch)
+            p2 = L.lower_conv2d(f"{tag}.c2", w2, b2, L.ACT_RELU, h, h, stride, 1, out_base=t2_off, out_pitch=cat_pitch,
+                                in_pitch=bufs["t1"])
             ops.append(AssessorOp("layer", "t1", cur, p2))
             sc = ("conv", ws, bs, stride, 0, h, h, L.cpitch(c)) if proj else ("identity", 0)
-            p3 = L.lower_conv2d(f"{tag}.c3", w3, b3, L.ACT_RELU, ho, ho, 1, 0, in_base=t2_off, out_pitch=cat_pitch, shortcut=sc)
+            p3 = L.lower_conv2d(f"{tag}.c3", w3, b3, L.ACT_RELU, ho, ho, 1, 0, in_base=t2_off, out_pitch=cat_pitch, shortcut=sc,
+                                in_pitch=cat_pitch)
             ops.append(AssessorOp("layer", cur, other, p3))
         else:
-            p2 = L.lower_conv2d(f"{tag}.c2", w2, b2, L.ACT_RELU, h, h, stride, 1, out_pitch=bufs["t2"])
+            p2 = L.lower_conv2d(f"{tag}.c2", w2, b2, L.ACT_RELU, h, h, stride, 1, out_pitch=bufs["t2"], in_pitch=bufs["t1"])
             ops.append(AssessorOp("layer", "t1", "t2", p2))
             res = cur
             if proj:
-                pd = L.lower_conv2d(f"{tag}.ds", ws, bs, L.ACT_NONE, h, h, stride, 0, out_pitch=cat_pitch)
+                pd = L.lower_conv2d(f"{tag}.ds", ws, bs, L.ACT_NONE, h, h, stride, 0, out_pitch=cat_pitch, in_pitch=cat_pitch)
                 ops.append(AssessorOp("layer", cur, "ds", pd))
                 res = "ds"
-            p3 = L.lower_conv2d(f"{tag}.c3", w3, b3, L.ACT_RELU, ho, ho, 1, 0, residual=True, out_pitch=cat_pitch)
+            p3 = L.lower_conv2d(f"{tag}.c3", w3, b3, L.ACT_RELU, ho, ho, 1, 0, residual=True, out_pitch=cat_pitch, in_pitch=bufs["t2"])
             ops.append(AssessorOp("layer", "t2", other, p3, res=res))
         cur, other = other, cur
     wf = _np(sd["fc.weight"]).astype(np.float32)
     fc = L.lower_conv_full("a.fc", wf.reshape(wf.shape[0], wf.shape[1], 1, 1), _np(sd["fc.bias"]).astype(np.float32), L.ACT_NONE,
-                           in_cp=L.cpitch(c_last))
+                           in_cp=L.cpitch(c_last), in_pitch=cat_pitch)
     ops.append(AssessorOp("layer", cur, None, fc, dst32="logits"))
     bufs["logits"] = fc.out32_pitch
     return ops, bufs

@@ -147,9 +147,10 @@ int psob_pack_image(const float* img, int64_t P, void* out_bf16, psob_stream_t s
  * with a 40-element row pitch (the stem's banded-GEMM input); rescale != 0 applies the per-image min-max rescale
  * (src/utils/util_data.py:129-135) first; out32 (optional, fp32 [P, 784]) receives the rescaled image. */
 int psob_pack_image_stem(const float* img, int64_t P, int32_t rescale, void* out_bf16, float* out32, psob_stream_t s);
-/* MaxPool2d(k, stride, pad) on a bf16 NHWC activation [P, h * w * cp] (src/pso/util_cnn.py:88), cp % 8 == 0. */
+/* MaxPool2d(k, stride, pad) on a bf16 NHWC activation [P, h * w * cp] (src/pso/util_cnn.py:88), cp % 8 == 0.
+ * y_tiled != 0: y is tile-major [ceil(P/128)][y_pitch/64][128][64] (the engine's internal activation layout). */
 int psob_maxpool_nhwc(const void* x, int64_t x_pitch, int64_t P, int32_t h, int32_t w, int32_t cp, int32_t k, int32_t stride,
-                      int32_t pad, void* y, int64_t y_pitch, psob_stream_t s);
+                      int32_t pad, void* y, int64_t y_pitch, int32_t y_tiled, psob_stream_t s);
 /* Swarm.mse (src/pso/util_pso.py:76-86): *sum_out (device double) = sum over unordered pairs i < j of |pos_i - pos_j|_2;
  * the caller divides by P (P - 1) / 2.  pos: fp32 [P, pitch], D <= pitch. */
 int psob_pairwise_distance_sum(const float* pos, int64_t P, int32_t D, int32_t pitch, double* sum_out, psob_stream_t s);

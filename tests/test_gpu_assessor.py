@@ -77,14 +77,18 @@ def test_stem_pack_rescale_and_maxpool_bit_exact(engine):
     x = torch.randn(37, 14 * 14 * 64, generator=gen).bfloat16()
     y = torch.zeros(37, 7 * 7 * 64, dtype=torch.bfloat16, device="cuda")
     xc = x.cuda()
-    _ffi.check(_ffi.lib().psob_maxpool_nhwc(xc.data_ptr(), xc.stride(0), 37, 14, 14, 64, 3, 2, 1, y.data_ptr(), y.stride(0), None), "maxpool")
+    _ffi.check(_ffi.lib().psob_maxpool_nhwc(xc.data_ptr(), xc.stride(0), 37, 14, 14, 64, 3, 2, 1, y.data_ptr(), y.stride(0), 0, None), "maxpool")
     ref = torch.nn.functional.max_pool2d(x.float().view(37, 14, 14, 64).permute(0, 3, 1, 2), 3, 2, 1).permute(0, 2, 3, 1).reshape(37, -1)
     assert torch.equal(y.float().cpu(), ref)
+    # tile-major output (the engine's internal layout) holds the same values
+    yt = torch.zeros(128, 7 * 7 * 64, dtype=torch.bfloat16, device="cuda")
+    _ffi.check(_ffi.lib().psob_maxpool_nhwc(xc.data_ptr(), xc.stride(0), 37, 14, 14, 64, 3, 2, 1, yt.data_ptr(), yt.stride(0), 1, None), "maxpool")
+    assert torch.equal(engine.untile(yt, 37).float().cpu(), ref)
     # the general kernel (any window): 2x2 stride 1 pad 1 on a 7x5 map with 128 channels, into a wider output row
     x = torch.randn(37, 7 * 5 * 128, generator=gen).bfloat16()
     xc = x.cuda()
     y = torch.zeros(37, 8 * 6 * 128 + 64, dtype=torch.bfloat16, device="cuda")
-    _ffi.check(_ffi.lib().psob_maxpool_nhwc(xc.data_ptr(), xc.stride(0), 37, 7, 5, 128, 2, 1, 1, y.data_ptr(), y.stride(0), None), "maxpool")
+    _ffi.check(_ffi.lib().psob_maxpool_nhwc(xc.data_ptr(), xc.stride(0), 37, 7, 5, 128, 2, 1, 1, y.data_ptr(), y.stride(0), 0, None), "maxpool")
     ref = torch.nn.functional.max_pool2d(x.float().view(37, 7, 5, 128).permute(0, 3, 1, 2), 2, 1, 1).permute(0, 2, 3, 1).reshape(37, -1)
     assert torch.equal(y[:, :8 * 6 * 128].float().cpu(), ref) and float(y[:, 8 * 6 * 128:].abs().max()) == 0.0
 

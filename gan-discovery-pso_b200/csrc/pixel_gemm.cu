@@ -109,6 +109,36 @@ __device__ __forceinline__ float act_fn(float v) {
   return v;
 }
 
+// Two accumulator values -> bias -> activation -> one packed bf16x2 word, on Blackwell's packed fp32 pipe:
+// add.rn.f32x2 (FADD2) for the bias, mul.rn.f32x2 (FMUL2) for the leaky slope, cvt.rn.relu.bf16x2.f32 folds ReLU into
+// the conversion.  Each lane is an ordinary round-to-nearest fp32 op, so the results are bit-identical to the
+// scalar form; the epilogue is issue-bound (2 warps per scheduler), and this halves its arithmetic instructions.
+template <int kAct>
+__device__ __forceinline__ uint32_t bias_act_pack(uint32_t v0, uint32_t v1, float b0, float b1) {
+  if (kAct == PSOB_ACT_TANH || kAct == PSOB_ACT_SIGMOID)
+    return pack_bf16x2(act_fn<kAct>(__uint_as_float(v0) + b0), act_fn<kAct>(__uint_as_float(v1) + b1));
+  unsigned long long s;
+  float lo, hi;
+  uint32_t d;
+  asm("{\n\t.reg .b64 a, b;\n\tmov.b64 a, {%1, %2};\n\tmov.b64 b, {%3, %4};\n\tadd.rn.f32x2 %0, a, b;\n\t}"
+      : "=l"(s) : "r"(v0), "r"(v1), "f"(b0), "f"(b1));
+  if (kAct == PSOB_ACT_LEAKY) {
+    unsigned long long t;
+    float tl, th;
+    asm("{\n\t.reg .b64 c;\n\tmov.b64 c, {%1, %1};\n\tmul.rn.f32x2 %0, %2, c;\n\t}" : "=l"(t) : "f"(0.2f), "l"(s));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(s));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(tl), "=f"(th) : "l"(t));
+    lo = fmaxf(lo, tl);
+    hi = fmaxf(hi, th);
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
+  }
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(s));
+  if (kAct == PSOB_ACT_RELU) asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+
 // kTmaStore: bf16 NHWC outputs whose 64-column chunks are contiguous 128-byte rows leave through a
 // swizzled shared-memory tile and one TMA store per chunk (two epilogue groups alternate chunks);
 // otherwise (image / score outputs, nt = 16..64) group 0 stores directly from registers.
@@ -487,10 +517,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 }
               }
               uint4 o;
-              o.x = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 0]) + b0.x), act_fn<kAct>(__uint_as_float(v[8 * j + 1]) + b0.y));
-              o.y = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 2]) + b0.z), act_fn<kAct>(__uint_as_float(v[8 * j + 3]) + b0.w));
-              o.z = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 4]) + b1.x), act_fn<kAct>(__uint_as_float(v[8 * j + 5]) + b1.y));
-              o.w = pack_bf16x2(act_fn<kAct>(__uint_as_float(v[8 * j + 6]) + b1.z), act_fn<kAct>(__uint_as_float(v[8 * j + 7]) + b1.w));
+              o.x = bias_act_pack<kAct>(v[8 * j + 0], v[8 * j + 1], b0.x, b0.y);
+              o.y = bias_act_pack<kAct>(v[8 * j + 2], v[8 * j + 3], b0.z, b0.w);
+              o.z = bias_act_pack<kAct>(v[8 * j + 4], v[8 * j + 5], b1.x, b1.y);
+              o.w = bias_act_pack<kAct>(v[8 * j + 6], v[8 * j + 7], b1.z, b1.w);
               ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);   // SWIZZLE_128B: 16-byte slot j of row r lives at j ^ (r % 8)
             };
             if (q_band) {

@@ -23,9 +23,17 @@ for _p in (ROOT, os.path.join(ROOT, "gan-discovery-pso_b200")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
-# rank 0 prints exactly one JSON line on stdout: keep NCCL's version banner (NCCL_DEBUG=VERSION on some boxes) off it
-if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-    os.environ["NCCL_DEBUG"] = "WARN"
+# Rank 0 prints exactly ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to
+# stdout at NCCL_DEBUG >= VERSION), so file descriptor 1 is pointed at stderr for the whole run and the JSON line
+# goes to the saved original descriptor.
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+sys.stdout.flush()
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
 
 import numpy as np
 import torch
@@ -115,7 +123,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -384,7 +392,7 @@ def run_psob(args):
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks.summary(),
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -139,3 +139,35 @@ def test_dropin_discovery_with_mirror_resnet(engine, golden_resnet):
         history, _, _, it = sw.optimize(schedule_inertia=False, early_stopping=False)
     assert it == 5 and 0.1 <= float(np.asarray(sw.g_best_val[-1]).reshape(-1)[0]) <= 1.1
     assert all(b <= a for a, b in zip(sw.g_best_val, sw.g_best_val[1:]))
+
+
+def test_full_size_assessor_size_independent_properties(engine, golden_resnet):
+    """ResNet-50 assessor at the bench size (65 536 images): an image's logits do not depend on its batch (whole batch ==
+    two halves == reversed order, bit for bit); the golden images planted in the batch give the golden logits; 24 random
+    rows agree with the fp32 oracle."""
+    P = 65536
+    m = _model(golden_resnet, "r50_c8")
+    gen = torch.Generator(device="cuda").manual_seed(4)
+    base = torch.rand(P, 784, generator=gen, device="cuda")
+    # structured images: low-frequency fields, so that logits differ between rows
+    coarse = torch.rand(P, 1, 4, 4, generator=gen, device="cuda")
+    x = (0.3 * base + torch.nn.functional.interpolate(coarse, size=28, mode="bilinear").reshape(P, 784)).contiguous()
+    gx = torch.from_numpy(golden_resnet["x"]).reshape(-1, 784).cuda()
+    x[1000:1000 + gx.shape[0]] = gx
+    x[P - gx.shape[0]:] = gx
+    whole = engine.AssessorNet(m.state_dict(), P).forward(x).clone()
+    assert bool(torch.isfinite(whole).all())
+    half = engine.AssessorNet(m.state_dict(), P // 2)
+    a = half.forward(x[:P // 2].contiguous()).clone()
+    b = half.forward(x[P // 2:].contiguous()).clone()
+    assert torch.equal(torch.cat([a, b]), whole)
+    del half
+    rev = engine.AssessorNet(m.state_dict(), P).forward(x.flip(0).contiguous())
+    assert torch.equal(rev.flip(0), whole)
+    ref = golden_resnet["r50_c8/logits"]
+    for s in (1000, P - gx.shape[0]):
+        assert np.abs(whole[s:s + gx.shape[0]].cpu().numpy() - ref).max() <= 0.03 * np.abs(ref).max()
+    idx = torch.randperm(P, generator=torch.Generator().manual_seed(2))[:24]
+    with torch.no_grad():
+        oracle = m(x[idx.cuda()].cpu().view(-1, 1, 28, 28)).numpy()
+    assert np.abs(whole[idx.cuda()].cpu().numpy() - oracle).max() <= 0.03 * np.abs(oracle).max()

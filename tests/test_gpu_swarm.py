@@ -230,3 +230,56 @@ def test_inverter_swarm_and_on_disk_history_format(engine, golden, tmp_path):
         data[particle_idx, :] = back[p_key].iloc[-1, :]
     final = np.stack([p.pos for p in sw.swarm]).astype(np.float32)
     assert list(back.keys()) == [f"particle_{i}" for i in range(8)] and np.array_equal(data, final)
+
+
+def test_full_size_step_size_independent_properties(engine):
+    """BASELINE configs[1] at its full size (65 536 particles, Generator(100,1,64) + Discriminator(1,64)), where the
+    oracle cannot run: properties that do not depend on the size.  (1) A particle's fitness does not depend on which
+    other particles share its batch: the swarm evaluated whole, as two shards with global indices, and in reversed
+    order gives the same bits per particle.  (2) pbest / gbest are the strict-< rules applied to that vector.
+    (3) The Philox move depends on the GLOBAL index only.  (4) 48 particles spot-checked against the oracle."""
+    P, D = 65536, 100
+    gen, disc = _models(5)
+    g = torch.Generator(device="cuda").manual_seed(11)
+    pos0 = torch.randn(P, D, generator=g, device="cuda")
+    vel0 = (torch.randn(P, D, generator=g, device="cuda") - 0.5) / 10
+
+    def one_step(pos, vel, offset):
+        n = pos.shape[0]
+        gnet = engine.GeneratorNet(gen.state_dict(), n)
+        dnet = engine.DiscriminatorNet(disc.state_dict(), n)
+        sw = engine.SwarmEngine(n, D, generator=gnet, fitness=engine.DScoreFitness(dnet), w_inertia=0.73, w_cogn=1.496,
+                                w_soci=1.496, seed=42, index_offset=offset)
+        sw.init_particles(pos=pos, vel=vel)
+        sw.evaluate()
+        fit = sw.fit.clone()
+        sw.personal_and_global_best()
+        return sw, fit
+
+    whole, fit = one_step(pos0, vel0, 0)
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(fit).all()) and 0.1 <= float(fit.min()) and float(fit.max()) <= 1.1
+    # (1) batch-composition independence, bit for bit
+    h = P // 2
+    _, fit_a = one_step(pos0[:h].contiguous(), vel0[:h].contiguous(), 0)
+    _, fit_b = one_step(pos0[h:].contiguous(), vel0[h:].contiguous(), h)
+    assert torch.equal(torch.cat([fit_a, fit_b]), fit)
+    _, fit_r = one_step(pos0.flip(0).contiguous(), vel0.flip(0).contiguous(), 0)
+    assert torch.equal(fit_r.flip(0), fit)
+    # (2) the reference's rules on the engine's own fitness vector (src/pso/util_pso.py:122-124,135-151)
+    f = fit.cpu().numpy()
+    gval, gidx = port.gbest_scan(f, np.inf)
+    assert np.array_equal(whole.pbest_val.cpu().numpy(), f) and float(whole.gbest_val) == gval
+    assert gidx == int(np.flatnonzero(f == f.min())[0])
+    assert torch.equal(whole.gbest_pos[:D], pos0[gidx])
+    # (3) the move: shards with global indices reproduce the whole swarm's trajectory bit for bit
+    whole.move()
+    r1, r2 = port.philox_r1r2(42, 1, 0, P)
+    rows = np.r_[0:8, h - 4:h + 4, P - 8:P]
+    p_ref, v_ref = port.pso_move(pos0.cpu().numpy()[rows], vel0.cpu().numpy()[rows], pos0.cpu().numpy()[rows],
+                                 pos0[gidx].cpu().numpy(), r1[rows], r2[rows], 0.73, 1.496, 1.496, dtype=np.float32)
+    assert np.array_equal(whole.pos.cpu().numpy()[rows, :D], p_ref) and np.array_equal(whole.vel.cpu().numpy()[rows, :D], v_ref)
+    # (4) spot check against the fp32 oracle
+    idx = torch.randperm(P, generator=torch.Generator().manual_seed(1))[:48]
+    fit_ref, _ = port.fitness_dscore(gen, disc, pos0[idx.cuda()].cpu(), D)
+    np.testing.assert_allclose(f[idx.numpy()], fit_ref, atol=5e-3, rtol=0)

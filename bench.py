@@ -58,34 +58,71 @@ def peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
 
 
-def make_models(seed=42):
-    from oracle import port
+def make_models(seed=42, oracle=False):
+    """Synthetic weights of the BASELINE configs[1] networks with the reference's init (src/utils/util_dcgan.py:45-48).
+    The GPU arm builds them with the product's own modules; only the CPU legs (cpu_baseline / --impl reference) use
+    the oracle's torch modules (same constructors and draws, so both arms see the same weights)."""
+    if oracle:
+        from oracle import port as M
+    else:
+        from src.utils import util_dcgan as M
     torch.manual_seed(seed)
-    gen = port.Generator(D_LATENT, 1, 64)
-    disc = port.Discriminator(1, 64)
-    port.initialize_weights(gen)          # the reference's init (src/utils/util_dcgan.py:45-48)
-    port.initialize_weights(disc)
+    gen = M.Generator(D_LATENT, 1, 64)
+    disc = M.Discriminator(1, 64)
+    M.initialize_weights(gen)
+    M.initialize_weights(disc)
     return gen.eval(), disc.eval()
+
+
+def seeded_fill(model, seed):
+    """'Trained-like' synthetic ResNet parameters, independent of construction order: every state_dict entry drawn in
+    sorted-key order from one seeded generator (conv N(0, 2/fan_in), BN gamma U(0.7, 1.3) / U(0.1, 0.4) for a block's last
+    BN, beta and running_mean N(0, 0.1), running_var U(0.5, 1.5), fc N(0, 0.07)) -- same draws as the test fixtures."""
+    gen = torch.Generator().manual_seed(seed)
+    sd = model.state_dict()
+    with torch.no_grad():
+        for k in sorted(sd.keys()):
+            v = sd[k]
+            if k.endswith("num_batches_tracked"):
+                continue
+            if v.dim() == 4:
+                v.copy_(torch.randn(v.shape, generator=gen) * (2.0 / (v.shape[1] * v.shape[2] * v.shape[3])) ** 0.5)
+            elif k.endswith("running_var"):
+                v.copy_(torch.rand(v.shape, generator=gen) + 0.5)
+            elif k.endswith("running_mean"):
+                v.copy_(torch.randn(v.shape, generator=gen) * 0.1)
+            elif k.startswith("fc."):
+                v.copy_(torch.randn(v.shape, generator=gen) * (0.07 if v.dim() == 2 else 0.1))
+            elif k.endswith(".weight"):
+                lo, hi = (0.1, 0.4) if ".bn3." in k else (0.7, 1.3)
+                v.copy_(torch.rand(v.shape, generator=gen) * (hi - lo) + lo)
+            else:
+                v.copy_(torch.randn(v.shape, generator=gen) * 0.1)
+
+
+def make_assessor(seed=11, oracle=False):
+    """ResNet-50 assessor of configs[0] (8 classes, 1-channel 28x28) with synthetic parameters."""
+    if oracle:
+        from oracle import port
+        m = port.Resnet([3, 4, 6, 3], 1, list(range(8)), 8).eval()
+    else:
+        from src.pso import util_cnn
+        m = util_cnn.get_cnn("ResNet50", 1, iid_classes=list(range(8)), n_class=8).eval()
+    seeded_fill(m, seed)
+    return m
 
 
 # ------------------------------------------------------------------------------------------------
 # CPU baseline: the reference's per-particle loop (oracle port), bounded sample
 # ------------------------------------------------------------------------------------------------
 
-def make_assessor(seed=11):
-    from oracle import port
-    m = port.Resnet([3, 4, 6, 3], 1, list(range(8)), 8).eval()
-    port.seeded_fill(m, seed)
-    return m
-
-
 def cpu_reference_rate(n_particles=64, n_iters=2, seed=42, workload="dscore"):
     """Times the faithful restatement of Swarm.optimize (python loop over particles, batch-1 G and D / assessor,
     numpy fp64 state).  Returns (particle-evals/s, seconds, threads)."""
     from oracle import port
-    gen, disc = make_models(seed)
+    gen, disc = make_models(seed, oracle=True)
     if workload == "assessor":
-        obj = port.make_assessor_objective(gen, make_assessor(), D_LATENT, class_index=0)
+        obj = port.make_assessor_objective(gen, make_assessor(oracle=True), D_LATENT, class_index=0)
     else:
         obj = port.make_dscore_objective(gen, disc, D_LATENT)
     sw = port.PortSwarm(obj, num_particles=n_particles, n_iterations=n_iters, dim_space=D_LATENT, tolerance=1e-5,

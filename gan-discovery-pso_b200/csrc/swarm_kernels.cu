@@ -380,12 +380,97 @@ pairwise_distance_sum_kernel(const float* __restrict__ pos, long long P, int D, 
 
 // ------------------------------------------------------------------------------------------
 // Nearest codebook entry -- `vq` (src/inverter/utils_vq_vae/util_function.py:4-23):
-// argmin_k (|c_k|^2 + |x|^2 - 2 x.c_k), lowest k on ties (torch.min).  One warp per input row; the
-// codebook is staged through shared memory in slabs of rows (pitch D + 1), lane l scans entries
-// l, l + 32, ...; the warp reduces (distance, index) lexicographically.
+// argmin_k (|c_k|^2 + |x|^2 - 2 x.c_k), lowest k on ties (torch.min).  A block owns 64 input rows (shared memory,
+// pitch D + 1) and walks the codebook in slabs of 64 codes; thread (ty, tx) of 16 x 16 keeps a 4 x 4 register tile of
+// dot products (rows ty + 16 i, codes tx + 16 j: conflict-free shared loads, 8 loads per 16 FMAs), folds each slab into
+// its running (distance, index) minimum, and the 16 threads of a row reduce lexicographically at the end.
 // ------------------------------------------------------------------------------------------
+constexpr int kVqTile = 64;
+
 __global__ void __launch_bounds__(256)
-vq_nearest_kernel(const float* __restrict__ x, long long P, int D, int x_pitch, const float* __restrict__ cb, int K, int slab,
+vq_nearest_kernel(const float* __restrict__ x, long long P, int D, int x_pitch, const float* __restrict__ cb, int K,
+                  long long* __restrict__ idx_out, float* __restrict__ dist_out) {
+  extern __shared__ float sm[];
+  const int ld = D + 1;
+  float* X = sm;                          // [64][ld]
+  float* C = X + kVqTile * ld;            // [64][ld]
+  float* X2 = C + kVqTile * ld;           // [64]
+  float* C2 = X2 + kVqTile;               // [64]
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const long long row0 = (long long)blockIdx.x * kVqTile;
+  for (int idx = threadIdx.x; idx < kVqTile * D; idx += 256) {
+    const int r = idx / D, c = idx - r * D;
+    X[r * ld + c] = row0 + r < P ? x[(row0 + r) * x_pitch + c] : 0.f;
+  }
+  __syncthreads();
+  if (threadIdx.x < kVqTile) {
+    float s2 = 0.f;
+    for (int c = 0; c < D; ++c) s2 = fmaf(X[threadIdx.x * ld + c], X[threadIdx.x * ld + c], s2);
+    X2[threadIdx.x] = s2;
+  }
+  float best[4];
+  int best_k[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { best[i] = INFINITY; best_k[i] = 0x7fffffff; }
+  for (int k0 = 0; k0 < K; k0 += kVqTile) {
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < kVqTile * D; idx += 256) {
+      const int r = idx / D, c = idx - r * D;
+      C[r * ld + c] = k0 + r < K ? cb[(size_t)(k0 + r) * D + c] : 0.f;
+    }
+    __syncthreads();
+    if (threadIdx.x < kVqTile) {
+      float s2 = 0.f;
+      for (int c = 0; c < D; ++c) s2 = fmaf(C[threadIdx.x * ld + c], C[threadIdx.x * ld + c], s2);
+      C2[threadIdx.x] = s2;
+    }
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int c = 0; c < D; ++c) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = X[(ty + 16 * i) * ld + c]; b[i] = C[(tx + 16 * i) * ld + c]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();                       // C2 of this slab is complete
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {          // ascending code index per thread: strict < keeps the lowest index
+      const int k = k0 + tx + 16 * j;
+      if (k >= K) continue;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float d = (C2[tx + 16 * j] + X2[ty + 16 * i]) - 2.f * acc[i][j];
+        if (d < best[i]) { best[i] = d; best_k[i] = k; }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float bd = best[i];
+    int bk = best_k[i];
+    for (int o = 8; o > 0; o >>= 1) {      // the 16 threads of a row are 16 consecutive lanes
+      const float od = __shfl_xor_sync(0xffffffffu, bd, o);
+      const int ok = __shfl_xor_sync(0xffffffffu, bk, o);
+      if (od < bd || (od == bd && ok < bk)) { bd = od; bk = ok; }
+    }
+    const long long row = row0 + ty + 16 * i;
+    if (tx == 0 && row < P) {
+      idx_out[row] = bk;
+      if (dist_out) dist_out[row] = bd;
+    }
+  }
+}
+
+// Wide rows (2 x 64 x (D + 1) floats no longer fit in shared memory): one warp per input row, lane l scans codes
+// l, l + 32, ... of a shared-memory codebook slab.
+__global__ void __launch_bounds__(256)
+vq_nearest_rowwarp_kernel(const float* __restrict__ x, long long P, int D, int x_pitch, const float* __restrict__ cb, int K, int slab,
                   long long* __restrict__ idx_out, float* __restrict__ dist_out) {
   extern __shared__ float sm[];
   const int ld = D + 1;
@@ -733,13 +818,21 @@ int psob_pairwise_distance_sum(const float* pos, int64_t P, int32_t D, int32_t p
 int psob_vq_nearest(const float* x, int64_t P, int32_t D, int32_t x_pitch, const float* codebook, int32_t K,
                     int64_t* idx_out, float* dist_out, psob_stream_t s) {
   if (!x || !codebook || !idx_out || P <= 0 || D <= 0 || K <= 0 || x_pitch < D) return fail(PSOB_E_ARG, "psob_vq_nearest: bad arguments");
-  int slab = K;
-  auto bytes = [&](int sl) { return ((size_t)sl * (D + 1) + sl + (size_t)8 * D) * sizeof(float); };
-  while (slab > 32 && bytes(slab) > 160 * 1024) slab = (slab + 1) / 2;
-  if (bytes(slab) > 200 * 1024) return fail(PSOB_E_UNSUPPORTED, "psob_vq_nearest: D = %d is too large", D);
-  PSOB_CUDA(cudaFuncSetAttribute(vq_nearest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes(slab)));
-  vq_nearest_kernel<<<(unsigned)((P + 7) / 8), 256, bytes(slab), (cudaStream_t)s>>>(x, P, D, x_pitch, codebook, K, slab,
-                                                                                  reinterpret_cast<long long*>(idx_out), dist_out);
+  const size_t smem = ((size_t)2 * kVqTile * (D + 1) + 2 * kVqTile) * sizeof(float);
+  if (smem > 160 * 1024) {
+    int slab = K;
+    auto bytes = [&](int sl) { return ((size_t)sl * (D + 1) + sl + (size_t)8 * D) * sizeof(float); };
+    while (slab > 32 && bytes(slab) > 160 * 1024) slab = (slab + 1) / 2;
+    if (bytes(slab) > 200 * 1024) return fail(PSOB_E_UNSUPPORTED, "psob_vq_nearest: D = %d is too large", D);
+    PSOB_CUDA(cudaFuncSetAttribute(vq_nearest_rowwarp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes(slab)));
+    vq_nearest_rowwarp_kernel<<<(unsigned)((P + 7) / 8), 256, bytes(slab), (cudaStream_t)s>>>(
+        x, P, D, x_pitch, codebook, K, slab, reinterpret_cast<long long*>(idx_out), dist_out);
+    PSOB_LAUNCH_CHECK("vq_nearest_rowwarp_kernel");
+    return 0;
+  }
+  PSOB_CUDA(cudaFuncSetAttribute(vq_nearest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  vq_nearest_kernel<<<(unsigned)((P + kVqTile - 1) / kVqTile), 256, smem, (cudaStream_t)s>>>(
+      x, P, D, x_pitch, codebook, K, reinterpret_cast<long long*>(idx_out), dist_out);
   PSOB_LAUNCH_CHECK("vq_nearest_kernel");
   return 0;
 }

@@ -74,10 +74,11 @@ def test_mean_pairwise_distance_vs_oracle(engine, P, D):
     ref = port.mean_pairwise_distance(pos.numpy())
     got = engine.mean_pairwise_distance(pos.cuda())
     assert abs(got - ref) <= 2e-6 * ref
-    # a strided view (the engine's padded position rows) gives the same number bit for bit
+    # a strided view (the engine's padded position rows) gives the same number (the order of the per-block
+    # atomicAdd(double) is not fixed, so to 1e-12 rather than bit for bit)
     wide = torch.zeros(P, D + 3)
     wide[:, :D] = pos
-    assert engine.mean_pairwise_distance(wide.cuda()[:, :D]) == got
+    assert abs(engine.mean_pairwise_distance(wide.cuda()[:, :D]) - got) <= 1e-12 * got
 
 
 def test_mean_pairwise_distance_degenerate(engine):

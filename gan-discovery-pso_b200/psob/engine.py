@@ -154,7 +154,8 @@ class GeneratorNet(Network):
             m_last = int(os.environ.get("PSOB_M_LAST", "2"))      # image-layer block size (tuning knob)
         if prefix is None:
             prefix = "gen" if any(k.startswith("gen.") for k in sd) else "decoder"
-        self.z_dim = int(sd[f"{prefix}.0.0.weight"].shape[0])
+        first = f"{prefix}.0.0.weight" if f"{prefix}.0.0.weight" in sd else f"{prefix}.0.weight"     # BN blocks / BN-free decoder
+        self.z_dim = int(sd[first].shape[0])
         if f"{prefix}.3.0.weight" in sd:
             progs = nets.g256_programs(sd, prefix)
         else:

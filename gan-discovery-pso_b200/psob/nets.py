@@ -36,11 +36,20 @@ def fold_bn_convt(sd: Dict, conv: str, bn: str):
 
 
 def generator_programs(sd: Dict, prefix: str = "gen", m_last: int = 2) -> List[L.LayerProgram]:
-    """DCGAN / VQ-VAE-GAN decoder 28x28 generator: z -> 7x7x2f -> 14x14xf -> 28x28x1."""
-    w1, b1 = fold_bn_convt(sd, f"{prefix}.0.0", f"{prefix}.0.1")
-    w2, b2 = fold_bn_convt(sd, f"{prefix}.1.0", f"{prefix}.1.1")
-    w3 = _np(sd[f"{prefix}.2.weight"]).astype(np.float32)
-    b3 = _np(sd[f"{prefix}.2.bias"]).astype(np.float32)
+    """DCGAN / VQ-VAE-GAN decoder 28x28 generator: z -> 7x7x2f -> 14x14xf -> 28x28x1.  Also the BatchNorm-free
+    `VectorQuantizedVAE_MNIST.decoder` (src/inverter/utils_vq_vae/util_model.py:237-244: ConvT / ReLU / ConvT / ReLU /
+    ConvT / Tanh under `{prefix}.{0,2,4}`; on a 1x1 input its stride-2 first layer equals the stride-1 form)."""
+    if f"{prefix}.0.0.weight" in sd:
+        w1, b1 = fold_bn_convt(sd, f"{prefix}.0.0", f"{prefix}.0.1")
+        w2, b2 = fold_bn_convt(sd, f"{prefix}.1.0", f"{prefix}.1.1")
+        last = f"{prefix}.2"
+    else:
+        f32 = lambda k: _np(sd[k]).astype(np.float32)
+        w1, b1 = f32(f"{prefix}.0.weight"), f32(f"{prefix}.0.bias")
+        w2, b2 = f32(f"{prefix}.2.weight"), f32(f"{prefix}.2.bias")
+        last = f"{prefix}.4"
+    w3 = _np(sd[f"{last}.weight"]).astype(np.float32)
+    b3 = _np(sd[f"{last}.bias"]).astype(np.float32)
     assert w1.shape[2] == 7 and w2.shape[2] == 4 and w3.shape[1] == 1, "28x28 single-channel generator expected"
     l1 = L.lower_convt_from_1x1("g.l1", w1, b1, L.ACT_RELU)
     l2 = L.lower_convt_k4s2p1("g.l2", w2, b2, L.ACT_RELU, 7, 7, m=1)

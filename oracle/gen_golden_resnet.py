@@ -78,6 +78,20 @@ def main():
     for k, v in gen.state_dict().items():
         g[f"fit/gen/{k}"] = v.numpy()
     print("fitness", g["fit/optimize_out_training"], g["fit/optimize_in_training"])
+    # the BatchNorm-free VQ-VAE decoder (VectorQuantizedVAE_MNIST.decoder, util_model.py:237-244), small widths, with
+    # non-zero biases so that the bias path is exercised
+    torch.manual_seed(21)
+    vq = ref.vq_model.VectorQuantizedVAE_MNIST(1, embedded_dim=100, num_embedding=32, data_pso=None, num_hiddens=16).eval()
+    with torch.no_grad():
+        for m_ in vq.decoder:
+            if hasattr(m_, "bias") and m_.bias is not None:
+                m_.bias.copy_(torch.randn(m_.bias.shape, generator=tg) * 0.1)
+        zq = torch.randn(6, 100, 1, 1, generator=tg)
+        g["vqmnist/z"] = zq.numpy()
+        g["vqmnist/out"] = vq.decoder(zq).numpy()
+    for k, v in vq.state_dict().items():
+        if k.startswith("decoder."):
+            g[f"vqmnist/{k}"] = v.numpy()
     np.savez_compressed(OUT, **g)
     print("wrote", OUT, os.path.getsize(OUT) // 1024, "KiB,", len(g), "arrays")
 

@@ -115,6 +115,27 @@ class VQDecoderGAN(nn.Module):
         return self.decoder(x)
 
 
+class VQDecoderMNIST(nn.Module):
+    """`VectorQuantizedVAE_MNIST.decoder` (src/inverter/utils_vq_vae/util_model.py:237-244): the BatchNorm-free variant,
+    ConvT(D -> h, k7, s2, p0) ReLU ConvT(h -> h/2, k4, s2, p1) ReLU ConvT(h/2 -> C, k4, s2, p1) Tanh, stored under
+    `decoder.{0,2,4}`; xavier-uniform weights and zero biases (`weights_init`, :39-46)."""
+
+    def __init__(self, channels_img: int = 1, embedded_dim: int = 64, num_hiddens: int = 64):
+        super().__init__()
+        h = num_hiddens
+        self.decoder = nn.Sequential(
+            nn.ConvTranspose2d(embedded_dim, h, 7, 2, 0), nn.ReLU(True),
+            nn.ConvTranspose2d(h, h // 2, 4, 2, 1), nn.ReLU(True),
+            nn.ConvTranspose2d(h // 2, channels_img, 4, 2, 1), nn.Tanh())
+        for m in self.modules():
+            if isinstance(m, nn.ConvTranspose2d):
+                nn.init.xavier_uniform_(m.weight.data)
+                m.bias.data.fill_(0)
+
+    def forward(self, x):
+        return self.decoder(x)
+
+
 class G256(nn.Module):
     """EXTENSION: 1x256x256 generator built from the reference's `_block`
     (src/utils/util_dcgan.py:141-146) because the reference G is hard-wired to 28x28.

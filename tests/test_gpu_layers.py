@@ -226,3 +226,16 @@ def test_g256_generator_small_widths_vs_reference(mods):
     got = res[ffi.IMPL_TCGEN05]
     assert np.abs(got - ref).max() <= IMG_TOL
     assert np.linalg.norm(got - ref) / np.linalg.norm(ref) <= REL_TOL
+
+
+def test_bn_free_vq_decoder_vs_reference(mods, golden_resnet):
+    """`VectorQuantizedVAE_MNIST.decoder` (BatchNorm-free, keys decoder.{0,2,4}) through the engine vs the reference's output."""
+    engine, L, nets, ffi = mods
+    g = golden_resnet
+    sd = {k[len("vqmnist/"):]: torch.from_numpy(v.copy()) for k, v in g.items() if k.startswith("vqmnist/decoder.")}
+    net = engine.GeneratorNet(sd, 6, prefix="decoder")
+    assert net.z_dim == 100
+    _, img = net.forward(_rows(g["vqmnist/z"].reshape(6, 100), net.in_pitch))
+    ref = g["vqmnist/out"].reshape(6, 784)
+    got = img.cpu().numpy()
+    assert np.abs(got - ref).max() <= 2e-2 and np.linalg.norm(got - ref) <= 5e-3 * np.linalg.norm(ref)

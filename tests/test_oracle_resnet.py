@@ -39,3 +39,22 @@ def test_port_fitness_with_resnet_assessor_matches_reference_discovery(golden_re
         fit = np.concatenate([port.fitness_assessor(gen, m, g["fit/pos"][i], 100, mode=mode, class_index=2)[0]
                               for i in range(g["fit/pos"].shape[0])])
         np.testing.assert_allclose(fit, g[f"fit/{mode}"], rtol=1e-5, atol=1e-6)
+
+
+def test_port_bn_free_vq_decoder_matches_reference(golden_resnet):
+    """`VectorQuantizedVAE_MNIST.decoder` (src/inverter/utils_vq_vae/util_model.py:237-244) restated, and its lowering to
+    engine tables (numpy emulation, bf16 operands)."""
+    from psob import nets
+    g = golden_resnet
+    m = port.VQDecoderMNIST(1, 100, 16).eval()
+    sd = {k[len("vqmnist/"):]: torch.from_numpy(v.copy()) for k, v in g.items() if k.startswith("vqmnist/decoder.")}
+    m.load_state_dict(sd)
+    with torch.no_grad():
+        out = m(torch.from_numpy(g["vqmnist/z"])).numpy()
+    np.testing.assert_allclose(out, g["vqmnist/out"], rtol=1e-5, atol=1e-6)
+    progs = nets.generator_programs({k: v.numpy() for k, v in sd.items()}, prefix="decoder")
+    z = np.zeros((6, progs[0].in_pitch), np.float32)
+    from psob import lowering as L
+    z[:, :100] = L.to_bf16_f32(g["vqmnist/z"].reshape(6, 100))
+    _, img = nets.emulate_chain(progs, z)
+    assert np.abs(img[:, :784] - g["vqmnist/out"].reshape(6, 784)).max() <= 2e-2

@@ -67,6 +67,7 @@ struct EngineParams {
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4, strided;
   int step_stride;           // int4 words per step in the shared-memory copy of the step table (1 when no step has > 2 ops)
+  int warp_store;            // every epilogue warp stores its own 32 rows of a chunk (32-row TMA box): no barriers inside a group
   int band;                  // image-band epilogue (lower_convt_image_band): 4 chunks of two padded image rows each
   int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
   int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
@@ -167,6 +168,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const int q_band = p.band;
   const int q_in_tiled = p.in_tiled;
   const int q_out_tiled = p.out_tiled;
+  const bool q_warp_store = kTmaStore && p.warp_store != 0;
   const int q_n_in_chunks = p.n_in_chunks;
   const int q_n_out_chunks = p.n_out_chunks;
   const uint32_t q_idesc = p.idesc;
@@ -501,11 +503,17 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             }
             const uint32_t sbuf = sbuf0 + sflip * kATileBytes;
             const uint32_t srow = sbuf + (uint32_t)row * 128u;
-            if (issuer_warp) {
-              if (ptx::elect_one()) { if (q_stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
+            if (q_warp_store) {
+              // the warp's own slice (32 rows = 4 KB) of the staging tile, tracked by ITS lane 0's bulk groups
+              if (lane == 0) { if (q_stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
               __syncwarp();
-            }   // the store that last used this tile has drained it
-            ptx::named_bar_sync(1 + grp, 128);
+            } else {
+              if (issuer_warp) {
+                if (ptx::elect_one()) { if (q_stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
+                __syncwarp();
+              }   // the store that last used this tile has drained it
+              ptx::named_bar_sync(1 + grp, 128);
+            }
             if (prof) { const long long t = clock64(); e_free += (unsigned long long)(t - tq); tq = t; }
             auto emit_slot = [&](int j, const float4& b0, const float4& b1) {
               if (has_res) {
@@ -562,13 +570,22 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             }
             if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
             ptx::fence_proxy_async();                    // generic-proxy writes -> visible to the TMA (async proxy)
-            ptx::named_bar_sync(1 + grp, 128);
-            if (issuer_warp) {
-              if (ptx::elect_one()) {
-                ptx::tma_store_2d(&tmY, sbuf, out_c0(j0.z + cm), out_c1(ptile, j0.z + cm));   // row-major: rows >= P are clipped by the tensor map
+            if (q_warp_store) {
+              __syncwarp();
+              if (lane == 0) {
+                ptx::tma_store_2d(&tmY, sbuf + (uint32_t)q * 4096u, out_c0(j0.z + cm), out_c1(ptile, j0.z + cm) + q * 32);
                 ptx::bulk_commit();
               }
               __syncwarp();
+            } else {
+              ptx::named_bar_sync(1 + grp, 128);
+              if (issuer_warp) {
+                if (ptx::elect_one()) {
+                  ptx::tma_store_2d(&tmY, sbuf, out_c0(j0.z + cm), out_c1(ptile, j0.z + cm));   // row-major: rows >= P are clipped by the tensor map
+                  ptx::bulk_commit();
+                }
+                __syncwarp();
+              }
             }
             if (q_stg_bufs == 2) sflip ^= 1u;
             if (prof) { const long long t = clock64(); e_pub += (unsigned long long)(t - tq); tq = t; }
@@ -626,7 +643,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         }
         }   // jobs of the chain
       }
-      if (kTmaStore && issuer_warp && ptx::elect_one()) ptx::bulk_wait_all0();      // staging tiles must outlive their TMA stores
+      if (kTmaStore && q_warp_store) { if (lane == 0) ptx::bulk_wait_all0(); }
+      else if (kTmaStore && issuer_warp && ptx::elect_one()) ptx::bulk_wait_all0();      // staging tiles must outlive their TMA stores
       if (prof && warp < 4 && lane == 0) {        // per lane-quadrant warp of group 0: {tmem load, staging/barrier wait, math, publish}
         unsigned long long* q4 = p.prof + blockIdx.x * 32 + 16 + 4 * warp;
         q4[0] = e_ld; q4[1] = e_free; q4[2] = e_math; q4[3] = e_pub;
@@ -785,6 +803,7 @@ struct psob_layer {
   __nv_bfloat16* wpack = nullptr;
   CUtensorMap tmB;
   bool have_tmB = false;
+  bool warp_store = false;         // per-warp 32-row TMA stores in the chunked epilogue (PSOB_WARP_STORE)
   bool eye = false;                // some step is an identity op (streamed layers): 8 KB identity tile at res_off
   const void* attr_fn = nullptr;   // kernel instantiation whose dynamic-SMEM limit has been raised
   bool tma_store = false, vec4 = false, pair = false, strided = false;
@@ -996,7 +1015,8 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->stg_off = l->res_off + res_bytes;
   l->bar_off = l->stg_off + stg_bytes;
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
-  { const char* e = getenv("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }     // tuning knob (default: strided)
+  { const char* e = getenv("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }
+  { const char* e = getenv("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * d->nt)) cols <<= 1;
   l->tmem_cols = cols;
@@ -1042,6 +1062,7 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
   p.in_tiled = d.in_tiled; p.out_tiled = d.out_tiled; p.n_in_chunks = d.in_pitch / kKChunk; p.n_out_chunks = d.out_pitch / kKChunk;
   p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.epi_groups = l->epi_groups; p.step_stride = l->step_stride; p.band = (l->band && p.y != nullptr) ? 1 : 0;
+  p.warp_store = l->warp_store ? 1 : 0;
   if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
@@ -1082,8 +1103,9 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
                       : make_tmap(&tmA, x, (uint64_t)x_pitch, (uint64_t)P, (uint64_t)x_pitch, kTileM);
   if (rc) return rc;
   if (tma_store) {
-    rc = d.out_tiled ? make_tmap(&tmY, y, kKChunk, (uint64_t)n_ptiles * (d.out_pitch / kKChunk) * kTileM, kKChunk, kTileM)
-                     : make_tmap(&tmY, y, (uint64_t)d.out_pitch, (uint64_t)P, (uint64_t)d.out_pitch, kTileM);
+    const uint32_t box_rows = l->warp_store ? 32u : (uint32_t)kTileM;
+    rc = d.out_tiled ? make_tmap(&tmY, y, kKChunk, (uint64_t)n_ptiles * (d.out_pitch / kKChunk) * kTileM, kKChunk, box_rows)
+                     : make_tmap(&tmY, y, (uint64_t)d.out_pitch, (uint64_t)P, (uint64_t)d.out_pitch, box_rows);
     if (rc) return rc;
   } else {
     tmY = tmA;

@@ -12,7 +12,7 @@
 using namespace psob;
 
 template <bool kPair>
-__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int reps, int n_b, int per_commit, uint32_t idesc, unsigned long long* cycles) {
+__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int reps, int n_b, int per_commit, uint32_t idesc, int issuers, unsigned long long* cycles) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int reps, int 
   const uint32_t slot = bar + 16u;
   const int warp = threadIdx.x >> 5;
   const uint32_t crank = kPair ? ptx::cluster_ctarank() : 0u;
-  const uint32_t n_commits = (uint32_t)((reps + per_commit - 1) / per_commit);
+  const uint32_t n_commits = (uint32_t)((reps + per_commit - 1) / per_commit) * (uint32_t)issuers;
   if (threadIdx.x == 0) { ptx::mbar_init(bar, n_commits); ptx::fence_barrier_init(); }     // ONE phase: completes after the last commit
   for (uint32_t i = threadIdx.x; i < (16384u + (uint32_t)n_b * b_bytes) / 4u; i += 128) reinterpret_cast<uint32_t*>(smem_raw + (base - raw))[i] = 0x3c003c00u;
   ptx::fence_proxy_async();
@@ -34,13 +34,14 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int reps, int 
   if (kPair) ptx::cluster_sync_all(); else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_raw + (slot - raw));
-  if (warp == 0 && crank == 0) {
+  if ((warp == 0 || (warp == 2 && issuers == 2)) && crank == 0) {      // two issuers: warp 0 -> TMEM buffer 0, warp 2 -> buffer 1
+    const bool lane0 = (threadIdx.x & 31) == 0;
     const uint64_t adesc = ptx::smem_desc_sw128(a_addr);
     const long long t0 = clock64();
     for (int r = 0; r < reps; ++r) {
       if (ptx::elect_one()) {
         const uint64_t bdesc = ptx::smem_desc_sw128(b_addr + (uint32_t)(r % n_b) * b_bytes);
-        const uint32_t d = tmem_base + (uint32_t)(r & 1) * 256u;
+        const uint32_t d = tmem_base + (issuers == 2 ? (uint32_t)(warp >> 1) : (uint32_t)(r & 1)) * 256u;
         const bool commit = (r % per_commit) == per_commit - 1 || r == reps - 1;
         if (commit) {
           if (kPair) ptx::umma_bf16_k64_commit_pair(d, adesc, bdesc, idesc, 1u, bar);
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int reps, int 
     const long long t_issue = clock64();
     ptx::mbar_wait(bar, 0u);
     const long long t1 = clock64();
-    if (threadIdx.x == 0) { cycles[2 * blockIdx.x] = (unsigned long long)(t1 - t0); cycles[2 * blockIdx.x + 1] = (unsigned long long)(t_issue - t0); }
+    if (warp == 0 && lane0) { cycles[2 * blockIdx.x] = (unsigned long long)(t1 - t0); cycles[2 * blockIdx.x + 1] = (unsigned long long)(t_issue - t0); }
   }
   ptx::tc_fence_before();
   if (kPair) ptx::cluster_sync_all(); else __syncthreads();
@@ -73,9 +74,11 @@ int main(int argc, char** argv) {
   const int reps = 4000;
   printf("%d SMs, %d K=64 ops per CTA (4 x tcgen05.mma K=16 each)\n", sms, reps);
   printf("%-6s %4s %4s %10s | %12s %12s %14s | %12s\n", "mode", "N", "n_b", "ops/commit", "cyc/instr", "issue-only", "MAC/clk/SM", "% of 4096");
+  for (int issuers = 1; issuers <= 2; ++issuers)
   for (int pair = 0; pair < 2; ++pair)
     for (int n : {64, 96, 128, 256})
       for (int per_commit : {1, 4}) {
+        if (issuers == 2 && per_commit == 1) continue;
         const int n_b = 4;
         if (pair && n % 32) continue;
         const size_t smem = 1024 + 16384 + (size_t)n_b * (pair ? n / 2 : n) * 128 + 64;
@@ -89,10 +92,10 @@ int main(int argc, char** argv) {
           cudaLaunchAttribute at[1];
           at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
           cfg.attrs = at; cfg.numAttrs = 1;
-          e = cudaLaunchKernelEx(&cfg, umma_rate_kernel<true>, n, reps, n_b, per_commit, make_idesc_bf16(256, n), d_cyc);
+          e = cudaLaunchKernelEx(&cfg, umma_rate_kernel<true>, n, reps, n_b, per_commit, make_idesc_bf16(256, n), issuers, d_cyc);
         } else {
           cudaFuncSetAttribute(umma_rate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-          umma_rate_kernel<false><<<grid, 128, smem>>>(n, reps, n_b, per_commit, make_idesc_bf16(128, n), d_cyc);
+          umma_rate_kernel<false><<<grid, 128, smem>>>(n, reps, n_b, per_commit, make_idesc_bf16(128, n), issuers, d_cyc);
           e = cudaGetLastError();
         }
         cudaError_t e2 = cudaDeviceSynchronize();
@@ -102,10 +105,10 @@ int main(int argc, char** argv) {
         double tot = 0, iss = 0; int cnt = 0;
         for (int b = 0; b < grid; ++b) if (h[2 * b]) { tot += (double)h[2 * b]; iss += (double)h[2 * b + 1]; ++cnt; }
         tot /= cnt; iss /= cnt;
-        const double per_instr = tot / (reps * 4.0);
+        const double per_instr = tot / (reps * 4.0 * issuers);
         const double macs = 128.0 * n * 16.0;           // per SM per instruction (pair: each SM does 128 rows x n)
-        printf("%-6s %4d %4d %10d | %12.1f %12.1f %14.0f | %11.1f%%\n", pair ? "pair" : "solo", n, n_b, per_commit, per_instr,
-               iss / (reps * 4.0), macs / per_instr, 100.0 * macs / per_instr / 4096.0);
+        printf("%-6s %4d %4d %10d | %12.1f %12.1f %14.0f | %11.1f%%\n", pair ? (issuers == 2 ? "pair x2" : "pair") : (issuers == 2 ? "solo x2" : "solo"), n, n_b,
+               per_commit, per_instr, iss / (reps * 4.0 * issuers), macs / per_instr, 100.0 * macs / per_instr / 4096.0);
       }
   return 0;
 }

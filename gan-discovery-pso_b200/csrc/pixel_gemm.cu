@@ -17,6 +17,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <vector>
 #include <new>
 
 namespace psob {
@@ -41,9 +42,10 @@ __host__ __device__ __forceinline__ int op_b_row(int op) { return (op & 0xFFFF) 
 __host__ __device__ __forceinline__ int op_d_col(int op) { return ((op >> 16) & 0xFF) << 1; }
 __host__ __device__ __forceinline__ int op_next(int op) { return (op >> 24) & 1; }
 __host__ __device__ __forceinline__ int op_acc(int op) { return (op >> 25) & 1; }
-__host__ __device__ __forceinline__ int op_eye(int op) { return (op >> 26) & 1; }   // D[:, d_col : d_col + 64] (+)= A (N = 64 against the identity tile)                  // job descriptors staged in SMEM (32 B each)
+__host__ __device__ __forceinline__ int op_eye(int op) { return (op >> 26) & 1; }
+__host__ __device__ __forceinline__ int op_region(int op) { return (op >> 27) & 1; }   // set by psob_layer_create: parity of the op's column region (2 issuers)   // D[:, d_col : d_col + 64] (+)= A (N = 64 against the identity tile)                  // job descriptors staged in SMEM (32 B each)
 constexpr int kMaxEpiGroups = 2;                  // epilogue groups of 4 warps (one per TMEM lane quadrant)
-constexpr int kMaxThreads = 32 * (4 * kMaxEpiGroups + 2);   // + TMA warp + MMA warp; blockDim = 32 * (4 * epi_groups + 2)
+constexpr int kMaxThreads = 32 * (4 * kMaxEpiGroups + 3);   // + TMA warp + 1 or 2 MMA warps; blockDim = 32 * (4 * epi_groups + 1 + issuers)
 // The SMSP arbiter favours the highest warp id: the two single-thread roles that must never wait for
 // an issue slot (TMA producer, MMA issuer) get the top ids; epilogue warps 0..7 map to TMEM quadrant w % 4.
 // (warp ids 4 * epi_groups and 4 * epi_groups + 1, see kTmaWarp / kMmaWarp in the kernel)
@@ -68,6 +70,8 @@ struct EngineParams {
   int vec4, strided;
   int step_stride;           // int4 words per step in the shared-memory copy of the step table (1 when no step has > 2 ops)
   int warp_store;            // every epilogue warp stores its own 32 rows of a chunk (32-row TMA box): no barriers inside a group
+  int issuers;               // MMA-issuing warps (1 or 2): one thread sustains only ~1 tcgen05.mma per 85-94 cycles (tools/umma_bench.cu)
+  int issue_split;           // 2 issuers: ownership of an op by (accumulator buffer + column region) parity (1) or by buffer only (0)
   int band;                  // image-band epilogue (lower_convt_image_band): 4 chunks of two padded image rows each
   int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
   int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
@@ -224,10 +228,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   if (threadIdx.x == 0) {
     for (int s = 0; s < q_n_stages; ++s) {
       ptx::mbar_init(full_bar(s), 1);
-      ptx::mbar_init(empty_bar(s), 1);
+      ptx::mbar_init(empty_bar(s), (uint32_t)p.issuers);      // every issuing warp commits every step
     }
     for (int b = 0; b < 2; ++b) {
-      ptx::mbar_init(tfull_bar(b), 1);
+      ptx::mbar_init(tfull_bar(b), (uint32_t)p.issuers);
       ptx::mbar_init(tempty_bar(b), (kTmaStore ? 4 * q_epi_groups : 4) * (kPair ? 2 : 1));   // pair: both CTAs' epilogue warps
     }
     ptx::mbar_init(res_bar, 1);
@@ -348,16 +352,21 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       }
       if (prof && lane == 0) { p.prof[blockIdx.x * 32 + 0] = w_empty; p.prof[blockIdx.x * 32 + 1] = (unsigned long long)(clock64() - t_start); }
     }
-  } else if (warp == kMmaWarp && leader) {
+  } else if (warp >= kMmaWarp && leader) {
     // ------------------------------------------------------------------ MMA issuer (pair: leader CTA only)
     if (!kPair && q_b_resident) ptx::mbar_wait(res_bar, 0);
     int stage = 0;
     uint32_t phase = 0;
     uint32_t it = 0;
-    const bool prof = p.prof != nullptr;
+    const bool prof = p.prof != nullptr && warp == kMmaWarp;
     unsigned long long w_full = 0, w_tempty = 0;
     const long long t_start = clock64();
     bool next_acquired = false;          // the next job's accumulator buffer was already acquired by a NEXT op
+    // Two issuing warps: warp w owns the ops whose (accumulator buffer + column region) parity is w, so every
+    // accumulator column has ONE issuer for its whole life (deterministic accumulation order); both warps walk all
+    // steps and both commit on every stage / accumulator barrier.
+    const uint32_t wsel = (uint32_t)(warp - kMmaWarp);
+    const bool two = p.issuers == 2;
     for (long long item = item_begin; item < item_end; item += item_step) {
       const int2 ch = chains[(uint32_t)item % n_chains_u];
       for (int job = ch.x; job < ch.x + ch.y; ++job, ++it) {
@@ -399,7 +408,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                            : (res ? base + q_res_off + (uint32_t)op_b_row(op) * 128u : a_addr + kATileBytes);
             };
             auto d_of = [&](int op) { return tmem_base + (buf ^ (uint32_t)op_next(op)) * (uint32_t)q_nt + (uint32_t)op_d_col(op); };
-            if (n_ops == 1) {
+            auto mine = [&](int op) { return !two || (((buf ^ (uint32_t)op_next(op)) + (uint32_t)op_region(op)) & 1u) == wsel; };
+            auto commit_only = [&]() { if (kPair) ptx::umma_commit_pair(empty_bar(stage)); else ptx::umma_commit(empty_bar(stage)); };
+            if (n_ops == 1 && !mine(st.z)) {
+              commit_only();
+            } else if (n_ops == 1) {
               // 4 x (K = 16) with +32 B descriptor advances inside the 128 B swizzle row, then commit -> stage free
               const bool eye = !kPair && (st.y & kMetaEye) != 0;
               const uint64_t bdesc = ptx::smem_desc_sw128(eye ? base + q_res_off : b_addr_of(st.z));
@@ -407,15 +420,24 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               else ptx::umma_bf16_k64_commit(d_of(st.z), adesc, bdesc, eye ? p.idesc_eye : q_idesc, (uint32_t)op_acc(st.z), empty_bar(stage));
             } else {
               // one A tile, several weight tiles: own / next job's accumulators (resident weights only)
-              const int ops[4] = {st.z, n_ops > 1 ? st.w : st.z, n_ops > 2 ? st2.x : st.z, n_ops > 3 ? st2.y : st.z};
-              uint32_t dd[4], aa[4];
-              uint64_t bb[4];
+              const int all_ops[4] = {st.z, n_ops > 1 ? st.w : st.z, n_ops > 2 ? st2.x : st.z, n_ops > 3 ? st2.y : st.z};
+              int ops[4] = {st.z, st.z, st.z, st.z};
+              int m = 0;
 #pragma unroll
-              for (int o = 0; o < 4; ++o) {
-                dd[o] = d_of(ops[o]); aa[o] = (uint32_t)op_acc(ops[o]); bb[o] = ptx::smem_desc_sw128(b_addr_of(ops[o]));
+              for (int o = 0; o < 4; ++o)
+                if (o < n_ops && mine(all_ops[o])) ops[m++] = all_ops[o];        // this warp's ops, in table order
+              if (m == 0) {
+                commit_only();
+              } else {
+                uint32_t dd[4], aa[4];
+                uint64_t bb[4];
+#pragma unroll
+                for (int o = 0; o < 4; ++o) {
+                  dd[o] = d_of(ops[o]); aa[o] = (uint32_t)op_acc(ops[o]); bb[o] = ptx::smem_desc_sw128(b_addr_of(ops[o]));
+                }
+                if (kPair) ptx::umma_bf16_k64x4_commit_pair(dd, adesc, bb, q_idesc, aa, m, empty_bar(stage));
+                else ptx::umma_bf16_k64x4_commit(dd, adesc, bb, q_idesc, aa, m, empty_bar(stage));
               }
-              if (kPair) ptx::umma_bf16_k64x4_commit_pair(dd, adesc, bb, q_idesc, aa, n_ops, empty_bar(stage));
-              else ptx::umma_bf16_k64x4_commit(dd, adesc, bb, q_idesc, aa, n_ops, empty_bar(stage));
             }
           }
           __syncwarp();
@@ -425,7 +447,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         __syncwarp();
       }
     }
-    if (prof && lane == 0) {
+    if (prof && lane == 0) {       // first issuing warp only
       p.prof[blockIdx.x * 32 + 2] = w_full; p.prof[blockIdx.x * 32 + 3] = w_tempty;
       p.prof[blockIdx.x * 32 + 4] = (unsigned long long)(clock64() - t_start);
     }
@@ -804,6 +826,8 @@ struct psob_layer {
   CUtensorMap tmB;
   bool have_tmB = false;
   bool warp_store = false;         // per-warp 32-row TMA stores in the chunked epilogue (PSOB_WARP_STORE)
+  int issuers = 1;                 // MMA-issuing warps
+  bool issue_split = true;
   bool eye = false;                // some step is an identity op (streamed layers): 8 KB identity tile at res_off
   const void* attr_fn = nullptr;   // kernel instantiation whose dynamic-SMEM limit has been raised
   bool tma_store = false, vec4 = false, pair = false, strided = false;
@@ -931,7 +955,23 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   PSOB_CUDA_L(cudaMalloc(&l->col_map32, sizeof(int) * d->nt));
   PSOB_CUDA_L(cudaMalloc(&l->bias, sizeof(float) * d->nt * d->n_bias_rows));
   PSOB_CUDA_L(cudaMalloc(&l->wpack, (size_t)d->n_wrows * kKChunk * 2));
-  PSOB_CUDA_L(cudaMemcpy(l->steps, d->steps, sizeof(int4) * 2 * d->n_steps, cudaMemcpyHostToDevice));
+  {
+    // Two MMA-issuing warps (PSOB_ISSUERS, default 2) pay off when a job's ops cover several accumulator regions (N < 256
+    // ops, NEXT ops of chained jobs).  Ops are split by column region when every op sits on a multiple of mma_n (identity
+    // ops fall inside a region); layers with overlapping column windows (image band) are split by buffer only.
+    const char* e = getenv("PSOB_ISSUERS");
+    l->issuers = e ? (atoi(e) == 2 ? 2 : 1) : 1;
+    l->issue_split = true;
+    std::vector<int32_t> st(d->steps, d->steps + (size_t)8 * d->n_steps);
+    for (int s = 0; s < d->n_steps; ++s)
+      for (int o = 0; o < (st[8 * s + 1] & kMetaOpsMask); ++o)
+        if (!op_eye(st[8 * s + 2 + o]) && op_d_col(st[8 * s + 2 + o]) % d->mma_n) l->issue_split = false;
+    if (l->issue_split)
+      for (int s = 0; s < d->n_steps; ++s)
+        for (int o = 0; o < (st[8 * s + 1] & kMetaOpsMask); ++o)
+          st[8 * s + 2 + o] |= ((op_d_col(st[8 * s + 2 + o]) / d->mma_n) & 1) << 27;
+    PSOB_CUDA_L(cudaMemcpy(l->steps, st.data(), sizeof(int4) * 2 * d->n_steps, cudaMemcpyHostToDevice));
+  }
   PSOB_CUDA_L(cudaMemcpy(l->jobs, d->jobs, sizeof(int4) * 2 * d->n_jobs, cudaMemcpyHostToDevice));
   PSOB_CUDA_L(cudaMemcpy(l->col_map, d->col_map, sizeof(int) * d->nt, cudaMemcpyHostToDevice));
   PSOB_CUDA_L(cudaMemcpy(l->col_map32, d->col_map32, sizeof(int) * d->nt, cudaMemcpyHostToDevice));
@@ -1062,6 +1102,7 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
   p.in_tiled = d.in_tiled; p.out_tiled = d.out_tiled; p.n_in_chunks = d.in_pitch / kKChunk; p.n_out_chunks = d.out_pitch / kKChunk;
   p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.epi_groups = l->epi_groups; p.step_stride = l->step_stride; p.band = (l->band && p.y != nullptr) ? 1 : 0;
+  p.issuers = l->issuers; p.issue_split = l->issue_split ? 1 : 0;
   p.warp_store = l->warp_store ? 1 : 0;
   if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
@@ -1114,7 +1155,7 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
     const long long pairs = p.n_items < l->sm_count / 2 ? p.n_items : l->sm_count / 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(2 * pairs));
-    cfg.blockDim = dim3(32 * (4 * l->epi_groups + 2));
+    cfg.blockDim = dim3(32 * (4 * l->epi_groups + 1 + l->issuers));
     cfg.dynamicSmemBytes = (size_t)l->smem_bytes;
     cfg.stream = (cudaStream_t)s;
     cudaLaunchAttribute attr[1];
@@ -1127,7 +1168,7 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
     return 0;
   }
   long long grid = p.n_items < l->sm_count ? p.n_items : l->sm_count;
-  fn<<<(unsigned)grid, 32 * (4 * l->epi_groups + 2), l->smem_bytes, (cudaStream_t)s>>>(tmA, l->tmB, tmY, p);
+  fn<<<(unsigned)grid, 32 * (4 * l->epi_groups + 1 + l->issuers), l->smem_bytes, (cudaStream_t)s>>>(tmA, l->tmB, tmY, p);
   PSOB_LAUNCH_CHECK("pixel_gemm_umma_kernel");
   return 0;
 }

@@ -421,11 +421,22 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             } else {
               // one A tile, several weight tiles: own / next job's accumulators (resident weights only)
               const int all_ops[4] = {st.z, n_ops > 1 ? st.w : st.z, n_ops > 2 ? st2.x : st.z, n_ops > 3 ? st2.y : st.z};
-              int ops[4] = {st.z, st.z, st.z, st.z};
-              int m = 0;
-#pragma unroll
-              for (int o = 0; o < 4; ++o)
-                if (o < n_ops && mine(all_ops[o])) ops[m++] = all_ops[o];        // this warp's ops, in table order
+              int ops[4] = {all_ops[0], all_ops[1], all_ops[2], all_ops[3]};
+              int m = n_ops;
+              if (two) {
+                // this warp's ops, in table order, compacted to the front with register selects (no indexed local array)
+                const bool k0 = mine(all_ops[0]), k1 = n_ops > 1 && mine(all_ops[1]), k2 = n_ops > 2 && mine(all_ops[2]),
+                           k3 = n_ops > 3 && mine(all_ops[3]);
+                m = 0;
+                int c0 = st.z, c1 = st.z, c2 = st.z, c3 = st.z;
+                auto push = [&](bool k, int op) {
+                  if (!k) return;
+                  if (m == 0) c0 = op; else if (m == 1) c1 = op; else if (m == 2) c2 = op; else c3 = op;
+                  ++m;
+                };
+                push(k0, all_ops[0]); push(k1, all_ops[1]); push(k2, all_ops[2]); push(k3, all_ops[3]);
+                ops[0] = c0; ops[1] = c1; ops[2] = c2; ops[3] = c3;
+              }
               if (m == 0) {
                 commit_only();
               } else {

@@ -319,53 +319,76 @@ using namespace psob;
 
 // ------------------------------------------------------------------------------------------
 // Swarm diversity: mean Euclidean distance over all unordered particle pairs -- `Swarm.mse`
-// (src/pso/util_pso.py:76-86; reporting only, O(P^2 D)).  One block per 64 x 64 tile of the upper
-// triangle; both 64-particle slabs sit in shared memory (row pitch D + 1: conflict-free), every
-// thread owns a 4 x 4 patch of pairs.  Differences are squared directly (no Gram-matrix
-// cancellation), distances are summed per block in double and added with one atomicAdd(double).
+// (src/pso/util_pso.py:76-86; reporting only, O(P^2 D)).  One block per 128 x 128 tile of the upper
+// triangle; both 128-particle slabs sit in shared memory (the second one transposed, so that two neighbouring
+// particles of one dimension are one 8-byte load), every thread owns an 8 x 8 patch of pairs and advances two
+// pairs per instruction on the packed fp32 pipe (sub.f32x2 + fma.f32x2: one instruction per pair and dimension).
+// Differences are squared directly (no Gram-matrix cancellation), distances are summed per block in double and
+// added with one atomicAdd(double).
 // ------------------------------------------------------------------------------------------
-constexpr int kPairTile = 64;
+constexpr int kPairTile = 128;
+
+// packed fp32 pair: {lo, hi} in one 64-bit register (Blackwell FADD2 / FFMA2: two IEEE fp32 lanes per instruction)
+__device__ __forceinline__ unsigned long long f2_pack(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ unsigned long long f2_sqdiff_acc(unsigned long long a, unsigned long long b, unsigned long long acc) {
+  unsigned long long d, r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(r) : "l"(d), "l"(acc));
+  return r;
+}
 
 __global__ void __launch_bounds__(256)
 pairwise_distance_sum_kernel(const float* __restrict__ pos, long long P, int D, int pitch, int n_tiles, double* __restrict__ out) {
-  extern __shared__ float sm[];
+  extern __shared__ __align__(16) float sm[];
   // linear block index -> (ti <= tj) of the upper triangle
   long long b = blockIdx.x;
   int ti = 0;
   while (b >= (long long)(n_tiles - ti)) { b -= (n_tiles - ti); ++ti; }
   const int tj = ti + (int)b;
-  const int ld = D + 1;
+  const int lda = D + 1;                  // A: [128 rows][D + 1]  (row reads are warp broadcasts)
+  const int ldb = kPairTile + 2;          // B: transposed [D][128 + 2]: two neighbouring particles of one dimension = one 8-byte load
   float* A = sm;
-  float* B = sm + kPairTile * ld;
+  float* Bt = sm + ((kPairTile * lda + 1) & ~1);
   for (int idx = threadIdx.x; idx < kPairTile * D; idx += 256) {
     const int r = idx / D, c = idx - r * D;
     const long long ia = (long long)ti * kPairTile + r, ib = (long long)tj * kPairTile + r;
-    A[r * ld + c] = ia < P ? pos[ia * pitch + c] : 0.f;
-    B[r * ld + c] = ib < P ? pos[ib * pitch + c] : 0.f;
+    A[r * lda + c] = ia < P ? pos[ia * pitch + c] : 0.f;
+    Bt[c * ldb + r] = ib < P ? pos[ib * pitch + c] : 0.f;
   }
   __syncthreads();
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  float acc[4][4];
+  // thread tile: rows ty + 16 i (i < 8) x column pairs (2 tx + 32 j, 2 tx + 32 j + 1) (j < 4)
+  unsigned long long acc[8][4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0ull;
   for (int c = 0; c < D; ++c) {
-    float a[4], bb[4];
+    unsigned long long bb[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { a[i] = A[(ty + 16 * i) * ld + c]; bb[i] = B[(tx + 16 * i) * ld + c]; }
+    for (int j = 0; j < 4; ++j) bb[j] = *reinterpret_cast<const unsigned long long*>(Bt + c * ldb + 2 * tx + 32 * j);
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < 8; ++i) {
+      const float a = A[(ty + 16 * i) * lda + c];
+      const unsigned long long aa = f2_pack(a, a);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) { const float d = a[i] - bb[j]; acc[i][j] = fmaf(d, d, acc[i][j]); }
+      for (int j = 0; j < 4; ++j) acc[i][j] = f2_sqdiff_acc(aa, bb[j], acc[i][j]);
+    }
   }
   double sum = 0.0;
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < 8; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const long long gi = (long long)ti * kPairTile + ty + 16 * i, gj = (long long)tj * kPairTile + tx + 16 * j;
-      if (gi < gj && gj < P) sum += (double)sqrtf(acc[i][j]);
+      float lo, hi;
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc[i][j]));
+      const long long gi = (long long)ti * kPairTile + ty + 16 * i, gj = (long long)tj * kPairTile + 2 * tx + 32 * j;
+      if (gi < gj && gj < P) sum += (double)sqrtf(lo);
+      if (gi < gj + 1 && gj + 1 < P) sum += (double)sqrtf(hi);
     }
   __shared__ double red[8];
   for (int o = 16; o > 0; o >>= 1) sum += __shfl_down_sync(0xffffffffu, sum, o);
@@ -806,7 +829,7 @@ int psob_pairwise_distance_sum(const float* pos, int64_t P, int32_t D, int32_t p
   const long long n_tiles = (P + kPairTile - 1) / kPairTile;
   const long long n_blocks = n_tiles * (n_tiles + 1) / 2;
   if (n_blocks >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_pairwise_distance_sum: P = %lld is too large (sub-sample the swarm)", (long long)P);
-  const size_t smem = (size_t)2 * kPairTile * (D + 1) * sizeof(float);
+  const size_t smem = ((size_t)((kPairTile * (D + 1) + 1) & ~1) + (size_t)D * (kPairTile + 2)) * sizeof(float);
   if (smem > 200 * 1024) return fail(PSOB_E_UNSUPPORTED, "psob_pairwise_distance_sum: D = %d is too large", D);
   PSOB_CUDA(cudaFuncSetAttribute(pairwise_distance_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   PSOB_CUDA(cudaMemsetAsync(sum_out, 0, sizeof(double), (cudaStream_t)s));

@@ -72,6 +72,8 @@ struct EngineParams {
   int warp_store;            // every epilogue warp stores its own 32 rows of a chunk (32-row TMA box): no barriers inside a group
   int issuers;               // MMA-issuing warps (1 or 2): one thread sustains only ~1 tcgen05.mma per 85-94 cycles (tools/umma_bench.cu)
   int issue_split;           // 2 issuers: ownership of an op by (accumulator buffer + column region) parity (1) or by buffer only (0)
+  int half_store;            // warp stores with a single staging tile: the warp's 4 KB slice is two 32-column halves (SWIZZLE_64B)
+                             // published by separate TMA stores, so one half drains while the other is written
   int band;                  // image-band epilogue (lower_convt_image_band): 4 chunks of two padded image rows each
   int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
   int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
@@ -173,6 +175,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const int q_in_tiled = p.in_tiled;
   const int q_out_tiled = p.out_tiled;
   const bool q_warp_store = kTmaStore && p.warp_store != 0;
+  const bool q_half = q_warp_store && p.half_store != 0;
   const int q_n_in_chunks = p.n_in_chunks;
   const int q_n_out_chunks = p.n_out_chunks;
   const uint32_t q_idesc = p.idesc;
@@ -536,7 +539,23 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             }
             const uint32_t sbuf = sbuf0 + sflip * kATileBytes;
             const uint32_t srow = sbuf + (uint32_t)row * 128u;
-            if (q_warp_store) {
+            const uint32_t hbase = sbuf0 + (uint32_t)q * 4096u;          // half mode: this warp's two 2 KB halves
+            auto half_open = [&](int) {                                  // at most the OTHER half's store may still be reading
+              if (lane == 0) ptx::bulk_wait_read1();
+              __syncwarp();
+            };
+            auto half_publish = [&](int h) {
+              ptx::fence_proxy_async();
+              __syncwarp();
+              if (lane == 0) {
+                ptx::tma_store_2d(&tmY, hbase + (uint32_t)h * 2048u, out_c0(j0.z + cm) + 32 * h, out_c1(ptile, j0.z + cm) + q * 32);
+                ptx::bulk_commit();
+              }
+              __syncwarp();
+            };
+            if (q_half) {
+              // nothing to wait for here: every half waits for its own previous store just before it is rewritten
+            } else if (q_warp_store) {
               // the warp's own slice (32 rows = 4 KB) of the staging tile, tracked by ITS lane 0's bulk groups
               if (lane == 0) { if (q_stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
               __syncwarp();
@@ -562,7 +581,14 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               o.y = bias_act_pack<kAct>(v[8 * j + 2], v[8 * j + 3], b0.z, b0.w);
               o.z = bias_act_pack<kAct>(v[8 * j + 4], v[8 * j + 5], b1.x, b1.y);
               o.w = bias_act_pack<kAct>(v[8 * j + 6], v[8 * j + 7], b1.z, b1.w);
-              ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);   // SWIZZLE_128B: 16-byte slot j of row r lives at j ^ (r % 8)
+              if (q_half) {
+                // SWIZZLE_64B half tile [32 rows x 64 B]: 16-byte slot jj of row r lives at jj ^ ((r / 2) % 4)
+                if ((j & 3) == 0) half_open(j >> 2);
+                ptx::st_shared_v4(hbase + (uint32_t)(j >> 2) * 2048u + (uint32_t)lane * 64u + ((((uint32_t)j & 3u) ^ (((uint32_t)lane >> 1) & 3u)) << 4), o);
+                if ((j & 3) == 3) half_publish(j >> 2);
+              } else {
+                ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);   // SWIZZLE_128B: 16-byte slot j of row r lives at j ^ (r % 8)
+              }
             };
             if (q_band) {
               // out element e = 32 * rr + px of the 128-byte row <- column rr * 30 + px; the padding columns and the
@@ -602,6 +628,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 emit_slot(j, __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j)), __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4)));
             }
             if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
+            if (q_half) {
+              if (prof) { const long long t = clock64(); e_pub += (unsigned long long)(t - tq); tq = t; }
+              continue;                                  // both halves were published from inside the slot loop
+            }
             ptx::fence_proxy_async();                    // generic-proxy writes -> visible to the TMA (async proxy)
             if (q_warp_store) {
               __syncwarp();
@@ -806,15 +836,16 @@ static EncodeTiledFn get_encode() {
 }
 
 // bf16 matrix [rows, cols] with row pitch `pitch` elements; box = [box_rows x 64], SWIZZLE_128B
-static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, uint64_t pitch, uint32_t box_rows) {
+static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, uint64_t pitch, uint32_t box_rows,
+                     uint32_t box_cols = (uint32_t)kKChunk, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return fail(PSOB_E_DEVICE, "cuTensorMapEncodeTiled entry point not available");
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {pitch * 2};
-  cuuint32_t box[2] = {(cuuint32_t)kKChunk, box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail((int)r, "cuTensorMapEncodeTiled failed with CUresult %d (cols=%llu rows=%llu pitch=%llu box_rows=%u)",
                                      (int)r, (unsigned long long)cols, (unsigned long long)rows, (unsigned long long)pitch, box_rows);
@@ -1115,6 +1146,7 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
   p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.epi_groups = l->epi_groups; p.step_stride = l->step_stride; p.band = (l->band && p.y != nullptr) ? 1 : 0;
   p.issuers = l->issuers; p.issue_split = l->issue_split ? 1 : 0;
   p.warp_store = l->warp_store ? 1 : 0;
+  { const char* e = getenv("PSOB_HALF_STORE"); p.half_store = (l->warp_store && l->stg_bufs == 1 && !l->band && l->tma_store && (e ? atoi(e) != 0 : true)) ? 1 : 0; }   // measured: d.c2 -2.7 %, g.l2 -1 %
   if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
@@ -1156,8 +1188,10 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
   if (rc) return rc;
   if (tma_store) {
     const uint32_t box_rows = l->warp_store ? 32u : (uint32_t)kTileM;
-    rc = d.out_tiled ? make_tmap(&tmY, y, kKChunk, (uint64_t)n_ptiles * (d.out_pitch / kKChunk) * kTileM, kKChunk, box_rows)
-                     : make_tmap(&tmY, y, (uint64_t)d.out_pitch, (uint64_t)P, (uint64_t)d.out_pitch, box_rows);
+    const uint32_t box_cols = p.half_store ? 32u : (uint32_t)kKChunk;
+    const CUtensorMapSwizzle sw = p.half_store ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
+    rc = d.out_tiled ? make_tmap(&tmY, y, kKChunk, (uint64_t)n_ptiles * (d.out_pitch / kKChunk) * kTileM, kKChunk, box_rows, box_cols, sw)
+                     : make_tmap(&tmY, y, (uint64_t)d.out_pitch, (uint64_t)P, (uint64_t)d.out_pitch, box_rows, box_cols, sw);
     if (rc) return rc;
   } else {
     tmY = tmA;

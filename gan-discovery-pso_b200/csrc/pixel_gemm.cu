@@ -470,7 +470,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     // 8 warps = 2 groups x 4 TMEM lane quadrants (quadrant = warp % 4, the hardware's access rule)
     const uint32_t tempty0_leader = kPair ? ptx::map_to_cta(tempty_bar(0), 0u) : 0u;
     auto release_tmem = [&](uint32_t buf) {
-      if (kPair) ptx::mbar_arrive_cluster(tempty0_leader + 8u * buf); else ptx::mbar_arrive(tempty_bar(buf));
+      // the accumulator has been read into registers (tcgen05.wait::ld returned): a pure signal, no memory to publish
+      if (kPair) ptx::mbar_arrive_cluster_relaxed(tempty0_leader + 8u * buf); else ptx::mbar_arrive_relaxed(tempty_bar(buf));
     };
     const int q = warp & 3;
     const int grp = warp >> 2;

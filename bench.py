@@ -297,10 +297,8 @@ def run_psob(args):
         stage_ms["assessor_tensor_floor_ms"] = float(2.0 * anet.macs_exact * P / (peaks()["tf_sustained"] * 1e12) * 1e3)
         stage_ms["assessor_total"] = float(sum(v for k, v in stage_ms.items() if k.startswith("a.") or k == "assessor_pack_rescale"))
     else:
-        cur = gnet.image_padded_bf16()
-        for layer, y, y32 in zip(dnet.layers, dnet.acts, dnet.acts32):
-            timed(layer.prog.name, lambda l=layer, c=cur, y=y, y32=y32: l.run(c, P, y, y32))
-            cur = y
+        for name, launch in dnet.launch_plan(gnet.image_padded_bf16()):      # fused head: d.c1, d.c2 (+ head dot), d.c3.finish
+            timed(name, launch)
         timed("score_fitness", lambda: engine.score_fitness(dnet.acts32[-1], sw.fit, "optimize_out_training"))
     timed("pbest_gbest", sw.personal_and_global_best)
     timed("pso_update", sw.move)
@@ -412,7 +410,7 @@ def run_psob(args):
 
     if rank == 0:
         # layers, score, pbest+candidate+apply, update (assessor: + pack, max pool, softmax pick)
-        launches_per_step = len(gnet.layers) + (len(anet.ops) + 2 if assessor else len(dnet.layers)) + 1 + 3 + 1
+        launches_per_step = len(gnet.layers) + (len(anet.ops) + 2 if assessor else len(dnet.launch_plan(gnet.image_padded_bf16()))) + 1 + 3 + 1
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",

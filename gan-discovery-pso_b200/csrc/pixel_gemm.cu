@@ -82,6 +82,10 @@ struct EngineParams {
   uint32_t idesc, tmem_cols;
   uint32_t idesc_eye;        // instruction descriptor of identity ops (M = 128, N = 64)
   int eye;                   // the layer has identity ops: the kernel builds the identity tile at res_off
+  // dot epilogue (kDot): the layer's bf16 output never leaves the SM; every output row is reduced against dot_w
+  // (bf16 [out_pitch], the weights of a following full-map conv with ONE output channel) as it comes out of TMEM
+  const uint16_t* dot_w;
+  float* dot_part;           // fp32 [n_jobs * epi_groups][P]: one partial sum per (job, epilogue group) and particle
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {
@@ -156,7 +160,13 @@ __device__ __forceinline__ uint32_t bias_act_pack(uint32_t v0, uint32_t v1, floa
 // L2 traffic is each CTA's own 16 KB A tile (the L2 slices deliver ~42 B/clk/SM with all SMs pulling:
 // streaming a 32 KB B tile per 512-cycle step had every heavy layer L2-bound at ~45 % of the MMA rate).
 // The leader (rank 0) issues all MMAs; its commits arrive on the barriers of both CTAs.
-template <int kAct, bool kTmaStore, bool kPair, bool kRes = false>
+//
+// kDot: the chunked epilogue without the store.  Each thread owns one particle row of the accumulator, so the
+// per-particle reduction of a following Cout = 1 full-map conv (Discriminator's last layer, src/utils/util_dcgan.py:117)
+// is a thread-local dot product of the bf16-rounded activations with that conv's weights (kept in the unused
+// staging tiles): no staging, no TMA store, no HBM round trip of the activation, and the next layer disappears.
+// Partial sums are written per (job, epilogue group) in a fixed order, so the result is deterministic.
+template <int kAct, bool kTmaStore, bool kPair, bool kRes = false, bool kDot = false>
 __global__ void __launch_bounds__(kMaxThreads, 1)
 pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmY, const EngineParams p) {
@@ -280,6 +290,12 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   }
   if (bias_in_smem)
     for (int i = threadIdx.x; i < p.n_bias_rows * q_nt; i += kThreads) s_bias[i] = p.bias[i];
+  if (kDot) {
+    // weights of the fused head, indexed by this layer's output column (16-byte copies; out_pitch % 8 == 0)
+    const uint4* src = reinterpret_cast<const uint4*>(p.dot_w);
+    uint4* dst = reinterpret_cast<uint4*>(gbase + p.stg_off);
+    for (int i = threadIdx.x; i < (q_out_pitch >> 3); i += kThreads) dst[i] = __ldg(src + i);
+  }
   if (p.eye && threadIdx.x < 64) {
     // identity tile, K-major SWIZZLE_128B: row r is 128 B, its 16-byte slot j lives at j ^ (r % 8); element (r, r) = 1
     const uint32_t r = threadIdx.x;
@@ -499,6 +515,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         mbar_wait_t(tfull_bar(buf), use & 1u, prof, w_tfull);
         ptx::tc_fence_after();
         const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)q_nt;
+        float dacc0 = 0.f, dacc1 = 0.f, dacc2 = 0.f, dacc3 = 0.f;      // kDot: this row's partial dot product over the job
         if (kTmaStore) {
           const int n_chunks = q_nt >> 6;
           int last = -1;                      // last chunk this group will read: release TMEM right after it
@@ -537,6 +554,34 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               ptx::tc_fence_before();
               __syncwarp();
               if (lane == 0) release_tmem(buf);
+            }
+            if (kDot) {
+              // all lanes read the same 16 bytes of weights (shared-memory broadcast); bf16 -> fp32 is a shift / mask
+              const uint32_t waddr = base + (uint32_t)p.stg_off + (uint32_t)(j0.z + cm) * 2u;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                float4 b0, b1;
+                if (bias_in_smem) {
+                  const uint32_t baddr = s_bias_addr + (uint32_t)(j1.z * q_nt + n0 + 8 * j) * 4u;
+                  b0 = ptx::ld_shared_f4(baddr); b1 = ptx::ld_shared_f4(baddr + 16u);
+                } else {
+                  b0 = __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j)); b1 = __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4));
+                }
+                const float4 wf = ptx::ld_shared_f4(waddr + 16u * (uint32_t)j);
+                const uint32_t w[4] = {__float_as_uint(wf.x), __float_as_uint(wf.y), __float_as_uint(wf.z), __float_as_uint(wf.w)};
+                const uint32_t o[4] = {bias_act_pack<kAct>(v[8 * j + 0], v[8 * j + 1], b0.x, b0.y), bias_act_pack<kAct>(v[8 * j + 2], v[8 * j + 3], b0.z, b0.w),
+                                       bias_act_pack<kAct>(v[8 * j + 4], v[8 * j + 5], b1.x, b1.y), bias_act_pack<kAct>(v[8 * j + 6], v[8 * j + 7], b1.z, b1.w)};
+                dacc0 = fmaf(__uint_as_float(o[0] << 16), __uint_as_float(w[0] << 16), dacc0);
+                dacc1 = fmaf(__uint_as_float(o[0] & 0xFFFF0000u), __uint_as_float(w[0] & 0xFFFF0000u), dacc1);
+                dacc2 = fmaf(__uint_as_float(o[1] << 16), __uint_as_float(w[1] << 16), dacc2);
+                dacc3 = fmaf(__uint_as_float(o[1] & 0xFFFF0000u), __uint_as_float(w[1] & 0xFFFF0000u), dacc3);
+                dacc0 = fmaf(__uint_as_float(o[2] << 16), __uint_as_float(w[2] << 16), dacc0);
+                dacc1 = fmaf(__uint_as_float(o[2] & 0xFFFF0000u), __uint_as_float(w[2] & 0xFFFF0000u), dacc1);
+                dacc2 = fmaf(__uint_as_float(o[3] << 16), __uint_as_float(w[3] << 16), dacc2);
+                dacc3 = fmaf(__uint_as_float(o[3] & 0xFFFF0000u), __uint_as_float(w[3] & 0xFFFF0000u), dacc3);
+              }
+              if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
+              continue;
             }
             const uint32_t sbuf = sbuf0 + sflip * kATileBytes;
             const uint32_t srow = sbuf + (uint32_t)row * 128u;
@@ -654,6 +699,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             if (q_stg_bufs == 2) sflip ^= 1u;
             if (prof) { const long long t = clock64(); e_pub += (unsigned long long)(t - tq); tq = t; }
           }
+          if (kDot) {
+            // one coalesced 128-byte store per warp; slots without a valid chunk hold 0
+            const long long particle = (long long)tile_row(ptile) + row;
+            if (particle < q_P) p.dot_part[(size_t)(job * q_epi_groups + grp) * (size_t)q_P + particle] = (dacc0 + dacc1) + (dacc2 + dacc3);
+          }
         } else {
           const long long particle = (long long)tile_row(ptile) + row;
           const bool valid = particle < q_P;
@@ -731,7 +781,13 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 }
 
 typedef void (*UmmaKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const EngineParams);
-static UmmaKernelFn umma_kernel_for(int act, bool tma_store, bool pair, bool res) {
+static UmmaKernelFn umma_kernel_for(int act, bool tma_store, bool pair, bool res, bool dot = false) {
+  if (dot) {            // fused Cout = 1 head: chunked epilogue layers with LeakyReLU / ReLU (discriminator / encoder-style stacks)
+    if (res || !tma_store) return nullptr;
+    if (act == PSOB_ACT_LEAKY) return pair ? pixel_gemm_umma_kernel<PSOB_ACT_LEAKY, true, true, false, true> : pixel_gemm_umma_kernel<PSOB_ACT_LEAKY, true, false, false, true>;
+    if (act == PSOB_ACT_RELU) return pair ? pixel_gemm_umma_kernel<PSOB_ACT_RELU, true, true, false, true> : pixel_gemm_umma_kernel<PSOB_ACT_RELU, true, false, false, true>;
+    return nullptr;
+  }
   if (res) {            // residual add: solo CTAs, TMA-store epilogue, the bottleneck's ReLU (or none)
     if (pair || !tma_store) return nullptr;
     if (act == PSOB_ACT_RELU) return pixel_gemm_umma_kernel<PSOB_ACT_RELU, true, false, true>;
@@ -883,6 +939,9 @@ struct psob_layer {
   int sm_count = 0;
   int device = -1;
 };
+
+static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, const void* res,
+                          int64_t res_pitch, const void* dot_w, float* dot_part, int32_t impl, psob_stream_t s);
 
 extern "C" {
 
@@ -1114,13 +1173,40 @@ int psob_layer_profile(psob_layer* l, void* counters) {
 }
 
 int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, int32_t impl, psob_stream_t s) {
-  return psob_layer_run_residual(l, x, x_pitch, P, y, y32, nullptr, 0, impl, s);
+  return layer_run_impl(l, x, x_pitch, P, y, y32, nullptr, 0, nullptr, nullptr, impl, s);
 }
 
 int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, const void* res,
                             int64_t res_pitch, int32_t impl, psob_stream_t s) {
+  return layer_run_impl(l, x, x_pitch, P, y, y32, res, res_pitch, nullptr, nullptr, impl, s);
+}
+
+int psob_layer_dot_slots(const psob_layer* l) {
+  if (!l) return fail(PSOB_E_ARG, "psob_layer_dot_slots: null layer");
+  if (!l->tma_store || l->band) return fail(PSOB_E_UNSUPPORTED, "psob_layer_dot_slots: the layer has no chunked bf16 epilogue");
+  return l->d.n_jobs * l->epi_groups;
+}
+
+int psob_layer_run_dot(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, const void* dot_w, float* part, psob_stream_t s) {
+  if (!dot_w || !part) return fail(PSOB_E_ARG, "psob_layer_run_dot: null weights or partial-sum buffer");
+  return layer_run_impl(l, x, x_pitch, P, nullptr, nullptr, nullptr, 0, dot_w, part, PSOB_IMPL_TCGEN05, s);
+}
+
+}  // extern "C"
+
+static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, const void* res,
+                          int64_t res_pitch, const void* dot_w, float* dot_part, int32_t impl, psob_stream_t s) {
   if (!l || !x || P <= 0) return fail(PSOB_E_ARG, "psob_layer_run: bad arguments");
   const psob_layer_desc& d = l->d;
+  const bool dot = dot_w != nullptr;
+  if (dot) {
+    if (!l->tma_store || l->band || d.out32_pitch)       // the output layout (row- / tile-major) is irrelevant: nothing is stored
+      return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_dot: needs a layer with the chunked bf16 epilogue");
+    if (d.out_pitch * 2 > l->epi_groups * l->stg_bufs * kATileBytes)
+      return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_dot: %d B of head weights do not fit the layer's %d B of staging tiles", d.out_pitch * 2,
+                  l->epi_groups * l->stg_bufs * kATileBytes);
+    if (!aligned16(dot_w) || (reinterpret_cast<uintptr_t>(dot_part) & 3)) return fail(PSOB_E_ARG, "psob_layer_run_dot: misaligned weights / partial sums");
+  }
   if (res) {
     if (!l->tma_store || l->band || !y) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_residual: the residual add needs the chunked bf16 (TMA-store) epilogue");
     if (!aligned16(res) || (d.out_tiled ? res_pitch != d.out_pitch : (res_pitch < d.out_pitch || res_pitch % 8)))
@@ -1128,13 +1214,14 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
   }
   if (d.in_tiled && x_pitch != d.in_pitch) return fail(PSOB_E_ARG, "psob_layer_run: a tile-major input has x_pitch == in_pitch (%d), got %lld", d.in_pitch, (long long)x_pitch);
   if (x_pitch < d.in_pitch || x_pitch % 8 || !aligned16(x)) return fail(PSOB_E_ARG, "psob_layer_run: x_pitch %lld < in_pitch %d, or misaligned", (long long)x_pitch, d.in_pitch);
-  if ((d.out_pitch && !y && !(d.out32_pitch && y32)) || (!d.out_pitch && !y32)) return fail(PSOB_E_ARG, "psob_layer_run: missing output buffer");
+  if (!dot && ((d.out_pitch && !y && !(d.out32_pitch && y32)) || (!d.out_pitch && !y32))) return fail(PSOB_E_ARG, "psob_layer_run: missing output buffer");
   if (y && !aligned16(y)) return fail(PSOB_E_ARG, "psob_layer_run: y must be 16-byte aligned");
   EngineParams p;
   p.steps = l->steps; p.jobs = l->jobs; p.chains = l->chains; p.n_chains = d.n_chains; p.chains_off = l->chains_off; p.col_map = l->col_map; p.col_map32 = l->col_map32; p.bias = l->bias;
   p.y = d.out_pitch ? reinterpret_cast<__nv_bfloat16*>(y) : nullptr;
   p.y32 = d.out32_pitch ? y32 : nullptr;
   p.res = reinterpret_cast<const __nv_bfloat16*>(res); p.res_pitch = res_pitch;
+  p.dot_w = reinterpret_cast<const uint16_t*>(dot_w); p.dot_part = dot_part;
   p.P = P;
   const long long n_ptiles = (P + kTileM - 1) / kTileM;
   p.n_items = n_ptiles * d.n_chains;
@@ -1164,11 +1251,12 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
   }
   if (impl != PSOB_IMPL_TCGEN05) return fail(PSOB_E_ARG, "psob_layer_run: unknown impl %d", impl);
 
-  const bool tma_store = l->tma_store && p.y != nullptr;
+  const bool tma_store = l->tma_store && (p.y != nullptr || dot);
   if (d.out_tiled && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a tile-major output needs its bf16 output buffer");
   if (l->pair && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a CTA-pair layer needs its bf16 output buffer");
-  UmmaKernelFn fn = umma_kernel_for(d.act, tma_store, l->pair, res != nullptr);
-  if (!fn) return fail(PSOB_E_ARG, "psob_layer_run: no kernel for activation %d%s", d.act, res ? " with a residual (solo CTAs, ReLU / none only)" : "");
+  UmmaKernelFn fn = umma_kernel_for(d.act, tma_store, l->pair, res != nullptr, dot);
+  if (!fn) return fail(PSOB_E_ARG, "psob_layer_run: no kernel for activation %d%s", d.act,
+                       res ? " with a residual (solo CTAs, ReLU / none only)" : (dot ? " with a fused head (ReLU / LeakyReLU only)" : ""));
   if (l->pair) {
     p.n_items = ((n_ptiles + 1) / 2) * d.n_chains;                // items are (pair of particle tiles, chain of jobs)
     p.idesc = make_idesc_bf16(2 * kTileM, d.mma_n);
@@ -1187,7 +1275,7 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
   int rc = d.in_tiled ? make_tmap(&tmA, x, kKChunk, (uint64_t)n_ptiles * (d.in_pitch / kKChunk) * kTileM, kKChunk, kTileM)
                       : make_tmap(&tmA, x, (uint64_t)x_pitch, (uint64_t)P, (uint64_t)x_pitch, kTileM);
   if (rc) return rc;
-  if (tma_store) {
+  if (tma_store && !dot) {
     const uint32_t box_rows = l->warp_store ? 32u : (uint32_t)kTileM;
     const uint32_t box_cols = p.half_store ? 32u : (uint32_t)kKChunk;
     const CUtensorMapSwizzle sw = p.half_store ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
@@ -1219,4 +1307,19 @@ int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64
   return 0;
 }
 
-}  // extern "C"
+// out[p] = act(sum over slots of part[slot][p] + bias): the tail of the fused head (fixed summation order)
+__global__ void __launch_bounds__(256) dot_finish_kernel(const float* __restrict__ part, int n_slots, long long P, float bias, int act,
+                                                         float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  float acc = 0.f;
+  for (int sl = 0; sl < n_slots; ++sl) acc += part[(size_t)sl * (size_t)P + i];
+  out[i] = apply_act(acc + bias, act);
+}
+
+extern "C" int psob_dot_finish(const float* part, int32_t n_slots, int64_t P, float bias, int32_t act, float* out, psob_stream_t s) {
+  if (!part || !out || n_slots <= 0 || P <= 0) return fail(PSOB_E_ARG, "psob_dot_finish: bad arguments");
+  dot_finish_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)s>>>(part, n_slots, P, bias, act, out);
+  PSOB_LAUNCH_CHECK("dot_finish_kernel");
+  return 0;
+}

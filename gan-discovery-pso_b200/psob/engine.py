@@ -173,8 +173,57 @@ class GeneratorNet(Network):
 class DiscriminatorNet(Network):
     """DCGAN discriminator on the padded bf16 image (src/utils/util_dcgan.py:103-125) -> sigmoid score fp32 [P,1]."""
 
-    def __init__(self, state_dict, P, prefix="disc", device=None, impl=_ffi.IMPL_TCGEN05):
+    def __init__(self, state_dict, P, prefix="disc", device=None, impl=_ffi.IMPL_TCGEN05, fused_head=None):
         super().__init__(nets.discriminator_programs(_sd_numpy(state_dict), prefix), P, device, impl)
+        # Fused head (default on the product path): the hidden conv's epilogue reduces its own output against the
+        # final Conv2d(features, 1, k = whole map) -- psob_layer_run_dot + psob_dot_finish -- so the hidden
+        # activation is never written and the last layer is not launched.  PSOB_FUSED_HEAD=0 keeps the layer-by-layer
+        # path (A/B measurements, per-layer tests).
+        if fused_head is None:
+            fused_head = os.environ.get("PSOB_FUSED_HEAD", "1") != "0"
+        self.head = None
+        if fused_head and impl == _ffi.IMPL_TCGEN05:
+            self.head = self._make_head()
+
+    def _make_head(self):
+        hid, last = self.programs[-2], self.programs[-1]
+        if last.meta.get("kind") != "conv_full" or last.meta.get("out_c") != 1 or hid.out_pitch != last.in_pitch:
+            return None
+        if hid.act not in (L.ACT_LEAKY, L.ACT_RELU):
+            return None
+        lib = _ffi.lib()
+        slots = lib.psob_layer_dot_slots(self.layers[-2].handle)
+        if slots <= 0:
+            return None
+        w = nets.head_weights(last)                       # fp32 values (bf16-exact) indexed by the hidden layer's output column
+        with torch.cuda.device(self.device):
+            w_dev = torch.from_numpy(w).to(self.device).to(torch.bfloat16).contiguous()
+            part = torch.zeros(slots, self.P, dtype=torch.float32, device=self.device)
+        return dict(w=w_dev, part=part, slots=int(slots), bias=float(last.bias[0, 0]), act=int(last.act))
+
+    def launch_plan(self, x: torch.Tensor):
+        """The forward pass as a list of (name, launch) pairs -- what forward() runs and what bench.py times per stage."""
+        plan, cur, lib = [], x, _ffi.lib()
+        n_plain = len(self.layers) - (2 if self.head else 0)
+        for layer, y, y32 in list(zip(self.layers, self.acts, self.acts32))[:n_plain]:
+            plan.append((layer.prog.name, lambda l=layer, c=cur, y=y, y32=y32: l.run(c, self.P, y, y32, self.impl)))
+            cur = y
+        if self.head:
+            hd, hid = self.head, self.layers[-2]
+            plan.append((hid.prog.name, lambda c=cur: _ffi.check(lib.psob_layer_run_dot(
+                hid.handle, c.data_ptr(), c.stride(0), self.P, hd["w"].data_ptr(), hd["part"].data_ptr(), _stream()),
+                f"psob_layer_run_dot({hid.prog.name})")))
+            plan.append((self.programs[-1].name + ".finish", lambda: _ffi.check(lib.psob_dot_finish(
+                hd["part"].data_ptr(), hd["slots"], self.P, hd["bias"], hd["act"], self.acts32[-1].data_ptr(), _stream()),
+                "psob_dot_finish")))
+        return plan
+
+    def forward(self, x: torch.Tensor):
+        if not self.head:
+            return super().forward(x)
+        for _, launch in self.launch_plan(x):
+            launch()
+        return None, self.acts32[-1]
 
 
 class EncoderNet(Network):

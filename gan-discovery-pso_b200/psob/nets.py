@@ -95,6 +95,17 @@ def discriminator_programs(sd: Dict, prefix: str = "disc") -> List[L.LayerProgra
     return _down_programs(sd, prefix, "d", L.ACT_SIGMOID)
 
 
+def head_weights(last: L.LayerProgram) -> np.ndarray:
+    """Weights of a `lower_conv_full` layer with one output channel as a vector over its INPUT columns (= the output
+    columns of the layer before it): w[pix * cp + ch] = W[0, ch, ky, kx] (src/utils/util_dcgan.py:117), bf16-rounded like
+    the layer's own weight pack.  Columns no step reads (channel padding) stay 0."""
+    assert last.meta.get("kind") == "conv_full" and last.meta.get("out_c") == 1
+    w = np.zeros(last.in_pitch, np.float32)
+    for a_col, b_row, _d_col, _flags in np.asarray(last.steps)[:, :4]:
+        w[a_col:a_col + L.KCHUNK] = last.wpack[b_row]            # row 0 of the tile = output channel 0
+    return w
+
+
 def encoder_programs(sd: Dict, prefix: str = "enc") -> List[L.LayerProgram]:
     """[P,1,28,28] (padded bf16 image) -> latent fp32 [P,enc_dim]."""
     return _down_programs(sd, prefix, "e", L.ACT_NONE)

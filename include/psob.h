@@ -214,6 +214,19 @@ int psob_layer_run(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, voi
 int psob_layer_run_residual(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32,
                             const void* res, int64_t res_pitch, int32_t impl, psob_stream_t s);
 
+/* Fused single-channel head -- replaces the LAST TWO modules of Discriminator.forward (src/utils/util_dcgan.py:115-118:
+ * the hidden Conv2d + BatchNorm + LeakyReLU block and the final Conv2d(features, 1, k = whole map) + Sigmoid) by one
+ * launch plus a tiny reduction.  The layer's bf16 activation is never stored: every epilogue thread owns one particle
+ * row of the accumulator and reduces it, bf16-rounded exactly as the stored activation would be, against dot_w
+ * (device bf16 [out_pitch], the head conv's weight indexed by this layer's output column).  part: device fp32
+ * [psob_layer_dot_slots(l)][P], one partial sum per (job, epilogue group) and particle, every slot rewritten by every run;
+ * psob_dot_finish adds the slots in index order, then bias and activation: out[p] = act(sum + bias).  Deterministic.
+ * Only layers with the chunked bf16 epilogue, ReLU / LeakyReLU, out_pitch * 2 bytes <= the layer's staging tiles. */
+int psob_layer_dot_slots(const psob_layer* l);
+int psob_layer_run_dot(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, const void* dot_w, float* part,
+                       psob_stream_t s);
+int psob_dot_finish(const float* part, int32_t n_slots, int64_t P, float bias, int32_t act, float* out, psob_stream_t s);
+
 /* Debug: when `counters` (device, u64 [n_SMs][32]) is non-NULL, later runs of the layer record per CTA
  * { producer wait-empty, producer total, mma wait-full, mma wait-tmem-empty, mma total,
  *   epilogue wait-tmem-full, epilogue total, items, epilogue tmem-load, staging-free wait,

@@ -189,7 +189,7 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
         monkeypatch.setattr(L, "CHAIN_ROWS", bool(chain))
         monkeypatch.setattr(L, "CHAIN_CONVT", bool(chain))
         gnet = engine.GeneratorNet(gen.state_dict(), P)
-        dnet = engine.DiscriminatorNet(disc.state_dict(), P)
+        dnet = engine.DiscriminatorNet(disc.state_dict(), P, fused_head=False)     # layer by layer: every activation is compared
         assert any(l.out_tiled for l in gnet.layers) == bool(tiled)
         assert gnet.programs[1].b_resident == bool(pair) and dnet.programs[1].b_resident == bool(pair)
         _, img = gnet.forward(_rows(z.numpy(), gnet.in_pitch))
@@ -239,3 +239,51 @@ def test_bn_free_vq_decoder_vs_reference(mods, golden_resnet):
     ref = g["vqmnist/out"].reshape(6, 784)
     got = img.cpu().numpy()
     assert np.abs(got - ref).max() <= 2e-2 and np.linalg.norm(got - ref) <= 5e-3 * np.linalg.norm(ref)
+
+
+@pytest.mark.parametrize("P", [1, 129, 1000])
+def test_fused_discriminator_head_matches_layer_by_layer(mods, monkeypatch, P):
+    """psob_layer_run_dot + psob_dot_finish (hidden conv reduced against the final Conv2d(128, 1, 7) inside its own
+    epilogue, src/utils/util_dcgan.py:115-118) == the layer-by-layer path to fp32 summation-order noise, in the CTA-pair
+    and the solo execution mode; deterministic run to run; and equal to the numpy emulation of the tables."""
+    engine, L, nets, ffi = mods
+    torch.manual_seed(11)
+    disc = port.Discriminator(1, 64)
+    port.randomize_bn_stats(disc, torch.Generator().manual_seed(12))
+    with torch.no_grad():
+        for p_ in disc.parameters():            # weights large enough that the scores spread over (0, 1)
+            p_.mul_(3.0)
+    img = torch.rand(P, 784, generator=torch.Generator().manual_seed(P)) * 2 - 1
+    xp = torch.from_numpy(nets.pad_image_bf16(img.numpy())).to(torch.bfloat16).cuda()
+    for pair in (1, 0):
+        monkeypatch.setattr(L, "RESIDENT_PAIR", 256 * 1024 if pair else 0)
+        plain = engine.DiscriminatorNet(disc.state_dict(), P, fused_head=False)
+        fused = engine.DiscriminatorNet(disc.state_dict(), P, fused_head=True)
+        assert fused.head is not None and [n for n, _ in fused.launch_plan(xp)] == ["d.c1", "d.c2", "d.c3.finish"]
+        _, s0 = plain.forward(xp)
+        _, s1 = fused.forward(xp)
+        a = s1.clone()
+        fused.head["part"].fill_(float("nan"))          # every slot is rewritten by every run
+        _, s2 = fused.forward(xp)
+        torch.cuda.synchronize()
+        assert torch.equal(a, s2)
+        s0, s1 = s0.cpu().numpy()[:, 0], a.cpu().numpy()[:, 0]
+        assert s0.std() > 1e-3 or P == 1
+        np.testing.assert_allclose(s1, s0, atol=1e-5, rtol=0)       # fp32 summation order (tensor-core chain vs per-thread FMA)
+        # numpy emulation: bf16 hidden activation (emulate_chain) . bf16 head weights, fp64 sum, + bias, sigmoid
+        hid, _ = nets.emulate_chain(fused.programs[:2], xp.float().cpu().numpy())
+        w = nets.head_weights(fused.programs[2])
+        ref = 1.0 / (1.0 + np.exp(-(hid.astype(np.float64) @ w.astype(np.float64) + float(fused.programs[2].bias[0, 0]))))
+        np.testing.assert_allclose(s1, ref, atol=2e-5, rtol=0)
+
+
+def test_fused_head_rejects_layers_without_chunked_epilogue(mods):
+    engine, L, nets, ffi = mods
+    disc = port.Discriminator(1, 64)
+    d = engine.DiscriminatorNet(disc.state_dict(), 4, fused_head=False)
+    lib = ffi.lib()
+    assert lib.psob_layer_dot_slots(d.layers[2].handle) < 0            # the score layer itself stores fp32 directly
+    x = torch.zeros(4, d.programs[2].in_pitch, dtype=torch.bfloat16, device="cuda")
+    part = torch.zeros(64, 4, device="cuda")
+    rc = lib.psob_layer_run_dot(d.layers[2].handle, x.data_ptr(), x.stride(0), 4, x.data_ptr(), part.data_ptr(), 0)
+    assert rc < 0

@@ -20,10 +20,16 @@ cur = z
 print("layer        jobs steps | prod: wait_empty/total | mma: wait_full wait_tmem /total | epi: wait_tfull/total | cyc/item cyc/step | epi per chunk: ld free math pub")
 for net, x0 in ((gnet, z), (dnet, gnet.image_padded_bf16())):
     cur = x0
+    plan = dict(net.launch_plan(x0)) if hasattr(net, "launch_plan") else {}     # fused head: d.c2 runs psob_layer_run_dot, d.c3 is gone
     for layer, y, y32 in zip(net.layers, net.acts, net.acts32):
+        if plan and layer.prog.name not in plan:
+            continue
         buf.zero_()
         _ffi.check(_ffi.lib().psob_layer_profile(layer.handle, buf.data_ptr()))
-        layer.run(cur, P, y, y32)
+        if plan:
+            plan[layer.prog.name]()
+        else:
+            layer.run(cur, P, y, y32)
         torch.cuda.synchronize()
         _ffi.check(_ffi.lib().psob_layer_profile(layer.handle, None))
         b = buf.cpu().numpy().astype(np.float64)

@@ -111,11 +111,22 @@ __device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity, bool 
   acc += (unsigned long long)(clock64() - t0);
 }
 
+// tanh(v) = 1 - 2 / (exp(2v) + 1) on the SFU (ex2.approx + rcp.approx, 5 instructions, no branch).  libdevice's tanhf is
+// ~40 instructions with a divergent small-argument branch, and the image layer's epilogue evaluates 224 of them per
+// thread and job next to the single MMA-issuing thread on the same scheduler.  Absolute error <= ~3e-7 over the whole
+// range (saturates to +-1 through exp -> inf / 0), far below the bf16 image's 4e-3 and the 2e-2 image gate.
+__device__ __forceinline__ float tanh_sfu(float v) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(v * 2.8853900817779268f));     // exp(2v) = 2^(2v log2 e)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.f));
+  return fmaf(-2.f, r, 1.f);
+}
+
 template <int kAct>
 __device__ __forceinline__ float act_fn(float v) {
   if (kAct == PSOB_ACT_RELU) return fmaxf(v, 0.f);
   if (kAct == PSOB_ACT_LEAKY) return fmaxf(v, 0.2f * v);      // max(v, 0.2v) == leaky_relu(v, 0.2)
-  if (kAct == PSOB_ACT_TANH) return tanhf(v);
+  if (kAct == PSOB_ACT_TANH) return tanh_sfu(v);
   if (kAct == PSOB_ACT_SIGMOID) return 1.f / (1.f + expf(-v));
   return v;
 }
@@ -412,8 +423,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           if ((st.y & kMetaHasNext) && !next_acquired) {
             // this A tile also feeds the NEXT job of the chain: its accumulator buffer (the other one) must be drained
             const uint32_t nuse = (it + 1u) >> 1;
+            const long long t0 = prof ? clock64() : 0;
             if (kPair) ptx::mbar_wait_cluster(tempty_bar(buf ^ 1u), (nuse & 1u) ^ 1u);
             else ptx::mbar_wait(tempty_bar(buf ^ 1u), (nuse & 1u) ^ 1u);
+            if (prof) w_tempty += (unsigned long long)(clock64() - t0);
             next_acquired = true;
           }
           mbar_wait_t(full_bar(stage), phase, prof, w_full);

@@ -491,10 +491,16 @@ def lower_convt_image_band(name, w, b, act, in_cp=None) -> LayerProgram:
                     ops.append((tile_of[(key, kc)] * BAND_N, d_col, STEP_ACCUM))
                     if feeds_next:
                         if key == "bot":            # shared row: top-cut taps into the next band
+                            if not cleared_next:
+                                # The NEXT clears ride on the LAST step before the shared row: the issuer must own the next
+                                # band's accumulator buffer from the first NEXT op on, and that buffer is still being read by
+                                # the epilogue of the job before this one -- acquiring it on the first step of the band would
+                                # serialise that epilogue (the longest of all layers: tanh + masks) with this band's MMAs.
+                                prev = len(steps) - 1
+                                assert prev >= sb and prev not in xops
+                                xops[prev] = zero_ops(STEP_NEXT)
+                                cleared_next = True
                             ops.append((tile_of[("top", kc)] * BAND_N, 2 * ix, STEP_ACCUM | STEP_NEXT))
-                        elif not cleared_next and len(ops) == 1:
-                            ops += zero_ops(STEP_NEXT)
-                            cleared_next = True
                     assert len(ops) <= 4
                     b_row, dc, fl = ops[0]
                     if len(ops) > 1:

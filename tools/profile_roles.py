@@ -29,7 +29,8 @@ for net, x0 in ((gnet, z), (dnet, gnet.image_padded_bf16())):
         if plan:
             plan[layer.prog.name]()
         else:
-            layer.run(cur, P, y, y32)
+            # the image layer as the D-score step runs it: bf16 padded image only (PROFILE_F32=1: also the fp32 image)
+            layer.run(cur, P, y, y32 if (layer is not net.layers[-1] or y is None or os.environ.get("PROFILE_F32") == "1") else None)
         torch.cuda.synchronize()
         _ffi.check(_ffi.lib().psob_layer_profile(layer.handle, None))
         b = buf.cpu().numpy().astype(np.float64)

@@ -12,7 +12,7 @@
 using namespace psob;
 
 template <bool kPair>
-__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int reps, int n_b, int per_commit, uint32_t idesc, int issuers, unsigned long long* cycles) {
+__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int reps, int n_b, int per_commit, uint32_t idesc, int issuers, unsigned long long* cycles, int coloff = 0) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int reps, int 
     for (int r = 0; r < reps; ++r) {
       if (ptx::elect_one()) {
         const uint64_t bdesc = ptx::smem_desc_sw128(b_addr + (uint32_t)(r % n_b) * b_bytes);
-        const uint32_t d = tmem_base + (issuers == 2 ? (uint32_t)(warp >> 1) : (uint32_t)(r & 1)) * 256u;
+        const uint32_t d = tmem_base + (issuers == 2 ? (uint32_t)(warp >> 1) : (uint32_t)(r & 1)) * 256u + (uint32_t)(((r >> 1) % 5) * coloff);   // coloff: accumulator windows at arbitrary column offsets (image band)
         const bool commit = (r % per_commit) == per_commit - 1 || r == reps - 1;
         if (commit) {
           if (kPair) ptx::umma_bf16_k64_commit_pair(d, adesc, bdesc, idesc, 1u, bar);
@@ -92,7 +92,7 @@ int main(int argc, char** argv) {
           cudaLaunchAttribute at[1];
           at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
           cfg.attrs = at; cfg.numAttrs = 1;
-          e = cudaLaunchKernelEx(&cfg, umma_rate_kernel<true>, n, reps, n_b, per_commit, make_idesc_bf16(256, n), issuers, d_cyc);
+          e = cudaLaunchKernelEx(&cfg, umma_rate_kernel<true>, n, reps, n_b, per_commit, make_idesc_bf16(256, n), issuers, d_cyc, 0);
         } else {
           cudaFuncSetAttribute(umma_rate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
           umma_rate_kernel<false><<<grid, 128, smem>>>(n, reps, n_b, per_commit, make_idesc_bf16(128, n), issuers, d_cyc);
@@ -110,5 +110,21 @@ int main(int argc, char** argv) {
         printf("%-6s %4d %4d %10d | %12.1f %12.1f %14.0f | %11.1f%%\n", pair ? (issuers == 2 ? "pair x2" : "pair") : (issuers == 2 ? "solo x2" : "solo"), n, n_b,
                per_commit, per_instr, iss / (reps * 4.0 * issuers), macs / per_instr, 100.0 * macs / per_instr / 4096.0);
       }
+  // accumulator windows that start at arbitrary (even) columns, as the image-band layers use them: N = 96, solo
+  printf("solo N = 96, 4 ops per commit, accumulator window start = buffer + ((op / 2) %% 5) * coloff\n");
+  for (int coloff : {0, 2, 8, 16, 30, 32}) {
+    const int n = 96, n_b = 4;
+    const size_t smem = 1024 + 16384 + (size_t)n_b * n * 128 + 64;
+    cudaMemset(d_cyc, 0, 2 * sms * sizeof(unsigned long long));
+    cudaFuncSetAttribute(umma_rate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    umma_rate_kernel<false><<<sms, 128, smem>>>(n, reps, n_b, 4, make_idesc_bf16(128, n), 1, d_cyc, coloff);
+    cudaError_t e = cudaGetLastError(), e2 = cudaDeviceSynchronize();
+    if (e != cudaSuccess || e2 != cudaSuccess) { printf("launch failed: %s / %s\n", cudaGetErrorString(e), cudaGetErrorString(e2)); return 1; }
+    unsigned long long h[2 * 160];
+    cudaMemcpy(h, d_cyc, 2 * sms * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    double tot = 0; int cnt = 0;
+    for (int b = 0; b < sms; ++b) if (h[2 * b]) { tot += (double)h[2 * b]; ++cnt; }
+    printf("coloff %3d | %8.1f cycles per instruction\n", coloff, tot / cnt / (reps * 4.0));
+  }
   return 0;
 }

@@ -19,6 +19,7 @@
 #include <mutex>
 #include <vector>
 #include <new>
+#include <type_traits>
 
 namespace psob {
 
@@ -571,10 +572,12 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             if (kDot) {
               // all lanes read the same 16 bytes of weights (shared-memory broadcast); bf16 -> fp32 is a shift / mask
               const uint32_t waddr = base + (uint32_t)p.stg_off + (uint32_t)(j0.z + cm) * 2u;
+              auto dot_slots = [&](auto kSmemBiasTag) {
+              constexpr bool kSmemBias = decltype(kSmemBiasTag)::value;      // compile-time inside the loop: one basic block of 8 slots
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 float4 b0, b1;
-                if (bias_in_smem) {
+                if (kSmemBias) {
                   const uint32_t baddr = s_bias_addr + (uint32_t)(j1.z * q_nt + n0 + 8 * j) * 4u;
                   b0 = ptx::ld_shared_f4(baddr); b1 = ptx::ld_shared_f4(baddr + 16u);
                 } else {
@@ -593,6 +596,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 dacc2 = fmaf(__uint_as_float(o[3] << 16), __uint_as_float(w[3] << 16), dacc2);
                 dacc3 = fmaf(__uint_as_float(o[3] & 0xFFFF0000u), __uint_as_float(w[3] & 0xFFFF0000u), dacc3);
               }
+              };
+              if (bias_in_smem) dot_slots(std::true_type{}); else dot_slots(std::false_type{});
               if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
               continue;
             }
@@ -626,7 +631,12 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               ptx::named_bar_sync(1 + grp, 128);
             }
             if (prof) { const long long t = clock64(); e_free += (unsigned long long)(t - tq); tq = t; }
-            auto emit_slot = [&](int j, const float4& b0, const float4& b1) {
+            // kHalfTag (std::true_type / false_type): the half-store mode as a COMPILE-TIME property of the slot loop.  As a
+            // runtime flag it put a branch into every one of the 8 unrolled slots, the loop body fell apart into 8+ basic
+            // blocks and ptxas could not interleave the slots' bias -> activation -> pack chains: the epilogue warps issued
+            // one instruction per ~5 cycles (ncu: 37 % fixed-latency 'wait' stalls, 20 % issuing).
+            auto emit_slot = [&](auto kHalfTag, int j, const float4& b0, const float4& b1) {
+              constexpr bool kHalf = decltype(kHalfTag)::value;
               if (has_res) {
                 const uint32_t rw[4] = {rres[j].x, rres[j].y, rres[j].z, rres[j].w};
 #pragma unroll
@@ -640,7 +650,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               o.y = bias_act_pack<kAct>(v[8 * j + 2], v[8 * j + 3], b0.z, b0.w);
               o.z = bias_act_pack<kAct>(v[8 * j + 4], v[8 * j + 5], b1.x, b1.y);
               o.w = bias_act_pack<kAct>(v[8 * j + 6], v[8 * j + 7], b1.z, b1.w);
-              if (q_half) {
+              if (kHalf) {
                 // SWIZZLE_64B half tile [32 rows x 64 B]: 16-byte slot jj of row r lives at jj ^ ((r / 2) % 4)
                 if ((j & 3) == 0) half_open(j >> 2);
                 ptx::st_shared_v4(hbase + (uint32_t)(j >> 2) * 2048u + (uint32_t)lane * 64u + ((((uint32_t)j & 3u) ^ (((uint32_t)lane >> 1) & 3u)) << 4), o);
@@ -670,21 +680,26 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]); o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
                 ptx::st_shared_v4(srow + (((uint32_t)j ^ sw) << 4), o);
               }
-            } else if (bias_in_smem) {
-              // explicit ld.shared, software-pipelined one slot ahead: through a generic pointer every slot was a
-              // dependent LD -> math -> STS chain of ~110 cycles
-              const uint32_t baddr = s_bias_addr + (uint32_t)(j1.z * q_nt + n0) * 4u;
-              float4 b0 = ptx::ld_shared_f4(baddr), b1 = ptx::ld_shared_f4(baddr + 16u);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                float4 c0 = b0, c1 = b1;
-                if (j < 7) { b0 = ptx::ld_shared_f4(baddr + 32u * (j + 1)); b1 = ptx::ld_shared_f4(baddr + 32u * (j + 1) + 16u); }
-                emit_slot(j, c0, c1);
-              }
             } else {
+              auto run_slots = [&](auto kHalfTag) {
+                if (bias_in_smem) {
+                  // explicit ld.shared, software-pipelined one slot ahead: through a generic pointer every slot was a
+                  // dependent LD -> math -> STS chain of ~110 cycles
+                  const uint32_t baddr = s_bias_addr + (uint32_t)(j1.z * q_nt + n0) * 4u;
+                  float4 b0 = ptx::ld_shared_f4(baddr), b1 = ptx::ld_shared_f4(baddr + 16u);
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                emit_slot(j, __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j)), __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4)));
+                  for (int j = 0; j < 8; ++j) {
+                    float4 c0 = b0, c1 = b1;
+                    if (j < 7) { b0 = ptx::ld_shared_f4(baddr + 32u * (j + 1)); b1 = ptx::ld_shared_f4(baddr + 32u * (j + 1) + 16u); }
+                    emit_slot(kHalfTag, j, c0, c1);
+                  }
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j)
+                    emit_slot(kHalfTag, j, __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j)), __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4)));
+                }
+              };
+              if (q_half) run_slots(std::true_type{}); else run_slots(std::false_type{});
             }
             if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
             if (q_half) {

@@ -69,6 +69,7 @@ struct EngineParams {
   int b_resident, n_wrows, n_bias_rows, n_steps;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4, strided;
+  int rot_div;               // chain rotation: item (tile t, slot r) runs chain (r + t / rot_div) % n_chains (0: chain r) -- see pick_rotation
   int step_stride;           // int4 words per step in the shared-memory copy of the step table (1 when no step has > 2 ops)
   int warp_store;            // every epilogue warp stores its own 32 rows of a chunk (32-row TMA box): no barriers inside a group
   int issuers;               // MMA-issuing warps (1 or 2): one thread sustains only ~1 tcgen05.mma per 85-94 cycles (tools/umma_bench.cu)
@@ -239,6 +240,18 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const long long item_end = q_strided ? q_n_items : (item_begin + per_cta < q_n_items ? item_begin + per_cta : q_n_items);
   const long long item_step = q_strided ? n_workers : 1;
   const uint32_t n_chains_u = (uint32_t)q_n_chains;
+  // item -> (particle tile, chain).  With the strided item order worker w sees the slots (w + k W) % n_chains only; when
+  // gcd(W, n_chains) > 1 some workers would get nothing but the short chains of every tile (a border column group with
+  // half the pixels, the last image band) and idle at the end.  Rotating the slot -> chain map by the tile index
+  // (host-picked divisor) spreads every chain over every worker and keeps the chains of a tile on neighbouring workers.
+  const uint32_t q_rot_div = (uint32_t)p.rot_div;
+  auto item_chain = [&](long long item, int& ptile) -> uint32_t {
+    const uint32_t t = (uint32_t)item / n_chains_u;          // 32-bit: n_items < 2^31 (checked on the host)
+    uint32_t c = (uint32_t)item - t * n_chains_u;
+    if (q_rot_div) { c += (t / q_rot_div) % n_chains_u; if (c >= n_chains_u) c -= n_chains_u; }
+    ptile = (int)t;
+    return c;
+  };
   // particle-tile index of this CTA for TMA coordinates: pair tile t covers tiles 2t (leader) and 2t+1
   auto tile_idx = [&](int ptile) { return kPair ? 2 * ptile + (int)crank : ptile; };
   auto tile_row = [&](int ptile) { return tile_idx(ptile) * kTileM; };
@@ -354,8 +367,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       unsigned long long w_empty = 0;
       const long long t_start = clock64();
       for (long long item = item_begin; item < item_end; item += item_step) {
-        const int ptile = (int)((uint32_t)item / n_chains_u);        // 32-bit: n_items < 2^31 (checked on the host)
-        const int2 ch = chains[(uint32_t)item - (uint32_t)ptile * n_chains_u];
+        int ptile;
+        const int2 ch = chains[item_chain(item, ptile)];
         for (int job = ch.x; job < ch.x + ch.y; ++job) {
           const int4 j0 = jobs[2 * job];
           int4 st_next = steps[ss * j0.x];
@@ -399,7 +412,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const uint32_t wsel = (uint32_t)(warp - kMmaWarp);
     const bool two = p.issuers == 2;
     for (long long item = item_begin; item < item_end; item += item_step) {
-      const int2 ch = chains[(uint32_t)item % n_chains_u];
+      int ptile_unused;
+      const int2 ch = chains[item_chain(item, ptile_unused)];
       for (int job = ch.x; job < ch.x + ch.y; ++job, ++it) {
         const int4 j0 = jobs[2 * job];
         const uint32_t buf = it & 1u, use = it >> 1;
@@ -518,8 +532,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const long long t_start = clock64();
     if (kTmaStore ? grp < q_epi_groups : grp == 0) {
       for (long long item = item_begin; item < item_end; item += item_step) {
-        const int ptile = (int)((uint32_t)item / n_chains_u);
-        const int2 chn = chains[(uint32_t)item - (uint32_t)ptile * n_chains_u];
+        int ptile;
+        const int2 chn = chains[item_chain(item, ptile)];
         for (int job = chn.x; job < chn.x + chn.y; ++job, ++it) {
         const int4 j0 = jobs[2 * job];
         const int4 j1 = jobs[2 * job + 1];
@@ -966,7 +980,49 @@ struct psob_layer {
   uint32_t tmem_cols = 0;
   int sm_count = 0;
   int device = -1;
+  std::vector<int> chain_steps, chain_ops, chain_chunks;   // per chain: A-tile loads, MMA ops, stored 64-column chunks
+  std::mutex rot_mu;
+  long long rot_tiles = -1;        // tile count the cached rotation divisor was picked for
+  int rot_div = 0;
 };
+
+// Rotation divisor of the slot -> chain map (EngineParams::rot_div) for `tiles` (pair) tiles on `workers` CTAs (pairs):
+// the candidate with the best worst-case balance over three cost proxies (loads, MMA ops, epilogue chunks) of the
+// strided item order; 0 (no rotation) unless a candidate is better by more than 1 %.
+static int pick_rotation(psob_layer* l, long long tiles, int workers) {
+  std::lock_guard<std::mutex> g(l->rot_mu);
+  if (l->rot_tiles == tiles) return l->rot_div;
+  const int C = (int)l->chain_steps.size();
+  int best = 0;
+  if (C > 1 && workers > 0 && tiles * C > workers && !getenv("PSOB_NO_ROTATE")) {
+    const std::vector<int>* cost[3] = {&l->chain_steps, &l->chain_ops, &l->chain_chunks};
+    auto efficiency = [&](int div) {
+      double worst = 1.0;
+      for (int k = 0; k < 3; ++k) {
+        std::vector<double> load((size_t)workers, 0.0);
+        double total = 0.0;
+        for (long long i = 0; i < tiles * C; ++i) {
+          const long long t = i / C;
+          int c = (int)(i - t * C);
+          if (div) c = (int)((c + (t / div) % C) % C);
+          load[(size_t)(i % workers)] += (*cost[k])[(size_t)c];
+          total += (*cost[k])[(size_t)c];
+        }
+        double mx = 0.0;
+        for (double v : load) mx = v > mx ? v : mx;
+        if (mx > 0.0 && total / workers / mx < worst) worst = total / workers / mx;
+      }
+      return worst;
+    };
+    double best_eff = efficiency(0) + 0.01;
+    const int per_round = workers / C > 0 ? workers / C : 1;      // tiles a round of the strided order advances by
+    for (int div : {1, per_round, per_round + 1, 2 * per_round + 1, 3, 7})
+      if (div > 0) { const double e = efficiency(div); if (e > best_eff) { best_eff = e; best = div; } }
+  }
+  l->rot_tiles = tiles;
+  l->rot_div = best;
+  return best;
+}
 
 static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, const void* res,
                           int64_t res_pitch, const void* dot_w, float* dot_part, int32_t impl, psob_stream_t s);
@@ -1187,6 +1243,20 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
   { const char* e = getenv("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }
   { const char* e = getenv("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
+  for (int c = 0; c < d->n_chains; ++c) {
+    int n_st = 0, n_op = 0, n_ck = 0;
+    for (int j = d->chains[2 * c]; j < d->chains[2 * c] + d->chains[2 * c + 1]; ++j) {
+      const int32_t* jb = d->jobs + 8 * j;
+      n_st += jb[1];
+      for (int st = jb[0]; st < jb[0] + jb[1]; ++st) n_op += d->steps[8 * st + 1] & kMetaOpsMask;
+      const unsigned long long mask = (unsigned long long)(uint32_t)jb[4] | ((unsigned long long)(uint32_t)jb[5] << 32);
+      for (int n = 0; n < d->nt; n += 64) {
+        const int pix = n / d->cc;
+        if (l->band || (d->col_map[n] >= 0 && (pix >= 64 || ((mask >> pix) & 1ull)))) ++n_ck;
+      }
+    }
+    l->chain_steps.push_back(n_st); l->chain_ops.push_back(n_op); l->chain_chunks.push_back(n_ck);
+  }
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * d->nt)) cols <<= 1;
   l->tmem_cols = cols;
@@ -1268,6 +1338,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
   p.idesc_eye = make_idesc_bf16(kTileM, 64);
   p.eye = l->eye ? 1 : 0;
+  p.rot_div = 0;
   p.tmem_cols = l->tmem_cols;
 
   if (impl == PSOB_IMPL_SIMT) {
@@ -1289,6 +1360,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
     p.n_items = ((n_ptiles + 1) / 2) * d.n_chains;                // items are (pair of particle tiles, chain of jobs)
     p.idesc = make_idesc_bf16(2 * kTileM, d.mma_n);
   }
+  p.rot_div = l->strided ? pick_rotation(l, p.n_items / d.n_chains, l->pair ? l->sm_count / 2 : l->sm_count) : 0;
   if (!l->have_tmB) {
     int rc = make_tmap(&l->tmB, l->wpack, kKChunk, (uint64_t)d.n_wrows, kKChunk, (uint32_t)(l->pair ? d.mma_n / 2 : d.mma_n));
     if (rc) return rc;

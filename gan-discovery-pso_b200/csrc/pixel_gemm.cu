@@ -974,6 +974,8 @@ struct psob_layer {
   bool tma_store = false, vec4 = false, pair = false, strided = false;
   int epi_groups = 2, step_stride = 2;
   bool band = false;
+  bool dot_head = false;           // dot-only layer: staging area = the head's weights, 2 epilogue groups
+  int stg_bytes = 0;               // bytes of the staging area in the shared-memory plan
   unsigned long long* prof = nullptr;
   int bias_off = -1, steps_off = -1, jobs_off = -1, chains_off = -1, tab_bytes = 0, stg_bufs = 0;
   int n_stages = 0, stage_bytes = 0, res_off = 0, bar_off = 0, stg_off = 0, smem_bytes = 0;
@@ -1225,11 +1227,25 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->epi_groups = (l->pair && (long long)d->n_steps * 2 * d->mma_n >= 6000ll * d->n_jobs) ? 1 : 2;   // a third group measured no faster (TMA-bound)
   { const char* e = getenv("PSOB_EPI_GROUPS"); if (e && atoi(e) >= 1 && atoi(e) <= kMaxEpiGroups) l->epi_groups = atoi(e); }
   if (!l->tma_store) l->epi_groups = 2;             // the direct-store epilogue uses group 0 only (thread layout of 2 groups)
-  if (l->tma_store) {
+  l->dot_head = d->dot_head != 0;
+  if (l->dot_head && (!l->tma_store || l->band || d->out32_pitch)) {
+    psob_layer_destroy(l);
+    return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: dot_head needs a layer with the chunked bf16 epilogue");
+  }
+  if (l->tma_store && !l->dot_head) {
     const int room = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes;
     l->stg_bufs = (room - 2 * l->epi_groups * kATileBytes) / l->stage_bytes >= (l->pair ? 4 : 3) ? 2 : 1;
   }
-  const int stg_bytes = l->epi_groups * l->stg_bufs * kATileBytes;
+  int stg_bytes = l->epi_groups * l->stg_bufs * kATileBytes;
+  if (l->dot_head) {
+    // nothing is staged: the area holds the head's bf16 weights, and the second epilogue group is free -- it halves the
+    // time an accumulator buffer stays occupied, which chained jobs wait for (they acquire the next buffer early)
+    const char* e = getenv("PSOB_EPI_GROUPS");
+    l->epi_groups = (e && atoi(e) == 1) ? 1 : 2;
+    l->stg_bufs = 1;
+    stg_bytes = (d->out_pitch * 2 + 1023) & ~1023;
+  }
+  l->stg_bytes = stg_bytes;
   int avail = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes - stg_bytes;
   l->n_stages = avail / l->stage_bytes;
   if (l->n_stages > kMaxStages) l->n_stages = kMaxStages;
@@ -1297,12 +1313,13 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   if (!l || !x || P <= 0) return fail(PSOB_E_ARG, "psob_layer_run: bad arguments");
   const psob_layer_desc& d = l->d;
   const bool dot = dot_w != nullptr;
+  if (l->dot_head && !dot) return fail(PSOB_E_ARG, "psob_layer_run: the layer was created with dot_head and only runs through psob_layer_run_dot");
   if (dot) {
     if (!l->tma_store || l->band || d.out32_pitch)       // the output layout (row- / tile-major) is irrelevant: nothing is stored
       return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_dot: needs a layer with the chunked bf16 epilogue");
-    if (d.out_pitch * 2 > l->epi_groups * l->stg_bufs * kATileBytes)
+    if (d.out_pitch * 2 > l->stg_bytes)
       return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_dot: %d B of head weights do not fit the layer's %d B of staging tiles", d.out_pitch * 2,
-                  l->epi_groups * l->stg_bufs * kATileBytes);
+                  l->stg_bytes);
     if (!aligned16(dot_w) || (reinterpret_cast<uintptr_t>(dot_part) & 3)) return fail(PSOB_E_ARG, "psob_layer_run_dot: misaligned weights / partial sums");
   }
   if (res) {

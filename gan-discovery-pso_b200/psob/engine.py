@@ -39,9 +39,10 @@ def require_cuda():
 class Layer:
     """One pixel-GEMM layer program resident on the current device."""
 
-    def __init__(self, prog: L.LayerProgram, in_tiled: bool = False, out_tiled: bool = False):
+    def __init__(self, prog: L.LayerProgram, in_tiled: bool = False, out_tiled: bool = False, dot_head: bool = False):
         require_cuda()
         self.prog = prog
+        self.dot_head = bool(dot_head)
         self.in_tiled, self.out_tiled = bool(in_tiled), bool(out_tiled)
         wbits = np.ascontiguousarray(L.bf16_bits(prog.wpack))
         steps = np.ascontiguousarray(L.pack_steps(prog), dtype=np.int32)
@@ -54,7 +55,7 @@ class Layer:
             mma_n=prog.mma_n, nt=prog.nt, cc=prog.cc, act=prog.act, in_pitch=prog.in_pitch,
             out_pitch=prog.out_pitch, out32_pitch=prog.out32_pitch, b_resident=int(prog.b_resident),
             vec8=int(prog.vec8), n_steps=prog.n_steps, n_jobs=prog.n_jobs, n_wrows=wbits.shape[0],
-            n_bias_rows=bias.shape[0], n_chains=chains.shape[0], chains=chains.ctypes.data, in_tiled=int(in_tiled), out_tiled=int(out_tiled),
+            n_bias_rows=bias.shape[0], n_chains=chains.shape[0], chains=chains.ctypes.data, in_tiled=int(in_tiled), out_tiled=int(out_tiled), dot_head=int(dot_head),
             band_pitch=(prog.meta["band"][1] if prog.meta.get("kind") == "convt_image_band" and os.environ.get("PSOB_BAND_EPI", "1") != "0" else 0), wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
             col_map=cm.ctypes.data, col_map32=cm32.ctypes.data, bias=bias.ctypes.data)
         h = C.c_void_p()
@@ -192,9 +193,16 @@ class DiscriminatorNet(Network):
         if hid.act not in (L.ACT_LEAKY, L.ACT_RELU):
             return None
         lib = _ffi.lib()
-        slots = lib.psob_layer_dot_slots(self.layers[-2].handle)
-        if slots <= 0:
+        if lib.psob_layer_dot_slots(self.layers[-2].handle) <= 0:
             return None
+        # re-create the hidden layer as a dot-only layer (no staging tiles, two epilogue groups); its activation buffer and
+        # the score layer's handle are not needed any more
+        old = self.layers[-2]
+        with torch.cuda.device(self.device):
+            self.layers[-2] = Layer(hid, in_tiled=old.in_tiled, out_tiled=False, dot_head=True)
+        self.acts[-2] = None
+        slots = lib.psob_layer_dot_slots(self.layers[-2].handle)
+        assert slots > 0
         w = nets.head_weights(last)                       # fp32 values (bf16-exact) indexed by the hidden layer's output column
         with torch.cuda.device(self.device):
             w_dev = torch.from_numpy(w).to(self.device).to(torch.bfloat16).contiguous()

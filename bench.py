@@ -346,6 +346,7 @@ def run_psob(args):
     # Two device staging buffers and a copy stream: the upload of step k+1's inputs and the read-back of step k's
     # results overlap step k's / k+1's kernels (every step still moves all of its bytes inside the timed region).
     cs = torch.cuda.Stream(device=dev)
+    cs_out = torch.cuda.Stream(device=dev)       # read-backs on their own stream: they must not queue behind the next step's upload
     stage_pos = [torch.empty_like(sw.pos) for _ in range(2)]
     stage_vel = [torch.empty_like(sw.vel) for _ in range(2)]
     ev_h2d = [torch.cuda.Event() for _ in range(2)]
@@ -376,12 +377,12 @@ def run_psob(args):
             main.wait_event(ev_d2h)                 # the previous step's results have left sw.fit / gbest
             sw.step()
             ev_done.record(main)
-            with torch.cuda.stream(cs):
-                cs.wait_event(ev_done)
+            with torch.cuda.stream(cs_out):
+                cs_out.wait_event(ev_done)
                 h_fit.copy_(sw.fit, non_blocking=True)
                 h_best[:D_LATENT].copy_(sw.gbest_pos[:D_LATENT], non_blocking=True)
                 h_best[D_LATENT:].copy_(sw.gbest_val, non_blocking=True)
-                ev_d2h.record(cs)
+                ev_d2h.record(cs_out)
         main.wait_event(ev_d2h)
 
     for t in stage_pos + stage_vel:

@@ -182,7 +182,14 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
     disc = port.Discriminator(1, 64)
     z = torch.randn(P, 100, generator=torch.Generator().manual_seed(P))
     results = {}
-    for tiled, pair, strided, chain in ((1, 1, 1, 1), (1, 1, 1, 0), (0, 1, 1, 1), (1, 0, 1, 1), (1, 1, 0, 1), (0, 0, 0, 0)):
+    for tiled, pair, strided, chain in ((1, 1, 1, 1), (1, 1, 1, 0), (0, 1, 1, 1), (1, 0, 1, 1), (1, 1, 0, 1), (0, 0, 0, 0), (1, 1, 2, 1)):
+        # strided == 2: the strided item order WITHOUT the chain rotation (scheduling only: same bits)
+        if strided == 2:
+            monkeypatch.setenv("PSOB_NO_ROTATE", "1")
+        else:
+            monkeypatch.delenv("PSOB_NO_ROTATE", raising=False)
+        key = (tiled, pair, strided, chain)
+        strided = min(strided, 1)
         monkeypatch.setenv("PSOB_TILED", str(tiled))
         monkeypatch.setenv("PSOB_STRIDED", str(strided))
         monkeypatch.setattr(L, "RESIDENT_PAIR", 256 * 1024 if pair else 0)
@@ -196,7 +203,7 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
         _, score = dnet.forward(gnet.image_padded_bf16())
         torch.cuda.synchronize()
         assert (len(dnet.programs[1].chains) < dnet.programs[1].n_jobs) == bool(pair and chain)
-        results[(tiled, pair, strided, chain)] = [gnet.activation(i).cpu() for i in range(3)] + \
+        results[key] = [gnet.activation(i).cpu() for i in range(3)] + \
             [dnet.activation(i).cpu() for i in range(2)] + [img.cpu(), score.cpu()]
     base = results[(0, 0, 0, 0)]
     for key, got in results.items():

@@ -137,3 +137,24 @@ def test_program_tables_are_tma_legal():
             assert p.chains[:, 1].sum() == p.n_jobs and (p.chains[1:, 0] == p.chains[:-1, 0] + p.chains[:-1, 1]).all()
             packed = L.pack_steps(p)
             assert ((packed[:, 1] & 7) >= 1).all() and ((packed[:, 1] & 7) <= 4).all()
+
+
+def test_head_weights_reproduce_the_score_layer():
+    """nets.head_weights (the vector psob_layer_run_dot reduces against) . hidden activation + bias, through the sigmoid,
+    equals the score layer's own table emulation (lower_conv_full, src/utils/util_dcgan.py:117-118) on the same input."""
+    torch.manual_seed(3)
+    disc = port.Discriminator(1, 64)
+    progs = nets.discriminator_programs({k: v.detach().numpy() for k, v in disc.state_dict().items()})
+    hid, last = progs[1], progs[2]
+    assert last.meta["kind"] == "conv_full" and last.meta["out_c"] == 1 and last.in_pitch == hid.out_pitch
+    w = nets.head_weights(last)
+    assert w.shape == (hid.out_pitch,) and np.array_equal(L.to_bf16_f32(w), w)            # bf16-exact values
+    assert np.count_nonzero(w) == 128 * 49                                               # every (pixel, channel) of the 7x7x128 map
+    rng = np.random.default_rng(0)
+    x = L.to_bf16_f32(rng.standard_normal((5, last.in_pitch)).astype(np.float32))
+    _, score = L.emulate(last, x)
+    ref = 1.0 / (1.0 + np.exp(-(x.astype(np.float64) @ w.astype(np.float64) + float(last.bias[0, 0]))))
+    np.testing.assert_allclose(score[:, 0], ref, atol=1e-6, rtol=0)
+    # conv weight layout: w[pix * 128 + ch] = W[0, ch, ky, kx]
+    W = disc.state_dict()["disc.3.weight"].numpy()
+    np.testing.assert_array_equal(w.reshape(49, 128), L.to_bf16_f32(W[0].reshape(128, 49).T))

@@ -836,11 +836,12 @@ static UmmaKernelFn umma_kernel_for(int act, bool tma_store, bool pair, bool res
     if (act == PSOB_ACT_NONE) return pixel_gemm_umma_kernel<PSOB_ACT_NONE, true, false, true>;
     return nullptr;
   }
-  if (pair) {           // pair mode exists for the hidden conv layers only (TMA-store epilogue, ReLU / LeakyReLU / none)
+  if (pair) {           // pair mode: hidden conv layers (TMA-store epilogue, ReLU / LeakyReLU / none) and the tanh image band
     switch (act) {
       case PSOB_ACT_NONE: return pixel_gemm_umma_kernel<PSOB_ACT_NONE, true, true>;
       case PSOB_ACT_RELU: return pixel_gemm_umma_kernel<PSOB_ACT_RELU, true, true>;
       case PSOB_ACT_LEAKY: return pixel_gemm_umma_kernel<PSOB_ACT_LEAKY, true, true>;
+      case PSOB_ACT_TANH: return pixel_gemm_umma_kernel<PSOB_ACT_TANH, true, true>;
     }
     return nullptr;
   }
@@ -1201,8 +1202,15 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   for (int s = 0; s < d->n_steps; ++s) if (d->steps[8 * s + 1] & kMetaEye) l->eye = true;
   const int full_res_bytes = d->b_resident ? d->n_wrows * 128 : (l->eye ? kEyeBytes : 0);
   l->pair = d->b_resident && full_res_bytes > kMaxSoloResident;
+  // The image band is bound by the single thread that issues its N = 96 instructions (~840 cycles per step against 4 x ~100
+  // of issue floor and an HBM floor below that): as a CTA pair one instruction covers 256 particles, which halves the issue
+  // cost per particle.  PSOB_BAND_PAIR=0 keeps the solo form.
+  if (l->band && d->b_resident && d->mma_n % 32 == 0 && d->n_wrows % d->mma_n == 0 && l->sm_count >= 2) {
+    const char* e = getenv("PSOB_BAND_PAIR");
+    if (e ? atoi(e) != 0 : true) l->pair = true;
+  }
   if (l->pair && (!l->tma_store || full_res_bytes / 2 > kMaxPairResident || d->mma_n % 32 || d->n_wrows % d->mma_n ||
-                  (d->act != PSOB_ACT_NONE && d->act != PSOB_ACT_RELU && d->act != PSOB_ACT_LEAKY) || l->sm_count < 2)) {
+                  (d->act != PSOB_ACT_NONE && d->act != PSOB_ACT_RELU && d->act != PSOB_ACT_LEAKY && !(l->band && d->act == PSOB_ACT_TANH)) || l->sm_count < 2)) {
     psob_layer_destroy(l);
     return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: %d B of resident weights need the CTA-pair mode, which this layer cannot use", full_res_bytes);
   }
@@ -1224,7 +1232,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   // half of the time: give the second group's staging tile to the A ring (3 -> 4 stages next to 128 KB of weights)
   // layers with short chains (K = 128 per 256 output columns) are bound by the epilogue's latency chain
   // (TMEM load -> bias/activation -> swizzled st.shared -> TMA store): a third group hides more of it
-  l->epi_groups = (l->pair && (long long)d->n_steps * 2 * d->mma_n >= 6000ll * d->n_jobs) ? 1 : 2;   // a third group measured no faster (TMA-bound)
+  l->epi_groups = (l->pair && !l->band && (long long)d->n_steps * 2 * d->mma_n >= 6000ll * d->n_jobs) ? 1 : 2;   // a third group measured no faster (TMA-bound)
   { const char* e = getenv("PSOB_EPI_GROUPS"); if (e && atoi(e) >= 1 && atoi(e) <= kMaxEpiGroups) l->epi_groups = atoi(e); }
   if (!l->tma_store) l->epi_groups = 2;             // the direct-store epilogue uses group 0 only (thread layout of 2 groups)
   l->dot_head = d->dot_head != 0;

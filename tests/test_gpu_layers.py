@@ -189,6 +189,7 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
         else:
             monkeypatch.delenv("PSOB_NO_ROTATE", raising=False)
         key = (tiled, pair, strided, chain)
+        monkeypatch.setenv("PSOB_BAND_PAIR", "1" if pair else "0")        # image band as a CTA pair / solo
         strided = min(strided, 1)
         monkeypatch.setenv("PSOB_TILED", str(tiled))
         monkeypatch.setenv("PSOB_STRIDED", str(strided))

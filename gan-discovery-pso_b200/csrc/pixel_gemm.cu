@@ -335,7 +335,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   ptx::tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gbase + p.bar_off + 8 * (2 * kMaxStages + 5));
 
-  if (kPair) {
+  if (kPair && q_b_resident) {
     // each CTA loads ITS half of every weight tile (rows [crank*mma_n/2, +mma_n/2) of the tile); the leader's
     // MMAs read both halves, so nobody starts before both CTAs have seen their loads complete
     if (warp == kTmaWarp) {
@@ -380,9 +380,13 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             if (ptx::elect_one()) {
               const uint32_t a_dst = base + (uint32_t)stage * q_stage_bytes;
               if (kPair) {
-                // both CTAs' A tiles are counted on the leader's barrier (the leader issues the pair MMA)
-                if (leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2u * (uint32_t)kATileBytes);
+                // both CTAs' tiles are counted on the leader's barrier (the leader issues the pair MMA).  Streamed weights:
+                // each CTA fetches ITS half of the weight tile (rows [crank * mma_n / 2, + mma_n / 2)), so a step pulls
+                // 16 KB + half a tile through this SM's L2 port instead of 16 KB + the whole tile
+                const uint32_t half_b = res ? 0u : (uint32_t)q_mma_n * 64u;
+                if (leader) ptx::mbar_arrive_expect_tx(full_bar(stage), 2u * ((uint32_t)kATileBytes + half_b));
                 ptx::tma_load_2d_pair(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full0_leader + 8u * (uint32_t)stage);
+                if (!res) ptx::tma_load_2d_pair(a_dst + kATileBytes, &tmB, 0, op_b_row(st.z) + (int)crank * (q_mma_n >> 1), full0_leader + 8u * (uint32_t)stage);
               } else {
                 ptx::mbar_arrive_expect_tx(full_bar(stage), (uint32_t)kATileBytes + (res ? 0u : (uint32_t)q_mma_n * 128u));
                 ptx::tma_load_2d(a_dst, &tmA, in_c0(st.x), in_c1(ptile, st.x), full_bar(stage));
@@ -451,8 +455,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             const uint64_t adesc = ptx::smem_desc_sw128(a_addr);
             const bool res = (st.y & kMetaResident) != 0;
             auto b_addr_of = [&](int op) {
-              return kPair ? base + q_res_off + (uint32_t)op_b_row(op) * 64u
-                           : (res ? base + q_res_off + (uint32_t)op_b_row(op) * 128u : a_addr + kATileBytes);
+              return !res ? a_addr + kATileBytes
+                          : (kPair ? base + q_res_off + (uint32_t)op_b_row(op) * 64u : base + q_res_off + (uint32_t)op_b_row(op) * 128u);
             };
             auto d_of = [&](int op) { return tmem_base + (buf ^ (uint32_t)op_next(op)) * (uint32_t)q_nt + (uint32_t)op_d_col(op); };
             auto mine = [&](int op) { return !two || (((buf ^ (uint32_t)op_next(op)) + (uint32_t)op_region(op)) & 1u) == wsel; };
@@ -1197,7 +1201,6 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   // shared-memory plan.  Resident weights beyond what one CTA can hold next to a useful ring are split over a
   // CTA pair (cta_group::2): each CTA keeps half of every weight tile.
   const int b_tile = d->mma_n * 128;
-  l->stage_bytes = kATileBytes + (d->b_resident ? 0 : b_tile);
   l->eye = false;
   for (int s = 0; s < d->n_steps; ++s) if (d->steps[8 * s + 1] & kMetaEye) l->eye = true;
   const int full_res_bytes = d->b_resident ? d->n_wrows * 128 : (l->eye ? kEyeBytes : 0);
@@ -1214,6 +1217,30 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     psob_layer_destroy(l);
     return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: %d B of resident weights need the CTA-pair mode, which this layer cannot use", full_res_bytes);
   }
+  // Streamed weights as a CTA pair: every step pulls A (16 KB) + the weight tile through the SM's L2 port, which delivers
+  // ~60 B/clk; an N = 256 tile (32 KB per 512 tensor cycles) overruns it.  In a pair each CTA fetches half of the tile and one
+  // instruction covers 256 particles.  Not with identity ops (their built-in tile is a solo construct); the residual
+  // epilogue (psob_layer_run_residual) stays solo as well, which is checked at run time.  PSOB_STREAM_PAIR=0/1 overrides.
+  if (!l->pair && !d->b_resident && !l->eye && l->tma_store && !l->band && d->mma_n % 32 == 0 && l->sm_count >= 2 &&
+      (d->act == PSOB_ACT_NONE || d->act == PSOB_ACT_RELU || d->act == PSOB_ACT_LEAKY) && !d->solo) {
+    // Only where the MMA chain of a job outweighs its epilogue: in a pair an accumulator buffer is released by BOTH CTAs'
+    // epilogue warps, which costs epilogue-bound layers (few K-steps per 256 output columns) more than the halved weight
+    // traffic gives back (G256's 64 -> 64 layer: 8.98 -> 9.7 ms as a pair; its 512 -> 256 layer: 7.5 -> 5.7 ms).
+    long long n_ops = 0, n_chunks = 0;
+    for (int s = 0; s < d->n_steps; ++s) n_ops += d->steps[8 * s + 1] & kMetaOpsMask;
+    for (int j = 0; j < d->n_jobs; ++j) {
+      const unsigned long long mask = (unsigned long long)(uint32_t)d->jobs[8 * j + 4] | ((unsigned long long)(uint32_t)d->jobs[8 * j + 5] << 32);
+      for (int n = 0; n < d->nt; n += 64) {
+        const int pix = n / d->cc;
+        if (d->col_map[n] >= 0 && (pix >= 64 || ((mask >> pix) & 1ull))) ++n_chunks;
+      }
+    }
+    const long long mma_cycles = n_ops * 4 * (d->mma_n / 2 > 90 ? d->mma_n / 2 : 90);     // per instruction: N / 2 cycles, issue floor ~90
+    const long long epi_cycles = n_chunks * 500;                                          // ~1000 cycles per chunk and group, 2 groups
+    const char* e = getenv("PSOB_STREAM_PAIR");
+    l->pair = e ? atoi(e) != 0 : (d->mma_n >= 128 && 2 * mma_cycles >= 3 * epi_cycles);
+  }
+  l->stage_bytes = kATileBytes + (d->b_resident ? 0 : (l->pair ? b_tile / 2 : b_tile));
   const int res_bytes = l->pair ? full_res_bytes / 2 : full_res_bytes;
   // table area: col_map + col_map32 + pix (fixed 2304 B), then optional bias rows, steps, jobs
   int tab = 256 * 4 * 2 + 256;
@@ -1331,6 +1358,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
     if (!aligned16(dot_w) || (reinterpret_cast<uintptr_t>(dot_part) & 3)) return fail(PSOB_E_ARG, "psob_layer_run_dot: misaligned weights / partial sums");
   }
   if (res) {
+    if (l->pair) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_residual: the layer runs as a CTA pair (create it with PSOB_STREAM_PAIR=0 for the residual epilogue)");
     if (!l->tma_store || l->band || !y) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_residual: the residual add needs the chunked bf16 (TMA-store) epilogue");
     if (!aligned16(res) || (d.out_tiled ? res_pitch != d.out_pitch : (res_pitch < d.out_pitch || res_pitch % 8)))
       return fail(PSOB_E_ARG, "psob_layer_run_residual: res must have the output's layout (pitch %lld vs out_pitch %d) and 16-byte alignment", (long long)res_pitch, d.out_pitch);

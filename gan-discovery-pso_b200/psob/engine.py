@@ -55,7 +55,7 @@ class Layer:
             mma_n=prog.mma_n, nt=prog.nt, cc=prog.cc, act=prog.act, in_pitch=prog.in_pitch,
             out_pitch=prog.out_pitch, out32_pitch=prog.out32_pitch, b_resident=int(prog.b_resident),
             vec8=int(prog.vec8), n_steps=prog.n_steps, n_jobs=prog.n_jobs, n_wrows=wbits.shape[0],
-            n_bias_rows=bias.shape[0], n_chains=chains.shape[0], chains=chains.ctypes.data, in_tiled=int(in_tiled), out_tiled=int(out_tiled), dot_head=int(dot_head),
+            n_bias_rows=bias.shape[0], n_chains=chains.shape[0], chains=chains.ctypes.data, in_tiled=int(in_tiled), out_tiled=int(out_tiled), dot_head=int(dot_head), solo=int(bool(prog.meta.get("residual"))),
             band_pitch=(prog.meta["band"][1] if prog.meta.get("kind") == "convt_image_band" and os.environ.get("PSOB_BAND_EPI", "1") != "0" else 0), wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
             col_map=cm.ctypes.data, col_map32=cm32.ctypes.data, bias=bias.ctypes.data)
         h = C.c_void_p()

@@ -186,6 +186,7 @@ typedef struct {
                                 * 8 padded image rows x band_pitch columns; stored as four 64-element chunks (2 rows each) */
   int32_t dot_head;            /* != 0: the layer will only run through psob_layer_run_dot (fused single-channel head): no staging
                                 * tiles are planned (the head weights take their place), two epilogue groups drain the accumulator */
+  int32_t solo;                /* != 0: never run as a CTA pair (layers that are run through psob_layer_run_residual) */
   const uint16_t* wpack;     /* HOST bf16 bits [n_wrows, 64] */
   const int32_t*  steps;     /* HOST [n_steps, 8]: a_col, meta, op0, op1, op2, op3, 0, 0.  One A tile (TMA load) feeds 1..4 MMA ops.
                               * meta: bits 0-2 op count, bit 3 weights resident, bit 4 some op targets the NEXT job of the chain,

@@ -154,7 +154,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD if args.workload == "dscore" else WORKLOAD_ASSESSOR, "sample": sample,
+        "config": {"workload": (WORKLOAD if args.workload == "dscore" else WORKLOAD_ASSESSOR).replace("swarm=65,536", f"swarm={args.particles:,}"), "sample": sample,
                    "host": "oracle/port.py PortSwarm (reference is pure Python; no GPU)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -416,7 +416,7 @@ def run_psob(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD_ASSESSOR if assessor else WORKLOAD, "particles_per_gpu": P, "latent_dim": D_LATENT, "parallelism": f"dp{world}",
+            "config": {"workload": (WORKLOAD_ASSESSOR if assessor else WORKLOAD).replace("swarm=65,536", f"swarm={P:,}"), "particles_per_gpu": P, "latent_dim": D_LATENT, "parallelism": f"dp{world}",
                        "l2_policy": "inputs_exceed_l2 (per-step working set %s)" % ("~12 GB" if assessor else "~5 GB"), "cuda_graph": bool(use_graph),
                        "state_dtype": "f32", "rng": "philox4x32-10 in-kernel"},
             "roofline": roofline, "roofline_update": roofline_update,

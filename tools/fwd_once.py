@@ -1,5 +1,5 @@
 """Two warm-up forward passes and one more (G stack, then the D stack as the product runs it: fused head) at the BASELINE
-config-2 size -- the ncu target: `ncu -k regex:pixel_gemm_umma --launch-skip 10 --launch-count 5 ... python tools/fwd_once.py`."""
+config-2 size -- the ncu target: `ncu -k regex:pixel_gemm_umma --launch-skip 10 --launch-count 5 ... python tools/fwd_once.py (three passes in all)`."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "gan-discovery-pso_b200"))

@@ -1,11 +1,14 @@
 // Pixel-GEMM engine: executes the layer programs of psob/lowering.py on sm_100a.
 //
-//   one CTA per SM, persistent over work items (particle tile of 128 rows, job)
-//   warp 0      TMA producer   : A tile [128 particles x 64 ch] + B tile [mma_n x 64] per step,
-//                                SWIZZLE_128B, n_stages-deep mbarrier ring
-//   warp 1      MMA issuer     : 4 x tcgen05.mma (K = 16 each) per step into a TMEM accumulator
-//                                (2 accumulator buffers of nt columns), tcgen05.commit frees stages
-//   warps 2..5  epilogue       : tcgen05.ld -> bias + activation -> bf16 / fp32 global stores
+//   one persistent CTA per SM (or a cluster of two: tcgen05 cta_group::2) over work items (particle tile of 128 / 256
+//   rows, chain of jobs); blockDim = 32 * (4 * epilogue groups + 1 + MMA issuers)
+//   warps 0..7   epilogue, 1-2 groups x four TMEM lane quadrants: tcgen05.ld -> bias + activation -> bf16 -> swizzled
+//                staging tile -> TMA store per 64-column chunk; or the fused-head reduction (kDot); or direct stores
+//                (image / score outputs)
+//   next warp    TMA producer: A tile [128 particles x 64 ch] (+ the weight tile or, in a pair, this CTA's half of it,
+//                when weights are streamed) per step, SWIZZLE_128B, n_stages-deep mbarrier ring
+//   last warp(s) MMA issuer (pair: leader CTA only): 4 x tcgen05.mma (K = 16) per op into a TMEM accumulator
+//                (2 buffers of nt columns), tcgen05.commit frees the stage
 //
 // Replaces the cuDNN calls behind nn.ConvTranspose2d / nn.Conv2d in Generator.forward /
 // Discriminator.forward (src/utils/util_dcgan.py:103-149).  A SIMT interpreter of the same tables

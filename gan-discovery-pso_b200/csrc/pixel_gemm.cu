@@ -642,11 +642,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               // nothing to wait for here: every half waits for its own previous store just before it is rewritten
             } else if (q_warp_store) {
               // the warp's own slice (32 rows = 4 KB) of the staging tile, tracked by ITS lane 0's bulk groups
-              if (lane == 0) { if (q_stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
+              if (lane == 0) { if (q_stg_bufs == 3) ptx::bulk_wait_read2(); else if (q_stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
               __syncwarp();
             } else {
               if (issuer_warp) {
-                if (ptx::elect_one()) { if (q_stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
+                if (ptx::elect_one()) { if (q_stg_bufs == 3) ptx::bulk_wait_read2(); else if (q_stg_bufs == 2) ptx::bulk_wait_read1(); else ptx::bulk_wait_read0(); }
                 __syncwarp();
               }   // the store that last used this tile has drained it
               ptx::named_bar_sync(1 + grp, 128);
@@ -745,7 +745,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 __syncwarp();
               }
             }
-            if (q_stg_bufs == 2) sflip ^= 1u;
+            if (q_stg_bufs > 1) { if (++sflip == (uint32_t)q_stg_bufs) sflip = 0; }
             if (prof) { const long long t = clock64(); e_pub += (unsigned long long)(t - tq); tq = t; }
           }
           if (kDot) {
@@ -1273,6 +1273,10 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   if (l->tma_store && !l->dot_head) {
     const int room = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes;
     l->stg_bufs = (room - 2 * l->epi_groups * kATileBytes) / l->stage_bytes >= (l->pair ? 4 : 3) ? 2 : 1;
+    // a third staging tile per group where the ring stays >= 4 deep (PSOB_STG3=1; A/B knob): the epilogue warps of
+    // store-bound layers wait ~10 % of their time for the store of two chunks ago to release its tile
+    const char* e = getenv("PSOB_STG3");
+    if (l->stg_bufs == 2 && !l->band && e && atoi(e) != 0 && (room - 3 * l->epi_groups * kATileBytes) / l->stage_bytes >= 4) l->stg_bufs = 3;
   }
   int stg_bytes = l->epi_groups * l->stg_bufs * kATileBytes;
   if (l->dot_head) {

@@ -411,7 +411,7 @@ def run_psob(args):
 
     if rank == 0:
         # layers, score, pbest+candidate+apply, update (assessor: + pack, max pool, softmax pick)
-        launches_per_step = len(gnet.layers) + (len(anet.ops) + 2 if assessor else len(dnet.launch_plan(gnet.image_padded_bf16()))) + 1 + 3 + 1
+        launches_per_step = len(gnet.layers) + (1 if gnet.programs[0].meta.get("ones_cols") else 0) + (len(anet.ops) + 2 if assessor else len(dnet.launch_plan(gnet.image_padded_bf16()))) + 1 + 3 + 1
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",

@@ -72,6 +72,7 @@ struct EngineParams {
   int b_resident, n_wrows, n_bias_rows, n_steps;
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4, strided;
+  int no_bias;               // every bias entry is 0 (e.g. folded into the K padding): the chunked epilogue skips the loads and adds
   int rot_div;               // chain rotation: item (tile t, slot r) runs chain (r + t / rot_div) % n_chains (0: chain r) -- see pick_rotation
   int step_stride;           // int4 words per step in the shared-memory copy of the step table (1 when no step has > 2 ops)
   int warp_store;            // every epilogue warp stores its own 32 rows of a chunk (32-row TMA box): no barriers inside a group
@@ -164,6 +165,15 @@ __device__ __forceinline__ uint32_t bias_act_pack(uint32_t v0, uint32_t v1, floa
   if (kAct == PSOB_ACT_RELU) asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
   else asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
   return d;
+}
+
+// the same without a bias (all-zero bias rows): ReLU is a bare cvt.rn.relu.bf16x2.f32
+template <int kAct>
+__device__ __forceinline__ uint32_t act_pack(uint32_t v0, uint32_t v1) {
+  uint32_t d;
+  if (kAct == PSOB_ACT_RELU) { asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(__uint_as_float(v1)), "f"(__uint_as_float(v0))); return d; }
+  if (kAct == PSOB_ACT_NONE) { asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(__uint_as_float(v1)), "f"(__uint_as_float(v0))); return d; }
+  return bias_act_pack<kAct>(v0, v1, 0.f, 0.f);
 }
 
 // kTmaStore: bf16 NHWC outputs whose 64-column chunks are contiguous 128-byte rows leave through a
@@ -656,8 +666,9 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             // runtime flag it put a branch into every one of the 8 unrolled slots, the loop body fell apart into 8+ basic
             // blocks and ptxas could not interleave the slots' bias -> activation -> pack chains: the epilogue warps issued
             // one instruction per ~5 cycles (ncu: 37 % fixed-latency 'wait' stalls, 20 % issuing).
-            auto emit_slot = [&](auto kHalfTag, int j, const float4& b0, const float4& b1) {
+            auto emit_slot = [&](auto kHalfTag, auto kNoBiasTag, int j, const float4& b0, const float4& b1) {
               constexpr bool kHalf = decltype(kHalfTag)::value;
+              constexpr bool kNoBias = decltype(kNoBiasTag)::value && !has_res;
               if (has_res) {
                 const uint32_t rw[4] = {rres[j].x, rres[j].y, rres[j].z, rres[j].w};
 #pragma unroll
@@ -667,10 +678,15 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 }
               }
               uint4 o;
+              if (kNoBias) {
+                o.x = act_pack<kAct>(v[8 * j + 0], v[8 * j + 1]); o.y = act_pack<kAct>(v[8 * j + 2], v[8 * j + 3]);
+                o.z = act_pack<kAct>(v[8 * j + 4], v[8 * j + 5]); o.w = act_pack<kAct>(v[8 * j + 6], v[8 * j + 7]);
+              } else {
               o.x = bias_act_pack<kAct>(v[8 * j + 0], v[8 * j + 1], b0.x, b0.y);
               o.y = bias_act_pack<kAct>(v[8 * j + 2], v[8 * j + 3], b0.z, b0.w);
               o.z = bias_act_pack<kAct>(v[8 * j + 4], v[8 * j + 5], b1.x, b1.y);
               o.w = bias_act_pack<kAct>(v[8 * j + 6], v[8 * j + 7], b1.z, b1.w);
+              }
               if (kHalf) {
                 // SWIZZLE_64B half tile [32 rows x 64 B]: 16-byte slot jj of row r lives at jj ^ ((r / 2) % 4)
                 if ((j & 3) == 0) half_open(j >> 2);
@@ -703,7 +719,11 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               }
             } else {
               auto run_slots = [&](auto kHalfTag) {
-                if (bias_in_smem) {
+                if (p.no_bias && !has_res) {
+                  const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) emit_slot(kHalfTag, std::true_type{}, j, z4, z4);
+                } else if (bias_in_smem) {
                   // explicit ld.shared, software-pipelined one slot ahead: through a generic pointer every slot was a
                   // dependent LD -> math -> STS chain of ~110 cycles
                   const uint32_t baddr = s_bias_addr + (uint32_t)(j1.z * q_nt + n0) * 4u;
@@ -712,12 +732,12 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                   for (int j = 0; j < 8; ++j) {
                     float4 c0 = b0, c1 = b1;
                     if (j < 7) { b0 = ptx::ld_shared_f4(baddr + 32u * (j + 1)); b1 = ptx::ld_shared_f4(baddr + 32u * (j + 1) + 16u); }
-                    emit_slot(kHalfTag, j, c0, c1);
+                    emit_slot(kHalfTag, std::false_type{}, j, c0, c1);
                   }
                 } else {
 #pragma unroll
                   for (int j = 0; j < 8; ++j)
-                    emit_slot(kHalfTag, j, __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j)), __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4)));
+                    emit_slot(kHalfTag, std::false_type{}, j, __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j)), __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4)));
                 }
               };
               if (q_half) run_slots(std::true_type{}); else run_slots(std::false_type{});
@@ -982,6 +1002,7 @@ struct psob_layer {
   bool tma_store = false, vec4 = false, pair = false, strided = false;
   int epi_groups = 2, step_stride = 2;
   bool band = false;
+  bool no_bias = false;            // all bias entries are 0
   bool dot_head = false;           // dot-only layer: staging area = the head's weights, 2 epilogue groups
   int stg_bytes = 0;               // bytes of the staging area in the shared-memory plan
   unsigned long long* prof = nullptr;
@@ -1301,6 +1322,8 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
   { const char* e = getenv("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }
   { const char* e = getenv("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
+  l->no_bias = true;
+  for (int i = 0; i < d->nt * d->n_bias_rows; ++i) if (d->bias[i] != 0.f) { l->no_bias = false; break; }
   for (int c = 0; c < d->n_chains; ++c) {
     int n_st = 0, n_op = 0, n_ck = 0;
     for (int j = d->chains[2 * c]; j < d->chains[2 * c] + d->chains[2 * c + 1]; ++j) {
@@ -1398,6 +1421,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
   p.idesc_eye = make_idesc_bf16(kTileM, 64);
   p.eye = l->eye ? 1 : 0;
+  p.no_bias = l->no_bias ? 1 : 0;
   p.rot_div = 0;
   p.tmem_cols = l->tmem_cols;
 

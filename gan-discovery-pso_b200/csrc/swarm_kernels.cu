@@ -692,6 +692,13 @@ maxpool_nhwc_kernel(const __nv_bfloat16* __restrict__ x, long long P, int h, int
   *reinterpret_cast<uint4*>(y + out_offset(p, ((long long)oy * wo + ox) * cp + 8 * c, y_pitch, y_tiled)) = o;
 }
 
+__global__ void __launch_bounds__(256) fill_columns_bf16_kernel(__nv_bfloat16* __restrict__ x, long long P, long long pitch, int col0, int n,
+                                                                __nv_bfloat16 value) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P * n) return;
+  x[(i / n) * pitch + col0 + (i % n)] = value;
+}
+
 extern "C" {
 
 int psob_version(void) { return PSOB_VERSION; }
@@ -733,6 +740,15 @@ int psob_update(const psob_update_args* a, psob_stream_t s) {
   if (a->r1) pso_update_kernel<false><<<blocks, 256, 0, (cudaStream_t)s>>>(u);
   else       pso_update_kernel<true><<<blocks, 256, 0, (cudaStream_t)s>>>(u);
   PSOB_LAUNCH_CHECK("pso_update_kernel");
+  return 0;
+}
+
+int psob_fill_columns_bf16(void* x, int64_t P, int64_t pitch, int32_t col0, int32_t n, float value, psob_stream_t s) {
+  if (!x || P <= 0 || n <= 0 || col0 < 0 || col0 + n > pitch) return fail(PSOB_E_ARG, "psob_fill_columns_bf16: bad arguments");
+  const long long total = (long long)P * n;
+  fill_columns_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)s>>>(
+      reinterpret_cast<__nv_bfloat16*>(x), P, pitch, col0, n, __float2bfloat16_rn(value));
+  PSOB_LAUNCH_CHECK("fill_columns_bf16_kernel");
   return 0;
 }
 

@@ -16,7 +16,7 @@ EXPORTS = [
     "psob_softmax_select", "psob_recon_fitness", "psob_rescale_minmax", "psob_pack_image",
     "psob_pairwise_distance_sum", "psob_vq_nearest", "psob_pack_image_stem", "psob_maxpool_nhwc",
     "psob_layer_create", "psob_layer_destroy", "psob_layer_run", "psob_layer_run_residual", "psob_layer_profile",
-    "psob_layer_dot_slots", "psob_layer_run_dot", "psob_dot_finish",
+    "psob_layer_dot_slots", "psob_layer_run_dot", "psob_dot_finish", "psob_fill_columns_bf16",
 ]
 
 MODE_IN_TRAINING, MODE_OUT_TRAINING = 0, 1
@@ -96,6 +96,7 @@ def lib():
         "psob_layer_dot_slots": ([vp], C.c_int),
         "psob_layer_run_dot": ([vp, vp, i64, i64, vp, vp, vp], C.c_int),
         "psob_dot_finish": ([vp, i32, i64, f32, i32, vp, vp], C.c_int),
+        "psob_fill_columns_bf16": ([vp, i64, i64, i32, i32, f32, vp], C.c_int),
     }
     for name, (args, res) in sig.items():
         fn = getattr(l, name)

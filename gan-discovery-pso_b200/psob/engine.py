@@ -164,6 +164,13 @@ class GeneratorNet(Network):
         super().__init__(progs, P, device, impl)
         self.image_elems = progs[-1].out32_pitch
 
+    def forward(self, x: torch.Tensor):
+        oc = self.programs[0].meta.get("ones_cols")
+        if oc:      # the first layer's bias rides on two 1.0 columns of the latent row's K padding (lowering.lower_convt_from_1x1)
+            _ffi.check(_ffi.lib().psob_fill_columns_bf16(x.data_ptr(), self.P, x.stride(0), oc[0], oc[1], 1.0, _stream()),
+                       "psob_fill_columns_bf16")
+        return super().forward(x)
+
     def image(self) -> torch.Tensor:
         return self.acts32[-1]
 

@@ -33,6 +33,7 @@ MAX_N = 256           # UMMA N limit / TMEM columns per accumulator buffer
 ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3, 4
 STEP_ACCUM, STEP_B_RESIDENT, STEP_NEXT, STEP_EYE = 1, 2, 4, 8     # NEXT: the op accumulates into the next job of the chain
 ROUND_WEIGHTS = True   # tests switch this off to check the geometry exactly in fp32
+BIAS_IN_K = os.environ.get("PSOB_BIAS_IN_K", "1") != "0"      # first generator layer: bias folded into the K padding of the latent row
 # Weight packs up to RESIDENT_SOLO bytes stay in one CTA's shared memory for its lifetime; packs up to
 # RESIDENT_PAIR are split over a CTA pair (tcgen05 cta_group::2, csrc/pixel_gemm.cu) when the layer has the
 # TMA-store epilogue (64-channel NHWC chunks).  PSOB_PAIR=0 falls back to streaming the weights per step.
@@ -219,6 +220,17 @@ def lower_convt_from_1x1(name, w, b, act, in_pitch=None) -> LayerProgram:
     wp[:cin, :cout] = w
     bp = np.zeros(cp, np.float32)
     bp[:cout] = b
+    meta_extra = {}
+    if BIAS_IN_K and kp - cin >= 2:
+        # The K padding of the latent row carries the bias: input columns cin, cin + 1 hold 1.0 (written by
+        # GeneratorNet.forward / nets.emulate_chain) and their weight rows the bias as a bf16 hi + lo pair (2^-17 relative),
+        # so the accumulator already contains it and the epilogue is a bare ReLU + convert -- this layer is bound by its
+        # epilogue's instruction chain, not by the two K-steps of its MMA.
+        hi = to_bf16_f32(bp)
+        wp[cin, :, :, :] = hi[:, None, None]
+        wp[cin + 1, :, :, :] = (bp - hi)[:, None, None]
+        bp = np.zeros(cp, np.float32)
+        meta_extra = dict(ones_cols=(cin, 2))
     for p0 in range(0, npix, gpix):
         for ch in range(nco):
             sb = len(steps)
@@ -237,7 +249,7 @@ def lower_convt_from_1x1(name, w, b, act, in_pitch=None) -> LayerProgram:
     bias = [[bp[ch * cc + n % cc] for n in range(nt)] for ch in range(nco)]
     return _finish(name, nt, nt, cc, act, in_pitch, npix * cp, 0, tiles, False, steps, jobs, col_map,
                    [-1] * nt, bias, macs_exact=cin * cout * npix,
-                   meta=dict(kind="convt1x1", out_hw=(k, k), out_c=cout, out_cp=cp))
+                   meta=dict(kind="convt1x1", out_hw=(k, k), out_c=cout, out_cp=cp, **meta_extra))
 
 
 # ----------------------------------------------------------------------------------------------

@@ -122,6 +122,10 @@ def pad_image_bf16(img: np.ndarray) -> np.ndarray:
 def emulate_chain(progs: List[L.LayerProgram], x: np.ndarray, round_out=True):
     """CPU emulation of a whole stack; returns (last bf16 output, last fp32 output)."""
     y, y32 = x, None
+    oc = progs[0].meta.get("ones_cols")
+    if oc:                                  # the layer's bias rides on two 1.0 columns of the K padding (lower_convt_from_1x1)
+        y = np.array(x, dtype=np.float32, copy=True)
+        y[:, oc[0]:oc[0] + oc[1]] = 1.0
     for pr in progs:
         y, y32 = L.emulate(pr, y, round_out=round_out)
     return y, y32

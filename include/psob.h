@@ -87,6 +87,10 @@ typedef struct {
 
 int psob_update(const psob_update_args* a, psob_stream_t s);
 
+/* x[p, col0 .. col0 + n) = value for every row of a bf16 matrix [P, pitch]: the constant-1 columns in the K padding of the
+ * latent rows that carry the first generator layer's bias (Generator.forward's first ConvTranspose2d + BatchNorm shift,
+ * src/utils/util_dcgan.py:133-135, folded into the MMA) */
+int psob_fill_columns_bf16(void* x, int64_t P, int64_t pitch, int32_t col0, int32_t n, float value, psob_stream_t s);
 /* fp32 [P, D] -> zero-padded bf16 [P, z_pitch] (initial generator input) */
 int psob_pack_latent(const float* pos, int64_t P, int32_t D, void* z_bf16, int32_t z_pitch, psob_stream_t s);
 

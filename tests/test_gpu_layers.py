@@ -295,3 +295,31 @@ def test_fused_head_rejects_layers_without_chunked_epilogue(mods):
     part = torch.zeros(64, 4, device="cuda")
     rc = lib.psob_layer_run_dot(d.layers[2].handle, x.data_ptr(), x.stride(0), 4, x.data_ptr(), part.data_ptr(), 0)
     assert rc < 0
+
+
+def test_bias_in_k_padding_matches_bias_table(mods, monkeypatch):
+    """First generator layer with its bias folded into the latent row's K padding (two 1.0 columns written by
+    GeneratorNet.forward, bf16 hi + lo weight rows, no-bias epilogue) == the same layer with an fp32 bias table."""
+    engine, L, nets, ffi = mods
+    torch.manual_seed(21)
+    gen = port.Generator(100, 1, 64)
+    port.randomize_bn_stats(gen, torch.Generator().manual_seed(22))      # non-zero folded BatchNorm shifts
+    P = 300
+    z = torch.randn(P, 100, generator=torch.Generator().manual_seed(23))
+    out = {}
+    for fold in (True, False):
+        monkeypatch.setattr(L, "BIAS_IN_K", fold)
+        net = engine.GeneratorNet(gen.state_dict(), P)
+        assert bool(net.programs[0].meta.get("ones_cols")) == fold
+        assert (float(np.abs(net.programs[0].bias).max()) == 0.0) == fold
+        x = _rows(z.numpy(), net.in_pitch)
+        _, img = net.forward(x)
+        torch.cuda.synchronize()
+        if fold:
+            assert torch.all(x[:, 100:102].float() == 1.0) and torch.all(x[:, 102:].float() == 0.0)
+        out[fold] = (net.activation(0).float().cpu().numpy(), img.cpu().numpy())
+    assert np.abs(out[False][0]).max() > 0.1
+    np.testing.assert_allclose(out[True][0], out[False][0], rtol=1.0 / 128, atol=1e-3)      # one bf16 ulp
+    # the image sees the first layer's one-ulp flips through two more bf16 layers (seen: 13 of 235 200 pixels off by <= 3e-3)
+    np.testing.assert_allclose(out[True][1], out[False][1], rtol=0, atol=1e-2)
+    assert np.mean(np.abs(out[True][1] - out[False][1]) > 2e-3) < 1e-3

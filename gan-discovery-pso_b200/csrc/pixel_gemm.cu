@@ -173,6 +173,15 @@ __device__ __forceinline__ uint32_t act_pack(uint32_t v0, uint32_t v1) {
   uint32_t d;
   if (kAct == PSOB_ACT_RELU) { asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(__uint_as_float(v1)), "f"(__uint_as_float(v0))); return d; }
   if (kAct == PSOB_ACT_NONE) { asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(__uint_as_float(v1)), "f"(__uint_as_float(v0))); return d; }
+  if (kAct == PSOB_ACT_LEAKY) {           // max(v, 0.2 v): one packed multiply, two max, one convert
+    unsigned long long t;
+    float tl, th;
+    asm("{\n\t.reg .b64 a, c;\n\tmov.b64 a, {%1, %2};\n\tmov.b64 c, {%3, %3};\n\tmul.rn.f32x2 %0, a, c;\n\t}" : "=l"(t) : "r"(v0), "r"(v1), "f"(0.2f));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(tl), "=f"(th) : "l"(t));
+    const float lo = fmaxf(__uint_as_float(v0), tl), hi = fmaxf(__uint_as_float(v1), th);
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
+  }
   return bias_act_pack<kAct>(v0, v1, 0.f, 0.f);
 }
 

@@ -146,6 +146,14 @@ def _sd_numpy(sd):
     return {k: (v.detach().cpu().numpy() if hasattr(v, "detach") else np.asarray(v)) for k, v in sd.items()}
 
 
+def _fill_ones(net: "Network", x: torch.Tensor):
+    """Constant-1 input columns that carry the first layer's bias through the MMA (`ones_cols` of the first program)."""
+    oc = net.programs[0].meta.get("ones_cols")
+    if oc:
+        _ffi.check(_ffi.lib().psob_fill_columns_bf16(x.data_ptr(), net.P, x.stride(0), oc[0], oc[1], 1.0, _stream()),
+                   "psob_fill_columns_bf16")
+
+
 class GeneratorNet(Network):
     """28x28 DCGAN generator / VQ-VAE-GAN decoder (src/utils/util_dcgan.py:128-149)."""
 
@@ -165,10 +173,7 @@ class GeneratorNet(Network):
         self.image_elems = progs[-1].out32_pitch
 
     def forward(self, x: torch.Tensor):
-        oc = self.programs[0].meta.get("ones_cols")
-        if oc:      # the first layer's bias rides on two 1.0 columns of the latent row's K padding (lowering.lower_convt_from_1x1)
-            _ffi.check(_ffi.lib().psob_fill_columns_bf16(x.data_ptr(), self.P, x.stride(0), oc[0], oc[1], 1.0, _stream()),
-                       "psob_fill_columns_bf16")
+        _fill_ones(self, x)      # the first layer's bias rides on two 1.0 columns of the latent row's K padding (lowering.lower_convt_from_1x1)
         return super().forward(x)
 
     def image(self) -> torch.Tensor:
@@ -219,6 +224,8 @@ class DiscriminatorNet(Network):
     def launch_plan(self, x: torch.Tensor):
         """The forward pass as a list of (name, launch) pairs -- what forward() runs and what bench.py times per stage."""
         plan, cur, lib = [], x, _ffi.lib()
+        if self.programs[0].meta.get("ones_cols"):
+            plan.append((self.programs[0].name + ".ones", lambda: _fill_ones(self, x)))
         n_plain = len(self.layers) - (2 if self.head else 0)
         for layer, y, y32 in list(zip(self.layers, self.acts, self.acts32))[:n_plain]:
             plan.append((layer.prog.name, lambda l=layer, c=cur, y=y, y32=y32: l.run(c, self.P, y, y32, self.impl)))
@@ -235,6 +242,7 @@ class DiscriminatorNet(Network):
 
     def forward(self, x: torch.Tensor):
         if not self.head:
+            _fill_ones(self, x)
             return super().forward(x)
         for _, launch in self.launch_plan(x):
             launch()
@@ -246,6 +254,10 @@ class EncoderNet(Network):
 
     def __init__(self, state_dict, P, prefix="enc", device=None, impl=_ffi.IMPL_TCGEN05):
         super().__init__(nets.encoder_programs(_sd_numpy(state_dict), prefix), P, device, impl)
+
+    def forward(self, x: torch.Tensor):
+        _fill_ones(self, x)
+        return super().forward(x)
 
 
 class AssessorNet:

@@ -33,6 +33,7 @@ MAX_N = 256           # UMMA N limit / TMEM columns per accumulator buffer
 ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3, 4
 STEP_ACCUM, STEP_B_RESIDENT, STEP_NEXT, STEP_EYE = 1, 2, 4, 8     # NEXT: the op accumulates into the next job of the chain
 ROUND_WEIGHTS = True   # tests switch this off to check the geometry exactly in fp32
+BIAS_IN_K_IMAGE = os.environ.get("PSOB_BIAS_IN_K_IMAGE", "1") != "0"   # ... and of the first discriminator / encoder conv (constant K-chunk)
 BIAS_IN_K = os.environ.get("PSOB_BIAS_IN_K", "1") != "0"      # first generator layer: bias folded into the K padding of the latent row
 # Weight packs up to RESIDENT_SOLO bytes stay in one CTA's shared memory for its lifetime; packs up to
 # RESIDENT_PAIR are split over a CTA pair (tcgen05 cta_group::2, csrc/pixel_gemm.cu) when the layer has the
@@ -680,6 +681,25 @@ def lower_conv_image_k4s2p1(name, w, b, act) -> LayerProgram:
                 if 0 <= kx < 4:
                     t[oxl * cpo:oxl * cpo + cout, kk] = w[:, 0, r, kx]
         tiles.append(t)
+    bp = np.zeros(cpo, np.float32)
+    bp[:cout] = b
+    # Bias through the MMA (see lower_convt_from_1x1): a third K-chunk per job reads padded rows 29-30, whose last two elements
+    # (row 30, columns 30 and 31: no window multiplies them with a non-zero weight) hold 1.0 -- written by
+    # DiscriminatorNet / EncoderNet.forward -- against the bias as a bf16 hi + lo pair.  The layer is bound by its epilogue's
+    # instruction chain (two K-steps of MMA per 256 output columns), so the extra step is free and the epilogue loses its
+    # bias loads and adds.
+    ones_at = (IMG_PAD_ROWS - 1) * IMG_PAD_PITCH + IMG_PAD_PITCH - 2
+    fold = BIAS_IN_K and BIAS_IN_K_IMAGE
+    meta_extra = {}
+    if fold:
+        t = np.zeros((nt, KCHUNK), np.float32)
+        hi_b = to_bf16_f32(bp)
+        for oxl in range(gox):
+            t[oxl * cpo:(oxl + 1) * cpo, KCHUNK - 2] = hi_b
+            t[oxl * cpo:(oxl + 1) * cpo, KCHUNK - 1] = bp - hi_b
+        tiles.append(t)
+        bp = np.zeros(cpo, np.float32)
+        meta_extra = dict(ones_cols=(ones_at, 2))
     steps, jobs = [], []
     for oy in range(ho):
         for g in range((wo + gox - 1) // gox):
@@ -687,16 +707,16 @@ def lower_conv_image_k4s2p1(name, w, b, act) -> LayerProgram:
             start = 2 * oy * IMG_PAD_PITCH + 2 * gox * g      # padded row 2oy == real row 2oy-1; padded col == real col-1+1
             for kc in range(2):
                 steps.append((start + kc * KCHUNK, kc * nt, 0, STEP_B_RESIDENT | (STEP_ACCUM if kc else 0)))
+            if fold:
+                steps.append((ones_at + 2 - KCHUNK, 2 * nt, 0, STEP_B_RESIDENT | STEP_ACCUM))
             lo, hi = _mask_words([gox * g + j < wo for j in range(gox)])
-            jobs.append((sb, 2, (oy * wo + gox * g) * cpo, 0, lo, hi, 0, 0))
-    bp = np.zeros(cpo, np.float32)
-    bp[:cout] = b
+            jobs.append((sb, len(steps) - sb, (oy * wo + gox * g) * cpo, 0, lo, hi, 0, 0))
     assert steps[-1][0] + KCHUNK <= IMG_PAD_ROWS * IMG_PAD_PITCH
     # exact MACs: taps inside the image
     taps = sum(1 for o in range(14) for kk in range(4) if 0 <= 2 * o - 1 + kk < 28)
     return _finish(name, nt, nt, cpo, act, IMG_PAD_ROWS * IMG_PAD_PITCH, ho * wo * cpo, 0, tiles, True, steps, jobs,
                    list(range(nt)), [-1] * nt, [bp[n % cpo] for n in range(nt)], macs_exact=taps * taps * cout,
-                   meta=dict(kind="conv_image", out_hw=(ho, wo), out_c=cout, out_cp=cpo))
+                   meta=dict(kind="conv_image", out_hw=(ho, wo), out_c=cout, out_cp=cpo, **meta_extra))
 
 
 # ----------------------------------------------------------------------------------------------

@@ -26,6 +26,14 @@
 
 namespace psob {
 
+// A/B tuning knobs (PSOB_* environment variables) are read only when PSOB_TUNING=1: a stray PSOB_* variable in a user's
+// shell must not change how the product path executes.  tools/ and the mode-equivalence tests set PSOB_TUNING=1.
+static const char* knob(const char* name) {
+  const char* t = getenv("PSOB_TUNING");
+  if (!t || t[0] != '1' || t[1] != 0) return nullptr;
+  return getenv(name);
+}
+
 constexpr int kMaxStages = 8;
 constexpr int kTileM = 128;
 constexpr int kKChunk = 64;
@@ -92,7 +100,18 @@ struct EngineParams {
   // (bf16 [out_pitch], the weights of a following full-map conv with ONE output channel) as it comes out of TMEM
   const uint16_t* dot_w;
   float* dot_part;           // fp32 [n_jobs * epi_groups][P]: one partial sum per (job, epilogue group) and particle
+  // reconstruction epilogue (image layers): every thread owns one particle row of the image, so the per-particle
+  // sum((target - G(z))^2) of Discovery.fitness_pso_inverter (src/pso/util_discovery.py:97) is accumulated from the fp32
+  // pixel it already holds in a register; partial sums per (job, epilogue group), fixed order -> deterministic
+  const void* recon_target;  // [P, recon_pitch] fp32 or bf16, laid out like the fp32 image output
+  float* recon_part;         // fp32 [n_jobs * (band ? epi_groups : 1)][P]
+  int recon_bf16, recon_pitch;
 };
+
+__device__ __forceinline__ float recon_load(const void* base, int is_bf16, long long idx) {
+  return is_bf16 ? __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(base) + idx))
+                 : __ldg(reinterpret_cast<const float*>(base) + idx);
+}
 
 __device__ __forceinline__ float apply_act(float v, int act) {
   switch (act) {
@@ -570,6 +589,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         ptx::tc_fence_after();
         const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)q_nt;
         float dacc0 = 0.f, dacc1 = 0.f, dacc2 = 0.f, dacc3 = 0.f;      // kDot: this row's partial dot product over the job
+        float racc = 0.f;                                              // reconstruction: this row's sum of squared differences over the job
         if (kTmaStore) {
           const int n_chunks = q_nt >> 6;
           int last = -1;                      // last chunk this group will read: release TMEM right after it
@@ -711,6 +731,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               const float bz = bias_in_smem ? s_bias[0] : __ldg(p.bias);
               const long long particle = (long long)tile_row(ptile) + row;
               float* y32row = (p.y32 && particle < q_P) ? p.y32 + particle * q_out32_pitch + j0.w + ch * 2 * 28 : nullptr;
+              const bool recon = p.recon_part != nullptr && particle < q_P;
+              const long long tbase_idx = particle * (long long)p.recon_pitch + j0.w + ch * 2 * 28;
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 const int rr = j >> 2;
@@ -721,6 +743,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                   const int px = (8 * j + i) & 31;
                   f[i] = (px >= 1 && px <= 28 && rowok) ? act_fn<kAct>(__uint_as_float(v[(rr * kBandPitch + px) & 63]) + bz) : 0.f;
                   if (px >= 1 && px <= 28 && rowok && y32row) y32row[rr * 28 + px - 1] = f[i];
+                  if (px >= 1 && px <= 28 && rowok && recon) {
+                    const float dlt = recon_load(p.recon_target, p.recon_bf16, tbase_idx + rr * 28 + px - 1) - f[i];
+                    racc = fmaf(dlt, dlt, racc);
+                  }
                 }
                 uint4 o;
                 o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]); o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
@@ -782,11 +808,17 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             const long long particle = (long long)tile_row(ptile) + row;
             if (particle < q_P) p.dot_part[(size_t)(job * q_epi_groups + grp) * (size_t)q_P + particle] = (dacc0 + dacc1) + (dacc2 + dacc3);
           }
+          if (!kDot && q_band && p.recon_part != nullptr) {
+            const long long particle = (long long)tile_row(ptile) + row;
+            if (particle < q_P) p.recon_part[(size_t)(job * q_epi_groups + grp) * (size_t)q_P + particle] = racc;
+          }
         } else {
           const long long particle = (long long)tile_row(ptile) + row;
           const bool valid = particle < q_P;
           __nv_bfloat16* yrow = p.y ? p.y + particle * q_out_pitch + j0.z : nullptr;
           float* y32row = p.y32 ? p.y32 + particle * q_out32_pitch + j0.w : nullptr;
+          const bool recon = p.recon_part != nullptr;
+          const long long tbase_idx = particle * (long long)p.recon_pitch + j0.w;
           for (int c0 = 0; c0 < q_nt; c0 += 16) {
             uint32_t v[16];
             __syncwarp();                       // tcgen05.ld is .sync.aligned: reconverge after the masked stores
@@ -816,6 +848,13 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 #pragma unroll
                   for (int i = 0; i < 4; ++i) { const int c32 = s_cm32[n + i]; if (c32 >= 0 && ((m4 >> i) & 1u)) y32row[c32] = f[i]; }
                 }
+                if (recon) {
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    const int c32 = s_cm32[n + i];
+                    if (c32 >= 0 && ((m4 >> i) & 1u)) { const float dlt = recon_load(p.recon_target, p.recon_bf16, tbase_idx + c32) - f[i]; racc = fmaf(dlt, dlt, racc); }
+                  }
+                }
               }
             } else {
 #pragma unroll
@@ -826,12 +865,14 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 const float f = act_fn<kAct>(__uint_as_float(v[i]) + bias[n]);
                 if (yrow) { const int cm = s_cm[n]; if (cm >= 0) yrow[cm] = __float2bfloat16_rn(f); }
                 if (y32row) { const int cm = s_cm32[n]; if (cm >= 0) y32row[cm] = f; }
+                if (recon) { const int cm = s_cm32[n]; if (cm >= 0) { const float dlt = recon_load(p.recon_target, p.recon_bf16, tbase_idx + cm) - f; racc = fmaf(dlt, dlt, racc); } }
               }
             }
           }
           ptx::tc_fence_before();
           __syncwarp();
           if (lane == 0) release_tmem(buf);
+          if (recon && valid) p.recon_part[(size_t)job * (size_t)q_P + particle] = racc;
         }
         }   // jobs of the chain
       }
@@ -1034,7 +1075,7 @@ static int pick_rotation(psob_layer* l, long long tiles, int workers) {
   if (l->rot_tiles == tiles) return l->rot_div;
   const int C = (int)l->chain_steps.size();
   int best = 0;
-  if (C > 1 && workers > 0 && tiles * C > workers && !getenv("PSOB_NO_ROTATE")) {
+  if (C > 1 && workers > 0 && tiles * C > workers && !knob("PSOB_NO_ROTATE")) {
     const std::vector<int>* cost[3] = {&l->chain_steps, &l->chain_ops, &l->chain_chunks};
     auto efficiency = [&](int div) {
       double worst = 1.0;
@@ -1064,8 +1105,10 @@ static int pick_rotation(psob_layer* l, long long tiles, int workers) {
   return best;
 }
 
+struct ReconArgs { const void* target = nullptr; int is_bf16 = 0; int n_pix = 0; float* part = nullptr; };
 static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, const void* res,
-                          int64_t res_pitch, const void* dot_w, float* dot_part, int32_t impl, psob_stream_t s);
+                          int64_t res_pitch, const void* dot_w, float* dot_part, int32_t impl, psob_stream_t s,
+                          const ReconArgs& rcn = ReconArgs());
 
 extern "C" {
 
@@ -1185,7 +1228,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     // Two MMA-issuing warps (PSOB_ISSUERS, default 2) pay off when a job's ops cover several accumulator regions (N < 256
     // ops, NEXT ops of chained jobs).  Ops are split by column region when every op sits on a multiple of mma_n (identity
     // ops fall inside a region); layers with overlapping column windows (image band) are split by buffer only.
-    const char* e = getenv("PSOB_ISSUERS");
+    const char* e = knob("PSOB_ISSUERS");
     l->issuers = e ? (atoi(e) == 2 ? 2 : 1) : 1;
     l->issue_split = true;
     std::vector<int32_t> st(d->steps, d->steps + (size_t)8 * d->n_steps);
@@ -1242,7 +1285,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   // of issue floor and an HBM floor below that): as a CTA pair one instruction covers 256 particles, which halves the issue
   // cost per particle.  PSOB_BAND_PAIR=0 keeps the solo form.
   if (l->band && d->b_resident && d->mma_n % 32 == 0 && d->n_wrows % d->mma_n == 0 && l->sm_count >= 2) {
-    const char* e = getenv("PSOB_BAND_PAIR");
+    const char* e = knob("PSOB_BAND_PAIR");
     if (e ? atoi(e) != 0 : true) l->pair = true;
   }
   if (l->pair && (!l->tma_store || full_res_bytes / 2 > kMaxPairResident || d->mma_n % 32 || d->n_wrows % d->mma_n ||
@@ -1270,8 +1313,8 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     }
     const long long mma_cycles = n_ops * 4 * (d->mma_n / 2 > 90 ? d->mma_n / 2 : 90);     // per instruction: N / 2 cycles, issue floor ~90
     const long long epi_cycles = n_chunks * 500;                                          // ~1000 cycles per chunk and group, 2 groups
-    const char* e = getenv("PSOB_STREAM_PAIR");
-    l->pair = e ? atoi(e) != 0 : (d->mma_n >= 128 && mma_cycles * 100 >= epi_cycles * (getenv("PSOB_PAIR_RATIO") ? atoi(getenv("PSOB_PAIR_RATIO")) : 150));
+    const char* e = knob("PSOB_STREAM_PAIR");
+    l->pair = e ? atoi(e) != 0 : (d->mma_n >= 128 && mma_cycles * 100 >= epi_cycles * (knob("PSOB_PAIR_RATIO") ? atoi(knob("PSOB_PAIR_RATIO")) : 150));
   }
   l->stage_bytes = kATileBytes + (d->b_resident ? 0 : (l->pair ? b_tile / 2 : b_tile));
   const int res_bytes = l->pair ? full_res_bytes / 2 : full_res_bytes;
@@ -1293,7 +1336,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   // layers with short chains (K = 128 per 256 output columns) are bound by the epilogue's latency chain
   // (TMEM load -> bias/activation -> swizzled st.shared -> TMA store): a third group hides more of it
   l->epi_groups = (l->pair && !l->band && (long long)d->n_steps * 2 * d->mma_n >= 6000ll * d->n_jobs) ? 1 : 2;   // a third group measured no faster (TMA-bound)
-  { const char* e = getenv("PSOB_EPI_GROUPS"); if (e && atoi(e) >= 1 && atoi(e) <= kMaxEpiGroups) l->epi_groups = atoi(e); }
+  { const char* e = knob("PSOB_EPI_GROUPS"); if (e && atoi(e) >= 1 && atoi(e) <= kMaxEpiGroups) l->epi_groups = atoi(e); }
   if (!l->tma_store) l->epi_groups = 2;             // the direct-store epilogue uses group 0 only (thread layout of 2 groups)
   l->dot_head = d->dot_head != 0;
   if (l->dot_head && (!l->tma_store || l->band || d->out32_pitch)) {
@@ -1305,14 +1348,14 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     l->stg_bufs = (room - 2 * l->epi_groups * kATileBytes) / l->stage_bytes >= (l->pair ? 4 : 3) ? 2 : 1;
     // a third staging tile per group where the ring stays >= 4 deep (PSOB_STG3=1; A/B knob): the epilogue warps of
     // store-bound layers wait ~10 % of their time for the store of two chunks ago to release its tile
-    const char* e = getenv("PSOB_STG3");
+    const char* e = knob("PSOB_STG3");
     if (l->stg_bufs == 2 && !l->band && e && atoi(e) != 0 && (room - 3 * l->epi_groups * kATileBytes) / l->stage_bytes >= 4) l->stg_bufs = 3;
   }
   int stg_bytes = l->epi_groups * l->stg_bufs * kATileBytes;
   if (l->dot_head) {
     // nothing is staged: the area holds the head's bf16 weights, and the second epilogue group is free -- it halves the
     // time an accumulator buffer stays occupied, which chained jobs wait for (they acquire the next buffer early)
-    const char* e = getenv("PSOB_EPI_GROUPS");
+    const char* e = knob("PSOB_EPI_GROUPS");
     l->epi_groups = (e && atoi(e) == 1) ? 1 : 2;
     l->stg_bufs = 1;
     stg_bytes = (d->out_pitch * 2 + 1023) & ~1023;
@@ -1329,8 +1372,8 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->stg_off = l->res_off + res_bytes;
   l->bar_off = l->stg_off + stg_bytes;
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
-  { const char* e = getenv("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }
-  { const char* e = getenv("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
+  { const char* e = knob("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }
+  { const char* e = knob("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
   l->no_bias = true;
   for (int i = 0; i < d->nt * d->n_bias_rows; ++i) if (d->bias[i] != 0.f) { l->no_bias = false; break; }
   for (int c = 0; c < d->n_chains; ++c) {
@@ -1375,6 +1418,20 @@ int psob_layer_dot_slots(const psob_layer* l) {
   return l->d.n_jobs * l->epi_groups;
 }
 
+int psob_layer_recon_slots(const psob_layer* l) {
+  if (!l) return fail(PSOB_E_ARG, "psob_layer_recon_slots: null layer");
+  if (!l->d.out32_pitch || (l->tma_store && !l->band)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_recon_slots: not an image layer");
+  return l->d.n_jobs * (l->band ? l->epi_groups : 1);
+}
+
+int psob_layer_run_recon(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, const void* target,
+                         int32_t target_is_bf16, int32_t n_pix, float* part, psob_stream_t s) {
+  if (!target || !part) return fail(PSOB_E_ARG, "psob_layer_run_recon: null target or partial-sum buffer");
+  ReconArgs rc;
+  rc.target = target; rc.is_bf16 = target_is_bf16 ? 1 : 0; rc.n_pix = n_pix; rc.part = part;
+  return layer_run_impl(l, x, x_pitch, P, y, y32, nullptr, 0, nullptr, nullptr, PSOB_IMPL_TCGEN05, s, rc);
+}
+
 int psob_layer_run_dot(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, const void* dot_w, float* part, psob_stream_t s) {
   if (!dot_w || !part) return fail(PSOB_E_ARG, "psob_layer_run_dot: null weights or partial-sum buffer");
   return layer_run_impl(l, x, x_pitch, P, nullptr, nullptr, nullptr, 0, dot_w, part, PSOB_IMPL_TCGEN05, s);
@@ -1383,7 +1440,8 @@ int psob_layer_run_dot(psob_layer* l, const void* x, int64_t x_pitch, int64_t P,
 }  // extern "C"
 
 static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, const void* res,
-                          int64_t res_pitch, const void* dot_w, float* dot_part, int32_t impl, psob_stream_t s) {
+                          int64_t res_pitch, const void* dot_w, float* dot_part, int32_t impl, psob_stream_t s,
+                          const ReconArgs& rcn) {
   if (!l || !x || P <= 0) return fail(PSOB_E_ARG, "psob_layer_run: bad arguments");
   const psob_layer_desc& d = l->d;
   const bool dot = dot_w != nullptr;
@@ -1404,7 +1462,14 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   }
   if (d.in_tiled && x_pitch != d.in_pitch) return fail(PSOB_E_ARG, "psob_layer_run: a tile-major input has x_pitch == in_pitch (%d), got %lld", d.in_pitch, (long long)x_pitch);
   if (x_pitch < d.in_pitch || x_pitch % 8 || !aligned16(x)) return fail(PSOB_E_ARG, "psob_layer_run: x_pitch %lld < in_pitch %d, or misaligned", (long long)x_pitch, d.in_pitch);
-  if (!dot && ((d.out_pitch && !y && !(d.out32_pitch && y32)) || (!d.out_pitch && !y32))) return fail(PSOB_E_ARG, "psob_layer_run: missing output buffer");
+  const bool recon = rcn.part != nullptr;
+  if (recon) {
+    if (impl != PSOB_IMPL_TCGEN05 || dot || res) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_recon: tcgen05 path only, no residual / fused head");
+    if (!d.out32_pitch || rcn.n_pix != d.out32_pitch || !rcn.target) return fail(PSOB_E_ARG, "psob_layer_run_recon: the layer must be an image layer with %d fp32 pixels per particle (target has %d)", d.out32_pitch, rcn.n_pix);
+    if (l->tma_store && !l->band) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_recon: the layer has neither the image-band nor the direct fp32 epilogue");
+    if (l->band && !y) return fail(PSOB_E_ARG, "psob_layer_run_recon: an image-band layer needs its bf16 output buffer");
+  }
+  if (!dot && !recon && ((d.out_pitch && !y && !(d.out32_pitch && y32)) || (!d.out_pitch && !y32))) return fail(PSOB_E_ARG, "psob_layer_run: missing output buffer");
   if (y && !aligned16(y)) return fail(PSOB_E_ARG, "psob_layer_run: y must be 16-byte aligned");
   EngineParams p;
   p.steps = l->steps; p.jobs = l->jobs; p.chains = l->chains; p.n_chains = d.n_chains; p.chains_off = l->chains_off; p.col_map = l->col_map; p.col_map32 = l->col_map32; p.bias = l->bias;
@@ -1412,6 +1477,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   p.y32 = d.out32_pitch ? y32 : nullptr;
   p.res = reinterpret_cast<const __nv_bfloat16*>(res); p.res_pitch = res_pitch;
   p.dot_w = reinterpret_cast<const uint16_t*>(dot_w); p.dot_part = dot_part;
+  p.recon_target = rcn.target; p.recon_part = rcn.part; p.recon_bf16 = rcn.is_bf16; p.recon_pitch = rcn.n_pix;
   p.P = P;
   const long long n_ptiles = (P + kTileM - 1) / kTileM;
   p.n_items = n_ptiles * d.n_chains;
@@ -1424,7 +1490,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.epi_groups = l->epi_groups; p.step_stride = l->step_stride; p.band = (l->band && p.y != nullptr) ? 1 : 0;
   p.issuers = l->issuers; p.issue_split = l->issue_split ? 1 : 0;
   p.warp_store = l->warp_store ? 1 : 0;
-  { const char* e = getenv("PSOB_HALF_STORE"); p.half_store = (l->warp_store && l->stg_bufs == 1 && !l->band && l->tma_store && (e ? atoi(e) != 0 : true)) ? 1 : 0; }   // measured: d.c2 -2.7 %, g.l2 -1 %
+  { const char* e = knob("PSOB_HALF_STORE"); p.half_store = (l->warp_store && l->stg_bufs == 1 && !l->band && l->tma_store && (e ? atoi(e) != 0 : true)) ? 1 : 0; }   // measured: d.c2 -2.7 %, g.l2 -1 %
   if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);

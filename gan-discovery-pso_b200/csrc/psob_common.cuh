@@ -37,7 +37,8 @@ inline int fail(int code, const char* fmt, ...) {
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-// order-preserving float -> uint32 (NaN with sign 0 sorts above +inf)
+// order-preserving float -> uint32 (NaN with sign 0 sorts above +inf); -0.0 is canonicalised to +0.0 so that the two
+// zeros tie like they do under the reference's `<` (lowest index wins, src/pso/util_pso.py:139-143)
 __host__ __device__ inline uint32_t order_key(float f) {
 #ifdef __CUDA_ARCH__
   uint32_t b = __float_as_uint(f);
@@ -45,6 +46,7 @@ __host__ __device__ inline uint32_t order_key(float f) {
   uint32_t b;
   memcpy(&b, &f, 4);
 #endif
+  if (b == 0x80000000u) b = 0u;
   return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
 }
 

@@ -165,8 +165,10 @@ __global__ void __launch_bounds__(256) pbest_minloc_kernel(const float* __restri
 
 __global__ void gbest_candidate_kernel(const unsigned long long* key, const float* pos, const float* pbest_pos,
                                        const uint8_t* improved, const float* pbest_val, long long P,
-                                       unsigned long long index_offset, int D, float* rec) {
+                                       unsigned long long index_offset, int D, float* rec, unsigned long long* rearm) {
   unsigned long long k = *key;
+  __syncthreads();                                  // every thread has read the key before it is re-armed
+  if (rearm != nullptr && threadIdx.x == 0) *rearm = ~0ull;
   long long local = (long long)(uint32_t)(k & 0xffffffffull) - (long long)(uint32_t)index_offset;
   bool ok = local >= 0 && local < P;
   if (threadIdx.x == 0) {
@@ -200,10 +202,13 @@ __global__ void gbest_apply_kernel(const float* recs, int n_rec, int D, float* g
     bool rep = cand < inc;                    // equal never replaces (src/pso/util_pso.py:144)
     if (rep) *gbest_val = cand;
     if (hist != nullptr) {
-      int hrow = dyn ? (int)dyn->iteration : 0;
-      if (hrow >= hist_rows) hrow = hist_rows - 1;
-      hist[2 * hrow] = rep ? cand : inc;
-      hist[2 * hrow + 1] = rep ? 1.f : 0.f;
+      // rows past the recorder's capacity are dropped (never clamped onto the last row): SwarmEngine.history() returns
+      // min(iteration, hist_rows) rows and SwarmEngine.run refuses to go past max_iterations with a recorder attached
+      const int hrow = dyn ? (int)dyn->iteration : 0;
+      if (hrow < hist_rows) {
+        hist[2 * hrow] = rep ? cand : inc;
+        hist[2 * hrow + 1] = rep ? 1.f : 0.f;
+      }
     }
     if (dyn != nullptr) {
       // `if i > 1 and schedule_inertia: w = 0.99*w` runs after the global best and before the move
@@ -218,6 +223,119 @@ __global__ void gbest_apply_kernel(const float* recs, int n_rec, int D, float* g
   if (s_replace) {
     const float* src = recs + (size_t)s_best * (4 + D) + 4;
     for (int d = threadIdx.x; d < D; d += blockDim.x) gbest_pos[d] = src[d];
+  }
+}
+
+// Single-rank global best: psob_gbest_candidate + psob_gbest_apply in one launch, and the min-loc key is re-armed
+// (reset to ~0) for the next iteration's psob_fitness_tail, so no memset node sits in the iteration.
+__global__ void gbest_local_kernel(unsigned long long* key, const float* pos, const float* pbest_pos, const uint8_t* improved,
+                                   const float* pbest_val, long long P, unsigned long long index_offset, int D, float* gbest_val,
+                                   float* gbest_pos, float* hist, int hist_rows, psob_iter_state* dyn, float inertia_decay) {
+  __shared__ long long s_local;
+  __shared__ int s_replace;
+  if (threadIdx.x == 0) {
+    const unsigned long long k = *key;
+    *key = ~0ull;
+    const long long local = (long long)(uint32_t)(k & 0xffffffffull) - (long long)(uint32_t)index_offset;
+    const bool ok = local >= 0 && local < P;
+    const float cand = ok ? pbest_val[local] : INFINITY;
+    const float inc = *gbest_val;
+    const bool rep = cand < inc;                    // equal never replaces (src/pso/util_pso.py:144)
+    if (rep) *gbest_val = cand;
+    if (hist != nullptr) {
+      const int hrow = dyn ? (int)dyn->iteration : 0;
+      if (hrow < hist_rows) {
+        hist[2 * hrow] = rep ? cand : inc;
+        hist[2 * hrow + 1] = rep ? 1.f : 0.f;
+      }
+    }
+    if (dyn != nullptr) {
+      const uint32_t i_now = dyn->iteration + 1;
+      dyn->iteration = i_now;
+      if (i_now > 1 && inertia_decay != 1.0f) dyn->w = inertia_decay * dyn->w;
+    }
+    s_local = local;
+    s_replace = (rep && ok) ? 1 : 0;
+  }
+  __syncthreads();
+  if (s_replace) {
+    const long long local = s_local;
+    const float* src = (improved != nullptr && improved[local]) ? pos + local * D : pbest_pos + local * D;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) gbest_pos[d] = src[d];
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Fused fitness tail: everything between the last network layer and the global best in ONE launch --
+//   fused-head finish (partial sums + bias + sigmoid)  |  softmax pick  |  ready score
+//   -> clamp / affine (src/pso/util_discovery.py:75-80)
+//   -> + w_rec * mean((target - G(z))^2) + eps from the image epilogue's partial sums (:97-101)
+//   -> strict-< personal-best compare (src/pso/util_pso.py:122-124) -> block min-loc -> atomicMin(key)
+// Every arithmetic step is the one the separate kernels (dot_finish, score_fitness, softmax_select, recon_fitness,
+// pbest_minloc) perform, in the same order, so the results are bit-identical to the unfused chain.
+// ------------------------------------------------------------------------------------------
+struct TailParams {
+  const float* part; int n_slots; float bias; int act;
+  const float* score; int score_stride;
+  const float* logits; int n_class, class_idx;
+  const float* fit_in;
+  int mode; float thr, eps;
+  const float* recon_part; int n_recon_slots; float n_pix; float w_ass, w_rec, eps_rec;
+  float* fit; float* pbest_val; uint8_t* improved; long long P; unsigned long long index_offset; unsigned long long* key;
+};
+
+__global__ void __launch_bounds__(256) fitness_tail_kernel(const TailParams a) {
+  __shared__ unsigned long long s_k[8];
+  unsigned long long k = ~0ull;
+  for (long long p = (long long)blockIdx.x * 256 + threadIdx.x; p < a.P; p += (long long)gridDim.x * 256) {
+    float f;
+    bool have_score = true;
+    float sc = 0.f;
+    if (a.part != nullptr) {
+      float acc = 0.f;
+      for (int sl = 0; sl < a.n_slots; ++sl) acc += a.part[(size_t)sl * (size_t)a.P + p];
+      const float v = acc + a.bias;
+      sc = a.act == PSOB_ACT_SIGMOID ? 1.f / (1.f + expf(-v)) : v;
+    } else if (a.logits != nullptr) {
+      const float* l = a.logits + p * a.n_class;
+      float m = -INFINITY;
+      for (int c = 0; c < a.n_class; ++c) m = fmaxf(m, l[c]);
+      float sum = 0.f;
+      for (int c = 0; c < a.n_class; ++c) sum += expf(l[c] - m);
+      sc = expf(l[a.class_idx] - m) / sum;
+    } else if (a.score != nullptr) {
+      sc = a.score[p * a.score_stride];
+    } else {
+      have_score = false;
+    }
+    if (have_score) {
+      const float s = fminf(__fadd_rn(sc, a.thr), 1.0f);
+      f = a.mode == PSOB_MODE_IN_TRAINING ? __fadd_rn(s, a.eps) : __fadd_rn(__fsub_rn(1.0f, s), a.eps);
+    } else {
+      f = a.fit_in != nullptr ? a.fit_in[p] : 0.f;
+    }
+    if (a.recon_part != nullptr) {
+      float acc = 0.f;
+      for (int sl = 0; sl < a.n_recon_slots; ++sl) acc += a.recon_part[(size_t)sl * (size_t)a.P + p];
+      const float mse = acc / a.n_pix;
+      const float ass = (have_score || a.fit_in != nullptr) ? a.w_ass * f : 0.f;
+      f = ass + a.w_rec * mse + a.eps_rec;
+    }
+    if (a.fit != nullptr) a.fit[p] = f;
+    float pv = a.pbest_val[p];
+    const bool imp = f < pv;                       // strict; NaN never improves (src/pso/util_pso.py:122)
+    if (imp) { a.pbest_val[p] = f; pv = f; }
+    a.improved[p] = imp ? 1 : 0;
+    const unsigned long long kk = ((unsigned long long)order_key(pv) << 32) | (unsigned long long)(uint32_t)(a.index_offset + p);
+    k = kk < k ? kk : k;
+  }
+  k = warp_min_u64(k);
+  if ((threadIdx.x & 31) == 0) s_k[threadIdx.x >> 5] = k;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    k = threadIdx.x < 8 ? s_k[threadIdx.x] : ~0ull;
+    k = warp_min_u64(k);
+    if (threadIdx.x == 0) atomicMin(a.key, k);
   }
 }
 
@@ -699,6 +817,25 @@ __global__ void __launch_bounds__(256) fill_columns_bf16_kernel(__nv_bfloat16* _
   x[(i / n) * pitch + col0 + (i % n)] = value;
 }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is raised once per (kernel, device) to the largest size seen so far, not on
+// every call (the entry points promise to be plain stream work)
+#include <mutex>
+#include <map>
+#include <utility>
+static int ensure_dyn_smem(const void* fn, size_t bytes) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, size_t> seen;
+  int dev = 0;
+  PSOB_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> g(mu);
+  size_t& cur = seen[std::make_pair(fn, dev)];
+  if (bytes > cur) {
+    PSOB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    cur = bytes;
+  }
+  return 0;
+}
+
 extern "C" {
 
 int psob_version(void) { return PSOB_VERSION; }
@@ -785,8 +922,59 @@ int psob_gbest_candidate(const uint64_t* key, const float* pos, const float* pbe
                          const float* pbest_val, int64_t P, uint64_t index_offset, int32_t D, float* rec, psob_stream_t s) {
   if (!key || !pos || !pbest_pos || !pbest_val || !rec || P <= 0 || D <= 0) return fail(PSOB_E_ARG, "psob_gbest_candidate: bad arguments");
   gbest_candidate_kernel<<<1, 128, 0, (cudaStream_t)s>>>(reinterpret_cast<const unsigned long long*>(key), pos, pbest_pos,
-                                                        improved, pbest_val, P, index_offset, D, rec);
+                                                        improved, pbest_val, P, index_offset, D, rec, nullptr);
   PSOB_LAUNCH_CHECK("gbest_candidate_kernel");
+  return 0;
+}
+
+int psob_gbest_record(uint64_t* key, const float* pos, const float* pbest_pos, const uint8_t* improved,
+                      const float* pbest_val, int64_t P, uint64_t index_offset, int32_t D, float* rec, psob_stream_t s) {
+  if (!key || !pos || !pbest_pos || !pbest_val || !rec || P <= 0 || D <= 0) return fail(PSOB_E_ARG, "psob_gbest_record: bad arguments");
+  gbest_candidate_kernel<<<1, 128, 0, (cudaStream_t)s>>>(reinterpret_cast<const unsigned long long*>(key), pos, pbest_pos,
+                                                        improved, pbest_val, P, index_offset, D, rec,
+                                                        reinterpret_cast<unsigned long long*>(key));
+  PSOB_LAUNCH_CHECK("gbest_candidate_kernel");
+  return 0;
+}
+
+int psob_gbest_local(uint64_t* key, const float* pos, const float* pbest_pos, const uint8_t* improved, const float* pbest_val,
+                     int64_t P, uint64_t index_offset, int32_t D, float* gbest_val, float* gbest_pos, float* hist,
+                     int32_t hist_rows, psob_iter_state* dyn, float inertia_decay, psob_stream_t s) {
+  if (!key || !pos || !pbest_pos || !pbest_val || !gbest_val || !gbest_pos || P <= 0 || D <= 0 || (hist && hist_rows <= 0))
+    return fail(PSOB_E_ARG, "psob_gbest_local: bad arguments");
+  gbest_local_kernel<<<1, 128, 0, (cudaStream_t)s>>>(reinterpret_cast<unsigned long long*>(key), pos, pbest_pos, improved, pbest_val,
+                                                    P, index_offset, D, gbest_val, gbest_pos, hist, hist_rows, dyn, inertia_decay);
+  PSOB_LAUNCH_CHECK("gbest_local_kernel");
+  return 0;
+}
+
+int psob_fitness_tail(const psob_fitness_tail_args* a, psob_stream_t s) {
+  if (!a || !a->pbest_val || !a->improved || !a->key || a->P <= 0) return fail(PSOB_E_ARG, "psob_fitness_tail: null state pointer or P <= 0");
+  const int n_src = (a->part != nullptr) + (a->logits != nullptr) + (a->score != nullptr) + (a->fit_in != nullptr);
+  if (n_src > 1 || (n_src == 0 && a->recon_part == nullptr))
+    return fail(PSOB_E_ARG, "psob_fitness_tail: give exactly one of part / logits / score / fit_in (or only recon_part)");
+  if (a->part && a->n_slots <= 0) return fail(PSOB_E_ARG, "psob_fitness_tail: n_slots <= 0");
+  if (a->part && a->act != PSOB_ACT_SIGMOID && a->act != PSOB_ACT_NONE) return fail(PSOB_E_UNSUPPORTED, "psob_fitness_tail: head activation %d", a->act);
+  if (a->logits && (a->n_class <= 0 || a->class_idx < 0 || a->class_idx >= a->n_class)) return fail(PSOB_E_ARG, "psob_fitness_tail: class index out of range");
+  if (a->score && a->score_stride <= 0) return fail(PSOB_E_ARG, "psob_fitness_tail: score_stride <= 0");
+  if ((a->part || a->logits || a->score) && a->mode != PSOB_MODE_IN_TRAINING && a->mode != PSOB_MODE_OUT_TRAINING)
+    return fail(PSOB_E_ARG, "psob_fitness_tail: unknown mode %d", a->mode);
+  if (a->recon_part && (a->n_recon_slots <= 0 || a->n_pix <= 0)) return fail(PSOB_E_ARG, "psob_fitness_tail: recon partial sums need n_recon_slots > 0 and n_pix > 0");
+  if (a->index_offset + (uint64_t)a->P > (1ull << 32)) return fail(PSOB_E_UNSUPPORTED, "psob_fitness_tail: global index must fit 32 bits");
+  TailParams t;
+  t.part = a->part; t.n_slots = a->n_slots; t.bias = a->bias; t.act = a->act;
+  t.score = a->score; t.score_stride = a->score_stride;
+  t.logits = a->logits; t.n_class = a->n_class; t.class_idx = a->class_idx;
+  t.fit_in = a->fit_in;
+  t.mode = a->mode; t.thr = a->thr; t.eps = a->eps;
+  t.recon_part = a->recon_part; t.n_recon_slots = a->n_recon_slots; t.n_pix = (float)a->n_pix;
+  t.w_ass = a->w_ass; t.w_rec = a->w_rec; t.eps_rec = a->eps_rec;
+  t.fit = a->fit; t.pbest_val = a->pbest_val; t.improved = a->improved; t.P = a->P; t.index_offset = a->index_offset;
+  t.key = reinterpret_cast<unsigned long long*>(a->key);
+  long long blocks = (a->P + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  fitness_tail_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)s>>>(t);
+  PSOB_LAUNCH_CHECK("fitness_tail_kernel");
   return 0;
 }
 
@@ -847,7 +1035,7 @@ int psob_pairwise_distance_sum(const float* pos, int64_t P, int32_t D, int32_t p
   if (n_blocks >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_pairwise_distance_sum: P = %lld is too large (sub-sample the swarm)", (long long)P);
   const size_t smem = ((size_t)((kPairTile * (D + 1) + 1) & ~1) + (size_t)D * (kPairTile + 2)) * sizeof(float);
   if (smem > 200 * 1024) return fail(PSOB_E_UNSUPPORTED, "psob_pairwise_distance_sum: D = %d is too large", D);
-  PSOB_CUDA(cudaFuncSetAttribute(pairwise_distance_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (int rc = ensure_dyn_smem((const void*)pairwise_distance_sum_kernel, smem)) return rc;
   PSOB_CUDA(cudaMemsetAsync(sum_out, 0, sizeof(double), (cudaStream_t)s));
   pairwise_distance_sum_kernel<<<(unsigned)n_blocks, 256, smem, (cudaStream_t)s>>>(pos, P, D, pitch, (int)n_tiles, sum_out);
   PSOB_LAUNCH_CHECK("pairwise_distance_sum_kernel");
@@ -863,13 +1051,13 @@ int psob_vq_nearest(const float* x, int64_t P, int32_t D, int32_t x_pitch, const
     auto bytes = [&](int sl) { return ((size_t)sl * (D + 1) + sl + (size_t)8 * D) * sizeof(float); };
     while (slab > 32 && bytes(slab) > 160 * 1024) slab = (slab + 1) / 2;
     if (bytes(slab) > 200 * 1024) return fail(PSOB_E_UNSUPPORTED, "psob_vq_nearest: D = %d is too large", D);
-    PSOB_CUDA(cudaFuncSetAttribute(vq_nearest_rowwarp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes(slab)));
+    if (int rc = ensure_dyn_smem((const void*)vq_nearest_rowwarp_kernel, bytes(slab))) return rc;
     vq_nearest_rowwarp_kernel<<<(unsigned)((P + 7) / 8), 256, bytes(slab), (cudaStream_t)s>>>(
         x, P, D, x_pitch, codebook, K, slab, reinterpret_cast<long long*>(idx_out), dist_out);
     PSOB_LAUNCH_CHECK("vq_nearest_rowwarp_kernel");
     return 0;
   }
-  PSOB_CUDA(cudaFuncSetAttribute(vq_nearest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (int rc = ensure_dyn_smem((const void*)vq_nearest_kernel, smem)) return rc;
   vq_nearest_kernel<<<(unsigned)((P + kVqTile - 1) / kVqTile), 256, smem, (cudaStream_t)s>>>(
       x, P, D, x_pitch, codebook, K, reinterpret_cast<long long*>(idx_out), dist_out);
   PSOB_LAUNCH_CHECK("vq_nearest_kernel");

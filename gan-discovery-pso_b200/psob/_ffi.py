@@ -17,7 +17,9 @@ EXPORTS = [
     "psob_pairwise_distance_sum", "psob_vq_nearest", "psob_pack_image_stem", "psob_maxpool_nhwc",
     "psob_layer_create", "psob_layer_destroy", "psob_layer_run", "psob_layer_run_residual", "psob_layer_profile",
     "psob_layer_dot_slots", "psob_layer_run_dot", "psob_dot_finish", "psob_fill_columns_bf16",
+    "psob_fitness_tail", "psob_gbest_local", "psob_gbest_record", "psob_layer_recon_slots", "psob_layer_run_recon",
 ]
+VERSION = 200
 
 MODE_IN_TRAINING, MODE_OUT_TRAINING = 0, 1
 IMPL_TCGEN05, IMPL_SIMT = 0, 1
@@ -41,6 +43,20 @@ class UpdateArgs(C.Structure):
         ("v_max", C.c_float), ("lo", C.c_float), ("hi", C.c_float),
         ("seed", C.c_uint64), ("index_offset", C.c_uint64),
         ("iteration", C.c_uint32), ("reserved", C.c_uint32),
+    ]
+
+
+class FitnessTailArgs(C.Structure):
+    _fields_ = [
+        ("part", C.c_void_p), ("n_slots", C.c_int32), ("bias", C.c_float), ("act", C.c_int32),
+        ("score", C.c_void_p), ("score_stride", C.c_int32),
+        ("logits", C.c_void_p), ("n_class", C.c_int32), ("class_idx", C.c_int32),
+        ("fit_in", C.c_void_p),
+        ("mode", C.c_int32), ("thr", C.c_float), ("eps", C.c_float),
+        ("recon_part", C.c_void_p), ("n_recon_slots", C.c_int32), ("n_pix", C.c_int32),
+        ("w_ass", C.c_float), ("w_rec", C.c_float), ("eps_rec", C.c_float),
+        ("fit", C.c_void_p), ("pbest_val", C.c_void_p), ("improved", C.c_void_p),
+        ("P", C.c_int64), ("index_offset", C.c_uint64), ("key", C.c_void_p),
     ]
 
 
@@ -97,6 +113,11 @@ def lib():
         "psob_layer_run_dot": ([vp, vp, i64, i64, vp, vp, vp], C.c_int),
         "psob_dot_finish": ([vp, i32, i64, f32, i32, vp, vp], C.c_int),
         "psob_fill_columns_bf16": ([vp, i64, i64, i32, i32, f32, vp], C.c_int),
+        "psob_fitness_tail": ([C.POINTER(FitnessTailArgs), vp], C.c_int),
+        "psob_gbest_local": ([vp, vp, vp, vp, vp, i64, u64, i32, vp, vp, vp, i32, vp, f32, vp], C.c_int),
+        "psob_gbest_record": ([vp, vp, vp, vp, vp, i64, u64, i32, vp, vp], C.c_int),
+        "psob_layer_recon_slots": ([vp], C.c_int),
+        "psob_layer_run_recon": ([vp, vp, i64, i64, vp, vp, vp, i32, i32, vp, vp], C.c_int),
     }
     for name, (args, res) in sig.items():
         fn = getattr(l, name)
@@ -106,7 +127,12 @@ def lib():
     return l
 
 
+N_CALLS = 0      # C-ABI calls checked so far (every compute entry point is one kernel launch; bench.py counts launches with it)
+
+
 def check(rc: int, what: str = "") -> None:
+    global N_CALLS
+    N_CALLS += 1
     if rc != 0:
         msg = lib().psob_last_error().decode("utf-8", "replace")
         raise PsobError(f"{what or 'libpsob'} failed with code {rc}: {msg}")

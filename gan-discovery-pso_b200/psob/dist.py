@@ -24,6 +24,7 @@ def shard_range(total: int, rank: int, world: int) -> Tuple[int, int]:
 
 def order_key_np(x) -> np.ndarray:
     b = np.asarray(x, dtype=np.float32).view(np.uint32)
+    b = np.where(b == np.uint32(0x80000000), np.uint32(0), b)          # -0.0 ties with +0.0 (csrc/psob_common.cuh order_key)
     return np.where(b >> 31 != 0, ~b, b | np.uint32(0x80000000)).astype(np.uint32)
 
 

@@ -21,6 +21,7 @@ import numpy as np
 import torch
 
 from . import _ffi, lowering as L, nets
+from ._knobs import knob
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -56,7 +57,7 @@ class Layer:
             out_pitch=prog.out_pitch, out32_pitch=prog.out32_pitch, b_resident=int(prog.b_resident),
             vec8=int(prog.vec8), n_steps=prog.n_steps, n_jobs=prog.n_jobs, n_wrows=wbits.shape[0],
             n_bias_rows=bias.shape[0], n_chains=chains.shape[0], chains=chains.ctypes.data, in_tiled=int(in_tiled), out_tiled=int(out_tiled), dot_head=int(dot_head), solo=int(bool(prog.meta.get("residual"))),
-            band_pitch=(prog.meta["band"][1] if prog.meta.get("kind") == "convt_image_band" and os.environ.get("PSOB_BAND_EPI", "1") != "0" else 0), wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
+            band_pitch=(prog.meta["band"][1] if prog.meta.get("kind") == "convt_image_band" and knob("PSOB_BAND_EPI", "1") != "0" else 0), wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
             col_map=cm.ctypes.data, col_map32=cm32.ctypes.data, bias=bias.ctypes.data)
         h = C.c_void_p()
         _ffi.check(_ffi.lib().psob_layer_create(C.byref(d), C.byref(h)), f"psob_layer_create({prog.name})")
@@ -84,12 +85,12 @@ class Network:
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.P = P
         self.impl = impl
-        self.skip_f32 = False
         self.programs = programs
+        self._recon_slots = None
         # Internal edges use the tile-major layout [ceil(P/128)][pitch/64][128][64] whenever the producer has the
         # TMA-store epilogue and the consumer reads whole 64-column chunks; the network's own input and its last
         # output stay row-major [P, pitch].  PSOB_TILED=0 keeps everything row-major (A/B measurements).
-        tiled_ok = os.environ.get("PSOB_TILED", "1") != "0"
+        tiled_ok = knob("PSOB_TILED", "1") != "0"
         self.edge_tiled = [tiled_ok and L.can_store_tiled(a) and L.can_load_tiled(b) for a, b in zip(programs[:-1], programs[1:])]
         rows = (P + L.TILE_M - 1) // L.TILE_M * L.TILE_M
         with torch.cuda.device(self.device):
@@ -106,16 +107,48 @@ class Network:
     def in_pitch(self) -> int:
         return self.programs[0].in_pitch
 
-    def forward(self, x: torch.Tensor):
-        """x: bf16 [P, >= in_pitch].  Returns (last bf16 activation or None, last fp32 output or None)."""
-        cur = x
+    def launch_plan(self, x: torch.Tensor, write_f32: bool = True, recon=None):
+        """The forward pass as a list of (name, launch) pairs: what forward() runs and what bench.py times per stage.
+
+        write_f32=False skips the LAST layer's fp32 store when something else consumes its result (the padded bf16 image
+        for the D-score fitness, or `recon`); it is a per-call argument, so a net shared between a swarm and
+        `Generator.forward` / `Discovery.particles_to_img_batch` never returns a stale fp32 image.
+        recon=(target [P, n_pix] fp32|bf16, part fp32 [recon_slots, P]): the last layer accumulates the per-particle
+        sum((target - image)^2) in its epilogue (psob_layer_run_recon, src/pso/util_discovery.py:97)."""
+        plan, cur = [], x
+        if self.programs[0].meta.get("ones_cols"):
+            plan.append((self.programs[0].name + ".ones", lambda: _fill_ones(self, x)))
         last = len(self.layers) - 1
         for i, (layer, y, y32) in enumerate(zip(self.layers, self.acts, self.acts32)):
-            if i == last and self.skip_f32 and y is not None:
+            if i == last and recon is not None:
+                target, part = recon
+                assert target.is_cuda and target.is_contiguous() and target.dtype in (torch.float32, torch.bfloat16)
+                assert part.dtype == torch.float32 and part.shape == (self.recon_slots(), self.P)
+                plan.append((layer.prog.name, lambda l=layer, c=cur, y=y, y32=(y32 if write_f32 else None): _ffi.check(
+                    _ffi.lib().psob_layer_run_recon(l.handle, c.data_ptr(), c.stride(0), self.P, _ptr(y), _ptr(y32), target.data_ptr(),
+                                                    int(target.dtype == torch.bfloat16), target.numel() // self.P, part.data_ptr(),
+                                                    _stream()), f"psob_layer_run_recon({l.prog.name})")))
+                break
+            if i == last and not write_f32 and y is not None:
                 y32 = None                      # e.g. D-score fitness only consumes the padded bf16 image
-            layer.run(cur, self.P, y, y32, self.impl)
+            plan.append((layer.prog.name, lambda l=layer, c=cur, y=y, y32=y32: l.run(c, self.P, y, y32, self.impl)))
             cur = y
+        return plan
+
+    def forward(self, x: torch.Tensor, write_f32: bool = True, recon=None):
+        """x: bf16 [P, >= in_pitch].  Returns (last bf16 activation or None, last fp32 output or None)."""
+        for _, launch in self.launch_plan(x, write_f32=write_f32, recon=recon):
+            launch()
         return self.acts[-1], self.acts32[-1]
+
+    def recon_slots(self) -> int:
+        """Partial-sum slots per particle of the last layer's reconstruction epilogue (psob_layer_recon_slots)."""
+        if self._recon_slots is None:
+            n = _ffi.lib().psob_layer_recon_slots(self.layers[-1].handle)
+            if n <= 0:
+                _ffi.check(n, "psob_layer_recon_slots")
+            self._recon_slots = int(n)
+        return self._recon_slots
 
     def activation(self, i: int) -> Optional[torch.Tensor]:
         """Row-major [P, out_pitch] copy of layer i's bf16 output, whatever layout the edge uses (tests, debugging)."""
@@ -160,7 +193,7 @@ class GeneratorNet(Network):
     def __init__(self, state_dict, P, prefix="gen", device=None, impl=_ffi.IMPL_TCGEN05, m_last=None):
         sd = _sd_numpy(state_dict)
         if m_last is None:
-            m_last = int(os.environ.get("PSOB_M_LAST", "2"))      # image-layer block size (tuning knob)
+            m_last = int(knob("PSOB_M_LAST", "2"))      # image-layer block size (tuning knob)
         if prefix is None:
             prefix = "gen" if any(k.startswith("gen.") for k in sd) else "decoder"
         first = f"{prefix}.0.0.weight" if f"{prefix}.0.0.weight" in sd else f"{prefix}.0.weight"     # BN blocks / BN-free decoder
@@ -171,10 +204,6 @@ class GeneratorNet(Network):
             progs = nets.generator_programs(sd, prefix, m_last=m_last)
         super().__init__(progs, P, device, impl)
         self.image_elems = progs[-1].out32_pitch
-
-    def forward(self, x: torch.Tensor):
-        _fill_ones(self, x)      # the first layer's bias rides on two 1.0 columns of the latent row's K padding (lowering.lower_convt_from_1x1)
-        return super().forward(x)
 
     def image(self) -> torch.Tensor:
         return self.acts32[-1]
@@ -193,7 +222,7 @@ class DiscriminatorNet(Network):
         # activation is never written and the last layer is not launched.  PSOB_FUSED_HEAD=0 keeps the layer-by-layer
         # path (A/B measurements, per-layer tests).
         if fused_head is None:
-            fused_head = os.environ.get("PSOB_FUSED_HEAD", "1") != "0"
+            fused_head = knob("PSOB_FUSED_HEAD", "1") != "0"
         self.head = None
         if fused_head and impl == _ffi.IMPL_TCGEN05:
             self.head = self._make_head()
@@ -221,8 +250,11 @@ class DiscriminatorNet(Network):
             part = torch.zeros(slots, self.P, dtype=torch.float32, device=self.device)
         return dict(w=w_dev, part=part, slots=int(slots), bias=float(last.bias[0, 0]), act=int(last.act))
 
-    def launch_plan(self, x: torch.Tensor):
-        """The forward pass as a list of (name, launch) pairs -- what forward() runs and what bench.py times per stage."""
+    def launch_plan(self, x: torch.Tensor, finish: bool = True):
+        """The forward pass as a list of (name, launch) pairs -- what forward() runs and what bench.py times per stage.
+        finish=False leaves the fused head's partial sums for psob_fitness_tail (the swarm's fused iteration)."""
+        if not self.head:
+            return super().launch_plan(x)
         plan, cur, lib = [], x, _ffi.lib()
         if self.programs[0].meta.get("ones_cols"):
             plan.append((self.programs[0].name + ".ones", lambda: _fill_ones(self, x)))
@@ -235,18 +267,16 @@ class DiscriminatorNet(Network):
             plan.append((hid.prog.name, lambda c=cur: _ffi.check(lib.psob_layer_run_dot(
                 hid.handle, c.data_ptr(), c.stride(0), self.P, hd["w"].data_ptr(), hd["part"].data_ptr(), _stream()),
                 f"psob_layer_run_dot({hid.prog.name})")))
-            plan.append((self.programs[-1].name + ".finish", lambda: _ffi.check(lib.psob_dot_finish(
-                hd["part"].data_ptr(), hd["slots"], self.P, hd["bias"], hd["act"], self.acts32[-1].data_ptr(), _stream()),
-                "psob_dot_finish")))
+            if finish:
+                plan.append((self.programs[-1].name + ".finish", lambda: _ffi.check(lib.psob_dot_finish(
+                    hd["part"].data_ptr(), hd["slots"], self.P, hd["bias"], hd["act"], self.acts32[-1].data_ptr(), _stream()),
+                    "psob_dot_finish")))
         return plan
 
-    def forward(self, x: torch.Tensor):
-        if not self.head:
-            _fill_ones(self, x)
-            return super().forward(x)
-        for _, launch in self.launch_plan(x):
+    def forward(self, x: torch.Tensor, finish: bool = True):
+        for _, launch in self.launch_plan(x, finish=finish):
             launch()
-        return None, self.acts32[-1]
+        return (None if self.head else self.acts[-1]), self.acts32[-1]
 
 
 class EncoderNet(Network):
@@ -255,9 +285,6 @@ class EncoderNet(Network):
     def __init__(self, state_dict, P, prefix="enc", device=None, impl=_ffi.IMPL_TCGEN05):
         super().__init__(nets.encoder_programs(_sd_numpy(state_dict), prefix), P, device, impl)
 
-    def forward(self, x: torch.Tensor):
-        _fill_ones(self, x)
-        return super().forward(x)
 
 
 class AssessorNet:
@@ -277,7 +304,7 @@ class AssessorNet:
         self.n_class = sizes["logits"]
         # Buffers written and read by engine layers only (everything after the max pool) use the tile-major layout
         # [ceil(P/128)][pitch/64][128][64]: every operand tile and epilogue chunk is one contiguous 16 KB block.
-        tiled_ok = os.environ.get("PSOB_TILED", "1") != "0"
+        tiled_ok = knob("PSOB_TILED", "1") != "0"
         self.tiled = {k: tiled_ok and k not in ("img", "stem", "logits") for k in sizes}
         rows = (P + L.TILE_M - 1) // L.TILE_M * L.TILE_M
         with torch.cuda.device(self.device):
@@ -303,24 +330,31 @@ class AssessorNet:
         _ffi.check(_ffi.lib().psob_pack_image_stem(img.data_ptr(), self.P, int(bool(rescale)), self.buf["img"].data_ptr(),
                                                    _ptr(self.rescaled) if keep_rescaled else None, _stream()), "psob_pack_image_stem")
 
-    def run_graph(self):
-        lib = _ffi.lib()
+    def launch_plan(self, img: Optional[torch.Tensor] = None, rescale=False):
+        """(name, launch) pairs of the forward pass: the input pack (when `img` is given) and every node of the graph."""
+        lib, plan = _ffi.lib(), []
+        if img is not None:
+            plan.append(("assessor_pack_rescale", lambda: self.pack(img, rescale)))
         for op, layer in zip(self.ops, self.layers):
             src = self.buf[op.src]
             dst = self.buf[op.dst] if op.dst else None
             if op.kind == "maxpool":
                 q = op.pool
-                _ffi.check(lib.psob_maxpool_nhwc(src.data_ptr(), src.stride(0), self.P, q["h"], q["w"], q["cp"], q["k"], q["stride"],
-                                                 q["pad"], dst.data_ptr(), dst.stride(0), int(self.tiled[op.dst]), _stream()),
-                           "psob_maxpool_nhwc")
+                plan.append(("a.maxpool", lambda s_=src, d_=dst, q=q, o=op: _ffi.check(lib.psob_maxpool_nhwc(
+                    s_.data_ptr(), s_.stride(0), self.P, q["h"], q["w"], q["cp"], q["k"], q["stride"], q["pad"], d_.data_ptr(),
+                    d_.stride(0), int(self.tiled[o.dst]), _stream()), "psob_maxpool_nhwc")))
                 continue
             pr = op.prog
             assert dst is None or dst.stride(0) == pr.out_pitch
             res = self.buf[op.res] if op.res else None
-            _ffi.check(lib.psob_layer_run_residual(layer.handle, src.data_ptr(), src.stride(0), self.P, _ptr(dst),
-                                                   _ptr(self.logits if op.dst32 else None), _ptr(res),
-                                                   res.stride(0) if res is not None else 0, self.impl, _stream()),
-                       f"psob_layer_run({pr.name})")
+            plan.append((pr.name, lambda l=layer, s_=src, d_=dst, o=op, r=res: _ffi.check(lib.psob_layer_run_residual(
+                l.handle, s_.data_ptr(), s_.stride(0), self.P, _ptr(d_), _ptr(self.logits if o.dst32 else None), _ptr(r),
+                r.stride(0) if r is not None else 0, self.impl, _stream()), f"psob_layer_run({o.prog.name})")))
+        return plan
+
+    def run_graph(self):
+        for _, launch in self.launch_plan():
+            launch()
         return self.logits
 
     def forward(self, img: torch.Tensor, rescale=False) -> torch.Tensor:
@@ -428,6 +462,12 @@ def gbest_apply(recs, n_rec, D, gbest_val, gbest_pos, hist=None, dyn=None, inert
 # fitness stages
 # ----------------------------------------------------------------------------------------------
 
+def _mode_fields(mode: str, thr: float, eps: float) -> dict:
+    if mode not in ("optimize_in_training", "optimize_out_training"):
+        raise ValueError(mode)
+    return dict(mode=_ffi.MODE_IN_TRAINING if mode == "optimize_in_training" else _ffi.MODE_OUT_TRAINING, thr=float(thr), eps=float(eps))
+
+
 class DScoreFitness:
     """EXTENSION discriminator-score fitness: p = D(G(z)) on the raw image, then the
     clamp/affine of src/pso/util_discovery.py:75-80."""
@@ -437,10 +477,23 @@ class DScoreFitness:
             raise ValueError(mode)
         self.disc, self.mode, self.thr, self.eps = disc, mode, thr, eps
         self.needs_padded_image = True
+        self.needs_image_f32 = False
 
     def __call__(self, gen: GeneratorNet, fit: torch.Tensor):
         _, score = self.disc.forward(gen.image_padded_bf16())
         score_fitness(score, fit, self.mode, self.thr, self.eps)
+
+    def fused_plan(self, gen: GeneratorNet, z: torch.Tensor, write_f32: bool, recon=None):
+        """-> ((name, launch) pairs of the networks only, fields telling psob_fitness_tail where the score comes from)."""
+        plan = gen.launch_plan(z, write_f32=write_f32, recon=recon) + self.disc.launch_plan(gen.image_padded_bf16(), finish=False)
+        d = _mode_fields(self.mode, self.thr, self.eps)
+        hd = self.disc.head
+        if hd:
+            d.update(part=hd["part"].data_ptr(), n_slots=hd["slots"], bias=hd["bias"], act=hd["act"])
+        else:
+            score = self.disc.acts32[-1]
+            d.update(score=score.data_ptr(), score_stride=score.stride(0) if score.dim() > 1 else 1)
+        return plan, d
 
 
 class ReconFitness:
@@ -451,14 +504,35 @@ class ReconFitness:
         self.target = target.reshape(target.shape[0], -1).contiguous()
         self.w_rec, self.eps, self.assessor, self.w_ass = w_rec, eps, assessor, w_ass
         self.fit_ass = None
+        self.part = None
         if assessor is not None:
             self.fit_ass = torch.empty(target.shape[0], dtype=torch.float32, device=target.device)
 
+    @property
+    def needs_image_f32(self) -> bool:
+        return self.assessor is not None and getattr(self.assessor, "needs_image_f32", True)
+
     def __call__(self, gen: GeneratorNet, fit: torch.Tensor):
+        """Unfused form: reads the materialised fp32 image (tests, A/B measurements, single-particle API)."""
         if self.assessor is not None:
             self.assessor(gen, self.fit_ass)
         recon_fitness(gen.image(), self.target, fit, self.fit_ass, self.w_ass if self.assessor is not None else 0.0,
                       self.w_rec, self.eps)
+
+    def fused_plan(self, gen: GeneratorNet, z: torch.Tensor, write_f32: bool, recon=None):
+        """The squared error is accumulated in the generator's last-layer epilogue (never reads the image back);
+        psob_fitness_tail adds the slots, divides by the pixel count and forms w_ass * fitness + w_rec * mse + eps."""
+        assert recon is None
+        if self.part is None:
+            self.part = torch.zeros(gen.recon_slots(), gen.P, dtype=torch.float32, device=self.target.device)
+        rc = (self.target, self.part)
+        if self.assessor is not None:
+            plan, d = self.assessor.fused_plan(gen, z, write_f32 or self.needs_image_f32, recon=rc)
+        else:
+            plan, d = gen.launch_plan(z, write_f32=write_f32, recon=rc), {}
+        d.update(recon_part=self.part.data_ptr(), n_recon_slots=self.part.shape[0], n_pix=self.target.shape[1],
+                 w_ass=float(self.w_ass) if self.assessor is not None else 0.0, w_rec=float(self.w_rec), eps_rec=float(self.eps))
+        return plan, d
 
 
 class AssessorFitness:
@@ -487,6 +561,26 @@ class AssessorFitness:
         softmax_select(logits, idx, self.prob)
         score_fitness(self.prob, fit, self.mode, self.thr, self.eps)
 
+    needs_image_f32 = True
+
+    def fused_plan(self, gen: GeneratorNet, z: torch.Tensor, write_f32: bool, recon=None):
+        img = gen.image()
+        if self.rescaled is None:
+            self.rescaled = torch.empty_like(img)
+            with torch.no_grad():                  # static logits buffer: its address goes into the tail's arguments
+                probe = self.model_cnn(self.rescaled[:1].view(-1, *self.image_shape))
+            self._logits = torch.zeros(img.shape[0], probe.shape[1], dtype=torch.float32, device=img.device)
+
+        def run_cnn():
+            with torch.no_grad():
+                self._logits.copy_(self.model_cnn(self.rescaled.view(-1, *self.image_shape)))
+        plan = gen.launch_plan(z, write_f32=True, recon=recon) + [("rescale_minmax", lambda: rescale_minmax(img, self.rescaled)),
+                                                                  ("model_cnn (torch)", run_cnn)]
+        n_class = self._logits.shape[1]
+        d = _mode_fields(self.mode, self.thr, self.eps)
+        d.update(logits=self._logits.data_ptr(), n_class=n_class, class_idx=self.class_index if n_class > 2 else 1)
+        return plan, d
+
 
 class ResnetFitness:
     """`Discovery.fitness` (src/pso/util_discovery.py:52-82) with the reference's ResNet assessor running on the
@@ -505,6 +599,14 @@ class ResnetFitness:
         softmax_select(logits, idx, self.prob)
         score_fitness(self.prob, fit, self.mode, self.thr, self.eps)
 
+    needs_image_f32 = True
+
+    def fused_plan(self, gen: GeneratorNet, z: torch.Tensor, write_f32: bool, recon=None):
+        plan = gen.launch_plan(z, write_f32=True, recon=recon) + self.net.launch_plan(gen.image(), rescale=True)
+        d = _mode_fields(self.mode, self.thr, self.eps)
+        d.update(logits=self.net.logits.data_ptr(), n_class=self.net.n_class, class_idx=self.class_index if self.net.n_class > 2 else 1)
+        return plan, d
+
 
 # ----------------------------------------------------------------------------------------------
 # the swarm
@@ -517,21 +619,24 @@ class SwarmEngine:
 
     def __init__(self, P: int, D: int, *, generator: Optional[GeneratorNet] = None, fitness=None, objective=None,
                  w_inertia=0.5, w_cogn=0.8, w_soci=0.9, v_max=math.inf, lo=-math.inf, hi=math.inf, seed=42,
-                 index_offset=0, max_iterations=1024, group=None, device=None, need_image_f32=True):
+                 index_offset=0, max_iterations=1024, group=None, device=None, need_image_f32=True, distributed=True):
         require_cuda()
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.P, self.D_logical = P, D
         D = (D + 3) // 4 * 4          # rows are float4-aligned; padding dimensions stay exactly 0 forever
         self.D = D
         self.gen, self.fitness, self.objective = generator, fitness, objective
-        if generator is not None:
-            generator.skip_f32 = (not need_image_f32) and isinstance(fitness, DScoreFitness)
+        # whether the generator's last layer stores its fp32 image: a per-call argument of Network.forward (the net may be
+        # shared with Generator.forward / Discovery.*_batch), decided by who consumes the image
+        self.write_f32 = bool(need_image_f32) or bool(getattr(fitness, "needs_image_f32", True))
+        self.fused_tail = True                   # psob_fitness_tail + psob_gbest_local instead of the 5-launch chain
         self.w0, self.c_cogn, self.c_soci = float(w_inertia), float(w_cogn), float(w_soci)
         self.v_max, self.lo, self.hi = v_max, lo, hi
         self.seed, self.index_offset = int(seed), int(index_offset)
         self.group = group
         self.world = 1
-        if group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
+        # distributed=False: a single-rank swarm inside a multi-rank job (e.g. bench.py's unsharded parity run on rank 0)
+        if distributed and (group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized())):
             self.world = torch.distributed.get_world_size(group)
         dev = self.device
         f32 = dict(dtype=torch.float32, device=dev)
@@ -541,12 +646,15 @@ class SwarmEngine:
         self.pbest_val = torch.full((P,), math.inf, **f32)
         self.fit = torch.zeros(P, **f32)
         self.improved = torch.zeros(P, dtype=torch.uint8, device=dev)
-        self.key = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.key = torch.full((1,), -1, dtype=torch.int64, device=dev)      # armed (all ones) for psob_fitness_tail
         self.rec = torch.zeros(4 + D, **f32)
         self.recs = torch.zeros(self.world, 4 + D, **f32) if self.world > 1 else self.rec.view(1, -1)
         self.gbest_val = torch.full((1,), math.inf, **f32)
         self.gbest_pos = torch.zeros(D, **f32)
+        self.max_iterations = int(max_iterations)
         self.hist = torch.zeros(max_iterations + 1, 2, **f32)
+        self._pbest_pending = False               # improved[] not yet folded into pbest_pos by a move
+        self._plan = None
         self.dyn = torch.zeros(2, dtype=torch.int32, device=dev)     # psob_iter_state {iteration, w}
         self.z = None
         if generator is not None:
@@ -584,6 +692,8 @@ class SwarmEngine:
         self.gbest_val.fill_(math.inf)
         self.gbest_pos.zero_()
         self.improved.zero_()
+        self.key.fill_(-1)
+        self._pbest_pending = False
         self.hist.zero_()
         self.reset_iteration()
         if self.z is not None:
@@ -596,27 +706,94 @@ class SwarmEngine:
 
     # -- one iteration -------------------------------------------------------------------------
     def evaluate(self):
+        """Networks + fitness into self.fit (the unfused chain: separate finish / score / recon kernels)."""
         if self.gen is not None:
-            self.gen.forward(self.z)
+            self.gen.forward(self.z, write_f32=self.write_f32)
             self.fitness(self.gen, self.fit)
         else:
             self.objective(self.pos, self.fit)
 
-    def personal_and_global_best(self):
-        pbest_minloc(self.fit, self.pbest_val, self.improved, self.key, self.index_offset)
-        gbest_candidate(self.key, self.pos, self.pbest_pos, self.improved, self.pbest_val, self.rec, self.index_offset)
+    def flush_pbest(self):
+        """Fold a pending improved[] into pbest_pos.  The copy normally rides on the next psob_update; this is for callers that
+        look at pbest_pos, or evaluate again, between the personal best and the move (never on the graph-captured path)."""
+        if self._pbest_pending:
+            m = self.improved.bool()
+            self.pbest_pos[m] = self.pos[m]
+            self.improved.zero_()
+            self._pbest_pending = False
+
+    def set_inertia(self, w: float):
+        """Overwrite the device-resident inertia weight (Swarm.update_inertia / `swarm.w_inertia = ...`)."""
+        it, _ = self.iteration_state()
+        st = np.zeros(1, dtype=[("i", np.uint32), ("w", np.float32)])
+        st["i"], st["w"] = it, w
+        self.dyn.copy_(torch.from_numpy(st.view(np.int32).copy()).to(self.device))
+
+    def _global_best(self):
+        lib = _ffi.lib()
+        hist_rows = self.hist.shape[0]
         if self.world > 1:
+            _ffi.check(lib.psob_gbest_record(self.key.data_ptr(), self.pos.data_ptr(), self.pbest_pos.data_ptr(),
+                                             self.improved.data_ptr(), self.pbest_val.data_ptr(), self.P, self.index_offset,
+                                             self.D, self.rec.data_ptr(), _stream()), "psob_gbest_record")
             torch.distributed.all_gather_into_tensor(self.recs.view(-1), self.rec, group=self.group)
-        gbest_apply(self.recs, self.world, self.D, self.gbest_val, self.gbest_pos, self.hist, self.dyn, self.inertia_decay)
+            gbest_apply(self.recs, self.world, self.D, self.gbest_val, self.gbest_pos, self.hist, self.dyn, self.inertia_decay)
+        else:
+            _ffi.check(lib.psob_gbest_local(self.key.data_ptr(), self.pos.data_ptr(), self.pbest_pos.data_ptr(),
+                                            self.improved.data_ptr(), self.pbest_val.data_ptr(), self.P, self.index_offset, self.D,
+                                            self.gbest_val.data_ptr(), self.gbest_pos.data_ptr(), self.hist.data_ptr(), hist_rows,
+                                            self.dyn.data_ptr(), self.inertia_decay, _stream()), "psob_gbest_local")
+
+    def personal_and_global_best(self):
+        """Personal best + global best from self.fit (unfused: psob_pbest_minloc, then the record / apply kernels)."""
+        self.flush_pbest()
+        pbest_minloc(self.fit, self.pbest_val, self.improved, self.key, self.index_offset)
+        self._pbest_pending = True
+        self._global_best()
+
+    def launch_plan(self):
+        """The product iteration as (name, launch) pairs, in order: the networks, ONE psob_fitness_tail launch (head finish |
+        softmax pick | score -> clamp / affine -> reconstruction term -> personal best -> min-loc key), the global best
+        (psob_gbest_local; with ranks: record, all-gather, apply) and the move.  step() runs exactly this list, bench.py times
+        its entries one by one.  Built once per engine (all buffers are static)."""
+        if self._plan is not None:
+            return self._plan
+        lib = _ffi.lib()
+        if self.gen is not None:
+            plan, fields = self.fitness.fused_plan(self.gen, self.z, self.write_f32)
+            plan = list(plan)
+        else:
+            plan, fields = [("objective", lambda: self.objective(self.pos, self.fit))], dict(fit_in=self.fit.data_ptr())
+        args = _ffi.FitnessTailArgs(fit=None if "fit_in" in fields else self.fit.data_ptr(), pbest_val=self.pbest_val.data_ptr(),
+                                    improved=self.improved.data_ptr(), P=self.P, index_offset=self.index_offset,
+                                    key=self.key.data_ptr(), **fields)
+
+        def tail():
+            _ffi.check(lib.psob_fitness_tail(C.byref(args), _stream()), "psob_fitness_tail")
+            self._pbest_pending = True
+        plan += [("fitness_tail", tail), ("gbest", self._global_best), ("pso_update", self.move)]
+        self._plan = plan
+        return plan
+
+    def evaluate_and_best(self):
+        """The product iteration up to (not including) the move."""
+        self.flush_pbest()
+        for _, launch in self.launch_plan()[:-1]:
+            launch()
 
     def move(self):
         pso_update(self.pos, self.vel, self.pbest_pos, self.gbest_pos, improved=self.improved, r1=self.r1, r2=self.r2,
                    z=self.z, dyn=self.dyn, c_cogn=self.c_cogn, c_soci=self.c_soci, v_max=self.v_max, lo=self.lo, hi=self.hi,
                    seed=self.seed, index_offset=self.index_offset)
+        self._pbest_pending = False
 
     def step(self):
-        self.evaluate()
-        self.personal_and_global_best()
+        fused = self.fused_tail and (self.gen is None or hasattr(self.fitness, "fused_plan"))
+        if fused:
+            self.evaluate_and_best()
+        else:
+            self.evaluate()
+            self.personal_and_global_best()
         self.move()
 
     # -- graph ---------------------------------------------------------------------------------
@@ -624,7 +801,7 @@ class SwarmEngine:
         """Capture one iteration in a CUDA graph (launch-bound at small P)."""
         it, w = self.iteration_state()
         snap = [t.clone() for t in (self.pos, self.vel, self.pbest_pos, self.pbest_val, self.gbest_val, self.gbest_pos,
-                                     self.hist, self.dyn, self.improved)] + ([self.z.clone()] if self.z is not None else [])
+                                     self.hist, self.dyn, self.improved, self.key)] + ([self.z.clone()] if self.z is not None else [])
         s = torch.cuda.Stream(device=self.device)
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
@@ -636,12 +813,16 @@ class SwarmEngine:
         self._graph = g
         torch.cuda.synchronize(self.device)
         targets = [self.pos, self.vel, self.pbest_pos, self.pbest_val, self.gbest_val, self.gbest_pos, self.hist, self.dyn,
-                   self.improved] + ([self.z] if self.z is not None else [])
+                   self.improved, self.key] + ([self.z] if self.z is not None else [])
         for t, v in zip(targets, snap):
             t.copy_(v)
         return g
 
     def run(self, n_iterations: int, use_graph=True):
+        it, _ = self.iteration_state()
+        if it + n_iterations > self.hist.shape[0]:
+            raise _ffi.PsobError(f"SwarmEngine.run: {it} + {n_iterations} iterations exceed the history recorder "
+                                 f"({self.hist.shape[0]} rows = max_iterations + 1); construct the engine with a larger max_iterations")
         if use_graph and self._graph is None and self.r1 is None:
             self.capture()
         for _ in range(n_iterations):
@@ -653,5 +834,5 @@ class SwarmEngine:
     def history(self):
         """(g_best_val_dummy, replaced flags) for the iterations run so far."""
         it, _ = self.iteration_state()
-        h = self.hist[:it].cpu().numpy()
+        h = self.hist[:min(it, self.hist.shape[0])].cpu().numpy()
         return h[:, 0].copy(), h[:, 1] > 0.5

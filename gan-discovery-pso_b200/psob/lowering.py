@@ -26,6 +26,8 @@ from typing import List, Optional, Tuple
 
 import numpy as np
 
+from ._knobs import knob
+
 KCHUNK = 64           # K elements per step: 64 bf16 = one 128 B swizzle row
 TILE_M = 128          # particles per tile (UMMA M)
 MAX_N = 256           # UMMA N limit / TMEM columns per accumulator buffer
@@ -33,19 +35,19 @@ MAX_N = 256           # UMMA N limit / TMEM columns per accumulator buffer
 ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3, 4
 STEP_ACCUM, STEP_B_RESIDENT, STEP_NEXT, STEP_EYE = 1, 2, 4, 8     # NEXT: the op accumulates into the next job of the chain
 ROUND_WEIGHTS = True   # tests switch this off to check the geometry exactly in fp32
-BIAS_IN_K_IMAGE = os.environ.get("PSOB_BIAS_IN_K_IMAGE", "1") != "0"   # ... and of the first discriminator / encoder conv (constant K-chunk)
-BIAS_IN_K = os.environ.get("PSOB_BIAS_IN_K", "1") != "0"      # first generator layer: bias folded into the K padding of the latent row
+BIAS_IN_K_IMAGE = knob("PSOB_BIAS_IN_K_IMAGE", "1") != "0"   # ... and of the first discriminator / encoder conv (constant K-chunk)
+BIAS_IN_K = knob("PSOB_BIAS_IN_K", "1") != "0"      # first generator layer: bias folded into the K padding of the latent row
 # Weight packs up to RESIDENT_SOLO bytes stay in one CTA's shared memory for its lifetime; packs up to
 # RESIDENT_PAIR are split over a CTA pair (tcgen05 cta_group::2, csrc/pixel_gemm.cu) when the layer has the
 # TMA-store epilogue (64-channel NHWC chunks).  PSOB_PAIR=0 falls back to streaming the weights per step.
 RESIDENT_SOLO = 32 * 1024
-RESIDENT_PAIR = 256 * 1024 if os.environ.get("PSOB_PAIR", "1") != "0" else 0
-IMAGE_BAND = os.environ.get("PSOB_BAND", "1") != "0"       # band form of the 14x14 -> 28x28 image layer
-CHAIN_ROWS = os.environ.get("PSOB_CHAIN", "1") != "0"      # share input rows between vertically adjacent jobs (resident layers)
-CONV2D_RESIDENT = os.environ.get("PSOB_CONV2D_RESIDENT", "1") != "0"   # small general-conv weight packs resident + shared A tiles
+RESIDENT_PAIR = 256 * 1024 if knob("PSOB_PAIR", "1") != "0" else 0
+IMAGE_BAND = knob("PSOB_BAND", "1") != "0"       # band form of the 14x14 -> 28x28 image layer
+CHAIN_ROWS = knob("PSOB_CHAIN", "1") != "0"      # share input rows between vertically adjacent jobs (resident layers)
+CONV2D_RESIDENT = knob("PSOB_CONV2D_RESIDENT", "1") != "0"   # small general-conv weight packs resident + shared A tiles
 CONV2D_RESIDENT_MAX = 80 * 1024
-EYE_OPS = os.environ.get("PSOB_EYE", "1") != "0"           # identity shortcuts as N = 64 ops on the built-in identity tile
-CHAIN_CONVT = os.environ.get("PSOB_CHAIN_CONVT", "0") != "0"   # ... also for the transposed convs (measured slower, see below)
+EYE_OPS = knob("PSOB_EYE", "1") != "0"           # identity shortcuts as N = 64 ops on the built-in identity tile
+CHAIN_CONVT = knob("PSOB_CHAIN_CONVT", "0") != "0"   # ... also for the transposed convs (measured slower, see below)
 
 # image layouts
 IMG_PAD_ROWS, IMG_PAD_PITCH = 31, 32          # bf16 padded 28x28 image: real (y,x) at (y+1,x+1)
@@ -903,7 +905,7 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
 #     from (2 oy, 8 g)); the weight tiles are position-independent.
 # ----------------------------------------------------------------------------------------------
 STEM_PAD = 3
-STEM_RESIDENT = os.environ.get("PSOB_STEM_RESIDENT", "0") != "0"     # 160 KB of stem weights resident over a CTA pair: measured no faster (MMA-bound on the zero-padded window)
+STEM_RESIDENT = knob("PSOB_STEM_RESIDENT", "0") != "0"     # 160 KB of stem weights resident over a CTA pair: measured no faster (MMA-bound on the zero-padded window)
 STEM_PITCH = 40
 STEM_ROWS = 36
 

@@ -16,6 +16,7 @@ import os
 import numpy as np
 
 from . import lowering as L
+from ._knobs import knob
 
 BN_EPS = 1e-5
 
@@ -154,7 +155,7 @@ class AssessorOp:
         self.src_off, self.dst_off = src_off, dst_off
 
 
-SHORTCUT_MODE = os.environ.get("PSOB_SHORTCUT", "mma")     # "mma": skip connection as MMA steps; "epilogue": residual add in the epilogue
+SHORTCUT_MODE = knob("PSOB_SHORTCUT", "mma")     # "mma": skip connection as MMA steps; "epilogue": residual add in the epilogue
 
 
 def _assessor_geometry(sd):

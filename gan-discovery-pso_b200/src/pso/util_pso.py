@@ -51,6 +51,7 @@ class Particle:
         if name == "vel":
             return owner.engine.vel[i, :owner.dim_space].double().cpu().numpy()
         if name == "p_best_pos":
+            owner.engine.flush_pbest()        # the improved position is copied by the next move; fold it in before looking
             return owner.engine.pbest_pos[i, :owner.dim_space].double().cpu().numpy()
         if name == "p_best_val":
             return owner.engine.pbest_val[i:i + 1].cpu().numpy()
@@ -78,12 +79,36 @@ class Particle:
         self.history_vel.append(self.vel)
 
 
+class _ParticleViews:
+    """`Swarm.swarm`: a read-only sequence of `Particle` views onto the engine's SoA state, created on access (a list of
+    a million Python objects would cost more than the swarm's first iterations)."""
+
+    def __init__(self, owner, n):
+        self._owner, self._n, self._imgs = owner, n, {}
+
+    def __len__(self):
+        return self._n
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(self._n))]
+        if i < 0:
+            i += self._n
+        if not 0 <= i < self._n:
+            raise IndexError(i)
+        return Particle(self._owner.dim_space, img=self._imgs.get(i), _owner=self._owner, _index=i)
+
+    def __iter__(self):
+        return (self[i] for i in range(self._n))
+
+
 class Swarm:
     def __init__(self, plot_training_dir, discovery, num_particles, n_iterations, dim_space, device, tolerance=0.0001,
                  w_inertia=0.5, w_cogn=0.8, w_soci=0.9, *, seed=42, record_history=None, v_max=math.inf,
                  bounds=(-math.inf, math.inf), log_images_every=0, compute_diversity=None, group=None, index_offset=0,
                  use_graph=True):
         self.plot_training_dir = plot_training_dir
+        self.engine = None
         self.w_inertia = w_inertia
         self.w_cogn = w_cogn
         self.w_soci = w_soci
@@ -98,17 +123,54 @@ class Swarm:
         self.group, self.index_offset, self.use_graph = group, index_offset, use_graph
         hist_bytes = 2 * (n_iterations + 1) * num_particles * dim_space * 4
         self.record_history = (hist_bytes <= (1 << 30)) if record_history is None else record_history
-        self.compute_diversity = (num_particles <= 16384) if compute_diversity is None else compute_diversity
+        # Swarm.mse is O(P^2 D): exact up to DIVERSITY_EXACT_MAX particles, above that the same statistic on an evenly strided
+        # sample of that many particles (an estimate of the mean pairwise distance; history['mean_mse'] is never left empty)
+        self.compute_diversity = True if compute_diversity is None else compute_diversity
 
         self.g_best_pos = np.empty(self.dim_space)
         self.g_best_val = [np.inf]
         self.g_best_val_dummy = []
         self.swarm = []
-        self.engine = None
         self._hist = None
         self._hist_len = 0
         self._targets = None
         self._inertia_decay = 1.0
+
+    DIVERSITY_EXACT_MAX = 16384
+
+    # -- coefficients: assignments reach the engine (the move kernel reads w from device state) ----------------
+    @property
+    def w_inertia(self):
+        return self._w_inertia
+
+    @w_inertia.setter
+    def w_inertia(self, w):
+        self._w_inertia = w
+        if self.engine is not None:
+            self.engine.w0 = float(w)
+            self.engine.set_inertia(float(w))
+
+    @property
+    def w_cogn(self):
+        return self._w_cogn
+
+    @w_cogn.setter
+    def w_cogn(self, c):
+        self._w_cogn = c
+        if self.engine is not None and self.engine.c_cogn != float(c):
+            self.engine.c_cogn = float(c)
+            self.engine._graph = None              # launch arguments are baked into a captured iteration
+
+    @property
+    def w_soci(self):
+        return self._w_soci
+
+    @w_soci.setter
+    def w_soci(self, c):
+        self._w_soci = c
+        if self.engine is not None and self.engine.c_soci != float(c):
+            self.engine.c_soci = float(c)
+            self.engine._graph = None
 
     # -- engine construction -------------------------------------------------------------------
     def _build_engine(self, targets=None):
@@ -124,7 +186,7 @@ class Swarm:
                                               max_iterations=max(self.n_iterations, 1), group=self.group, device=self.device,
                                               need_image_f32=bool(self.log_images_every))
         self.engine.inertia_decay = self._inertia_decay
-        self.swarm = [Particle(D, _owner=self, _index=i) for i in range(P)]
+        self.swarm = _ParticleViews(self, P)
         if self.record_history:
             self._hist = torch.empty(self.n_iterations + 1, 2, P, D, dtype=torch.float32, device=self.device)
             self._hist_len = 0
@@ -142,16 +204,30 @@ class Swarm:
 
     # -- reference methods ---------------------------------------------------------------------
     def update_inertia(self):
-        self.w_inertia = 0.99 * self.w_inertia
+        self.w_inertia = 0.99 * self.w_inertia          # the setter writes the new weight into the engine's device state
         print(f"Update Inertia: {self.w_inertia}")
 
     def mse(self):
-        """Mean Euclidean distance over all unordered particle pairs (src/pso/util_pso.py:76-86)."""
-        return _engine.mean_pairwise_distance(self.engine.pos[:, :self.dim_space])
+        """Mean Euclidean distance over all unordered particle pairs (src/pso/util_pso.py:76-86); above DIVERSITY_EXACT_MAX
+        particles, over the pairs of an evenly strided sample of that size."""
+        pos = self.engine.pos[:, :self.dim_space]
+        if pos.shape[0] > self.DIVERSITY_EXACT_MAX:
+            idx = torch.linspace(0, pos.shape[0] - 1, self.DIVERSITY_EXACT_MAX, device=pos.device).long()
+            pos = pos.index_select(0, idx).contiguous()
+        return _engine.mean_pairwise_distance(pos)
+
+    def _reset_best(self):
+        """A fresh run on the same object (second optimize()): the host-side mirrors restart with the engine's state."""
+        self.g_best_pos = np.empty(self.dim_space)
+        self.g_best_val = [np.inf]
+        self.g_best_val_dummy = []
+        self._hist_len = 0
 
     def init_particles(self, generator: torch.Generator = None, pos=None, vel=None):
         if self.engine is None:
             self._build_engine()
+        self._reset_best()
+        self.engine.w0 = float(self._w_inertia)
         self.engine.init_particles(pos=pos, vel=vel, generator=generator)
         self._record()
         return self.engine.pos[:, :self.dim_space].double().cpu().numpy()
@@ -173,8 +249,8 @@ class Swarm:
             latent = encoder(targets.float()).reshape(len(imgs), -1)
         self._targets = targets
         self._build_engine(targets=targets.reshape(len(imgs), -1))
-        for p, im in zip(self.swarm, imgs):
-            p.img = im
+        self.swarm._imgs = dict(enumerate(imgs))
+        self._reset_best()
         self.engine.init_particles(pos=latent)
         self._record()
         return self.engine.pos[:, :self.dim_space].double().cpu().numpy()
@@ -195,7 +271,7 @@ class Swarm:
         e = self.engine
         it, w = e.iteration_state()
         vals, replaced = e.history()
-        for k in range(len(self.g_best_val_dummy), it):
+        for k in range(len(self.g_best_val_dummy), min(it, len(vals))):
             v = np.asarray([vals[k]], dtype=np.float32)
             if replaced[k]:
                 if len(self.g_best_val) == 1 and np.all(np.isinf(self.g_best_val[-1])):
@@ -205,7 +281,7 @@ class Swarm:
             self.g_best_val_dummy.append(v)
         self.g_best_pos = e.gbest_pos[:self.dim_space].double().cpu().numpy()
         if self._inertia_decay != 1.0:
-            self.w_inertia = w
+            self._w_inertia = w                    # mirror of the device-side schedule (no write-back)
 
     def move_particles(self):
         self.engine.move()

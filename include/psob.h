@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define PSOB_VERSION 100
+#define PSOB_VERSION 200
 
 #define PSOB_E_ARG        (-1)   /* bad argument (null pointer, misaligned, size) */
 #define PSOB_E_UNSUPPORTED (-2)  /* shape outside what the kernels implement */
@@ -120,6 +120,46 @@ int psob_gbest_candidate(const uint64_t* key, const float* pos, const float* pbe
 int psob_gbest_apply(const float* recs, int32_t n_rec, int32_t D, float* gbest_val,
                      float* gbest_pos, float* hist, int32_t hist_rows, psob_iter_state* dyn,
                      float inertia_decay, psob_stream_t s);
+
+/* Candidate record like psob_gbest_candidate, and *key is re-armed (reset to all ones) for the next iteration's
+ * psob_fitness_tail -- the multi-rank iteration needs no memset node. */
+int psob_gbest_record(uint64_t* key, const float* pos, const float* pbest_pos, const uint8_t* improved,
+                      const float* pbest_val, int64_t P, uint64_t index_offset, int32_t D, float* rec, psob_stream_t s);
+
+/* Single-rank global best: psob_gbest_candidate + psob_gbest_apply (Swarm.update_global_best, src/pso/util_pso.py:135-151,
+ * and the inertia schedule :72-74,178-179) in one launch; *key is consumed and re-armed. */
+int psob_gbest_local(uint64_t* key, const float* pos, const float* pbest_pos, const uint8_t* improved, const float* pbest_val,
+                     int64_t P, uint64_t index_offset, int32_t D, float* gbest_val, float* gbest_pos, float* hist,
+                     int32_t hist_rows, psob_iter_state* dyn, float inertia_decay, psob_stream_t s);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused fitness tail — replaces, in ONE launch, the arithmetic of Discovery.fitness after the assessor network
+ * (softmax pick, clamp / affine: src/pso/util_discovery.py:70-80), the inverter loss's weighted sum (:97-101) and the
+ * strict-< personal-best compare of Swarm.update_personal_best (src/pso/util_pso.py:122-124) with the local min-loc of
+ * Swarm.update_global_best (:139-143).  Exactly one score source:
+ *   part   fp32 [n_slots][P]   partial sums of a fused single-channel head (psob_layer_run_dot): score = act(sum + bias)
+ *   logits fp32 [P, n_class]   score = softmax(dim 1)[class_idx]
+ *   score  fp32 [P * stride]   a ready probability
+ *   fit_in fp32 [P]            a ready fitness value (generic objectives; no clamp / affine)
+ * (none of them with recon_part: pure reconstruction loss, w_ass ignored).  Then
+ *   fit = mode(min(score + thr, 1)) + eps                                                       (as psob_score_fitness)
+ *   fit = w_ass * fit + w_rec * (sum over slots of recon_part[slot][p]) / n_pix + eps_rec       (when recon_part != NULL)
+ *   improved[p] = fit < pbest_val[p]; pbest_val[p] = min; atomicMin(*key, order_key(pbest_val) << 32 | index_offset + p)
+ * fit (optional) receives the fitness.  *key must be all ones on entry (psob_gbest_local / psob_gbest_record re-arm it).
+ * Bit-identical to the chain psob_dot_finish -> psob_score_fitness -> psob_pbest_minloc.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct {
+  const float* part;   int32_t n_slots; float bias; int32_t act;
+  const float* score;  int32_t score_stride;
+  const float* logits; int32_t n_class, class_idx;
+  const float* fit_in;
+  int32_t mode; float thr, eps;
+  const float* recon_part; int32_t n_recon_slots, n_pix; float w_ass, w_rec, eps_rec;
+  float* fit; float* pbest_val; uint8_t* improved;
+  int64_t P; uint64_t index_offset; uint64_t* key;
+} psob_fitness_tail_args;
+
+int psob_fitness_tail(const psob_fitness_tail_args* a, psob_stream_t s);
 
 /* ------------------------------------------------------------------------------------------
  * Fitness transforms — replace Discovery.fitness / fitness_pso_inverter arithmetic
@@ -233,6 +273,17 @@ int psob_layer_dot_slots(const psob_layer* l);
 int psob_layer_run_dot(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, const void* dot_w, float* part,
                        psob_stream_t s);
 int psob_dot_finish(const float* part, int32_t n_slots, int64_t P, float bias, int32_t act, float* out, psob_stream_t s);
+
+/* Reconstruction loss in the image layer's epilogue — replaces `torch.mean((img - img_rec) ** 2)` of
+ * Discovery.fitness_pso_inverter (src/pso/util_discovery.py:97) without materialising the fp32 image: every epilogue thread
+ * owns one particle row of the generator's last layer and accumulates (target - tanh(acc))^2 from the fp32 pixel it holds in a
+ * register.  target: device fp32 or bf16 [P, n_pix] laid out like the fp32 image (n_pix == out32_pitch); part: device fp32
+ * [psob_layer_recon_slots(l)][P], every slot rewritten by every run, summed in slot order by psob_fitness_tail.  y / y32 as in
+ * psob_layer_run (y32 may be NULL: the image is then never written; an image-band layer still needs y).  Only image layers
+ * (image band or direct fp32 epilogue). */
+int psob_layer_recon_slots(const psob_layer* l);
+int psob_layer_run_recon(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, void* y, float* y32, const void* target,
+                         int32_t target_is_bf16, int32_t n_pix, float* part, psob_stream_t s);
 
 /* Debug: when `counters` (device, u64 [n_SMs][32]) is non-NULL, later runs of the layer record per CTA
  * { producer wait-empty, producer total, mma wait-full, mma wait-tmem-empty, mma total,

@@ -410,8 +410,10 @@ def gbest_scan(pbest_val, incumbent_val):
 
 def f32_order_key(x) -> np.ndarray:
     """Order-preserving float32 -> uint32 map (sign-flip trick) used by the packed
-    (value,index) min-loc key; NaN sorts above +inf.  """
-    b = np.asarray(x, dtype=np.float32).view(np.uint32)
+    (value,index) min-loc key; NaN sorts above +inf; -0.0 and +0.0 map to the same key, like the
+    reference's `<` treats them (src/pso/util_pso.py:139-143).  """
+    b = np.asarray(x, dtype=np.float32).view(np.uint32).copy()
+    b[...] = np.where(b == np.uint32(0x80000000), np.uint32(0), b)
     neg = (b >> 31).astype(bool)
     return np.where(neg, ~b, b | np.uint32(0x80000000)).astype(np.uint32)
 
@@ -607,3 +609,44 @@ def make_recon_objective(model_gan, dim_space, eps=0.1, w_rec=1.0):
     def obj(p: PortParticle):
         return fitness_inverter(model_gan, p.pos, p.img, dim_space, eps=eps, w_ass=0.0, w_rec=w_rec)[0]
     return obj
+
+
+# --------------------------------------------------------------------------------------
+# Batched fp32 torch-CPU RESTATEMENT of one PSO iteration with the discriminator-score fitness
+# (BASELINE.md section 4 step 4).  The reference itself cannot run this workload (a Discriminator as
+# `model_cnn` raises IndexError at src/pso/util_discovery.py:74) and evaluates one particle at a
+# time; this is the like-for-like CPU figure for BASELINE configs 2 / 5: the SAME arithmetic as
+# `PortSwarm` with `make_dscore_objective`, vectorised over the swarm -- batched G + D forward
+# (`fitness_dscore` on chunks), vectorised strict-< personal best, lowest-index argmin, vectorised
+# move with the Philox draws of SURVEY.md section 8.  Always labelled "restatement", never "reference".
+# --------------------------------------------------------------------------------------
+
+class BatchedDScoreSwarm:
+    def __init__(self, model_gan, model_disc, num_particles, dim_space, w_inertia=0.5, w_cogn=0.8, w_soci=0.9,
+                 seed=42, chunk=4096, mode="optimize_out_training"):
+        self.gen, self.disc, self.P, self.D = model_gan.eval(), model_disc.eval(), num_particles, dim_space
+        self.w, self.c_cogn, self.c_soci, self.seed, self.chunk, self.mode = w_inertia, w_cogn, w_soci, seed, chunk, mode
+        rng = np.random.RandomState(seed)
+        self.pos = rng.randn(num_particles, dim_space).astype(np.float32)
+        self.vel = ((rng.randn(num_particles, dim_space) - 0.5) / 10).astype(np.float32)
+        self.pbest_pos = self.pos.copy()
+        self.pbest_val = np.full(num_particles, np.inf, np.float32)
+        self.gbest_val, self.gbest_pos = np.float32(np.inf), np.zeros(dim_space, np.float32)
+        self.iteration = 0
+
+    @torch.no_grad()
+    def step(self):
+        fit = np.empty(self.P, np.float32)
+        for a in range(0, self.P, self.chunk):
+            b = min(self.P, a + self.chunk)
+            fit[a:b] = fitness_dscore(self.gen, self.disc, torch.from_numpy(self.pos[a:b]), self.D, mode=self.mode)[0]
+        self.pbest_val, improved = pbest_update(fit, self.pbest_val)
+        self.pbest_pos[improved] = self.pos[improved]
+        j = int(np.argmin(self.pbest_val))                     # first occurrence == the reference's in-order scan
+        if self.pbest_val[j] < self.gbest_val:
+            self.gbest_val, self.gbest_pos = self.pbest_val[j], self.pbest_pos[j].copy()
+        self.iteration += 1
+        r1, r2 = philox_r1r2(self.seed, self.iteration, 0, self.P)
+        self.pos, self.vel = pso_move(self.pos, self.vel, self.pbest_pos, self.gbest_pos, r1, r2, self.w, self.c_cogn,
+                                      self.c_soci, dtype=np.float32)
+        return fit

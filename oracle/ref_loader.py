@@ -45,6 +45,10 @@ def load():
     saved = {k: v for k, v in sys.modules.items() if k == "src" or k.startswith("src.")}
     for k in saved:
         del sys.modules[k]
+    # the reference's `src` has no __init__.py (a namespace package): any REGULAR package called `src` further down sys.path --
+    # the product's drop-in mirror -- would win the import, so such entries are hidden while the reference loads
+    old_path = list(sys.path)
+    sys.path[:] = [q for q in old_path if not os.path.isfile(os.path.join(q or ".", "src", "__init__.py"))]
     sys.path.insert(0, REFERENCE_ROOT)
     try:
         import src.pso.util_pso as util_pso
@@ -61,7 +65,7 @@ def load():
         finally:
             sys.path.remove(os.path.join(REFERENCE_ROOT, "src"))
     finally:
-        sys.path.remove(REFERENCE_ROOT)
+        sys.path[:] = old_path
         ref_mods = {k: v for k, v in sys.modules.items() if k == "src" or k.startswith("src.")}
         for k in ref_mods:
             del sys.modules[k]

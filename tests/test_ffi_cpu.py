@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(l, s), f"{s} declared in include/psob.h but not exported"
     assert sorted(_ffi.EXPORTS) == syms
-    assert l.psob_version() == 100
+    assert l.psob_version() == 200
 
 
 def test_no_cpu_fallback():

@@ -182,6 +182,7 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
     disc = port.Discriminator(1, 64)
     z = torch.randn(P, 100, generator=torch.Generator().manual_seed(P))
     results = {}
+    monkeypatch.setenv("PSOB_TUNING", "1")          # the PSOB_* A/B knobs are ignored without it
     for tiled, pair, strided, chain in ((1, 1, 1, 1), (1, 1, 1, 0), (0, 1, 1, 1), (1, 0, 1, 1), (1, 1, 0, 1), (0, 0, 0, 0), (1, 1, 2, 1)):
         # strided == 2: the strided item order WITHOUT the chain rotation (scheduling only: same bits)
         if strided == 2:

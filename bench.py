@@ -392,6 +392,8 @@ def shard_parity(args, rank, world, dev):
             detail = f"state {same_state}, gbest history {same_hist}, {improved} of {iters} iterations improved the global best"
             if not (same_state and same_hist and improved >= 1):
                 ok.zero_()
+        if rank == 0:
+            whole.release_graph()
         dist.broadcast(ok, src=0)
         # every rank must also hold the same global best as rank 0
         gb = torch.cat([sh.gbest_pos, sh.gbest_val]).clone()
@@ -399,7 +401,9 @@ def shard_parity(args, rank, world, dev):
         dist.broadcast(gb0, src=0)
         agree = torch.tensor([1.0 if torch.equal(gb, gb0) else 0.0], device=dev)
         dist.all_reduce(agree, op=dist.ReduceOp.MIN)
-        return bool(ok.item() > 0 and agree.item() > 0), detail
+        result = bool(ok.item() > 0 and agree.item() > 0)
+        sh.release_graph()
+        return result, detail
     finally:
         args.workload = saved
 
@@ -657,8 +661,21 @@ def run_psob(args):
             line["shard_parity_detail"] = parity_detail
         emit(line)
     if world > 1:
+        # Teardown.  The JSON line is out; captured graphs that hold the NCCL all-gather are dropped before the process group
+        # (a live one made destroy_process_group wait forever on this stack: torch 2.11 / NCCL 2.28.9), and a watchdog ends the
+        # process should the teardown still stall -- a benchmark must never hang on exit.
+        code = 0 if parity else 3
+        wd = threading.Timer(30.0, lambda: os._exit(code))
+        wd.daemon = True
+        wd.start()
+        sw.release_graph()
+        del sw
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
         dist.barrier()
         dist.destroy_process_group()
+        wd.cancel()
         if not parity:
             sys.exit(3)
 
@@ -681,7 +698,7 @@ def time_dropin(P, dev):
     out = {}
     for tag, kw, opt in (("defaults_early_stopping_on", dict(tolerance=0.0), dict(early_stopping=True)),
                          ("device_loop_early_stopping_off", dict(compute_diversity=False, record_history=False), dict(early_stopping=False))):
-        n_it = 20
+        n_it = 100
         sw = util_pso.Swarm("/tmp/psob_bench", disc, num_particles=P, n_iterations=n_it, dim_space=D_LATENT, device=str(dev),
                             w_inertia=0.73, w_cogn=1.496, w_soci=1.496, **kw)
         with contextlib.redirect_stdout(io.StringIO()):

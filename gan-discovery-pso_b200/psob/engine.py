@@ -87,6 +87,7 @@ class Network:
         self.impl = impl
         self.programs = programs
         self._recon_slots = None
+        self.fill_ones = False        # the model nets (generator / discriminator / encoder) write the constant-1 bias columns themselves
         # Internal edges use the tile-major layout [ceil(P/128)][pitch/64][128][64] whenever the producer has the
         # TMA-store epilogue and the consumer reads whole 64-column chunks; the network's own input and its last
         # output stay row-major [P, pitch].  PSOB_TILED=0 keeps everything row-major (A/B measurements).
@@ -116,7 +117,7 @@ class Network:
         recon=(target [P, n_pix] fp32|bf16, part fp32 [recon_slots, P]): the last layer accumulates the per-particle
         sum((target - image)^2) in its epilogue (psob_layer_run_recon, src/pso/util_discovery.py:97)."""
         plan, cur = [], x
-        if self.programs[0].meta.get("ones_cols"):
+        if self.fill_ones and self.programs[0].meta.get("ones_cols"):
             plan.append((self.programs[0].name + ".ones", lambda: _fill_ones(self, x)))
         last = len(self.layers) - 1
         for i, (layer, y, y32) in enumerate(zip(self.layers, self.acts, self.acts32)):
@@ -203,6 +204,7 @@ class GeneratorNet(Network):
         else:
             progs = nets.generator_programs(sd, prefix, m_last=m_last)
         super().__init__(progs, P, device, impl)
+        self.fill_ones = True
         self.image_elems = progs[-1].out32_pitch
 
     def image(self) -> torch.Tensor:
@@ -217,6 +219,7 @@ class DiscriminatorNet(Network):
 
     def __init__(self, state_dict, P, prefix="disc", device=None, impl=_ffi.IMPL_TCGEN05, fused_head=None):
         super().__init__(nets.discriminator_programs(_sd_numpy(state_dict), prefix), P, device, impl)
+        self.fill_ones = True
         # Fused head (default on the product path): the hidden conv's epilogue reduces its own output against the
         # final Conv2d(features, 1, k = whole map) -- psob_layer_run_dot + psob_dot_finish -- so the hidden
         # activation is never written and the last layer is not launched.  PSOB_FUSED_HEAD=0 keeps the layer-by-layer
@@ -284,6 +287,7 @@ class EncoderNet(Network):
 
     def __init__(self, state_dict, P, prefix="enc", device=None, impl=_ffi.IMPL_TCGEN05):
         super().__init__(nets.encoder_programs(_sd_numpy(state_dict), prefix), P, device, impl)
+        self.fill_ones = True
 
 
 
@@ -817,6 +821,13 @@ class SwarmEngine:
         for t, v in zip(targets, snap):
             t.copy_(v)
         return g
+
+    def release_graph(self):
+        """Drop the captured iteration (and the launch list, whose closures keep the engine alive).  Call it before
+        torch.distributed.destroy_process_group(): a live CUDA graph that captured the NCCL all-gather keeps the communicator busy
+        and the teardown waits on it."""
+        self._graph = None
+        self._plan = None
 
     def run(self, n_iterations: int, use_graph=True):
         it, _ = self.iteration_state()

@@ -105,13 +105,15 @@ def test_config4_g256_full_size(engine):
         assert err <= 1e-2, f"layer {i}: tcgen05 vs SIMT {err:.2e}"
 
 
-def test_config2_bench_weights_argmin_agrees_with_oracle(engine):
-    """The bench's own configuration (initialize_weights: N(0, 0.02) on every conv / BN weight) squeezes the
-    discriminator's score into ~0.5 +- 1e-3 for every particle, so the absolute score gate is vacuous there (the other
-    tests use torch-default init + randomised BN statistics for that reason).  What has to be right on THIS config is the
-    ORDER of the fitness values -- it decides the global best.  48 particles: the engine's fitness must correlate with the
-    fp32 oracle's (Spearman >= 0.98), agree to 1e-4 absolutely, and the oracle's best particle must be among the engine's
-    three best.  (bf16 activations carry ~3 significant digits; the fitness spread of this config is ~1e-3.)"""
+def test_config2_bench_weights_fitness_vs_oracle(engine):
+    """The bench's own configuration (initialize_weights: N(0, 0.02) on every conv / BN weight).  MEASURED on B200: the fp32
+    oracle's fitness over 48 particles spans 1.8e-7 -- three fp32 ulps of 0.6: with these weights the discriminator's score is
+    0.5 for every particle to fp32 resolution, so there is no fitness ORDER to agree on (the reference's own fp32 argmin is
+    rounding noise on this config; Spearman against the bf16 engine 0.46) and the global-best index of the bench run carries
+    no information.  What can be asserted here is the absolute agreement (measured 6.7e-5, gate 2e-4) and that the engine's
+    global best is the strict-< rule applied to ITS fitness vector; ordering / argmin agreement with the oracle is asserted
+    where the fitness has a spread to order: torch-default init + randomised BN statistics (test_gpu_swarm.py,
+    test_gpu_fused_tail.py, test_config2_default_init_argmin_agrees_with_oracle below)."""
     from src.utils import util_dcgan as M
     torch.manual_seed(42)
     gen, disc = M.Generator(100, 1, 64), M.Discriminator(1, 64)
@@ -131,10 +133,40 @@ def test_config2_bench_weights_argmin_agrees_with_oracle(engine):
     torch.cuda.synchronize()
     fit = sw.fit.cpu().numpy().astype(np.float64)
     ref = port.fitness_dscore(pg, pd_, pos0, D)[0].astype(np.float64)
+    err = float(np.abs(fit - ref).max())
+    print(f"bench-config fitness: oracle spread {ref.max() - ref.min():.2e}, max|d| {err:.2e}")
+    assert err <= 2e-4 and ref.max() - ref.min() <= 1e-5
+    f32 = sw.fit.cpu().numpy()
+    gval, gidx = port.gbest_scan(f32, np.inf)
+    assert int(sw.key) == -1 and float(sw.gbest_val) == gval and torch.equal(sw.gbest_pos[:D].cpu(), pos0[gidx])
+
+
+def test_config2_default_init_argmin_agrees_with_oracle(engine):
+    """Same networks with torch-default init, randomised BN statistics and the discriminator's weights scaled by 3 (as in
+    test_gpu_layers.py), so that the fitness has a spread to order (with plain default init it spans 1.9e-3 and the engine
+    agrees to 1.2e-4, Spearman 0.989 -- measured).  The engine's bf16 fitness must reproduce the oracle's order: Spearman
+    >= 0.98 over 48 particles and the oracle's best particle among the engine's three best."""
+    torch.manual_seed(7)
+    pg, pd_ = port.Generator(100, 1, 64), port.Discriminator(1, 64)
+    port.randomize_bn_stats(pg, torch.Generator().manual_seed(8))
+    with torch.no_grad():
+        for prm in pd_.parameters():
+            if prm.dim() == 4:
+                prm.mul_(3.0)
+    pg, pd_ = pg.eval(), pd_.eval()
+    P = 48
+    gnet = engine.GeneratorNet(pg.state_dict(), P)
+    dnet = engine.DiscriminatorNet(pd_.state_dict(), P)
+    sw = engine.SwarmEngine(P, D, generator=gnet, fitness=engine.DScoreFitness(dnet), seed=42)
+    sw.init_particles(generator=torch.Generator(device="cuda").manual_seed(42))
+    pos0 = sw.pos[:, :D].cpu()
+    sw.evaluate_and_best()
+    torch.cuda.synchronize()
+    fit = sw.fit.cpu().numpy().astype(np.float64)
+    ref = port.fitness_dscore(pg, pd_, pos0, D)[0].astype(np.float64)
     rank = lambda v: np.argsort(np.argsort(v)).astype(np.float64)
     rho = float(np.corrcoef(rank(fit), rank(ref))[0, 1])
     err = float(np.abs(fit - ref).max())
-    print(f"bench-config fitness: spread {ref.max() - ref.min():.2e}, max|d| {err:.2e}, Spearman {rho:.4f}")
-    assert err <= 1e-4 and rho >= 0.98
+    print(f"default-init fitness: oracle spread {ref.max() - ref.min():.2e}, max|d| {err:.2e}, Spearman {rho:.4f}")
+    assert err <= 5e-3 and rho >= 0.98 and ref.max() - ref.min() >= 1e-2
     assert int(np.argmin(ref)) in np.argsort(fit)[:3]
-    assert int(sw.key) == -1 and float(sw.gbest_val) == float(sw.fit.min())

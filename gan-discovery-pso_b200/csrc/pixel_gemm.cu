@@ -585,6 +585,21 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const unsigned long long mask = (unsigned long long)(uint32_t)j1.x | ((unsigned long long)(uint32_t)j1.y << 32);
         const float* bias = bias_in_smem ? s_bias + j1.z * q_nt : p.bias + (size_t)j1.z * q_nt;
         const uint32_t buf = it & 1u, use = it >> 1;
+        // Reconstruction epilogue of a direct-store image layer with one 16-column accumulator per job (the 2x2-block image
+        // layers): this row's 16 target pixels are fetched BEFORE waiting for the accumulator, so that their DRAM latency
+        // hides behind the job's MMAs instead of serialising 16 dependent load -> subtract -> fma chains behind the TMEM load.
+        float tv[16];
+        const bool rpre = !kTmaStore && p.recon_part != nullptr && q_nt <= 16;
+        if (!kTmaStore && rpre) {
+          const long long particle = (long long)tile_row(ptile) + row;
+          const long long tb = particle * (long long)p.recon_pitch + j0.w;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int pix = s_pix[i], cm = i < q_nt ? s_cm32[i] : -1;
+            const bool ok = particle < q_P && cm >= 0 && !(pix < 64 && !((mask >> pix) & 1ull));
+            tv[i] = ok ? recon_load(p.recon_target, p.recon_bf16, tb + cm) : 0.f;
+          }
+        }
         mbar_wait_t(tfull_bar(buf), use & 1u, prof, w_tfull);
         ptx::tc_fence_after();
         const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + buf * (uint32_t)q_nt;
@@ -865,7 +880,10 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 const float f = act_fn<kAct>(__uint_as_float(v[i]) + bias[n]);
                 if (yrow) { const int cm = s_cm[n]; if (cm >= 0) yrow[cm] = __float2bfloat16_rn(f); }
                 if (y32row) { const int cm = s_cm32[n]; if (cm >= 0) y32row[cm] = f; }
-                if (recon) { const int cm = s_cm32[n]; if (cm >= 0) { const float dlt = recon_load(p.recon_target, p.recon_bf16, tbase_idx + cm) - f; racc = fmaf(dlt, dlt, racc); } }
+                if (recon) {
+                  const int cm = s_cm32[n];
+                  if (cm >= 0) { const float dlt = (rpre ? tv[i] : recon_load(p.recon_target, p.recon_bf16, tbase_idx + cm)) - f; racc = fmaf(dlt, dlt, racc); }
+                }
               }
             }
           }

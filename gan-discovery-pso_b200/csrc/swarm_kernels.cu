@@ -810,6 +810,32 @@ maxpool_nhwc_kernel(const __nv_bfloat16* __restrict__ x, long long P, int h, int
   *reinterpret_cast<uint4*>(y + out_offset(p, ((long long)oy * wo + ox) * cp + 8 * c, y_pitch, y_tiled)) = o;
 }
 
+// fp32 NCHW latent grid [P, C, HW] -> bf16 NHWC rows [P, pitch] with channel pitch cp (padding channels 0), optional ReLU:
+// the input of VectorQuantizedVAE.decoder, whose first module is an in-place ReLU (src/inverter/utils_vq_vae/util_model.py:151-164)
+__global__ void __launch_bounds__(256) pack_grid_nchw_kernel(const float* __restrict__ x, long long P, int C, int HW, int cp, int relu,
+                                                             __nv_bfloat16* __restrict__ out, long long pitch) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long per = (long long)HW * cp;
+  if (i >= P * per) return;
+  const long long p = i / per;
+  const int r = (int)(i - p * per);
+  const int pix = r / cp, c = r - pix * cp;
+  float v = c < C ? x[(p * C + c) * HW + pix] : 0.f;
+  if (relu) v = fmaxf(v, 0.f);
+  out[p * pitch + r] = __float2bfloat16_rn(v);
+}
+
+// z[p, :] = bf16(codebook[idx[p], :]) zero-padded to z_pitch: the VQ-snapped generator input (vq + embedding lookup,
+// src/inverter/utils_vq_vae/util_model.py:133-136, util_function.py:4-23)
+__global__ void __launch_bounds__(256) gather_pack_latent_kernel(const float* __restrict__ codebook, const long long* __restrict__ idx, long long P,
+                                                                 int D, __nv_bfloat16* __restrict__ z, int z_pitch) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P * D) return;
+  const long long p = i / D;
+  const int j = (int)(i - p * D);
+  z[p * z_pitch + j] = __float2bfloat16_rn(codebook[idx[p] * D + j]);
+}
+
 __global__ void __launch_bounds__(256) fill_columns_bf16_kernel(__nv_bfloat16* __restrict__ x, long long P, long long pitch, int col0, int n,
                                                                 __nv_bfloat16 value) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -886,6 +912,23 @@ int psob_fill_columns_bf16(void* x, int64_t P, int64_t pitch, int32_t col0, int3
   fill_columns_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)s>>>(
       reinterpret_cast<__nv_bfloat16*>(x), P, pitch, col0, n, __float2bfloat16_rn(value));
   PSOB_LAUNCH_CHECK("fill_columns_bf16_kernel");
+  return 0;
+}
+
+int psob_pack_grid_nchw(const float* x, int64_t P, int32_t C, int32_t HW, int32_t cp, int32_t relu, void* out_bf16, int64_t pitch, psob_stream_t s) {
+  if (!x || !out_bf16 || P <= 0 || C <= 0 || HW <= 0 || cp < C || pitch < (int64_t)HW * cp) return fail(PSOB_E_ARG, "psob_pack_grid_nchw: bad arguments");
+  const long long total = (long long)P * HW * cp;
+  pack_grid_nchw_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)s>>>(x, P, C, HW, cp, relu, reinterpret_cast<__nv_bfloat16*>(out_bf16), pitch);
+  PSOB_LAUNCH_CHECK("pack_grid_nchw_kernel");
+  return 0;
+}
+
+int psob_gather_pack_latent(const float* codebook, const int64_t* idx, int64_t P, int32_t D, void* z, int32_t z_pitch, psob_stream_t s) {
+  if (!codebook || !idx || !z || P <= 0 || D <= 0 || z_pitch < D) return fail(PSOB_E_ARG, "psob_gather_pack_latent: bad arguments");
+  const long long total = (long long)P * D;
+  gather_pack_latent_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)s>>>(codebook, reinterpret_cast<const long long*>(idx), P, D,
+                                                                                     reinterpret_cast<__nv_bfloat16*>(z), z_pitch);
+  PSOB_LAUNCH_CHECK("gather_pack_latent_kernel");
   return 0;
 }
 

@@ -366,6 +366,54 @@ class AssessorNet:
         return self.run_graph()
 
 
+class VQGridDecoderNet:
+    """`VectorQuantizedVAE.decoder` (src/inverter/utils_vq_vae/util_model.py:194-203) on the pixel-GEMM engine: fp32 latent grid
+    [P, dim, 7, 7] -> image fp32 [P, 784] (+ the padded bf16 image).  Graph from `nets.vq_grid_decoder_programs`: per
+    ResBlockBatchNorm a 3x3 conv and a 1x1 conv whose accumulator takes the skip connection as identity ops on the operand
+    ring (BN folded on the host), then the two transposed convs; all buffers row-major bf16."""
+
+    def __init__(self, state_dict, P, prefix="decoder", device=None, impl=_ffi.IMPL_TCGEN05):
+        require_cuda()
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.P, self.impl = P, impl
+        self.ops, sizes, self.dim = nets.vq_grid_decoder_programs(_sd_numpy(state_dict), prefix)
+        self.cp = L.cpitch(self.dim)
+        rows = (P + L.TILE_M - 1) // L.TILE_M * L.TILE_M
+        with torch.cuda.device(self.device):
+            self.layers = [Layer(op.prog) for op in self.ops]
+            self.buf = {k: torch.zeros(rows, n, dtype=torch.bfloat16, device=self.device)[:P] for k, n in sizes.items() if k != "image"}
+            self.img32 = torch.zeros(P, sizes["image"], dtype=torch.float32, device=self.device)
+
+    @property
+    def macs_exact(self) -> int:
+        return sum(op.prog.macs_exact for op in self.ops)
+
+    def launch_plan(self, z: torch.Tensor):
+        """z: fp32 [P, dim, 7, 7] contiguous.  (name, launch) pairs: the ReLU + NHWC + bf16 input pack, then the six layers."""
+        assert z.is_cuda and z.dtype == torch.float32 and z.is_contiguous() and tuple(z.shape) == (self.P, self.dim, 7, 7)
+        lib = _ffi.lib()
+        x0 = self.buf["cat0"]
+        plan = [("v.pack", lambda: _ffi.check(lib.psob_pack_grid_nchw(z.data_ptr(), self.P, self.dim, 49, self.cp, 1, x0.data_ptr(),
+                                                                     x0.stride(0), _stream()), "psob_pack_grid_nchw"))]
+        for op, layer in zip(self.ops, self.layers):
+            src, dst = self.buf[op.src], self.buf[op.dst]
+            plan.append((op.prog.name, lambda l=layer, s_=src, d_=dst, o=op: _ffi.check(lib.psob_layer_run(
+                l.handle, s_.data_ptr(), s_.stride(0), self.P, d_.data_ptr(), _ptr(self.img32 if o.dst32 else None), self.impl,
+                _stream()), f"psob_layer_run({o.prog.name})")))
+        return plan
+
+    def forward(self, z: torch.Tensor) -> torch.Tensor:
+        for _, launch in self.launch_plan(z):
+            launch()
+        return self.img32
+
+    def image(self) -> torch.Tensor:
+        return self.img32
+
+    def image_padded_bf16(self) -> torch.Tensor:
+        return self.buf["img_pad"]
+
+
 # ----------------------------------------------------------------------------------------------
 # thin functional wrappers over the elementwise entry points (used by the engine and the tests)
 # ----------------------------------------------------------------------------------------------
@@ -623,7 +671,8 @@ class SwarmEngine:
 
     def __init__(self, P: int, D: int, *, generator: Optional[GeneratorNet] = None, fitness=None, objective=None,
                  w_inertia=0.5, w_cogn=0.8, w_soci=0.9, v_max=math.inf, lo=-math.inf, hi=math.inf, seed=42,
-                 index_offset=0, max_iterations=1024, group=None, device=None, need_image_f32=True, distributed=True):
+                 index_offset=0, max_iterations=1024, group=None, device=None, need_image_f32=True, distributed=True,
+                 snap_to_codebook: Optional[torch.Tensor] = None):
         require_cuda()
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.P, self.D_logical = P, D
@@ -663,6 +712,14 @@ class SwarmEngine:
         self.z = None
         if generator is not None:
             self.z = torch.zeros(P, generator.in_pitch, dtype=torch.bfloat16, device=dev)
+        # VQ-snapped swarm (the quantised-code variant of BASELINE config 3): the particle state stays continuous, but every
+        # particle is DECODED at its nearest codebook row -- `vq` (src/inverter/utils_vq_vae/util_function.py:4-23) + embedding
+        # lookup between the move and the decoder.  codebook: fp32 [K, D] (e.g. set from PSO positions by `pso_weights`)
+        self.codebook = None
+        if snap_to_codebook is not None:
+            assert generator is not None and snap_to_codebook.shape[1] == self.D_logical
+            self.codebook = snap_to_codebook.to(dev, torch.float32).contiguous()
+            self.code_idx = torch.zeros(P, dtype=torch.int64, device=dev)
         self.r1 = self.r2 = None
         self.inertia_decay = 1.0
         self._graph = None
@@ -702,6 +759,16 @@ class SwarmEngine:
         self.reset_iteration()
         if self.z is not None:
             pack_latent(self.pos, self.z)
+            self._snap()
+
+    def _snap(self):
+        if self.codebook is None:
+            return
+        lib = _ffi.lib()
+        _ffi.check(lib.psob_vq_nearest(self.pos.data_ptr(), self.P, self.D_logical, self.pos.stride(0), self.codebook.data_ptr(),
+                                       self.codebook.shape[0], self.code_idx.data_ptr(), None, _stream()), "psob_vq_nearest")
+        _ffi.check(lib.psob_gather_pack_latent(self.codebook.data_ptr(), self.code_idx.data_ptr(), self.P, self.D_logical,
+                                               self.z.data_ptr(), self.z.stride(0), _stream()), "psob_gather_pack_latent")
 
     def inject_r(self, r1: Optional[torch.Tensor], r2: Optional[torch.Tensor]):
         """Teacher-forced r1/r2 (parity runs); None restores the in-kernel Philox draws."""
@@ -790,6 +857,7 @@ class SwarmEngine:
                    z=self.z, dyn=self.dyn, c_cogn=self.c_cogn, c_soci=self.c_soci, v_max=self.v_max, lo=self.lo, hi=self.hi,
                    seed=self.seed, index_offset=self.index_offset)
         self._pbest_pending = False
+        self._snap()
 
     def step(self):
         fused = self.fused_tail and (self.gen is None or hasattr(self.fitness, "fused_plan"))

@@ -183,6 +183,10 @@ def _finish(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, tiles, b
     if chains is None:
         chains = np.stack([np.arange(jobs.shape[0]), np.ones(jobs.shape[0], np.int64)], axis=1)
     chains = np.asarray(chains, dtype=np.int32).reshape(-1, 2)
+    meta = dict(meta or {})
+    # compulsory HBM traffic per particle of a layer-by-layer execution: the input row once, the bf16 output once (the fp32
+    # image of an image layer is only written on request and is not counted); lowerings that share buffers set it themselves
+    meta.setdefault("hbm_bytes", 2 * (int(in_pitch) + int(out_pitch)))
     n_eye = int(np.count_nonzero(steps[:, 3] & STEP_EYE)) if steps.size else 0
     n_ops = int(steps.shape[0]) - n_eye + sum(len(v) for v in xops.values())
     return LayerProgram(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, wpack, b_resident, steps, jobs,
@@ -785,7 +789,7 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
     sc_kind = shortcut[0] if shortcut else None
     if sc_kind == "identity":
         x_base = shortcut[1]
-        assert cout == cpo and cpo % KCHUNK == 0
+        assert cpo % KCHUNK == 0      # cout < cpo is fine: x's padding channels are 0, so the identity adds nothing there
         in_need = max(in_need, x_base + ho * wo * cpo)
     elif sc_kind == "conv":
         _, w_s, b_s, stride_s, x_base, h_x, wd_x, x_cp = shortcut

@@ -267,3 +267,78 @@ def emulate_assessor(ops, bufs, img: np.ndarray, round_out=True):
         if op.dst32:
             mem[op.dst32] = y32
     return mem["logits"]
+
+
+# ----------------------------------------------------------------------------------------------
+# `VectorQuantizedVAE.decoder` (src/inverter/utils_vq_vae/util_model.py:194-203): two ResBlockBatchNorm(dim) on the 7x7
+# latent grid (:151-164), ReLU, ConvT(dim, dim, 4, 2, 1) + BN + ReLU, ConvT(dim, 1, 4, 2, 1) + Tanh.
+# ----------------------------------------------------------------------------------------------
+
+def fold_bn_conv_bias(sd: Dict, conv: str, bn: str):
+    """Conv2d WITH bias [Cout, Cin, k, k] followed by an eval-mode BN over Cout."""
+    w, b = _np(sd[f"{conv}.weight"]), _np(sd[f"{conv}.bias"])
+    g, beta = _np(sd[f"{bn}.weight"]), _np(sd[f"{bn}.bias"])
+    mean, var = _np(sd[f"{bn}.running_mean"]), _np(sd[f"{bn}.running_var"])
+    s = g / np.sqrt(var + BN_EPS)
+    return (w * s[:, None, None, None]).astype(np.float32), ((b - mean) * s + beta).astype(np.float32)
+
+
+def vq_grid_decoder_programs(sd: Dict, prefix: str = "decoder"):
+    """-> (ops, buffers, dim): the op graph over named row-major bf16 buffers, like `assessor_programs`.
+
+    The block's first ReLU is in place (`nn.ReLU(True)`), so `x + block(x)` evaluates relu(x) + block(relu(x)); the engine
+    therefore keeps every block input ALREADY rectified: the input pack applies the ReLU (psob_pack_grid_nchw), and each
+    block's 1x1 conv adds the skip connection as identity ops on the operand ring and ends with ReLU -- which is both the
+    next block's in-place ReLU and, after the second block, the decoder's own `nn.ReLU(True)`.
+    Buffers: "cat0" / "cat1" = [x | t] (block input and the 3x3 conv's output share a row, as in the assessor),
+    "x3" = the rectified output of block 2 in the exact pitch the transposed conv reads, "up" = 14x14 map, image outputs."""
+    dim = int(np.shape(sd[f"{prefix}.0.block.1.weight"])[0])
+    cp = L.cpitch(dim)
+    h = 7
+    x_elems = h * h * cp
+    cat_pitch = 2 * x_elems
+    ops, bufs = [], {"cat0": cat_pitch, "cat1": cat_pitch, "x3": x_elems}
+    cur, other = "cat0", "cat1"
+    for k in range(2):
+        w3, b3 = fold_bn_conv_bias(sd, f"{prefix}.{k}.block.1", f"{prefix}.{k}.block.2")
+        w1, b1 = fold_bn_conv_bias(sd, f"{prefix}.{k}.block.4", f"{prefix}.{k}.block.5")
+        pa = L.lower_conv2d(f"v.b{k}.c3", w3, b3, L.ACT_RELU, h, h, 1, 1, in_cp=cp, out_base=x_elems, out_pitch=cat_pitch, in_pitch=cat_pitch)
+        ops.append(AssessorOp("layer", cur, cur, pa))
+        last = k == 1
+        pb = L.lower_conv2d(f"v.b{k}.c1", w1, b1, L.ACT_RELU, h, h, 1, 0, in_cp=cp, in_base=x_elems,
+                            out_pitch=x_elems if last else cat_pitch, shortcut=("identity", 0), in_pitch=cat_pitch)
+        ops.append(AssessorOp("layer", cur, "x3" if last else other, pb))
+        cur, other = other, cur
+    wu, bu = fold_bn_convt(sd, f"{prefix}.3", f"{prefix}.4")
+    up = L.lower_convt_k4s2p1("v.up", wu, bu, L.ACT_RELU, h, h, m=1, in_cp=cp)
+    assert up.in_pitch == x_elems
+    bufs["up"] = up.out_pitch
+    ops.append(AssessorOp("layer", "x3", "up", up))
+    wi = _np(sd[f"{prefix}.6.weight"]).astype(np.float32)
+    bi = _np(sd[f"{prefix}.6.bias"]).astype(np.float32)
+    assert wi.shape[1] == 1, "single-channel image expected"
+    img = L.lower_convt_k4s2p1("v.img", wi, bi, L.ACT_TANH, 2 * h, 2 * h, m=2, image_out=True, in_cp=L.cpitch(wu.shape[1]))
+    assert img.in_pitch == up.out_pitch
+    bufs["img_pad"] = img.out_pitch
+    ops.append(AssessorOp("layer", "up", "img_pad", img, dst32="image"))
+    bufs["image"] = img.out32_pitch
+    return ops, bufs, dim
+
+
+def emulate_vq_grid_decoder(ops, bufs, dim, z: np.ndarray, round_out=True):
+    """z: [P, dim, 7, 7] fp32 -> image fp32 [P, 784] (numpy emulation of the graph; the pack applies ReLU + bf16)."""
+    p = z.shape[0]
+    cp = L.cpitch(dim)
+    mem = {k: np.zeros((p, n), np.float32) for k, n in bufs.items()}
+    x = np.zeros((p, 49, cp), np.float32)
+    x[:, :, :dim] = np.maximum(z.reshape(p, dim, 49).transpose(0, 2, 1), 0)
+    mem["cat0"][:, :49 * cp] = L.to_bf16_f32(x.reshape(p, -1)) if round_out else x.reshape(p, -1)
+    for op in ops:
+        pr = op.prog
+        y, y32 = L.emulate(pr, mem[op.src], round_out=round_out)
+        if op.dst and y is not None:
+            b0, n = pr.meta.get("out_base", 0), pr.meta.get("out_elems", pr.out_pitch)
+            mem[op.dst][:, b0:b0 + n] = y[:, b0:b0 + n]
+        if op.dst32:
+            mem[op.dst32] = y32
+    return mem["image"]

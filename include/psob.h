@@ -91,6 +91,16 @@ int psob_update(const psob_update_args* a, psob_stream_t s);
  * latent rows that carry the first generator layer's bias (Generator.forward's first ConvTranspose2d + BatchNorm shift,
  * src/utils/util_dcgan.py:133-135, folded into the MMA) */
 int psob_fill_columns_bf16(void* x, int64_t P, int64_t pitch, int32_t col0, int32_t n, float value, psob_stream_t s);
+/* fp32 NCHW latent grid [P, C, HW] -> bf16 NHWC rows [P, pitch >= HW * cp] with channel pitch cp (padding channels 0), relu != 0
+ * applies ReLU first: the input of VectorQuantizedVAE.decoder, whose first module is an in-place ReLU
+ * (src/inverter/utils_vq_vae/util_model.py:151-164,194-203) */
+int psob_pack_grid_nchw(const float* x, int64_t P, int32_t C, int32_t HW, int32_t cp, int32_t relu, void* out_bf16, int64_t pitch,
+                        psob_stream_t s);
+/* z[p, 0:D] = bf16(codebook[idx[p], :]) (columns D..z_pitch-1 untouched): the generator input of the VQ-snapped swarm -- particles
+ * are decoded at their nearest code (VQEmbedding.forward + embedding lookup, src/inverter/utils_vq_vae/util_model.py:133-136,
+ * after psob_vq_nearest); codebook fp32 [K, D] dense, idx int64 [P] */
+int psob_gather_pack_latent(const float* codebook, const int64_t* idx, int64_t P, int32_t D, void* z_bf16, int32_t z_pitch,
+                            psob_stream_t s);
 /* fp32 [P, D] -> zero-padded bf16 [P, z_pitch] (initial generator input) */
 int psob_pack_latent(const float* pos, int64_t P, int32_t D, void* z_bf16, int32_t z_pitch, psob_stream_t s);
 

@@ -136,6 +136,54 @@ class VQDecoderMNIST(nn.Module):
         return self.decoder(x)
 
 
+class ResBlockBN(nn.Module):
+    """`ResBlockBatchNorm` (src/inverter/utils_vq_vae/util_model.py:151-164): x + BN(Conv1x1(ReLU(BN(Conv3x3(ReLU(x)))))).
+    The block's first ReLU is IN PLACE (`nn.ReLU(True)`), so by the time the sum is formed `x` already holds relu(x):
+    the block computes relu(x) + block(relu(x)).  Restated explicitly here (no in-place op)."""
+
+    def __init__(self, dim: int):
+        super().__init__()
+        self.block = nn.Sequential(nn.ReLU(), nn.Conv2d(dim, dim, 3, 1, 1), nn.BatchNorm2d(dim), nn.ReLU(),
+                                   nn.Conv2d(dim, dim, 1), nn.BatchNorm2d(dim))
+
+    def forward(self, x):
+        r = torch.relu(x)
+        return r + self.block[1:](r)
+
+
+class VQGridDecoder(nn.Module):
+    """`VectorQuantizedVAE.decoder` (src/inverter/utils_vq_vae/util_model.py:194-203): two ResBlockBatchNorm(dim) on the
+    7x7 latent grid, ReLU, ConvT(dim, dim, 4, 2, 1) + BN + ReLU, ConvT(dim, C, 4, 2, 1) + Tanh; same state_dict keys
+    (`decoder.{0,1}.block.{1,2,4,5}.*`, `decoder.{3,4,6}.*`); xavier-uniform conv weights, zero biases (:39-46)."""
+
+    def __init__(self, channels_img: int = 1, embedded_dim: int = 64):
+        super().__init__()
+        d = embedded_dim
+        self.decoder = nn.Sequential(ResBlockBN(d), ResBlockBN(d), nn.ReLU(), nn.ConvTranspose2d(d, d, 4, 2, 1), nn.BatchNorm2d(d),
+                                     nn.ReLU(), nn.ConvTranspose2d(d, channels_img, 4, 2, 1), nn.Tanh())
+        for m in self.modules():
+            if isinstance(m, (nn.ConvTranspose2d, nn.Conv2d)):
+                nn.init.xavier_uniform_(m.weight.data)
+                m.bias.data.fill_(0)
+
+    def forward(self, x):
+        return self.decoder(x)
+
+
+def pso_weights_codebook(data) -> torch.Tensor:
+    """`pso_weights` (src/inverter/utils_vq_vae/util_model.py:49-54): the PSO particles' final positions (a float32 DataFrame,
+    one row per particle, built by training/vq_vae.py:35-57) BECOME the codebook: nn.Embedding.weight = tensor(data.values)."""
+    return torch.tensor(np.asarray(getattr(data, "values", data)))
+
+
+def decode_snapped(decoder: nn.Module, x: torch.Tensor, codebook: torch.Tensor):
+    """VQ-snapped variant of BASELINE config 3: positions -> nearest code (`vq`, util_function.py:4-23) -> codebook row ->
+    `VectorQuantizedVAE_GAN.decoder`.  Returns (indices, images)."""
+    idx = vq_nearest(x, codebook)
+    with torch.no_grad():
+        return idx, decoder(codebook[idx].view(x.shape[0], -1, 1, 1))
+
+
 class G256(nn.Module):
     """EXTENSION: 1x256x256 generator built from the reference's `_block`
     (src/utils/util_dcgan.py:141-146) because the reference G is hard-wired to 28x28.

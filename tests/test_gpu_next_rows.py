@@ -93,3 +93,68 @@ def test_mean_pairwise_distance_matches_reference_loop_value(engine, golden):
     pos = golden["loop/final_pos"]
     got = engine.mean_pairwise_distance(torch.from_numpy(pos).float().cuda())
     assert abs(got - golden["loop/mean_mse"][-1]) <= 2e-6 * got
+
+
+@pytest.fixture(scope="module")
+def golden_vq():
+    import os
+    path = os.path.join(os.path.dirname(__file__), "golden", "ref_vq.npz")
+    with np.load(path) as z:
+        return {k: z[k] for k in z.files}
+
+
+def test_vq_grid_decoder_pso_weights_and_snapped_swarm(golden_vq):
+    """SURVEY section 8 rows a20 / f4 against the live reference's outputs (oracle/gen_golden_vq.py):
+    `VectorQuantizedVAE.decoder` (two ResBlockBatchNorm on the 7x7 grid, in-place first ReLU) and `decode(latents)` through a
+    codebook set by `pso_weights`; tcgen05 == numpy emulation of the tables; the VQ-snapped variant of config 3 --
+    `decode_snapped` and a SwarmEngine with `snap_to_codebook` -- reproduces `vq`'s indices and decodes the selected rows."""
+    import pandas as pd
+    from psob import engine, nets, _ffi
+    from src.inverter.utils_vq_vae import util_model as U
+    g = golden_vq
+    m = U.VectorQuantizedVAE(1, 100, 256, pd.DataFrame(g["vqgrid/codebook"]))
+    assert np.array_equal(m.codebook.embedding.weight.numpy(), g["vqgrid/codebook"])           # pso_weights
+    sd = {k[len("vqgrid/"):]: torch.from_numpy(v.copy()) for k, v in g.items() if k.startswith("vqgrid/decoder.")}
+    m.load_state_dict(sd, strict=False)
+    m = m.cuda().eval()
+    out = m.decoder(torch.from_numpy(g["vqgrid/z"]).cuda()).cpu().numpy()
+    ref = g["vqgrid/out"]
+    err, rel = float(np.abs(out - ref).max()), float(np.linalg.norm(out - ref) / np.linalg.norm(ref))
+    print(f"VectorQuantizedVAE.decoder: max|d| {err:.2e}, rel-L2 {rel:.2e}")
+    assert err <= 2e-2 and rel <= 5e-3                        # measured 8.3e-3 / 4.0e-3 (six bf16 layers)
+    out = m.decode(torch.from_numpy(g["vqgrid/latents"]).cuda()).cpu().numpy()
+    ref = g["vqgrid/decode_out"]
+    assert np.abs(out - ref).max() <= 2e-2 and np.linalg.norm(out - ref) <= 5e-3 * np.linalg.norm(ref)
+    # engine == numpy emulation of the same tables (re-rounding noise only)
+    ops, bufs, dim = nets.vq_grid_decoder_programs({k: v.numpy() for k, v in sd.items()})
+    emu = nets.emulate_vq_grid_decoder(ops, bufs, dim, g["vqgrid/z"])
+    got = m.decoder(torch.from_numpy(g["vqgrid/z"]).cuda()).cpu().numpy().reshape(6, -1)
+    assert np.abs(got - emu).max() <= 4e-3
+    with pytest.raises(_ffi.PsobError):
+        m(torch.zeros(1, 1, 28, 28).cuda())
+    # VQ-snapped config 3
+    m2 = U.VectorQuantizedVAE_GAN(1, 100, 64, pd.DataFrame(g["vqsnap/codebook"]), features_g=16, features_d=16)
+    m2.load_state_dict({k[len("vqsnap/"):]: torch.from_numpy(v.copy()) for k, v in g.items() if k.startswith("vqsnap/decoder.")}, strict=False)
+    m2 = m2.cuda().eval()
+    x = torch.from_numpy(g["vqsnap/x"]).cuda()
+    idx, img = m2.decode_snapped(x)
+    assert np.array_equal(idx.cpu().numpy(), g["vqsnap/idx"])
+    ref = g["vqsnap/out"]
+    assert np.abs(img.cpu().numpy() - ref).max() <= 2e-2 and np.linalg.norm(img.cpu().numpy() - ref) <= 5e-3 * np.linalg.norm(ref)
+    P = 12
+    gsd = {"decoder." + k: v for k, v in m2.decoder.state_dict().items()}
+    gnet = engine.GeneratorNet(gsd, P, prefix="decoder")
+    tgt = torch.zeros(P, 784, device="cuda")
+    sw = engine.SwarmEngine(P, 100, generator=gnet, fitness=engine.ReconFitness(tgt), seed=1, snap_to_codebook=m2.codebook.embedding.weight)
+    sw.init_particles(pos=x, vel=torch.zeros_like(x))
+    assert np.array_equal(sw.code_idx.cpu().numpy(), g["vqsnap/idx"])
+    z_ref = torch.from_numpy(g["vqsnap/codebook"][g["vqsnap/idx"]]).to(torch.bfloat16)
+    assert torch.equal(sw.z[:, :100].cpu(), z_ref)
+    sw.step()
+    torch.cuda.synchronize()
+    # fitness was evaluated on the SNAPPED codes (targets are 0: fit = mean(img^2) + eps); the state moved continuously
+    fit_ref = (ref.reshape(P, -1) ** 2).mean(1) + 0.1
+    np.testing.assert_allclose(sw.fit.cpu().numpy(), fit_ref, atol=5e-3, rtol=0)
+    from oracle import port
+    idx2 = port.vq_nearest(sw.pos[:, :100].cpu(), torch.from_numpy(g["vqsnap/codebook"]))
+    assert np.array_equal(sw.code_idx.cpu().numpy(), idx2.numpy())

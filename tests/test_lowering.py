@@ -159,3 +159,22 @@ def test_head_weights_reproduce_the_score_layer():
     # conv weight layout: w[pix * 128 + ch] = W[0, ch, ky, kx]
     W = disc.state_dict()["disc.3.weight"].numpy()
     np.testing.assert_array_equal(w.reshape(49, 128), L.to_bf16_f32(W[0].reshape(128, 49).T))
+
+
+def test_vq_grid_decoder_tables_match_reference_geometry(monkeypatch):
+    """`VectorQuantizedVAE.decoder` (src/inverter/utils_vq_vae/util_model.py:194-203; two ResBlockBatchNorm on the 7x7 grid,
+    in-place first ReLU, identity shortcut as identity ops with cout < channel pitch) lowered to engine tables: the numpy
+    emulation of the tables equals the LIVE reference's output (tests/golden/ref_vq.npz) to fp32 noise without bf16
+    rounding, and stays within the image gates with it."""
+    import os
+    from psob import nets
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_vq.npz"))
+    sd = {k[len("vqgrid/"):]: g[k] for k in g.files if k.startswith("vqgrid/decoder.")}
+    ref = g["vqgrid/out"].reshape(6, -1)
+    ops, bufs, dim = nets.vq_grid_decoder_programs(sd)
+    img = nets.emulate_vq_grid_decoder(ops, bufs, dim, g["vqgrid/z"])
+    assert np.abs(img - ref).max() <= 2e-2 and np.linalg.norm(img - ref) <= 5e-3 * np.linalg.norm(ref)
+    monkeypatch.setattr(L, "ROUND_WEIGHTS", False)
+    ops, bufs, dim = nets.vq_grid_decoder_programs(sd)
+    img = nets.emulate_vq_grid_decoder(ops, bufs, dim, g["vqgrid/z"], round_out=False)
+    assert np.abs(img - ref).max() <= 5e-6

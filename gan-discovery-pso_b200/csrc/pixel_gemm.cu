@@ -81,6 +81,7 @@ struct EngineParams {
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4, strided;
   int no_bias;               // every bias entry is 0 (e.g. folded into the K padding): the chunked epilogue skips the loads and adds
+  int pf_dist;               // L2 prefetch distance of the TMA producer in steps (0: off)
   int rot_div;               // chain rotation: item (tile t, slot r) runs chain (r + t / rot_div) % n_chains (0: chain r) -- see pick_rotation
   int step_stride;           // int4 words per step in the shared-memory copy of the step table (1 when no step has > 2 ops)
   int warp_store;            // every epilogue warp stores its own 32 rows of a chunk (32-row TMA box): no barriers inside a group
@@ -88,7 +89,8 @@ struct EngineParams {
   int issue_split;           // 2 issuers: ownership of an op by (accumulator buffer + column region) parity (1) or by buffer only (0)
   int half_store;            // warp stores with a single staging tile: the warp's 4 KB slice is two 32-column halves (SWIZZLE_64B)
                              // published by separate TMA stores, so one half drains while the other is written
-  int band;                  // image-band epilogue (lower_convt_image_band): 4 chunks of two padded image rows each
+  int band;                  // image-band epilogue (lower_convt_image_band): 4 chunks of two padded image rows each; 2: tiled band
+  int band_w;                // tiled band: width of the image in pixels (row pitch of the fp32 image / the target)
   int epi_groups;            // TMA-store epilogue: 2 groups of 4 warps alternate chunks, or 1 group (frees a staging tile for the ring)
   int in_tiled, out_tiled, n_in_chunks, n_out_chunks;   // tile-major activations: [particle tile][64-col chunk][128][64]
   int bias_off, steps_off, jobs_off, chains_off, stg_bufs;   // SMEM table offsets from the table base (-1: stays in global)
@@ -407,6 +409,31 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const bool prof = p.prof != nullptr;
       unsigned long long w_empty = 0;
       const long long t_start = clock64();
+      // L2 prefetch cursor: a second walk over the same step sequence, `pf_dist` steps ahead of the loads.  Resident weights
+      // leave room for a 3-4-stage ring only, far less than the DRAM latency of an A tile in MMA steps (the MMA warp waited on
+      // `full` 13-23 % of its time while the producer waited on `empty`); a prefetched tile is an L2 hit when its real load is
+      // issued, so the short ring covers the remaining latency.  Costs no shared memory and no barrier.
+      const int pf_dist = p.pf_dist;
+      long long pf_item = item_begin;
+      int pf_job = 0, pf_job_end = 0, pf_s = 0, pf_s_end = 0, pf_ptile = 0;
+      bool pf_live = pf_dist > 0 && item_begin < item_end;
+      auto pf_open_item = [&]() { const int2 c = chains[item_chain(pf_item, pf_ptile)]; pf_job = c.x; pf_job_end = c.x + c.y; };
+      auto pf_open_job = [&]() { const int4 j = jobs[2 * pf_job]; pf_s = j.x; pf_s_end = j.x + j.y; };
+      if (pf_live) { pf_open_item(); pf_open_job(); }
+      auto pf_one = [&]() {              // prefetch the cursor's step and advance it
+        const int a_col = steps[ss * pf_s].x;
+        if (ptx::elect_one()) ptx::tma_prefetch_l2_2d(&tmA, in_c0(a_col), in_c1(pf_ptile, a_col));
+        __syncwarp();
+        if (++pf_s == pf_s_end) {
+          if (++pf_job == pf_job_end) {
+            pf_item += item_step;
+            if (pf_item >= item_end) { pf_live = false; return; }
+            pf_open_item();
+          }
+          pf_open_job();
+        }
+      };
+      for (int k = 0; k < pf_dist && pf_live; ++k) pf_one();
       for (long long item = item_begin; item < item_end; item += item_step) {
         int ptile;
         const int2 ch = chains[item_chain(item, ptile)];
@@ -416,6 +443,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           for (int s = j0.x; s < j0.x + j0.y; ++s) {
             const int4 st = st_next;
             if (s + 1 < j0.x + j0.y) st_next = steps[ss * (s + 1)];     // descriptor fetch overlaps the wait
+            if (pf_live) pf_one();
             mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
             const bool res = (st.y & (kMetaResident | kMetaEye)) != 0;      // no weight tile to stream for this step
             if (ptx::elect_one()) {
@@ -673,6 +701,31 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               }
               };
               if (bias_in_smem) dot_slots(std::true_type{}); else dot_slots(std::false_type{});
+              if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
+              continue;
+            }
+            if (q_band == 2) {
+              // tiled image band (wide images): nothing is staged; every thread finishes its particle's two image rows of the
+              // tile straight from the accumulator -- fp32 store and / or (target - tanh(acc))^2
+              const float bz = bias_in_smem ? s_bias[0] : __ldg(p.bias);
+              const long long particle = (long long)tile_row(ptile) + row;
+              const bool pv = particle < q_P;
+              const int n_cols = (int)((mask >> 8) & 0xFFull);
+              const bool recon = p.recon_part != nullptr;
+#pragma unroll
+              for (int rr = 0; rr < 2; ++rr) {
+                const bool rowok = pv && ((mask >> (2 * ch + rr)) & 1ull) != 0;
+                const long long pix0 = (long long)j0.w + (long long)(2 * ch + rr) * p.band_w;      // image pixel of padded column 1
+                float* y32row = (p.y32 && rowok) ? p.y32 + particle * q_out32_pitch + pix0 : nullptr;
+                const long long tidx = particle * (long long)p.recon_pitch + pix0;
+#pragma unroll
+                for (int px = 1; px <= 28; ++px) {
+                  const bool ok = rowok && px <= n_cols;
+                  const float f = act_fn<kAct>(__uint_as_float(v[rr * kBandPitch + px]) + bz);
+                  if (ok && y32row) y32row[px - 1] = f;
+                  if (ok && recon) { const float dlt = recon_load(p.recon_target, p.recon_bf16, tidx + px - 1) - f; racc = fmaf(dlt, dlt, racc); }
+                }
+              }
               if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
               continue;
             }
@@ -965,6 +1018,7 @@ pixel_gemm_simt_kernel(const __nv_bfloat16* __restrict__ x, long long x_pitch, c
     if (particle >= p.P) continue;
     const int pix = n / p.cc;
     if (pix < 64 && !((mask >> pix) & 1ull)) continue;
+    if (p.band_w) { const int px = n - pix * p.cc; if (px < 1 || px > (int)((mask >> 8) & 0xFFull)) continue; }      // tiled band: right border
     float acc = 0.f;
     // pass 0: the previous job of the chain (its NEXT ops accumulate into this job), pass 1: this job's own ops
     for (int pass = (j1.w ? 0 : 1); pass < 2; ++pass) {
@@ -1070,6 +1124,8 @@ struct psob_layer {
   bool tma_store = false, vec4 = false, pair = false, strided = false;
   int epi_groups = 2, step_stride = 2;
   bool band = false;
+  bool band_wide = false;          // tiled image band (no bf16 output; fp32 / reconstruction epilogue from registers)
+  int pf_dist = 0;                 // L2 prefetch distance of the producer (steps); resident-weight layers only by default
   bool no_bias = false;            // all bias entries are 0
   bool dot_head = false;           // dot-only layer: staging area = the head's weights, 2 epilogue groups
   int stg_bytes = 0;               // bytes of the staging area in the shared-memory plan
@@ -1268,6 +1324,11 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
 
   // epilogue flavour: TMA store when every 64-column chunk is one contiguous, 16-byte aligned 128-byte row
   l->band = d->band_pitch != 0;
+  l->band_wide = l->band && d->band_width != 0;
+  if (l->band_wide && (d->out_pitch != 0 || d->out32_pitch <= 0 || d->band_width % 4)) {
+    psob_layer_destroy(l);
+    return fail(PSOB_E_ARG, "psob_layer_create: a tiled image band has no bf16 output, an fp32 image and a width that is a multiple of 4");
+  }
   if (l->band && (d->band_pitch != kBandPitch || d->nt != 256 || d->cc != kBandPitch || d->out_pitch % 8 || d->in_tiled < 0 || d->out_tiled)) {
     psob_layer_destroy(l);
     return fail(PSOB_E_ARG, "psob_layer_create: an image-band layer has nt = 256, cc = band_pitch = %d and a row-major output", kBandPitch);
@@ -1361,7 +1422,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     psob_layer_destroy(l);
     return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: dot_head needs a layer with the chunked bf16 epilogue");
   }
-  if (l->tma_store && !l->dot_head) {
+  if (l->tma_store && !l->dot_head && !l->band_wide) {      // a tiled band stages nothing: its epilogue works from registers
     const int room = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes;
     l->stg_bufs = (room - 2 * l->epi_groups * kATileBytes) / l->stage_bytes >= (l->pair ? 4 : 3) ? 2 : 1;
     // a third staging tile per group where the ring stays >= 4 deep (PSOB_STG3=1; A/B knob): the epilogue warps of
@@ -1392,6 +1453,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
   { const char* e = knob("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }
   { const char* e = knob("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
+  { const char* e = knob("PSOB_PREFETCH"); l->pf_dist = e ? atoi(e) : 0; if (l->pf_dist < 0 || l->pf_dist > 64) l->pf_dist = 0; }
   l->no_bias = true;
   for (int i = 0; i < d->nt * d->n_bias_rows; ++i) if (d->bias[i] != 0.f) { l->no_bias = false; break; }
   for (int c = 0; c < d->n_chains; ++c) {
@@ -1485,7 +1547,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
     if (impl != PSOB_IMPL_TCGEN05 || dot || res) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_recon: tcgen05 path only, no residual / fused head");
     if (!d.out32_pitch || rcn.n_pix != d.out32_pitch || !rcn.target) return fail(PSOB_E_ARG, "psob_layer_run_recon: the layer must be an image layer with %d fp32 pixels per particle (target has %d)", d.out32_pitch, rcn.n_pix);
     if (l->tma_store && !l->band) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_recon: the layer has neither the image-band nor the direct fp32 epilogue");
-    if (l->band && !y) return fail(PSOB_E_ARG, "psob_layer_run_recon: an image-band layer needs its bf16 output buffer");
+    if (l->band && !l->band_wide && !y) return fail(PSOB_E_ARG, "psob_layer_run_recon: an image-band layer needs its bf16 output buffer");
   }
   if (!dot && !recon && ((d.out_pitch && !y && !(d.out32_pitch && y32)) || (!d.out_pitch && !y32))) return fail(PSOB_E_ARG, "psob_layer_run: missing output buffer");
   if (y && !aligned16(y)) return fail(PSOB_E_ARG, "psob_layer_run: y must be 16-byte aligned");
@@ -1505,7 +1567,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   p.b_resident = d.b_resident; p.n_wrows = d.n_wrows; p.n_bias_rows = d.n_bias_rows;
   p.n_stages = l->n_stages; p.stage_bytes = l->stage_bytes; p.res_off = l->res_off; p.bar_off = l->bar_off;
   p.in_tiled = d.in_tiled; p.out_tiled = d.out_tiled; p.n_in_chunks = d.in_pitch / kKChunk; p.n_out_chunks = d.out_pitch / kKChunk;
-  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.epi_groups = l->epi_groups; p.step_stride = l->step_stride; p.band = (l->band && p.y != nullptr) ? 1 : 0;
+  p.stg_off = l->stg_off; p.vec4 = l->vec4 ? 1 : 0; p.prof = l->prof; p.strided = l->strided ? 1 : 0; p.epi_groups = l->epi_groups; p.step_stride = l->step_stride; p.band = l->band_wide ? 2 : ((l->band && p.y != nullptr) ? 1 : 0); p.band_w = l->band_wide ? d.band_width : 0;
   p.issuers = l->issuers; p.issue_split = l->issue_split ? 1 : 0;
   p.warp_store = l->warp_store ? 1 : 0;
   { const char* e = knob("PSOB_HALF_STORE"); p.half_store = (l->warp_store && l->stg_bufs == 1 && !l->band && l->tma_store && (e ? atoi(e) != 0 : true)) ? 1 : 0; }   // measured: d.c2 -2.7 %, g.l2 -1 %
@@ -1516,6 +1578,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   p.eye = l->eye ? 1 : 0;
   p.no_bias = l->no_bias ? 1 : 0;
   p.rot_div = 0;
+  p.pf_dist = l->pf_dist;
   p.tmem_cols = l->tmem_cols;
 
   if (impl == PSOB_IMPL_SIMT) {
@@ -1527,7 +1590,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   }
   if (impl != PSOB_IMPL_TCGEN05) return fail(PSOB_E_ARG, "psob_layer_run: unknown impl %d", impl);
 
-  const bool tma_store = l->tma_store && (p.y != nullptr || dot);
+  const bool tma_store = l->tma_store && (p.y != nullptr || dot || l->band_wide);      // a tiled band has the chunked epilogue without a store
   if (d.out_tiled && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a tile-major output needs its bf16 output buffer");
   if (l->pair && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a CTA-pair layer needs its bf16 output buffer");
   UmmaKernelFn fn = umma_kernel_for(d.act, tma_store, l->pair, res != nullptr, dot);
@@ -1552,7 +1615,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   int rc = d.in_tiled ? make_tmap(&tmA, x, kKChunk, (uint64_t)n_ptiles * (d.in_pitch / kKChunk) * kTileM, kKChunk, kTileM)
                       : make_tmap(&tmA, x, (uint64_t)x_pitch, (uint64_t)P, (uint64_t)x_pitch, kTileM);
   if (rc) return rc;
-  if (tma_store && !dot) {
+  if (tma_store && !dot && !l->band_wide) {
     const uint32_t box_rows = l->warp_store ? 32u : (uint32_t)kTileM;
     const uint32_t box_cols = p.half_store ? 32u : (uint32_t)kKChunk;
     const CUtensorMapSwizzle sw = p.half_store ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;

@@ -68,7 +68,7 @@ class LayerDesc(C.Structure):
         ("b_resident", C.c_int32), ("vec8", C.c_int32),
         ("n_steps", C.c_int32), ("n_jobs", C.c_int32), ("n_wrows", C.c_int32), ("n_bias_rows", C.c_int32),
         ("n_chains", C.c_int32),
-        ("in_tiled", C.c_int32), ("out_tiled", C.c_int32), ("band_pitch", C.c_int32), ("dot_head", C.c_int32), ("solo", C.c_int32),
+        ("in_tiled", C.c_int32), ("out_tiled", C.c_int32), ("band_pitch", C.c_int32), ("dot_head", C.c_int32), ("solo", C.c_int32), ("band_width", C.c_int32),
         ("wpack", C.c_void_p), ("steps", C.c_void_p), ("jobs", C.c_void_p), ("chains", C.c_void_p),
         ("col_map", C.c_void_p), ("col_map32", C.c_void_p), ("bias", C.c_void_p),
     ]

@@ -57,7 +57,9 @@ class Layer:
             out_pitch=prog.out_pitch, out32_pitch=prog.out32_pitch, b_resident=int(prog.b_resident),
             vec8=int(prog.vec8), n_steps=prog.n_steps, n_jobs=prog.n_jobs, n_wrows=wbits.shape[0],
             n_bias_rows=bias.shape[0], n_chains=chains.shape[0], chains=chains.ctypes.data, in_tiled=int(in_tiled), out_tiled=int(out_tiled), dot_head=int(dot_head), solo=int(bool(prog.meta.get("residual"))),
-            band_pitch=(prog.meta["band"][1] if prog.meta.get("kind") == "convt_image_band" and knob("PSOB_BAND_EPI", "1") != "0" else 0), wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
+            band_pitch=(prog.meta["band"][1] if (prog.meta.get("kind") == "convt_image_band" and knob("PSOB_BAND_EPI", "1") != "0")
+                        or prog.meta.get("kind") == "convt_image_band_tiled" else 0),
+            band_width=int(prog.meta.get("band_width", 0)), wpack=wbits.ctypes.data, steps=steps.ctypes.data, jobs=jobs.ctypes.data,
             col_map=cm.ctypes.data, col_map32=cm32.ctypes.data, bias=bias.ctypes.data)
         h = C.c_void_p()
         _ffi.check(_ffi.lib().psob_layer_create(C.byref(d), C.byref(h)), f"psob_layer_create({prog.name})")
@@ -557,6 +559,7 @@ class ReconFitness:
         self.w_rec, self.eps, self.assessor, self.w_ass = w_rec, eps, assessor, w_ass
         self.fit_ass = None
         self.part = None
+        self._fit_tmp = None
         if assessor is not None:
             self.fit_ass = torch.empty(target.shape[0], dtype=torch.float32, device=target.device)
 
@@ -573,8 +576,22 @@ class ReconFitness:
 
     def fused_plan(self, gen: GeneratorNet, z: torch.Tensor, write_f32: bool, recon=None):
         """The squared error is accumulated in the generator's last-layer epilogue (never reads the image back);
-        psob_fitness_tail adds the slots, divides by the pixel count and forms w_ass * fitness + w_rec * mse + eps."""
+        psob_fitness_tail adds the slots, divides by the pixel count and forms w_ass * fitness + w_rec * mse + eps.
+        Only where the image layer has the band epilogue (one particle row of whole image rows per thread): the 2x2-block
+        direct epilogue handles 16 pixels per job and measured SLOWER with the target gather in it (G256's image layer 9.4 ->
+        12.2 ms), so such generators keep the materialised image + psob_recon_fitness, whose result enters the tail as a
+        ready fitness."""
         assert recon is None
+        if not str(gen.programs[-1].meta.get("kind", "")).startswith("convt_image_band"):
+            if self.assessor is not None:
+                plan = gen.launch_plan(z, write_f32=True) + [("assessor_fitness", lambda: self.assessor(_NoForward(gen), self.fit_ass))]
+            else:
+                plan = gen.launch_plan(z, write_f32=True)
+            if self._fit_tmp is None:
+                self._fit_tmp = torch.empty(gen.P, dtype=torch.float32, device=self.target.device)
+            plan = plan + [("recon_fitness", lambda: recon_fitness(gen.image(), self.target, self._fit_tmp, self.fit_ass,
+                                                                   self.w_ass if self.assessor is not None else 0.0, self.w_rec, self.eps))]
+            return plan, dict(fit_in=self._fit_tmp.data_ptr())
         if self.part is None:
             self.part = torch.zeros(gen.recon_slots(), gen.P, dtype=torch.float32, device=self.target.device)
         rc = (self.target, self.part)
@@ -585,6 +602,16 @@ class ReconFitness:
         d.update(recon_part=self.part.data_ptr(), n_recon_slots=self.part.shape[0], n_pix=self.target.shape[1],
                  w_ass=float(self.w_ass) if self.assessor is not None else 0.0, w_rec=float(self.w_rec), eps_rec=float(self.eps))
         return plan, d
+
+
+class _NoForward:
+    """View of a generator net whose forward has already run (the assessor callables only read its image buffers)."""
+
+    def __init__(self, gen):
+        self._gen = gen
+
+    def __getattr__(self, name):
+        return getattr(self._gen, name)
 
 
 class AssessorFitness:
@@ -835,7 +862,7 @@ class SwarmEngine:
             plan = list(plan)
         else:
             plan, fields = [("objective", lambda: self.objective(self.pos, self.fit))], dict(fit_in=self.fit.data_ptr())
-        args = _ffi.FitnessTailArgs(fit=None if "fit_in" in fields else self.fit.data_ptr(), pbest_val=self.pbest_val.data_ptr(),
+        args = _ffi.FitnessTailArgs(fit=None if fields.get("fit_in") == self.fit.data_ptr() else self.fit.data_ptr(), pbest_val=self.pbest_val.data_ptr(),
                                     improved=self.improved.data_ptr(), P=self.P, index_offset=self.index_offset,
                                     key=self.key.data_ptr(), **fields)
 

@@ -544,6 +544,94 @@ def lower_convt_image_band(name, w, b, act, in_cp=None) -> LayerProgram:
 
 
 # ----------------------------------------------------------------------------------------------
+# (b'') The band form for WIDE images (G256's 128 x 128 -> 256 x 256 image layer): a job owns a TILE of 8 padded image rows x
+#       28 image columns (+ one halo column on each side = the same 8 x 30 accumulator as (b')), so that ONE N = 96 MMA per
+#       input pixel still scatter-adds its whole 4 x 4 patch.  Input pixels left / right of the tile contribute only their two
+#       nearest taps (cut weight tiles "L" / "R", like "top" / "bot" for the rows); halo columns collect partial sums that
+#       the epilogue discards.  There is no bf16 padded image: the epilogue (csrc/pixel_gemm.cu, band == 2) stores fp32 pixels
+#       and / or accumulates the reconstruction loss, per particle row, straight from the accumulator.
+#       Job mask: bits 0-7 valid padded rows of the band, bits 8-15 valid image columns of the tile (28, or less at the
+#       right border).
+# ----------------------------------------------------------------------------------------------
+
+BAND_TILE_W = 28
+
+
+def lower_convt_image_band_tiled(name, w, b, act, h, wd, in_cp=None) -> LayerProgram:
+    """w: [Cin, 1, 4, 4], b: [1].  Input NHWC [h, wd, Cp_in] -> fp32 image [2h * 2wd] (no bf16 output)."""
+    cin, cout = w.shape[0], w.shape[1]
+    assert cout == 1 and tuple(w.shape[2:]) == (4, 4)
+    cpi = in_cp or cpitch(cin)
+    nkc = rup(cin, KCHUNK) // KCHUNK
+    ho, wo = 2 * h, 2 * wd
+    assert wo % 4 == 0
+    wp = np.zeros((nkc * KCHUNK, 4, 4), np.float32)
+    wp[:cin] = w[:, 0]
+    nt = 256
+    rowpos = {"full": lambda ky: ky, "top": lambda ky: ky - 2 if ky >= 2 else None, "bot": lambda ky: ky + 2 if ky < 2 else None}
+    colpos = {"mid": lambda kx: kx, "L": lambda kx: kx - 2 if kx >= 2 else None, "R": lambda kx: kx if kx < 2 else None}
+    tiles, tile_of = [], {}
+    for kc in range(nkc):
+        wk = wp[kc * KCHUNK:(kc + 1) * KCHUNK]
+        for rk, rf in rowpos.items():
+            for ck, cf in colpos.items():
+                t = np.zeros((BAND_N, KCHUNK), np.float32)
+                for ky in range(4):
+                    for kx in range(4):
+                        r, c = rf(ky), cf(kx)
+                        if r is not None and c is not None:
+                            t[r * BAND_PITCH + c] = wk[:, ky, kx]
+                tile_of[(rk, ck, kc)] = len(tiles)
+                tiles.append(t)
+    zero_row = len(tiles) * BAND_N
+    tiles.append(np.zeros((BAND_N, KCHUNK), np.float32))
+    n_bands = (ho + 2 + BAND_ROWS - 1) // BAND_ROWS
+    n_ct = (wo + BAND_TILE_W - 1) // BAND_TILE_W
+    steps, jobs, xops = [], [], {}
+    for band in range(n_bands):
+        for ct in range(n_ct):
+            sb = len(steps)
+            for iy in range(4 * band - 1, 4 * band + 4):
+                if not 0 <= iy < h:
+                    continue
+                r0 = 2 * iy - BAND_ROWS * band                  # band row of the patch's first row: -2, 0, 2, 4, 6
+                rk, rbase = ("top", 0) if r0 < 0 else (("full", r0) if r0 + 3 < BAND_ROWS else ("bot", r0 - 2))
+                for ix in range(14 * ct - 1, 14 * ct + 15):
+                    if not 0 <= ix < wd:
+                        continue
+                    c0 = 2 * (ix - 14 * ct)                     # padded tile column of the patch's first column: -2 .. 28
+                    ck, cbase = ("L", 0) if c0 < 0 else (("mid", c0) if c0 + 3 < BAND_PITCH else ("R", c0))
+                    for kc in range(nkc):
+                        d_col = rbase * BAND_PITCH + cbase
+                        assert d_col % 2 == 0 and d_col + BAND_N <= nt
+                        ops = []
+                        if len(steps) == sb:
+                            ops += [(zero_row, 0, 0), (zero_row, 96, 0), (zero_row, 160, 0)]      # three N = 96 clears cover 256 columns
+                        ops.append((tile_of[(rk, ck, kc)] * BAND_N, d_col, STEP_ACCUM))
+                        b_row, dc, fl = ops[0]
+                        if len(ops) > 1:
+                            xops[len(steps)] = ops[1:]
+                        steps.append(((iy * wd + ix) * cpi + kc * KCHUNK, b_row, dc, fl | STEP_B_RESIDENT))
+            assert len(steps) > sb
+            py0 = BAND_ROWS * band
+            n_cols = min(BAND_TILE_W, wo - BAND_TILE_W * ct)
+            bits = [1 <= py0 + r <= ho for r in range(BAND_ROWS)] + [bool((n_cols >> i) & 1) for i in range(8)]
+            lo, hi = _mask_words(bits)
+            jobs.append((sb, len(steps) - sb, 0, (py0 - 1) * wo + BAND_TILE_W * ct, lo, hi, 0, 0))
+    col_map32 = []
+    for n in range(nt):
+        r, px = divmod(n, BAND_PITCH)
+        col_map32.append(r * wo + px - 1 if (r < BAND_ROWS and 1 <= px <= BAND_TILE_W) else -1)
+    bias = np.full(nt, float(np.asarray(b).reshape(-1)[0]), np.float32)
+    conn_y = sum(1 for o in range(ho) for k in range(4) if (o + 1 - k) % 2 == 0 and 0 <= (o + 1 - k) // 2 < h)
+    conn_x = sum(1 for o in range(wo) for k in range(4) if (o + 1 - k) % 2 == 0 and 0 <= (o + 1 - k) // 2 < wd)
+    return _finish(name, BAND_N, nt, BAND_PITCH, act, h * wd * cpi, 0, ho * wo, tiles, True, steps, jobs,
+                   [-1] * nt, col_map32, bias, macs_exact=conn_y * conn_x * cin, xops=xops,
+                   meta=dict(kind="convt_image_band_tiled", out_hw=(ho, wo), out_c=1, out_cp=1, band=(BAND_ROWS, BAND_PITCH),
+                             band_width=wo))
+
+
+# ----------------------------------------------------------------------------------------------
 # (c) Conv2d(Cin -> Cout, k=4, s=2, p=1): H x W -> H/2 x W/2  (second discriminator / encoder
 #     conv, src/utils/util_dcgan.py:112, 116-121).  One accumulator of mma_n = Cp_out columns
 #     per output pixel, g pixels per job; taps whose input pixel is outside are dropped.
@@ -1040,9 +1128,12 @@ def emulate(prog: LayerProgram, x: np.ndarray, round_out=True, res: Optional[np.
                 ok = (prog.col_map >= 0) & (idx < res.shape[1])
                 pre[:, ok] = pre[:, ok] + res[:, idx[ok]]
             v = _act(pre, prog.act).astype(np.float32)
+            n_cols = (mask >> 8) & 0xFF if prog.meta.get("band_width") else 0
             for n in range(prog.nt):
                 pix = n // prog.cc
                 if pix < 64 and not (mask >> pix) & 1:
+                    continue
+                if n_cols and not 1 <= n % prog.cc <= n_cols:      # tiled image band: columns past the image's right border
                     continue
                 if y is not None and prog.col_map[n] >= 0:
                     y[:, base + prog.col_map[n]] = to_bf16_f32(v[:, n]) if round_out else v[:, n]

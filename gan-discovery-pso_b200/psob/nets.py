@@ -76,7 +76,11 @@ def g256_programs(sd: Dict, prefix: str = "gen") -> List[L.LayerProgram]:
         i += 1
     w = _np(sd[f"{prefix}.{i}.weight"]).astype(np.float32)
     b = _np(sd[f"{prefix}.{i}.bias"]).astype(np.float32)
-    progs.append(L.lower_convt_k4s2p1(f"g256.l{i}", w, b, L.ACT_TANH, h, h, m=2, image_out=True))
+    if L.IMAGE_BAND and w.shape[0] <= 64:
+        # tiled band form: one N = 96 MMA per input pixel scatter-adds its 4x4 patch into an 8-row x 28-column image tile
+        progs.append(L.lower_convt_image_band_tiled(f"g256.l{i}", w, b, L.ACT_TANH, h, h))
+    else:
+        progs.append(L.lower_convt_k4s2p1(f"g256.l{i}", w, b, L.ACT_TANH, h, h, m=2, image_out=True))
     for a, c in zip(progs[:-1], progs[1:]):
         assert a.out_pitch == c.in_pitch, (a.name, a.out_pitch, c.name, c.in_pitch)
     return progs

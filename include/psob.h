@@ -241,6 +241,10 @@ typedef struct {
   int32_t dot_head;            /* != 0: the layer will only run through psob_layer_run_dot (fused single-channel head): no staging
                                 * tiles are planned (the head weights take their place), two epilogue groups drain the accumulator */
   int32_t solo;                /* != 0: never run as a CTA pair (layers that are run through psob_layer_run_residual) */
+  int32_t band_width;          /* != 0 (with band_pitch): TILED image band for wide images (lower_convt_image_band_tiled): a job is a
+                                * tile of 8 padded image rows x 28 image columns of an image `band_width` pixels wide; no bf16 output,
+                                * the epilogue stores fp32 pixels and / or accumulates the reconstruction loss from the accumulator;
+                                * job mask bits 8-15 = valid image columns of the tile */
   const uint16_t* wpack;     /* HOST bf16 bits [n_wrows, 64] */
   const int32_t*  steps;     /* HOST [n_steps, 8]: a_col, meta, op0, op1, op2, op3, 0, 0.  One A tile (TMA load) feeds 1..4 MMA ops.
                               * meta: bits 0-2 op count, bit 3 weights resident, bit 4 some op targets the NEXT job of the chain,

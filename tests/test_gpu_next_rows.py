@@ -113,7 +113,7 @@ def test_vq_grid_decoder_pso_weights_and_snapped_swarm(golden_vq):
     from src.inverter.utils_vq_vae import util_model as U
     g = golden_vq
     m = U.VectorQuantizedVAE(1, 100, 256, pd.DataFrame(g["vqgrid/codebook"]))
-    assert np.array_equal(m.codebook.embedding.weight.numpy(), g["vqgrid/codebook"])           # pso_weights
+    assert np.array_equal(m.codebook.embedding.weight.detach().numpy(), g["vqgrid/codebook"])           # pso_weights
     sd = {k[len("vqgrid/"):]: torch.from_numpy(v.copy()) for k, v in g.items() if k.startswith("vqgrid/decoder.")}
     m.load_state_dict(sd, strict=False)
     m = m.cuda().eval()
@@ -145,7 +145,7 @@ def test_vq_grid_decoder_pso_weights_and_snapped_swarm(golden_vq):
     gsd = {"decoder." + k: v for k, v in m2.decoder.state_dict().items()}
     gnet = engine.GeneratorNet(gsd, P, prefix="decoder")
     tgt = torch.zeros(P, 784, device="cuda")
-    sw = engine.SwarmEngine(P, 100, generator=gnet, fitness=engine.ReconFitness(tgt), seed=1, snap_to_codebook=m2.codebook.embedding.weight)
+    sw = engine.SwarmEngine(P, 100, generator=gnet, fitness=engine.ReconFitness(tgt), seed=1, snap_to_codebook=m2.codebook.embedding.weight.detach())
     sw.init_particles(pos=x, vel=torch.zeros_like(x))
     assert np.array_equal(sw.code_idx.cpu().numpy(), g["vqsnap/idx"])
     z_ref = torch.from_numpy(g["vqsnap/codebook"][g["vqsnap/idx"]]).to(torch.bfloat16)

@@ -178,3 +178,22 @@ def test_vq_grid_decoder_tables_match_reference_geometry(monkeypatch):
     ops, bufs, dim = nets.vq_grid_decoder_programs(sd)
     img = nets.emulate_vq_grid_decoder(ops, bufs, dim, g["vqgrid/z"], round_out=False)
     assert np.abs(img - ref).max() <= 5e-6
+
+
+@pytest.mark.parametrize("h,wd,cin", [(14, 14, 8), (20, 18, 70), (6, 30, 5)])
+def test_tiled_image_band_matches_conv_transpose(monkeypatch, h, wd, cin):
+    """The band form for wide images (G256's 128^2 -> 256^2 image layer): tiles of 8 padded rows x 28 columns, cut weight
+    tiles at the tile's left / right neighbours, partial tiles at the right border -- exact against torch in fp32."""
+    monkeypatch.setattr(L, "ROUND_WEIGHTS", False)
+    torch.manual_seed(h * wd)
+    m = torch.nn.ConvTranspose2d(cin, 1, 4, 2, 1)
+    pr = L.lower_convt_image_band_tiled("t", m.weight.detach().numpy(), m.bias.detach().numpy(), L.ACT_TANH, h, wd)
+    x = torch.randn(3, cin, h, wd)
+    ref = torch.tanh(m(x)).detach().numpy().reshape(3, -1)
+    cp = L.cpitch(cin)
+    xin = np.zeros((3, h * wd * cp), np.float32)
+    xin.reshape(3, h * wd, cp)[:, :, :cin] = x.permute(0, 2, 3, 1).reshape(3, h * wd, cin).numpy()
+    _, y32 = L.emulate(pr, xin, round_out=False)
+    assert np.abs(y32 - ref).max() <= 5e-6
+    conn = lambda n_in: sum(1 for o in range(2 * n_in) for k in range(4) if (o + 1 - k) % 2 == 0 and 0 <= (o + 1 - k) // 2 < n_in)
+    assert pr.macs_exact == conn(h) * conn(wd) * cin and pr.out_pitch == 0 and pr.out32_pitch == 4 * h * wd

@@ -1270,6 +1270,10 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     for (int n = 0; n < d->nt; ++n) {
       int pix = n / d->cc;
       if (pix < 64 && !((mask >> pix) & 1ull)) continue;
+      if (d->band_width) {        // tiled image band: mask bits 8-15 = valid image columns of the tile (right border)
+        const int px = n - pix * d->cc;
+        if (px < 1 || px > (int)((mask >> 8) & 0xFFull)) continue;
+      }
       if (d->out_pitch && d->col_map[n] >= 0) {
         long long o = (long long)jb[2] + d->col_map[n];
         if (o < 0 || o >= d->out_pitch) return fail(PSOB_E_ARG, "job %d col %d: bf16 store offset %lld outside [0,%d)", j, n, o, d->out_pitch);

@@ -1667,3 +1667,58 @@ extern "C" int psob_dot_finish(const float* part, int32_t n_slots, int64_t P, fl
   PSOB_LAUNCH_CHECK("dot_finish_kernel");
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// Fused single-channel head WITHOUT any allocation by the caller or the library (psob_layer_run_dot_static): the partial
+// sums of psob_layer_run_dot -- pure scratch between the layer's epilogue and psob_dot_finish -- live in a file-scope
+// device array instead of a caller-allocated buffer.  Every GPU that loads libpsob.so holds PSOB_STATIC_SCRATCH_BYTES of it
+// until the process exits.  No counterpart in the reference; added for callers that
+// cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// In HOST code `g_dot_part_static` is only a stand-in for the symbol, not a device address: the kernels get the pointer
+// that cudaGetSymbolAddress returns, looked up once per device with that device current.
+// ------------------------------------------------------------------------------------------
+constexpr size_t kStaticPartFloats = PSOB_STATIC_SCRATCH_BYTES / sizeof(float);
+static __device__ __align__(256) float g_dot_part_static[kStaticPartFloats];
+
+static int static_part_address(float** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static float* addr[kMaxDevices] = {};
+  int dev = 0;
+  PSOB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run_dot_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> g(mu);
+  if (!addr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_dot_part_static);      // the CURRENT device's instance of the array
+    if (e != cudaSuccess || !p)
+      return fail((int)(e != cudaSuccess ? e : cudaErrorInvalidSymbol), "cudaGetSymbolAddress(g_dot_part_static) failed on device %d: %s", dev,
+                  cudaGetErrorString(e));
+    addr[dev] = reinterpret_cast<float*>(p);
+  }
+  *out = addr[dev];
+  return 0;
+}
+
+extern "C" int psob_layer_run_dot_static(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, const void* dot_w, float bias,
+                                         int32_t act, float* out, psob_stream_t s) {
+  if (!l || !x || !dot_w || !out || P <= 0) return fail(PSOB_E_ARG, "psob_layer_run_dot_static: bad arguments");
+  const int slots = psob_layer_dot_slots(l);
+  if (slots <= 0) return slots;                                         // not a layer with the chunked bf16 epilogue (message set)
+  // the limit is checked before anything touches the device
+  if ((unsigned long long)slots * (unsigned long long)P > (unsigned long long)kStaticPartFloats)
+    return fail(PSOB_E_UNSUPPORTED,
+                "psob_layer_run_dot_static: %d partial-sum slots x %lld particles = %llu bytes exceed the static scratch of %llu bytes "
+                "(at most %lld particles per call for this layer); split the batch or use psob_layer_run_dot with your own buffer",
+                slots, (long long)P, (unsigned long long)slots * (unsigned long long)P * 4ull, (unsigned long long)PSOB_STATIC_SCRATCH_BYTES,
+                (long long)(kStaticPartFloats / (size_t)slots));
+  float* part = nullptr;
+  if (int rc = static_part_address(&part)) return rc;
+  // every slot of rows < P is rewritten by the layer's epilogue on every run (slots without a valid chunk store 0), so the
+  // array's previous contents -- the last call's partial sums, possibly for another P -- never reach the result
+  if (int rc = layer_run_impl(l, x, x_pitch, P, nullptr, nullptr, nullptr, 0, dot_w, part, PSOB_IMPL_TCGEN05, s)) return rc;
+  dot_finish_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)s>>>(part, slots, P, bias, act, out);
+  PSOB_LAUNCH_CHECK("dot_finish_kernel");
+  return 0;
+}

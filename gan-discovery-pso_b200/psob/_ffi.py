@@ -18,8 +18,9 @@ EXPORTS = [
     "psob_layer_create", "psob_layer_destroy", "psob_layer_run", "psob_layer_run_residual", "psob_layer_profile",
     "psob_layer_dot_slots", "psob_layer_run_dot", "psob_dot_finish", "psob_fill_columns_bf16",
     "psob_fitness_tail", "psob_gbest_local", "psob_gbest_record", "psob_layer_recon_slots", "psob_layer_run_recon",
-    "psob_pack_grid_nchw", "psob_gather_pack_latent",
+    "psob_pack_grid_nchw", "psob_gather_pack_latent", "psob_layer_run_dot_static",
 ]
+STATIC_SCRATCH_BYTES = 8 << 20
 VERSION = 200
 
 MODE_IN_TRAINING, MODE_OUT_TRAINING = 0, 1
@@ -119,6 +120,7 @@ def lib():
         "psob_gbest_record": ([vp, vp, vp, vp, vp, i64, u64, i32, vp, vp], C.c_int),
         "psob_pack_grid_nchw": ([vp, i64, i32, i32, i32, i32, vp, i64, vp], C.c_int),
         "psob_gather_pack_latent": ([vp, vp, i64, i32, vp, i32, vp], C.c_int),
+        "psob_layer_run_dot_static": ([vp, vp, i64, i64, vp, f32, i32, vp, vp], C.c_int),
         "psob_layer_recon_slots": ([vp], C.c_int),
         "psob_layer_run_recon": ([vp, vp, i64, i64, vp, vp, vp, i32, i32, vp, vp], C.c_int),
     }

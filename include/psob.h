@@ -288,6 +288,22 @@ int psob_layer_run_dot(psob_layer* l, const void* x, int64_t x_pitch, int64_t P,
                        psob_stream_t s);
 int psob_dot_finish(const float* part, int32_t n_slots, int64_t P, float bias, int32_t act, float* out, psob_stream_t s);
 
+/* The fused head with NO allocation anywhere: psob_layer_run_dot + psob_dot_finish in one call, the partial sums in a static device
+ * array inside libpsob.so instead of a caller-allocated `part` buffer.  This entry point has no counterpart in the reference; it was
+ * added for callers that cannot allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  out[p] = act(sum of the layer's partial sums + bias), bit-identical to the two
+ * existing calls.  Limits and rules:
+ *   - psob_layer_dot_slots(l) * P * 4 bytes must not exceed PSOB_STATIC_SCRATCH_BYTES (8 MiB: 37 449 particles per call for the
+ *     DCGAN discriminator's 56 slots); larger calls are rejected with PSOB_E_UNSUPPORTED before anything is launched;
+ *   - every GPU that loads the library holds the array until the process exits;
+ *   - all calls share the array and it keeps the last call's contents (every slot a call reads is rewritten by that call first, so
+ *     nothing needs clearing); two calls that OVERLAP on one GPU (different streams, or threads) race on it -- serialise them;
+ *   - the call itself performs no cudaMalloc / cudaFree and calls no allocating library routine; the layer handle and the caller's
+ *     x / dot_w / out buffers are made beforehand. */
+#define PSOB_STATIC_SCRATCH_BYTES (8u << 20)
+int psob_layer_run_dot_static(psob_layer* l, const void* x, int64_t x_pitch, int64_t P, const void* dot_w, float bias, int32_t act,
+                              float* out, psob_stream_t s);
+
 /* Reconstruction loss in the image layer's epilogue — replaces `torch.mean((img - img_rec) ** 2)` of
  * Discovery.fitness_pso_inverter (src/pso/util_discovery.py:97) without materialising the fp32 image: every epilogue thread
  * owns one particle row of the generator's last layer and accumulates (target - tanh(acc))^2 from the fp32 pixel it holds in a

@@ -41,8 +41,8 @@ constexpr int kATileBytes = kTileM * kKChunk * 2;   // 16 KB
 constexpr int kSmemLimit = 232448;                  // 227 KB per CTA on sm_100
 constexpr int kBarBytes = 256;
 constexpr int kMaxBiasRowsSmem = 8;
-constexpr int kMaxStepsSmem = 1024;                // step descriptors staged in SMEM (16 B each)
-constexpr int kMaxJobsSmem = 256;
+constexpr int kMaxStepsSmem = 2048;                // step descriptors staged in SMEM (16 B each)
+constexpr int kMaxJobsSmem = 512;
 constexpr int kMaxSoloResident = 96 * 1024;       // resident weights of one CTA before the pair mode takes over
 constexpr int kMaxPairResident = 128 * 1024;      // per CTA of a pair
 constexpr int kBandPitch = 30;                    // accumulator columns per padded image row of an image band (psob/lowering.py)
@@ -50,6 +50,8 @@ constexpr int kBandPitch = 30;                    // accumulator columns per pad
 constexpr int kMetaOpsMask = 7, kMetaResident = 8, kMetaHasNext = 16, kMetaEye = 32;
 constexpr int kEyeBytes = 64 * 128;   // built-in 64 x 64 bf16 identity tile (SWIZZLE_128B rows): the B operand of an identity op
 // op word: bits 0-15 weight row / 16, bits 16-23 accumulator column / 2, bit 24 NEXT job's buffer, bit 25 accumulate
+// job word 7: bit 0 = the job has a chain predecessor, bits 1.. = (base column of the job's step list) / 8 (psob/lowering.py pack_tables)
+__host__ __device__ __forceinline__ int job_abase(const int4& j1) { return (int)(((unsigned)j1.w >> 1) << 3); }
 __host__ __device__ __forceinline__ int op_b_row(int op) { return (op & 0xFFFF) << 4; }
 __host__ __device__ __forceinline__ int op_d_col(int op) { return ((op >> 16) & 0xFF) << 1; }
 __host__ __device__ __forceinline__ int op_next(int op) { return (op >> 24) & 1; }
@@ -81,8 +83,8 @@ struct EngineParams {
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4, strided;
   int no_bias;               // every bias entry is 0 (e.g. folded into the K padding): the chunked epilogue skips the loads and adds
-  int pf_dist;               // L2 prefetch distance of the TMA producer in steps (0: off)
   int rot_div;               // chain rotation: item (tile t, slot r) runs chain (r + t / rot_div) % n_chains (0: chain r) -- see pick_rotation
+  int chain_ident;           // every chain is one job (chain c == job c): the chain table is not read
   int step_stride;           // int4 words per step in the shared-memory copy of the step table (1 when no step has > 2 ops)
   int warp_store;            // every epilogue warp stores its own 32 rows of a chunk (32-row TMA box): no barriers inside a group
   int issuers;               // MMA-issuing warps (1 or 2): one thread sustains only ~1 tcgen05.mma per 85-94 cycles (tools/umma_bench.cu)
@@ -348,6 +350,18 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     for (int i = threadIdx.x; i < p.step_stride * p.n_steps; i += kThreads)     // <= 2 ops per step: first word only (16 B)
       reinterpret_cast<int4*>(tab + p.steps_off)[i] = p.step_stride == 2 ? p.steps[i] : p.steps[2 * i];
   const int ss = p.steps_off >= 0 ? p.step_stride : 2;
+  // chain c of an item.  Layers without chained jobs (chain c == job c) never touch the chain table; when the job table is too
+  // large for shared memory (thousands of jobs: G256's late layers) the NEXT item's job descriptor is pulled into L1 while the
+  // current item runs -- from L2 a descriptor costs ~800 cycles per item and role, exposed because the ring holds about one job.
+  const bool q_chain_ident = p.chain_ident != 0;
+  const bool q_jobs_global = p.jobs_off < 0;
+  auto chain_of = [&](uint32_t c) { return q_chain_ident ? make_int2((int)c, 1) : chains[c]; };
+  auto prefetch_next_job = [&](long long item_next) {
+    if (!q_jobs_global || !q_chain_ident || item_next >= q_n_items) return;
+    int pt;
+    const uint32_t c = item_chain(item_next, pt);
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p.jobs + 2 * (size_t)c));
+  };
   if (p.jobs_off >= 0)
     for (int i = threadIdx.x; i < 2 * p.n_jobs; i += kThreads) reinterpret_cast<int4*>(tab + p.jobs_off)[i] = p.jobs[i];
   for (int i = threadIdx.x; i < q_nt; i += kThreads) {
@@ -409,41 +423,18 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const bool prof = p.prof != nullptr;
       unsigned long long w_empty = 0;
       const long long t_start = clock64();
-      // L2 prefetch cursor: a second walk over the same step sequence, `pf_dist` steps ahead of the loads.  Resident weights
-      // leave room for a 3-4-stage ring only, far less than the DRAM latency of an A tile in MMA steps (the MMA warp waited on
-      // `full` 13-23 % of its time while the producer waited on `empty`); a prefetched tile is an L2 hit when its real load is
-      // issued, so the short ring covers the remaining latency.  Costs no shared memory and no barrier.
-      const int pf_dist = p.pf_dist;
-      long long pf_item = item_begin;
-      int pf_job = 0, pf_job_end = 0, pf_s = 0, pf_s_end = 0, pf_ptile = 0;
-      bool pf_live = pf_dist > 0 && item_begin < item_end;
-      auto pf_open_item = [&]() { const int2 c = chains[item_chain(pf_item, pf_ptile)]; pf_job = c.x; pf_job_end = c.x + c.y; };
-      auto pf_open_job = [&]() { const int4 j = jobs[2 * pf_job]; pf_s = j.x; pf_s_end = j.x + j.y; };
-      if (pf_live) { pf_open_item(); pf_open_job(); }
-      auto pf_one = [&]() {              // prefetch the cursor's step and advance it
-        const int a_col = steps[ss * pf_s].x;
-        if (ptx::elect_one()) ptx::tma_prefetch_l2_2d(&tmA, in_c0(a_col), in_c1(pf_ptile, a_col));
-        __syncwarp();
-        if (++pf_s == pf_s_end) {
-          if (++pf_job == pf_job_end) {
-            pf_item += item_step;
-            if (pf_item >= item_end) { pf_live = false; return; }
-            pf_open_item();
-          }
-          pf_open_job();
-        }
-      };
-      for (int k = 0; k < pf_dist && pf_live; ++k) pf_one();
       for (long long item = item_begin; item < item_end; item += item_step) {
         int ptile;
-        const int2 ch = chains[item_chain(item, ptile)];
+        const int2 ch = chain_of(item_chain(item, ptile));
+        prefetch_next_job(item + item_step);
         for (int job = ch.x; job < ch.x + ch.y; ++job) {
           const int4 j0 = jobs[2 * job];
+          const int abase = job_abase(jobs[2 * job + 1]);       // step columns are relative to the job's base column
           int4 st_next = steps[ss * j0.x];
           for (int s = j0.x; s < j0.x + j0.y; ++s) {
-            const int4 st = st_next;
+            int4 st = st_next;
+            st.x += abase;
             if (s + 1 < j0.x + j0.y) st_next = steps[ss * (s + 1)];     // descriptor fetch overlaps the wait
-            if (pf_live) pf_one();
             mbar_wait_t(empty_bar(stage), phase ^ 1u, prof, w_empty);
             const bool res = (st.y & (kMetaResident | kMetaEye)) != 0;      // no weight tile to stream for this step
             if (ptx::elect_one()) {
@@ -486,7 +477,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const bool two = p.issuers == 2;
     for (long long item = item_begin; item < item_end; item += item_step) {
       int ptile_unused;
-      const int2 ch = chains[item_chain(item, ptile_unused)];
+      const int2 ch = chain_of(item_chain(item, ptile_unused));
+      prefetch_next_job(item + item_step);
       for (int job = ch.x; job < ch.x + ch.y; ++job, ++it) {
         const int4 j0 = jobs[2 * job];
         const uint32_t buf = it & 1u, use = it >> 1;
@@ -606,7 +598,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     if (kTmaStore ? grp < q_epi_groups : grp == 0) {
       for (long long item = item_begin; item < item_end; item += item_step) {
         int ptile;
-        const int2 chn = chains[item_chain(item, ptile)];
+        const int2 chn = chain_of(item_chain(item, ptile));
+        prefetch_next_job(item + item_step);
         for (int job = chn.x; job < chn.x + chn.y; ++job, ++it) {
         const int4 j0 = jobs[2 * job];
         const int4 j1 = jobs[2 * job + 1];
@@ -1021,14 +1014,16 @@ pixel_gemm_simt_kernel(const __nv_bfloat16* __restrict__ x, long long x_pitch, c
     if (p.band_w) { const int px = n - pix * p.cc; if (px < 1 || px > (int)((mask >> 8) & 0xFFull)) continue; }      // tiled band: right border
     float acc = 0.f;
     // pass 0: the previous job of the chain (its NEXT ops accumulate into this job), pass 1: this job's own ops
-    for (int pass = (j1.w ? 0 : 1); pass < 2; ++pass) {
+    for (int pass = ((j1.w & 1) ? 0 : 1); pass < 2; ++pass) {
       const int4 js = pass == 0 ? p.jobs[2 * (job - 1)] : j0;
+      const int abase = job_abase(pass == 0 ? p.jobs[2 * (job - 1) + 1] : j1);
       for (int s = js.x; s < js.x + js.y; ++s) {
         const int4 st = p.steps[2 * s];
         const int4 st2 = p.steps[2 * s + 1];
         const int ops[4] = {st.z, st.w, st2.x, st2.y};
-        const __nv_bfloat16* a = p.in_tiled ? x + (((size_t)ptile * p.n_in_chunks + (st.x >> 6)) * kTileM + row) * kKChunk
-                                            : x + particle * x_pitch + st.x;
+        const int a_col = st.x + abase;
+        const __nv_bfloat16* a = p.in_tiled ? x + (((size_t)ptile * p.n_in_chunks + (a_col >> 6)) * kTileM + row) * kKChunk
+                                            : x + particle * x_pitch + a_col;
         for (int o = 0; o < (st.y & kMetaOpsMask); ++o) {
           const int op = ops[o];
           if (op_next(op) != (pass == 0)) continue;
@@ -1125,7 +1120,7 @@ struct psob_layer {
   int epi_groups = 2, step_stride = 2;
   bool band = false;
   bool band_wide = false;          // tiled image band (no bf16 output; fp32 / reconstruction epilogue from registers)
-  int pf_dist = 0;                 // L2 prefetch distance of the producer (steps); resident-weight layers only by default
+  bool chain_ident = false;        // chains[c] == {c, 1} for every c
   bool no_bias = false;            // all bias entries are 0
   bool dot_head = false;           // dot-only layer: staging area = the head's weights, 2 epilogue groups
   int stg_bytes = 0;               // bytes of the staging area in the shared-memory plan
@@ -1212,8 +1207,8 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   if (d->n_chains <= 0 || !d->chains) return fail(PSOB_E_ARG, "psob_layer_create: no chains");
   for (int s = 0; s < d->n_steps; ++s) {
     const int32_t* st = d->steps + 8 * s;
-    if (st[0] < 0 || st[0] % 8 || st[0] + kKChunk > d->in_pitch || (d->in_tiled && st[0] % kKChunk))
-      return fail(PSOB_E_ARG, "step %d: a_col %d out of range (or not chunk-aligned for a tile-major input)", s, st[0]);
+    if (st[0] < 0 || st[0] % 8 || (d->in_tiled && st[0] % kKChunk))       // the range is checked per job below (a_col = job base + st[0])
+      return fail(PSOB_E_ARG, "step %d: relative a_col %d negative or misaligned (chunk alignment for a tile-major input)", s, st[0]);
     const int n_ops = st[1] & kMetaOpsMask;
     if (n_ops < 1 || n_ops > 4) return fail(PSOB_E_ARG, "step %d: %d ops", s, n_ops);
     if (((st[1] & kMetaResident) != 0) != (d->b_resident != 0)) return fail(PSOB_E_ARG, "step %d: resident flag disagrees with the layer", s);
@@ -1244,7 +1239,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
       if (jb != expect || jc <= 0) return fail(PSOB_E_ARG, "chain %d: jobs must be consecutive and non-empty", c);
       expect = jb + jc;
       for (int j = jb; j < jb + jc; ++j) {
-        if ((d->jobs[8 * j + 7] != 0) != (j > jb)) return fail(PSOB_E_ARG, "job %d: chain-predecessor flag is wrong", j);
+        if (((d->jobs[8 * j + 7] & 1) != 0) != (j > jb)) return fail(PSOB_E_ARG, "job %d: chain-predecessor flag is wrong", j);
         if (j == jb + jc - 1) {
           const int sb = d->jobs[8 * j], sc = d->jobs[8 * j + 1];
           for (int s = sb; s >= 0 && s < sb + sc && s < d->n_steps; ++s)
@@ -1263,6 +1258,13 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   for (int j = 0; j < d->n_jobs; ++j) {
     const int32_t* jb = d->jobs + 8 * j;
     if (jb[0] < 0 || jb[1] <= 0 || jb[0] + jb[1] > d->n_steps) return fail(PSOB_E_ARG, "job %d: step range out of bounds", j);
+    {
+      const long long abase = (long long)((uint32_t)jb[7] >> 1) * 8;
+      if (d->in_tiled && abase % kKChunk) return fail(PSOB_E_ARG, "job %d: base column %lld not chunk-aligned for a tile-major input", j, abase);
+      for (int st = jb[0]; st < jb[0] + jb[1]; ++st)
+        if (abase + d->steps[8 * st] + kKChunk > d->in_pitch)
+          return fail(PSOB_E_ARG, "job %d step %d: a_col %lld out of range", j, st, abase + d->steps[8 * st]);
+    }
     if (jb[6] < 0 || jb[6] >= d->n_bias_rows) return fail(PSOB_E_ARG, "job %d: bias row out of range", j);
     if (d->vec8 && jb[2] % 8) return fail(PSOB_E_ARG, "job %d: out_base not 8-aligned for vec8", j);
     // stores are masked per pixel, so only enabled pixels must stay inside the row
@@ -1385,8 +1387,9 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     // Only where the MMA chain of a job outweighs its epilogue: in a pair an accumulator buffer is released by BOTH CTAs'
     // epilogue warps, which costs epilogue-bound layers (few K-steps per 256 output columns) more than the halved weight
     // traffic gives back (G256's 64 -> 64 layer: 8.98 -> 9.7 ms as a pair; its 512 -> 256 layer: 7.5 -> 5.7 ms).
-    long long n_ops = 0, n_chunks = 0;
-    for (int s = 0; s < d->n_steps; ++s) n_ops += d->steps[8 * s + 1] & kMetaOpsMask;
+    long long n_ops = 0, n_chunks = 0;      // summed per JOB: jobs share step records (pack_tables), the table itself is not the work
+    for (int j = 0; j < d->n_jobs; ++j)
+      for (int s = d->jobs[8 * j]; s < d->jobs[8 * j] + d->jobs[8 * j + 1]; ++s) n_ops += d->steps[8 * s + 1] & kMetaOpsMask;
     for (int j = 0; j < d->n_jobs; ++j) {
       const unsigned long long mask = (unsigned long long)(uint32_t)d->jobs[8 * j + 4] | ((unsigned long long)(uint32_t)d->jobs[8 * j + 5] << 32);
       for (int n = 0; n < d->nt; n += 64) {
@@ -1406,11 +1409,17 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->bias_off = l->steps_off = l->jobs_off = -1;
   if (d->n_bias_rows <= kMaxBiasRowsSmem) { l->bias_off = tab; tab += d->n_bias_rows * d->nt * 4; }
   tab = (tab + 15) & ~15;
-  if (d->n_chains <= kMaxJobsSmem) { l->chains_off = tab; tab += (d->n_chains * 8 + 15) & ~15; }
+  { const char* e2 = knob("PSOB_MAX_JOBS_SMEM"); const int mj = e2 ? atoi(e2) : kMaxJobsSmem;
+    if (d->n_chains <= mj && d->n_chains <= kMaxJobsSmem) { l->chains_off = tab; tab += (d->n_chains * 8 + 15) & ~15; } }
   l->step_stride = 1;
   for (int s = 0; s < d->n_steps; ++s) if ((d->steps[8 * s + 1] & kMetaOpsMask) > 2) l->step_stride = 2;
-  if (d->n_steps <= kMaxStepsSmem) { l->steps_off = tab; tab += d->n_steps * 16 * l->step_stride; }
-  if (d->n_jobs <= kMaxJobsSmem) { l->jobs_off = tab; tab += d->n_jobs * 32; }
+  {
+    const char* e1 = knob("PSOB_MAX_STEPS_SMEM");
+    const char* e2 = knob("PSOB_MAX_JOBS_SMEM");
+    const int max_steps = e1 ? atoi(e1) : kMaxStepsSmem, max_jobs = e2 ? atoi(e2) : kMaxJobsSmem;
+    if (d->n_steps <= max_steps && d->n_steps <= kMaxStepsSmem && d->n_steps * 16 * l->step_stride <= 32 * 1024) { l->steps_off = tab; tab += d->n_steps * 16 * l->step_stride; }
+    if (d->n_jobs <= max_jobs && d->n_jobs <= kMaxJobsSmem) { l->jobs_off = tab; tab += d->n_jobs * 32; }
+  }
   l->tab_bytes = (tab + 127) & ~127;
   // staging tiles for the TMA-store epilogue: 2 per group if that still leaves a 3-stage ring
   l->stg_bufs = 0;
@@ -1418,7 +1427,9 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   // half of the time: give the second group's staging tile to the A ring (3 -> 4 stages next to 128 KB of weights)
   // layers with short chains (K = 128 per 256 output columns) are bound by the epilogue's latency chain
   // (TMEM load -> bias/activation -> swizzled st.shared -> TMA store): a third group hides more of it
-  l->epi_groups = (l->pair && !l->band && (long long)d->n_steps * 2 * d->mma_n >= 6000ll * d->n_jobs) ? 1 : 2;   // a third group measured no faster (TMA-bound)
+  long long total_steps = 0;                 // A-tile loads of one particle tile (per job, not per shared step record)
+  for (int j = 0; j < d->n_jobs; ++j) total_steps += d->jobs[8 * j + 1];
+  l->epi_groups = (l->pair && !l->band && total_steps * 2 * d->mma_n >= 6000ll * d->n_jobs) ? 1 : 2;   // a third group measured no faster (TMA-bound)
   { const char* e = knob("PSOB_EPI_GROUPS"); if (e && atoi(e) >= 1 && atoi(e) <= kMaxEpiGroups) l->epi_groups = atoi(e); }
   if (!l->tma_store) l->epi_groups = 2;             // the direct-store epilogue uses group 0 only (thread layout of 2 groups)
   l->dot_head = d->dot_head != 0;
@@ -1447,6 +1458,12 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   int avail = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes - stg_bytes;
   l->n_stages = avail / l->stage_bytes;
   if (l->n_stages > kMaxStages) l->n_stages = kMaxStages;
+  // The tiled image band streams a 2 MB-per-particle input from DRAM with 1.5x re-reads between neighbouring jobs: a deep ring
+  // puts too many loads in flight and DRAM efficiency drops -- measured on G256's 128^2 -> 256^2 layer (P = 8192, same box):
+  // 8 stages 6.91 ms, 6: 5.08, 4: 4.91, 3: 5.27 (profiles/r02_g256_ring_depth_ab.log).  The 28 x 28 band (25 KB per particle,
+  // at its HBM floor) is the opposite: 8 stages 0.311 ms, 4 stages 0.355 (profiles/r02_config2_ring_depth_ab.log).
+  if (l->band_wide && l->n_stages > 4) l->n_stages = 4;
+  { const char* e = knob("PSOB_MAX_STAGES"); if (e && atoi(e) >= 2 && l->n_stages > atoi(e)) l->n_stages = atoi(e); }
   if (l->n_stages < 2) {
     psob_layer_destroy(l);
     return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: resident weights (%d B) leave no room for a 2-stage ring", res_bytes);
@@ -1457,7 +1474,8 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
   { const char* e = knob("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }
   { const char* e = knob("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
-  { const char* e = knob("PSOB_PREFETCH"); l->pf_dist = e ? atoi(e) : 0; if (l->pf_dist < 0 || l->pf_dist > 64) l->pf_dist = 0; }
+  l->chain_ident = d->n_chains == d->n_jobs && !(knob("PSOB_CHAIN_IDENT") && atoi(knob("PSOB_CHAIN_IDENT")) == 0);
+  for (int c = 0; c < d->n_chains && l->chain_ident; ++c) if (d->chains[2 * c] != c || d->chains[2 * c + 1] != 1) l->chain_ident = false;
   l->no_bias = true;
   for (int i = 0; i < d->nt * d->n_bias_rows; ++i) if (d->bias[i] != 0.f) { l->no_bias = false; break; }
   for (int c = 0; c < d->n_chains; ++c) {
@@ -1582,7 +1600,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   p.eye = l->eye ? 1 : 0;
   p.no_bias = l->no_bias ? 1 : 0;
   p.rot_div = 0;
-  p.pf_dist = l->pf_dist;
+  p.chain_ident = l->chain_ident ? 1 : 0;
   p.tmem_cols = l->tmem_cols;
 
   if (impl == PSOB_IMPL_SIMT) {

@@ -46,8 +46,9 @@ class Layer:
         self.dot_head = bool(dot_head)
         self.in_tiled, self.out_tiled = bool(in_tiled), bool(out_tiled)
         wbits = np.ascontiguousarray(L.bf16_bits(prog.wpack))
-        steps = np.ascontiguousarray(L.pack_steps(prog), dtype=np.int32)
-        jobs = np.ascontiguousarray(L.pack_jobs(prog), dtype=np.int32)
+        steps, jobs = L.pack_tables(prog)          # step patterns shared between jobs, relative to a per-job base column
+        steps = np.ascontiguousarray(steps, dtype=np.int32)
+        jobs = np.ascontiguousarray(jobs, dtype=np.int32)
         chains = np.ascontiguousarray(prog.chains, dtype=np.int32)
         cm = np.ascontiguousarray(prog.col_map, dtype=np.int32)
         cm32 = np.ascontiguousarray(prog.col_map32, dtype=np.int32)
@@ -55,7 +56,7 @@ class Layer:
         d = _ffi.LayerDesc(
             mma_n=prog.mma_n, nt=prog.nt, cc=prog.cc, act=prog.act, in_pitch=prog.in_pitch,
             out_pitch=prog.out_pitch, out32_pitch=prog.out32_pitch, b_resident=int(prog.b_resident),
-            vec8=int(prog.vec8), n_steps=prog.n_steps, n_jobs=prog.n_jobs, n_wrows=wbits.shape[0],
+            vec8=int(prog.vec8), n_steps=int(steps.shape[0]), n_jobs=prog.n_jobs, n_wrows=wbits.shape[0],
             n_bias_rows=bias.shape[0], n_chains=chains.shape[0], chains=chains.ctypes.data, in_tiled=int(in_tiled), out_tiled=int(out_tiled), dot_head=int(dot_head), solo=int(bool(prog.meta.get("residual"))),
             band_pitch=(prog.meta["band"][1] if (prog.meta.get("kind") == "convt_image_band" and knob("PSOB_BAND_EPI", "1") != "0")
                         or prog.meta.get("kind") == "convt_image_band_tiled" else 0),
@@ -878,6 +879,30 @@ class SwarmEngine:
         self.flush_pbest()
         for _, launch in self.launch_plan()[:-1]:
             launch()
+
+    def evaluate_and_personal_best(self):
+        """Networks + psob_fitness_tail (`Swarm.update_personal_best`): fitness, personal best and the local min-loc key."""
+        self.flush_pbest()
+        for _, launch in self.launch_plan()[:-2]:
+            launch()
+
+    def global_best(self):
+        """`Swarm.update_global_best` after evaluate_and_personal_best()."""
+        self._global_best()
+
+    def report(self, first_row: int):
+        """(iteration, w, history rows [first_row, iteration) as (values, replaced flags), gbest_pos) in ONE device -> host copy:
+        what a host loop with per-iteration decisions (early stopping) needs after every global best."""
+        it_guess = min(self.hist.shape[0], first_row + 64)
+        packed = torch.cat([self.dyn.view(torch.float32), self.hist[first_row:it_guess].reshape(-1), self.gbest_pos]).cpu().numpy()
+        it = int(packed[:1].view(np.uint32)[0])
+        w = float(packed[1])
+        n = max(0, min(it, it_guess) - first_row)
+        rows = packed[2:2 + 2 * (it_guess - first_row)].reshape(-1, 2)[:n]
+        if it > it_guess:                      # more than 64 unseen rows (a device loop ran in between): take the slow path once
+            vals, rep = self.history()
+            return it, w, vals[first_row:], rep[first_row:], packed[-self.D:]
+        return it, w, rows[:, 0].copy(), rows[:, 1] > 0.5, packed[-self.D:]
 
     def move(self):
         pso_update(self.pos, self.vel, self.pbest_pos, self.gbest_pos, improved=self.improved, r1=self.r1, r2=self.r2,

@@ -132,7 +132,8 @@ def can_load_tiled(prog: "LayerProgram") -> bool:
 
 
 def pack_steps(prog: "LayerProgram") -> np.ndarray:
-    """Engine step records int32 [n_steps, 8]: a_col, meta, op0..op3, 0, 0 (include/psob.h)."""
+    """Engine step records int32 [n_steps, 8]: a_col, meta, op0..op3, 0, 0 (include/psob.h), one record per step of the program
+    (uncompressed; `pack_tables` is what the engine uploads)."""
     out = np.zeros((prog.n_steps, 8), np.int32)
 
     def enc(b_row, d_col, flags):
@@ -153,12 +154,38 @@ def pack_steps(prog: "LayerProgram") -> np.ndarray:
 
 
 def pack_jobs(prog: "LayerProgram") -> np.ndarray:
-    """Job records with the chain-predecessor flag in word 7."""
+    """Job records with the chain-predecessor flag in bit 0 of word 7 (a_base = 0: uncompressed steps)."""
     jobs = prog.jobs.copy()
     jobs[:, 7] = 0
     for jb, jc in prog.chains:
         jobs[jb + 1:jb + jc, 7] = 1
     return jobs
+
+
+def pack_tables(prog: "LayerProgram"):
+    """(steps int32 [n, 8], jobs int32 [n_jobs, 8]) as uploaded to the engine: step lists are stored RELATIVE to a per-job base
+    column and shared between jobs with the same pattern.  A conv layer's jobs differ only by where their window starts (and by a
+    handful of border variants), so e.g. G256's 128^2 -> 256^2 image band shrinks from 36 864 step records to a few hundred and fits
+    the kernel's shared-memory tables; from global memory every step descriptor costs an L2 round trip (~800 cycles, measured: the
+    layer ran at 815 cycles per 100-cycle MMA step).  Job word 7 = chain-predecessor flag | (a_base / 8) << 1."""
+    steps = pack_steps(prog)
+    jobs = pack_jobs(prog)
+    if knob("PSOB_PACK_DEDUP", "1") == "0":          # A/B: one record per step, base column 0
+        return steps, jobs
+    out_steps, seen = [], {}
+    for j in range(jobs.shape[0]):
+        sb, sc = int(jobs[j, 0]), int(jobs[j, 1])
+        blk = steps[sb:sb + sc].copy()
+        base = int(blk[:, 0].min()) // KCHUNK * KCHUNK        # multiple of 64: keeps 16-byte and chunk alignment of every a_col
+        blk[:, 0] -= base
+        key = blk.tobytes()
+        if key not in seen:
+            seen[key] = len(out_steps)
+            out_steps.extend(blk)
+        assert base % 8 == 0 and base // 8 < (1 << 30)
+        jobs[j, 0] = seen[key]
+        jobs[j, 7] = int(jobs[j, 7]) | ((base // 8) << 1)
+    return np.asarray(out_steps, dtype=np.int32).reshape(-1, 8), jobs
 
 
 def _finish(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, tiles, b_resident, steps, jobs,

@@ -256,22 +256,26 @@ class Swarm:
         return self.engine.pos[:, :self.dim_space].double().cpu().numpy()
 
     def update_personal_best(self, iteration, ood_patient=None):
-        self.engine.evaluate()
+        """Generator + fitness for the whole swarm, then the strict-< personal best (src/pso/util_pso.py:114-124), as the
+        engine's fused launches (networks + psob_fitness_tail)."""
+        self.engine.evaluate_and_personal_best()
         if self.log_images_every and iteration % self.log_images_every == 0:
             self._dump_images(iteration)
         self._pending_best = True
 
     def update_global_best(self):
-        e = self.engine
-        e.personal_and_global_best()
+        if not getattr(self, "_pending_best", False):
+            raise _ffi.PsobError("update_global_best() follows update_personal_best(): the min-loc key is produced there")
+        self.engine.global_best()
         self._pending_best = False
         self._sync_global_best()
 
     def _sync_global_best(self):
+        """Mirror the device-side global best into the reference's host attributes: one packed device -> host copy."""
         e = self.engine
-        it, w = e.iteration_state()
-        vals, replaced = e.history()
-        for k in range(len(self.g_best_val_dummy), min(it, len(vals))):
+        first = len(self.g_best_val_dummy)
+        it, w, vals, replaced, gpos = e.report(first)
+        for k in range(len(vals)):
             v = np.asarray([vals[k]], dtype=np.float32)
             if replaced[k]:
                 if len(self.g_best_val) == 1 and np.all(np.isinf(self.g_best_val[-1])):
@@ -279,7 +283,7 @@ class Swarm:
                 else:
                     self.g_best_val.append(v)
             self.g_best_val_dummy.append(v)
-        self.g_best_pos = e.gbest_pos[:self.dim_space].double().cpu().numpy()
+        self.g_best_pos = gpos[:self.dim_space].astype(np.float64)
         if self._inertia_decay != 1.0:
             self._w_inertia = w                    # mirror of the device-side schedule (no write-back)
 

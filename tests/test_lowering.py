@@ -1,5 +1,7 @@
 """CPU: the pixel-GEMM lowering tables reproduce torch's convolutions (geometry exact in fp32,
 bf16 pipeline within the stated tolerance)."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -197,3 +199,33 @@ def test_tiled_image_band_matches_conv_transpose(monkeypatch, h, wd, cin):
     assert np.abs(y32 - ref).max() <= 5e-6
     conn = lambda n_in: sum(1 for o in range(2 * n_in) for k in range(4) if (o + 1 - k) % 2 == 0 and 0 <= (o + 1 - k) // 2 < n_in)
     assert pr.macs_exact == conn(h) * conn(wd) * cin and pr.out_pitch == 0 and pr.out32_pitch == 4 * h * wd
+
+
+def test_pack_tables_reconstructs_every_step_list():
+    """The tables the engine uploads store step patterns relative to a per-job base column and share them between jobs
+    (`pack_tables`): expanding them again must give back `pack_steps` job by job -- for plain, chained (NEXT ops), banded, tiled-band
+    and identity-op layers -- and the wide layers must shrink enough to fit the kernel's shared-memory tables."""
+    torch.manual_seed(0)
+    g, d = port.Generator(100, 1, 64).eval(), port.Discriminator(1, 64).eval()
+    progs = nets.generator_programs({k: v.numpy() for k, v in g.state_dict().items()}) + \
+        nets.discriminator_programs({k: v.numpy() for k, v in d.state_dict().items()})
+    g256 = port.G256(10, 1, 8).eval()
+    progs += nets.g256_programs({k: v.numpy() for k, v in g256.state_dict().items()}, "gen")
+    vq = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_vq.npz"))
+    ops, _, _ = nets.vq_grid_decoder_programs({k[len("vqgrid/"):]: vq[k] for k in vq.files if k.startswith("vqgrid/decoder.")})
+    progs += [op.prog for op in ops]
+    for prog in progs:
+        full = L.pack_steps(prog)
+        steps, jobs = L.pack_tables(prog)
+        ref_jobs = L.pack_jobs(prog)
+        assert steps.shape[0] <= full.shape[0] and jobs.shape == ref_jobs.shape
+        for j in range(jobs.shape[0]):
+            sb, sc = int(ref_jobs[j, 0]), int(ref_jobs[j, 1])
+            base = (int(jobs[j, 7]) >> 1) * 8
+            blk = steps[int(jobs[j, 0]):int(jobs[j, 0]) + sc].copy()
+            assert int(jobs[j, 1]) == sc and base % 64 == 0 and (int(jobs[j, 7]) & 1) == int(ref_jobs[j, 7])
+            blk[:, 0] += base
+            assert np.array_equal(blk, full[sb:sb + sc]), f"{prog.name} job {j}"
+            assert np.array_equal(jobs[j, 1:7], ref_jobs[j, 1:7])
+    wide = next(p for p in progs if p.meta.get("kind") == "convt_image_band_tiled")
+    assert L.pack_tables(wide)[0].shape[0] <= 1024 < wide.n_steps

@@ -51,7 +51,21 @@ constexpr int kMetaOpsMask = 7, kMetaResident = 8, kMetaHasNext = 16, kMetaEye =
 constexpr int kEyeBytes = 64 * 128;   // built-in 64 x 64 bf16 identity tile (SWIZZLE_128B rows): the B operand of an identity op
 // op word: bits 0-15 weight row / 16, bits 16-23 accumulator column / 2, bit 24 NEXT job's buffer, bit 25 accumulate
 // job word 7: bit 0 = the job has a chain predecessor, bits 1.. = (base column of the job's step list) / 8 (psob/lowering.py pack_tables)
-__host__ __device__ __forceinline__ int job_abase(const int4& j1) { return (int)(((unsigned)j1.w >> 1) << 3); }
+// x / d for x < 2^31 as (x * magic) >> shift: L = ceil(log2 d), magic = ceil(2^(31 + L) / d) < 2^32, shift = 31 + L.
+// Exact because magic * d - 2^(31 + L) < d <= 2^L and x < 2^31.
+__host__ __device__ __forceinline__ uint32_t fast_div(uint32_t x, uint32_t magic, uint32_t shift) {
+  return (uint32_t)(((unsigned long long)x * magic) >> shift);
+}
+static inline void fast_div_magic(uint32_t d, uint32_t* magic, uint32_t* shift) {
+  uint32_t L = 0;
+  while ((1ull << L) < d) ++L;
+  const unsigned long long num = 1ull << (31 + L);
+  *magic = (uint32_t)((num + d - 1) / d);
+  *shift = 31 + L;
+}
+// j1.w = chain flag | (base column / 8) << 1; the DEVICE copy of the table carries the job's valid 64-column chunks in bits 28..31
+// (filled in by psob_layer_create from the column map and the pixel mask, so the epilogue does not look them up per job)
+__host__ __device__ __forceinline__ int job_abase(const int4& j1) { return (int)((((unsigned)j1.w & 0x0FFFFFFFu) >> 1) << 3); }
 __host__ __device__ __forceinline__ int op_b_row(int op) { return (op & 0xFFFF) << 4; }
 __host__ __device__ __forceinline__ int op_d_col(int op) { return ((op >> 16) & 0xFF) << 1; }
 __host__ __device__ __forceinline__ int op_next(int op) { return (op >> 24) & 1; }
@@ -83,6 +97,7 @@ struct EngineParams {
   int n_stages, stage_bytes, res_off, bar_off, stg_off;
   int vec4, strided;
   int no_bias;               // every bias entry is 0 (e.g. folded into the K padding): the chunked epilogue skips the loads and adds
+  uint32_t nc_magic, nc_shift, rot_magic, rot_shift;   // x / n_chains, x / rot_div for x < 2^31 as (x * magic) >> shift (fast_div_magic)
   int rot_div;               // chain rotation: item (tile t, slot r) runs chain (r + t / rot_div) % n_chains (0: chain r) -- see pick_rotation
   int chain_ident;           // every chain is one job (chain c == job c): the chain table is not read
   int step_stride;           // int4 words per step in the shared-memory copy of the step table (1 when no step has > 2 ops)
@@ -294,10 +309,17 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   // half the pixels, the last image band) and idle at the end.  Rotating the slot -> chain map by the tile index
   // (host-picked divisor) spreads every chain over every worker and keeps the chains of a tile on neighbouring workers.
   const uint32_t q_rot_div = (uint32_t)p.rot_div;
+  const uint32_t q_nc_magic = p.nc_magic, q_nc_shift = p.nc_shift, q_rot_magic = p.rot_magic, q_rot_shift = p.rot_shift;
   auto item_chain = [&](long long item, int& ptile) -> uint32_t {
-    const uint32_t t = (uint32_t)item / n_chains_u;          // 32-bit: n_items < 2^31 (checked on the host)
+    // 32-bit: n_items < 2^31 (checked on the host); divisions by multiply + shift -- the emulated 32-bit division is ~25
+    // dependent instructions, three of them per item and role sat in the epilogue's per-job prelude (ncu: 15 % of its samples)
+    const uint32_t t = fast_div((uint32_t)item, q_nc_magic, q_nc_shift);
     uint32_t c = (uint32_t)item - t * n_chains_u;
-    if (q_rot_div) { c += (t / q_rot_div) % n_chains_u; if (c >= n_chains_u) c -= n_chains_u; }
+    if (q_rot_div) {
+      const uint32_t r = fast_div(t, q_rot_magic, q_rot_shift);
+      c += r - fast_div(r, q_nc_magic, q_nc_shift) * n_chains_u;
+      if (c >= n_chains_u) c -= n_chains_u;
+    }
     ptile = (int)t;
     return c;
   };
@@ -594,6 +616,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     uint32_t sflip = 0;                       // staging tile in use (double-buffered when stg_bufs == 2)
     const uint32_t sw = (uint32_t)(row & 7);
     uint32_t it = 0;
+    uint32_t grp_chunks = 0;                  // chunks of a job this group handles: grp, grp + groups, ...
+    for (int ch = grp; ch < (q_nt >> 6); ch += q_epi_groups) grp_chunks |= 1u << ch;
     const bool prof = q_prof;
     constexpr bool has_res = kRes;      // residual epilogue: its own instantiation (32 more live registers)
     unsigned long long w_tfull = 0, e_ld = 0, e_free = 0, e_math = 0, e_pub = 0;
@@ -632,9 +656,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         float racc = 0.f;                                              // reconstruction: this row's sum of squared differences over the job
         if (kTmaStore) {
           const int n_chunks = q_nt >> 6;
-          uint32_t vchunks = 0;               // this group's valid chunks of the job, looked up once (column map + pixel mask)
-          for (int ch = grp; ch < n_chunks; ch += q_epi_groups)
-            if (q_band || (s_cm[ch << 6] >= 0 && ((mask >> s_pix[ch << 6]) & 1ull))) vchunks |= 1u << ch;
+          // this group's valid chunks of the job: bits 28..31 of the job word (psob_layer_create), all chunks for an image band
+          const uint32_t vchunks = (q_band ? 0xFu : (uint32_t)j1.w >> 28) & grp_chunks;
           const int last = 31 - __clz((int)vchunks);      // last chunk this group will read: release TMEM right after it (-1: none)
           if (last < 0) {
             ptx::tc_fence_before();
@@ -1333,7 +1356,22 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
           st[8 * s + 2 + o] |= ((op_d_col(st[8 * s + 2 + o]) / d->mma_n) & 1) << 27;
     PSOB_CUDA_L(cudaMemcpy(l->steps, st.data(), sizeof(int4) * 2 * d->n_steps, cudaMemcpyHostToDevice));
   }
-  PSOB_CUDA_L(cudaMemcpy(l->jobs, d->jobs, sizeof(int4) * 2 * d->n_jobs, cudaMemcpyHostToDevice));
+  {
+    // valid 64-column chunks of every job (column map entry >= 0 and the chunk's pixel set in the job's mask) -> bits 28..31 of
+    // job word 7 in the device copy; the chunked epilogue reads them instead of looking both up per job and chunk
+    std::vector<int32_t> jb(d->jobs, d->jobs + (size_t)8 * d->n_jobs);
+    for (int j = 0; j < d->n_jobs; ++j) {
+      const unsigned long long mask = (unsigned long long)(uint32_t)jb[8 * j + 4] | ((unsigned long long)(uint32_t)jb[8 * j + 5] << 32);
+      uint32_t bits = 0;
+      for (int ch = 0; ch < 4 && ch * 64 < d->nt; ++ch) {
+        const int pix = (ch * 64) / d->cc;
+        if (d->col_map[ch * 64] >= 0 && pix < 64 && ((mask >> pix) & 1ull)) bits |= 1u << ch;
+      }
+      if ((uint32_t)jb[8 * j + 7] >> 28) { psob_layer_destroy(l); return fail(PSOB_E_ARG, "psob_layer_create: job %d: base column beyond 2^30", j); }
+      jb[8 * j + 7] = (int32_t)((uint32_t)jb[8 * j + 7] | (bits << 28));
+    }
+    PSOB_CUDA_L(cudaMemcpy(l->jobs, jb.data(), sizeof(int4) * 2 * d->n_jobs, cudaMemcpyHostToDevice));
+  }
   PSOB_CUDA_L(cudaMemcpy(l->col_map, d->col_map, sizeof(int) * d->nt, cudaMemcpyHostToDevice));
   PSOB_CUDA_L(cudaMemcpy(l->col_map32, d->col_map32, sizeof(int) * d->nt, cudaMemcpyHostToDevice));
   PSOB_CUDA_L(cudaMemcpy(l->bias, d->bias, sizeof(float) * d->nt * d->n_bias_rows, cudaMemcpyHostToDevice));
@@ -1638,6 +1676,8 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
     p.idesc = make_idesc_bf16(2 * kTileM, d.mma_n);
   }
   p.rot_div = l->strided ? pick_rotation(l, p.n_items / d.n_chains, l->pair ? l->sm_count / 2 : l->sm_count) : 0;
+  fast_div_magic((uint32_t)d.n_chains, &p.nc_magic, &p.nc_shift);
+  fast_div_magic(p.rot_div > 0 ? (uint32_t)p.rot_div : 1u, &p.rot_magic, &p.rot_shift);
   if (!l->have_tmB) {
     int rc = make_tmap(&l->tmB, l->wpack, kKChunk, (uint64_t)d.n_wrows, kKChunk, (uint32_t)(l->pair ? d.mma_n / 2 : d.mma_n));
     if (rc) return rc;

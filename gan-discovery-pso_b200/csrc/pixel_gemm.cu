@@ -72,8 +72,11 @@ __host__ __device__ __forceinline__ int op_next(int op) { return (op >> 24) & 1;
 __host__ __device__ __forceinline__ int op_acc(int op) { return (op >> 25) & 1; }
 __host__ __device__ __forceinline__ int op_eye(int op) { return (op >> 26) & 1; }
 __host__ __device__ __forceinline__ int op_region(int op) { return (op >> 27) & 1; }   // set by psob_layer_create: parity of the op's column region (2 issuers)   // D[:, d_col : d_col + 64] (+)= A (N = 64 against the identity tile)                  // job descriptors staged in SMEM (32 B each)
-constexpr int kMaxEpiGroups = 2;                  // epilogue groups of 4 warps (one per TMEM lane quadrant)
-constexpr int kMaxThreads = 32 * (4 * kMaxEpiGroups + 3);   // + TMA warp + 1 or 2 MMA warps; blockDim = 32 * (4 * epi_groups + 1 + issuers)
+constexpr int kMaxEpiGroups = 3;                  // epilogue groups of 4 warps (one per TMEM lane quadrant); 3: lean kernels only
+constexpr int kMaxThreads = 32 * (4 * 2 + 3);     // + TMA warp + 1 or 2 MMA warps; blockDim = 32 * (4 * epi_groups + 1 + issuers)
+// lean kernels: up to 3 groups + TMA warp + ONE MMA warp = 14 warps.  ptxas keeps the lean epilogue in 128 registers without a
+// spill under this bound (it takes 168 under the 352-thread bound because it may, not because it must).
+constexpr int kMaxThreadsLean = 32 * (4 * kMaxEpiGroups + 2);
 // The SMSP arbiter favours the highest warp id: the two single-thread roles that must never wait for
 // an issue slot (TMA producer, MMA issuer) get the top ids; epilogue warps 0..7 map to TMEM quadrant w % 4.
 // (warp ids 4 * epi_groups and 4 * epi_groups + 1, see kTmaWarp / kMmaWarp in the kernel)
@@ -243,7 +246,7 @@ __device__ __forceinline__ uint32_t act_pack(uint32_t v0, uint32_t v1) {
 // role profiling.  ncu (r02_ncu_step_v22): the epilogue warps of the short-chain layers executed 288 instructions per 64-column
 // chunk, 32 conversions and 8 stores among them; the rest were uniform branches over these run-time modes.
 template <int kAct, bool kTmaStore, bool kPair, bool kRes = false, bool kDot = false, bool kLean = false>
-__global__ void __launch_bounds__(kMaxThreads, 1)
+__global__ void __launch_bounds__(kLean ? kMaxThreadsLean : kMaxThreads, 1)
 pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmY, const EngineParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -616,8 +619,23 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     uint32_t sflip = 0;                       // staging tile in use (double-buffered when stg_bufs == 2)
     const uint32_t sw = (uint32_t)(row & 7);
     uint32_t it = 0;
-    uint32_t grp_chunks = 0;                  // chunks of a job this group handles: grp, grp + groups, ...
-    for (int ch = grp; ch < (q_nt >> 6); ch += q_epi_groups) grp_chunks |= 1u << ch;
+    // chunks of a job this group handles: grp, grp + groups, ...  With THREE groups and 4 chunks per job that would leave
+    // group 0 with two chunks of every job (no faster than two groups): the assignment rotates with the job counter instead,
+    // chunk ch of this CTA's it-th job goes to group (ch + rot) % 3, rot = (it * n_chunks) % 3 -- every group gets 4 chunks
+    // of every 3 jobs, and a group that is done with its chunk of job j moves on to job j + 1 in the other accumulator.
+    uint32_t grp_chunks = 0, grp_chunks1 = 0, grp_chunks2 = 0;
+    const bool q_rot3 = kLean && q_epi_groups == 3;
+    if (q_rot3) {
+      for (int ch = 0; ch < (q_nt >> 6); ++ch) {
+        if ((ch + 0) % 3 == grp) grp_chunks |= 1u << ch;
+        if ((ch + 1) % 3 == grp) grp_chunks1 |= 1u << ch;
+        if ((ch + 2) % 3 == grp) grp_chunks2 |= 1u << ch;
+      }
+    } else {
+      for (int ch = grp; ch < (q_nt >> 6); ch += q_epi_groups) grp_chunks |= 1u << ch;
+    }
+    const uint32_t rot_inc = (uint32_t)(q_nt >> 6) % 3u;
+    uint32_t rot3 = 0;
     const bool prof = q_prof;
     constexpr bool has_res = kRes;      // residual epilogue: its own instantiation (32 more live registers)
     unsigned long long w_tfull = 0, e_ld = 0, e_free = 0, e_math = 0, e_pub = 0;
@@ -657,14 +675,16 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         if (kTmaStore) {
           const int n_chunks = q_nt >> 6;
           // this group's valid chunks of the job: bits 28..31 of the job word (psob_layer_create), all chunks for an image band
-          const uint32_t vchunks = (q_band ? 0xFu : (uint32_t)j1.w >> 28) & grp_chunks;
+          const uint32_t my_chunks = !q_rot3 ? grp_chunks : (rot3 == 0 ? grp_chunks : (rot3 == 1 ? grp_chunks1 : grp_chunks2));
+          if (q_rot3) { rot3 += rot_inc; if (rot3 >= 3u) rot3 -= 3u; }
+          const uint32_t vchunks = (q_band ? 0xFu : (uint32_t)j1.w >> 28) & my_chunks;
           const int last = 31 - __clz((int)vchunks);      // last chunk this group will read: release TMEM right after it (-1: none)
           if (last < 0) {
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) release_tmem(buf);
           }
-          for (int ch = grp; ch < n_chunks; ch += q_epi_groups) {
+          for (int ch = q_rot3 ? 0 : grp; ch < n_chunks; ch += q_rot3 ? 1 : q_epi_groups) {
             // image band: chunk ch = padded image rows 2ch, 2ch+1 of the band = accumulator columns [60 ch, 60 ch + 60)
             const int n0 = q_band ? ch * 2 * kBandPitch : ch << 6;
             if (!((vchunks >> ch) & 1u)) continue;                                    // uniform over the group
@@ -1480,7 +1500,28 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   long long total_steps = 0;                 // A-tile loads of one particle tile (per job, not per shared step record)
   for (int j = 0; j < d->n_jobs; ++j) total_steps += d->jobs[8 * j + 1];
   l->epi_groups = (l->pair && !l->band && total_steps * 2 * d->mma_n >= 6000ll * d->n_jobs) ? 1 : 2;   // a third group measured no faster (TMA-bound)
-  { const char* e = knob("PSOB_EPI_GROUPS"); if (e && atoi(e) >= 1 && atoi(e) <= kMaxEpiGroups) l->epi_groups = atoi(e); }
+  { const char* e = knob("PSOB_LEAN"); l->lean = e ? atoi(e) != 0 : true; }
+  { const char* e = knob("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
+  // three groups: lean kernels only (14 warps), i.e. no band, tile-major output, never a residual run (solo hint) or a fused head
+  const bool can3 = l->lean && l->warp_store && l->tma_store && !l->band && d->out_tiled && !d->solo && !d->dot_head && l->issuers == 1;
+  // ... chosen for layers with at most 4 A-tile loads per job (the MMA chain of a job is shorter than two chunks of epilogue)
+  // when the third group's staging tiles do not cost the ring a stage it needs (g.l2, 128 KB resident: 0.69 -> 0.80 ms with 3).
+  // Measured (profiles/r02_epi_groups3_ab.log): d.c1 0.428 -> 0.382 ms; g.l1 0.170 -> 0.171 (bound by the mixed TMA load + store
+  // traffic of its streamed weights, profiles/r01_tma_bench.log).  PSOB_EPI3=0 keeps two groups.
+  {
+    const int room = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes;
+    auto stages_for = [&](int groups) {       // ring depth next to `groups` groups' staging tiles (same rule as below)
+      const int bufs = (room - 2 * groups * kATileBytes) / l->stage_bytes >= (l->pair ? 4 : 3) ? 2 : 1;
+      const int n = (room - groups * bufs * kATileBytes) / l->stage_bytes;
+      return n > kMaxStages ? kMaxStages : n;
+    };
+    const int s2 = stages_for(2), s3 = stages_for(3);
+    const char* e = knob("PSOB_EPI3");
+    // resident weights only: with streamed weights the mixed TMA load + store traffic is the bound (profiles/r01_tma_bench.log)
+    // and a third group changes nothing or costs 1-3 % (g.l1, G256 l2, the assessor's 1x1 convs: profiles/r02_epi3_heuristic_ab.log)
+    if (can3 && l->epi_groups == 2 && d->b_resident && total_steps <= 4ll * d->n_jobs && s3 >= (s2 < 4 ? s2 : 4) && !(e && atoi(e) == 0)) l->epi_groups = 3;
+  }
+  { const char* e = knob("PSOB_EPI_GROUPS"); if (e && atoi(e) >= 1 && atoi(e) <= (can3 ? 3 : 2)) l->epi_groups = atoi(e); }
   if (!l->tma_store) l->epi_groups = 2;             // the direct-store epilogue uses group 0 only (thread layout of 2 groups)
   l->dot_head = d->dot_head != 0;
   if (l->dot_head && (!l->tma_store || l->band || d->out32_pitch)) {
@@ -1513,6 +1554,10 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   // 8 stages 6.91 ms, 6: 5.08, 4: 4.91, 3: 5.27 (profiles/r02_g256_ring_depth_ab.log).  The 28 x 28 band (25 KB per particle,
   // at its HBM floor) is the opposite: 8 stages 0.311 ms, 4 stages 0.355 (profiles/r02_config2_ring_depth_ab.log).
   if (l->band_wide && l->n_stages > 4) l->n_stages = 4;
+  if (knob("PSOB_VERBOSE"))
+    fprintf(stderr, "psob_layer_create: nt %d jobs %d steps %d (%lld loads per tile) pair %d resident %d in_tiled %d out_tiled %d tma_store %d band %d dot %d | "
+            "epi groups %d staging bufs %d ring %d x %d B\n", d->nt, d->n_jobs, d->n_steps, total_steps, (int)l->pair, d->b_resident, d->in_tiled, d->out_tiled,
+            (int)l->tma_store, (int)l->band, d->dot_head, l->epi_groups, l->stg_bufs, l->n_stages, l->stage_bytes);
   { const char* e = knob("PSOB_MAX_STAGES"); if (e && atoi(e) >= 2 && l->n_stages > atoi(e)) l->n_stages = atoi(e); }
   if (l->n_stages < 2) {
     psob_layer_destroy(l);
@@ -1523,8 +1568,6 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   l->bar_off = l->stg_off + stg_bytes;
   l->smem_bytes = l->bar_off + kBarBytes + l->tab_bytes + 1024;
   { const char* e = knob("PSOB_STRIDED"); l->strided = e ? atoi(e) != 0 : true; }
-  { const char* e = knob("PSOB_LEAN"); l->lean = e ? atoi(e) != 0 : true; }
-  { const char* e = knob("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
   l->chain_ident = d->n_chains == d->n_jobs && !(knob("PSOB_CHAIN_IDENT") && atoi(knob("PSOB_CHAIN_IDENT")) == 0);
   for (int c = 0; c < d->n_chains && l->chain_ident; ++c) if (d->chains[2 * c] != c || d->chains[2 * c + 1] != 1) l->chain_ident = false;
   l->no_bias = true;
@@ -1668,6 +1711,8 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   if (l->pair && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a CTA-pair layer needs its bf16 output buffer");
   // lean instantiation: every mode the generic kernel tests per chunk is the common one (A/B: PSOB_LEAN=0)
   const bool lean = l->lean && tma_store && !res && !l->band && !l->band_wide && l->warp_store && d.out_tiled && !l->prof;
+  if (l->epi_groups == 3 && !lean)
+    return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: a layer with three epilogue groups runs the lean kernel only (no residual, no role counters)");
   UmmaKernelFn fn = umma_kernel_for(d.act, tma_store, l->pair, res != nullptr, dot, lean);
   if (!fn) return fail(PSOB_E_ARG, "psob_layer_run: no kernel for activation %d%s", d.act,
                        res ? " with a residual (solo CTAs, ReLU / none only)" : (dot ? " with a fused head (ReLU / LeakyReLU only)" : ""));

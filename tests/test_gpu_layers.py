@@ -213,6 +213,51 @@ def test_layouts_and_execution_modes_agree_bit_for_bit(mods, monkeypatch, P):
             assert torch.equal(a, b), f"mode (tiled, pair, strided, chain)={key}: tensor {i} differs"
 
 
+@pytest.mark.parametrize("P", [129, 700])
+def test_epilogue_flavours_agree_bit_for_bit(mods, monkeypatch, golden_resnet, P):
+    """The epilogue's organisation is scheduling only: the generic kernel (PSOB_LEAN=0), the lean instantiation with one, two
+    and three epilogue groups (three: chunk -> group assignment rotating with the job counter; forced here on every layer
+    that can take it, so jobs of 4, 2 and 1 chunks and masked border jobs all go through the rotation) must give every hidden
+    activation, the image, the score and a shallow assessor's logits identical to the last bit."""
+    engine, L, nets, ffi = mods
+    torch.manual_seed(5)
+    gen = port.Generator(100, 1, 64)
+    port.randomize_bn_stats(gen, torch.Generator().manual_seed(6))
+    disc = port.Discriminator(1, 64)
+    g = golden_resnet
+    *layers, n_class, seed = (int(v) for v in g["r2121_c3/meta"])
+    cnn = port.Resnet(layers, 1, list(range(n_class)), n_class).eval()
+    port.seeded_fill(cnn, seed)
+    z = torch.randn(P, 100, generator=torch.Generator().manual_seed(P))
+    ximg = torch.rand(P, 784, generator=torch.Generator().manual_seed(P + 1))
+    monkeypatch.setenv("PSOB_TUNING", "1")
+    results = {}
+    for key, env in (("default", {}), ("generic", {"PSOB_LEAN": "0"}), ("two", {"PSOB_EPI3": "0"}),
+                     ("three", {"PSOB_EPI_GROUPS": "3"}), ("one", {"PSOB_EPI_GROUPS": "1"})):
+        for k in ("PSOB_LEAN", "PSOB_EPI3", "PSOB_EPI_GROUPS"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        gnet = engine.GeneratorNet(gen.state_dict(), P)
+        dnet = engine.DiscriminatorNet(disc.state_dict(), P, fused_head=False)
+        fused = engine.DiscriminatorNet(disc.state_dict(), P)
+        anet = engine.AssessorNet(cnn.state_dict(), P)
+        _, img = gnet.forward(_rows(z.numpy(), gnet.in_pitch))
+        _, score = dnet.forward(gnet.image_padded_bf16())
+        _, score_fused = fused.forward(gnet.image_padded_bf16())
+        logits = anet.forward(ximg.cuda())
+        torch.cuda.synchronize()
+        results[key] = [gnet.activation(i).cpu() for i in range(3)] + [dnet.activation(i).cpu() for i in range(2)] + \
+            [img.cpu(), score.cpu(), score_fused.cpu(), logits.cpu()]
+    for key, got in results.items():
+        for i, (a, b) in enumerate(zip(results["generic"], got)):
+            if key == "one" and i == 7:
+                # the fused head keeps one partial sum per (job, group): with one group the same terms are added in another order
+                assert torch.allclose(a, b, atol=1e-6, rtol=0)
+                continue
+            assert torch.equal(a, b), f"epilogue flavour {key}: tensor {i} differs from the generic kernel"
+
+
 def test_g256_generator_small_widths_vs_reference(mods):
     """EXTENSION generator 1x256x256 (BASELINE config 4 shape; port.G256) at reduced widths (128..4 channels): seven
     layers, streamed weights, chunked bias rows, fp32 image [P, 65536]; tcgen05 == SIMT interpreter and both within the

@@ -1710,7 +1710,7 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   if (d.out_tiled && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a tile-major output needs its bf16 output buffer");
   if (l->pair && !tma_store) return fail(PSOB_E_ARG, "psob_layer_run: a CTA-pair layer needs its bf16 output buffer");
   // lean instantiation: every mode the generic kernel tests per chunk is the common one (A/B: PSOB_LEAN=0)
-  const bool lean = l->lean && tma_store && !res && !l->band && !l->band_wide && l->warp_store && d.out_tiled && !l->prof;
+  const bool lean = l->lean && tma_store && !res && !l->band && !l->band_wide && l->warp_store && (d.out_tiled || dot) && !l->prof;   // a fused head stores nothing
   if (l->epi_groups == 3 && !lean)
     return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: a layer with three epilogue groups runs the lean kernel only (no residual, no role counters)");
   UmmaKernelFn fn = umma_kernel_for(d.act, tma_store, l->pair, res != nullptr, dot, lean);

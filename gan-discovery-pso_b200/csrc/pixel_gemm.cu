@@ -1499,7 +1499,12 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   // (TMEM load -> bias/activation -> swizzled st.shared -> TMA store): a third group hides more of it
   long long total_steps = 0;                 // A-tile loads of one particle tile (per job, not per shared step record)
   for (int j = 0; j < d->n_jobs; ++j) total_steps += d->jobs[8 * j + 1];
-  l->epi_groups = (l->pair && !l->band && total_steps * 2 * d->mma_n >= 6000ll * d->n_jobs) ? 1 : 2;   // a third group measured no faster (TMA-bound)
+  // threshold 3000 tensor cycles per job (it was 6000): with the lean epilogue one group keeps up with shorter chains, and the ring's
+  // extra stage is worth more -- G256's 128 -> 64 layer (7.76 loads per job) 8.81 -> 7.72 ms, g.l2 (6.1 loads per job) 0.686 -> 0.678,
+  // assessor unchanged (profiles/r02_group1_threshold_ab.log); PSOB_GROUP1_CYCLES overrides
+  long long group1_cycles = 3000;
+  { const char* e = knob("PSOB_GROUP1_CYCLES"); if (e && atoll(e) > 0) group1_cycles = atoll(e); }
+  l->epi_groups = (l->pair && !l->band && total_steps * 2 * d->mma_n >= group1_cycles * d->n_jobs) ? 1 : 2;
   { const char* e = knob("PSOB_LEAN"); l->lean = e ? atoi(e) != 0 : true; }
   { const char* e = knob("PSOB_WARP_STORE"); l->warp_store = e ? atoi(e) != 0 : true; }   // measured -4 % on the forward pass vs group stores     // tuning knob (default: strided)
   // three groups: lean kernels only (14 warps), i.e. no band, tile-major output, never a residual run (solo hint) or a fused head

@@ -107,7 +107,9 @@ struct EngineParams {
   int warp_store;            // every epilogue warp stores its own 32 rows of a chunk (32-row TMA box): no barriers inside a group
   int issuers;               // MMA-issuing warps (1 or 2): one thread sustains only ~1 tcgen05.mma per 85-94 cycles (tools/umma_bench.cu)
   int issue_split;           // 2 issuers: ownership of an op by (accumulator buffer + column region) parity (1) or by buffer only (0)
-  int half_store;            // warp stores with a single staging tile: the warp's 4 KB slice is two 32-column halves (SWIZZLE_64B)
+  int half_store;            // warp stores with a single staging tile: the warp's 4 KB slice is two 32-column halves (SWIZZLE_64B);
+                             // 2: QUARTER stores -- a 2 KB slice per warp, two 16-column quarters (SWIZZLE_32B), 8 KB of staging per group
+  int stg_group_bytes;       // staging bytes per epilogue group (stg_bufs * 16 KB, quarter stores: 8 KB)
                              // published by separate TMA stores, so one half drains while the other is written
   int band;                  // image-band epilogue (lower_convt_image_band): 4 chunks of two padded image rows each; 2: tiled band
   int band_w;                // tiled band: width of the image in pixels (row pitch of the fp32 image / the target)
@@ -266,6 +268,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const bool q_warp_store = kLean || (kTmaStore && p.warp_store != 0);
   const bool q_prof = !kLean && p.prof != nullptr;
   const bool q_half = q_warp_store && p.half_store != 0;
+  const bool q_quarter = q_warp_store && p.half_store == 2;
   const int q_n_in_chunks = p.n_in_chunks;
   const int q_n_out_chunks = p.n_out_chunks;
   const uint32_t q_idesc = p.idesc;
@@ -615,7 +618,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const int grp = warp >> 2;
     const int row = q * 32 + lane;
     const bool issuer_warp = (warp & 3) == 0;          // its elected lane issues / tracks the group's TMA stores
-    const uint32_t sbuf0 = base + p.stg_off + (uint32_t)(grp * q_stg_bufs) * kATileBytes;
+    const uint32_t sbuf0 = base + p.stg_off + (uint32_t)grp * (uint32_t)p.stg_group_bytes;
     uint32_t sflip = 0;                       // staging tile in use (double-buffered when stg_bufs == 2)
     const uint32_t sw = (uint32_t)(row & 7);
     uint32_t it = 0;
@@ -772,7 +775,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             }
             const uint32_t sbuf = sbuf0 + sflip * kATileBytes;
             const uint32_t srow = sbuf + (uint32_t)row * 128u;
-            const uint32_t hbase = sbuf0 + (uint32_t)q * 4096u;          // half mode: this warp's two 2 KB halves
+            // half mode: this warp's two 2 KB halves; quarter mode: two 1 KB quarters used alternately by the chunk's four quarters
+            const uint32_t hbase = sbuf0 + (uint32_t)q * (q_quarter ? 2048u : 4096u);
             auto half_open = [&](int) {                                  // at most the OTHER half's store may still be reading
               if (lane == 0) ptx::bulk_wait_read1();
               __syncwarp();
@@ -781,7 +785,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               ptx::fence_proxy_async();
               __syncwarp();
               if (lane == 0) {
-                ptx::tma_store_2d(&tmY, hbase + (uint32_t)h * 2048u, out_c0(j0.z + cm) + 32 * h, out_c1(ptile, j0.z + cm) + q * 32);
+                if (q_quarter) ptx::tma_store_2d(&tmY, hbase + (uint32_t)(h & 1) * 1024u, out_c0(j0.z + cm) + 16 * h, out_c1(ptile, j0.z + cm) + q * 32);
+                else ptx::tma_store_2d(&tmY, hbase + (uint32_t)h * 2048u, out_c0(j0.z + cm) + 32 * h, out_c1(ptile, j0.z + cm) + q * 32);
                 ptx::bulk_commit();
               }
               __syncwarp();
@@ -805,7 +810,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             // blocks and ptxas could not interleave the slots' bias -> activation -> pack chains: the epilogue warps issued
             // one instruction per ~5 cycles (ncu: 37 % fixed-latency 'wait' stalls, 20 % issuing).
             auto emit_slot = [&](auto kHalfTag, auto kNoBiasTag, int j, const float4& b0, const float4& b1) {
-              constexpr bool kHalf = decltype(kHalfTag)::value;
+              constexpr int kHalfMode = (int)decltype(kHalfTag)::value;      // 0 full tile, 1 halves, 2 quarters
+              constexpr bool kHalf = kHalfMode == 1;
               constexpr bool kNoBias = decltype(kNoBiasTag)::value && !has_res;
               if (has_res) {
                 const uint32_t rw[4] = {rres[j].x, rres[j].y, rres[j].z, rres[j].w};
@@ -825,7 +831,12 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               o.z = bias_act_pack<kAct>(v[8 * j + 4], v[8 * j + 5], b1.x, b1.y);
               o.w = bias_act_pack<kAct>(v[8 * j + 6], v[8 * j + 7], b1.z, b1.w);
               }
-              if (kHalf) {
+              if (kHalfMode == 2) {
+                // SWIZZLE_32B quarter tile [32 rows x 32 B]: 16-byte slot jj of row r lives at jj ^ ((r / 4) % 2)
+                if ((j & 1) == 0) half_open(j >> 1);
+                ptx::st_shared_v4(hbase + (uint32_t)((j >> 1) & 1) * 1024u + (uint32_t)lane * 32u + ((((uint32_t)j & 1u) ^ (((uint32_t)lane >> 2) & 1u)) << 4), o);
+                if ((j & 1) == 1) half_publish(j >> 1);
+              } else if (kHalf) {
                 // SWIZZLE_64B half tile [32 rows x 64 B]: 16-byte slot jj of row r lives at jj ^ ((r / 2) % 4)
                 if ((j & 3) == 0) half_open(j >> 2);
                 ptx::st_shared_v4(hbase + (uint32_t)(j >> 2) * 2048u + (uint32_t)lane * 64u + ((((uint32_t)j & 3u) ^ (((uint32_t)lane >> 1) & 3u)) << 4), o);
@@ -884,7 +895,9 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                     emit_slot(kHalfTag, std::false_type{}, j, __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j)), __ldg(reinterpret_cast<const float4*>(bias + n0 + 8 * j + 4)));
                 }
               };
-              if (q_half) run_slots(std::true_type{}); else run_slots(std::false_type{});
+              if (q_quarter) run_slots(std::integral_constant<int, 2>{});
+              else if (q_half) run_slots(std::integral_constant<int, 1>{});
+              else run_slots(std::integral_constant<int, 0>{});
             }
             if (prof) { const long long t = clock64(); e_math += (unsigned long long)(t - tq); tq = t; }
             if (q_half) {
@@ -1167,6 +1180,7 @@ struct psob_layer {
   bool have_tmB = false;
   bool warp_store = false;         // per-warp 32-row TMA stores in the chunked epilogue (PSOB_WARP_STORE)
   bool lean = true;                // the lean kernel instantiation where its conditions hold (PSOB_LEAN=0: A/B)
+  bool quarter = false;            // quarter stores: two groups on the staging bytes of one (8 KB each), see psob_layer_create
   int issuers = 1;                 // MMA-issuing warps
   bool issue_split = true;
   bool eye = false;                // some step is an identity op (streamed layers): 8 KB identity tile at res_off
@@ -1533,15 +1547,28 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     psob_layer_destroy(l);
     return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: dot_head needs a layer with the chunked bf16 epilogue");
   }
+  // Quarter stores (A/B knob, OFF by default): where the rule above gave a layer ONE epilogue group to buy a ring stage, two groups
+  // fit into the same 16 KB when every warp stages 16-column quarters (2 x 1 KB per warp, SWIZZLE_32B, four 32-row TMA stores per
+  // chunk) instead of 32-column halves.  Bit-identical (tests), but measured no faster: g.l2 0.670 vs 0.672 ms, G256's 128 -> 64
+  // layer 7.9 vs 7.8 (profiles/r02_quarter_store_ab.log) -- with the lean epilogue one group is not on the critical path there.
+  // PSOB_QUARTER=1 switches it on for those layers, =2 forces it on every layer that can take it.
+  {
+    const char* e = knob("PSOB_QUARTER");
+    l->quarter = l->lean && l->warp_store && l->tma_store && !l->band && !l->dot_head && d->out_tiled && l->pair && l->epi_groups == 1 &&
+                 !knob("PSOB_EPI_GROUPS") && e && atoi(e) >= 1;
+    if (e && atoi(e) == 2 && l->lean && l->warp_store && l->tma_store && !l->band && !l->dot_head && d->out_tiled && l->epi_groups <= 2) l->quarter = true;   // A/B: force
+    if (l->quarter) l->epi_groups = 2;
+  }
   if (l->tma_store && !l->dot_head && !l->band_wide) {      // a tiled band stages nothing: its epilogue works from registers
     const int room = kSmemLimit - 1024 - kBarBytes - l->tab_bytes - res_bytes;
     l->stg_bufs = (room - 2 * l->epi_groups * kATileBytes) / l->stage_bytes >= (l->pair ? 4 : 3) ? 2 : 1;
+    if (l->quarter) l->stg_bufs = 1;
     // a third staging tile per group where the ring stays >= 4 deep (PSOB_STG3=1; A/B knob): the epilogue warps of
     // store-bound layers wait ~10 % of their time for the store of two chunks ago to release its tile
     const char* e = knob("PSOB_STG3");
     if (l->stg_bufs == 2 && !l->band && e && atoi(e) != 0 && (room - 3 * l->epi_groups * kATileBytes) / l->stage_bytes >= 4) l->stg_bufs = 3;
   }
-  int stg_bytes = l->epi_groups * l->stg_bufs * kATileBytes;
+  int stg_bytes = l->quarter ? l->epi_groups * 8192 : l->epi_groups * l->stg_bufs * kATileBytes;
   if (l->dot_head) {
     // nothing is staged: the area holds the head's bf16 weights, and the second epilogue group is free -- it halves the
     // time an accumulator buffer stays occupied, which chained jobs wait for (they acquire the next buffer early)
@@ -1561,8 +1588,8 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
   if (l->band_wide && l->n_stages > 4) l->n_stages = 4;
   if (knob("PSOB_VERBOSE"))
     fprintf(stderr, "psob_layer_create: nt %d jobs %d steps %d (%lld loads per tile) pair %d resident %d in_tiled %d out_tiled %d tma_store %d band %d dot %d | "
-            "epi groups %d staging bufs %d ring %d x %d B\n", d->nt, d->n_jobs, d->n_steps, total_steps, (int)l->pair, d->b_resident, d->in_tiled, d->out_tiled,
-            (int)l->tma_store, (int)l->band, d->dot_head, l->epi_groups, l->stg_bufs, l->n_stages, l->stage_bytes);
+            "epi groups %d staging bufs %d quarter %d ring %d x %d B\n", d->nt, d->n_jobs, d->n_steps, total_steps, (int)l->pair, d->b_resident, d->in_tiled, d->out_tiled,
+            (int)l->tma_store, (int)l->band, d->dot_head, l->epi_groups, l->stg_bufs, (int)l->quarter, l->n_stages, l->stage_bytes);
   { const char* e = knob("PSOB_MAX_STAGES"); if (e && atoi(e) >= 2 && l->n_stages > atoi(e)) l->n_stages = atoi(e); }
   if (l->n_stages < 2) {
     psob_layer_destroy(l);
@@ -1692,6 +1719,8 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   p.issuers = l->issuers; p.issue_split = l->issue_split ? 1 : 0;
   p.warp_store = l->warp_store ? 1 : 0;
   { const char* e = knob("PSOB_HALF_STORE"); p.half_store = (l->warp_store && l->stg_bufs == 1 && !l->band && l->tma_store && (e ? atoi(e) != 0 : true)) ? 1 : 0; }   // measured: d.c2 -2.7 %, g.l2 -1 %
+  if (l->quarter) p.half_store = 2;
+  p.stg_group_bytes = l->quarter ? 8192 : l->stg_bufs * kATileBytes;
   if (p.n_items >= (1ll << 31)) return fail(PSOB_E_UNSUPPORTED, "psob_layer_run: %lld work items exceed 2^31", p.n_items);
   p.bias_off = l->bias_off; p.steps_off = l->steps_off; p.jobs_off = l->jobs_off; p.stg_bufs = l->stg_bufs; p.n_steps = d.n_steps;
   p.idesc = make_idesc_bf16(kTileM, d.mma_n);
@@ -1744,8 +1773,8 @@ static int layer_run_impl(psob_layer* l, const void* x, int64_t x_pitch, int64_t
   if (rc) return rc;
   if (tma_store && !dot && !l->band_wide) {
     const uint32_t box_rows = l->warp_store ? 32u : (uint32_t)kTileM;
-    const uint32_t box_cols = p.half_store ? 32u : (uint32_t)kKChunk;
-    const CUtensorMapSwizzle sw = p.half_store ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
+    const uint32_t box_cols = p.half_store == 2 ? 16u : (p.half_store ? 32u : (uint32_t)kKChunk);
+    const CUtensorMapSwizzle sw = p.half_store == 2 ? CU_TENSOR_MAP_SWIZZLE_32B : (p.half_store ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
     rc = d.out_tiled ? make_tmap(&tmY, y, kKChunk, (uint64_t)n_ptiles * (d.out_pitch / kKChunk) * kTileM, kKChunk, box_rows, box_cols, sw)
                      : make_tmap(&tmY, y, (uint64_t)d.out_pitch, (uint64_t)P, (uint64_t)d.out_pitch, box_rows, box_cols, sw);
     if (rc) return rc;

@@ -218,7 +218,9 @@ def test_epilogue_flavours_agree_bit_for_bit(mods, monkeypatch, golden_resnet, P
     """The epilogue's organisation is scheduling only: the generic kernel (PSOB_LEAN=0), the lean instantiation with one, two
     and three epilogue groups (three: chunk -> group assignment rotating with the job counter; forced here on every layer
     that can take it, so jobs of 4, 2 and 1 chunks and masked border jobs all go through the rotation) must give every hidden
-    activation, the image, the score and a shallow assessor's logits identical to the last bit."""
+    activation, the image, the score and a shallow assessor's logits identical to the last bit.  The same for the staging flavour:
+    16-column quarter stores (SWIZZLE_32B; default on the CTA-pair layers that would otherwise run one group) forced on every
+    layer that can take them, and switched off."""
     engine, L, nets, ffi = mods
     torch.manual_seed(5)
     gen = port.Generator(100, 1, 64)
@@ -233,8 +235,9 @@ def test_epilogue_flavours_agree_bit_for_bit(mods, monkeypatch, golden_resnet, P
     monkeypatch.setenv("PSOB_TUNING", "1")
     results = {}
     for key, env in (("default", {}), ("generic", {"PSOB_LEAN": "0"}), ("two", {"PSOB_EPI3": "0"}),
-                     ("three", {"PSOB_EPI_GROUPS": "3"}), ("one", {"PSOB_EPI_GROUPS": "1"})):
-        for k in ("PSOB_LEAN", "PSOB_EPI3", "PSOB_EPI_GROUPS"):
+                     ("three", {"PSOB_EPI_GROUPS": "3"}), ("one", {"PSOB_EPI_GROUPS": "1"}),
+                     ("quarter_forced", {"PSOB_QUARTER": "2"}), ("quarter_off", {"PSOB_QUARTER": "0"})):
+        for k in ("PSOB_LEAN", "PSOB_EPI3", "PSOB_EPI_GROUPS", "PSOB_QUARTER"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)

@@ -1,6 +1,8 @@
 """Per-role wait-cycle breakdown of the G256 layers (BASELINE config 4: P = 8192, f = 64), image layer with the fused
 reconstruction epilogue.  Knobs from the environment (with PSOB_TUNING=1)."""
 import os, sys
+# role counters exist in the generic kernel only: keep every layer on at most two epilogue groups (three run the lean kernel only)
+os.environ.setdefault("PSOB_TUNING", "1"); os.environ.setdefault("PSOB_EPI3", "0")
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "gan-discovery-pso_b200"))
 import numpy as np, torch

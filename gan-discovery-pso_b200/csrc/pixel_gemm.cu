@@ -1484,7 +1484,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     const long long mma_cycles = n_ops * 4 * (d->mma_n / 2 > 90 ? d->mma_n / 2 : 90);     // per instruction: N / 2 cycles, issue floor ~90
     const long long epi_cycles = n_chunks * 500;                                          // ~1000 cycles per chunk and group, 2 groups
     const char* e = knob("PSOB_STREAM_PAIR");
-    l->pair = e ? atoi(e) != 0 : (d->mma_n >= 128 && mma_cycles * 100 >= epi_cycles * (knob("PSOB_PAIR_RATIO") ? atoi(knob("PSOB_PAIR_RATIO")) : 150));
+    l->pair = e ? atoi(e) != 0 : (d->mma_n >= 128 && mma_cycles * 100 >= epi_cycles * (knob("PSOB_PAIR_RATIO") ? atoi(knob("PSOB_PAIR_RATIO")) : 100));   // 150 before the lean epilogue; at 100 the assessor's stem pairs up: 0.70 -> 0.61 ms (profiles/r02_pair_ratio_ab.log)
   }
   l->stage_bytes = kATileBytes + (d->b_resident ? 0 : (l->pair ? b_tile / 2 : b_tile));
   const int res_bytes = l->pair ? full_res_bytes / 2 : full_res_bytes;

@@ -71,6 +71,9 @@ __host__ __device__ __forceinline__ int op_d_col(int op) { return ((op >> 16) & 
 __host__ __device__ __forceinline__ int op_next(int op) { return (op >> 24) & 1; }
 __host__ __device__ __forceinline__ int op_acc(int op) { return (op >> 25) & 1; }
 __host__ __device__ __forceinline__ int op_eye(int op) { return (op >> 26) & 1; }
+// op width: the op covers (1 + w) * mma_n accumulator columns and weight rows (bits 28..29; resident weights, solo CTAs) --
+// neighbouring output pixels fed by one input pixel through neighbouring taps are one wider tcgen05.mma
+__host__ __device__ __forceinline__ int op_width(int op) { return 1 + (((unsigned)op >> 28) & 3); }
 __host__ __device__ __forceinline__ int op_region(int op) { return (op >> 27) & 1; }   // set by psob_layer_create: parity of the op's column region (2 issuers)   // D[:, d_col : d_col + 64] (+)= A (N = 64 against the identity tile)                  // job descriptors staged in SMEM (32 B each)
 constexpr int kMaxEpiGroups = 3;                  // epilogue groups of 4 warps (one per TMEM lane quadrant); 3: lean kernels only
 constexpr int kMaxThreads = 32 * (4 * 2 + 3);     // + TMA warp + 1 or 2 MMA warps; blockDim = 32 * (4 * epi_groups + 1 + issuers)
@@ -553,6 +556,8 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             };
             auto d_of = [&](int op) { return tmem_base + (buf ^ (uint32_t)op_next(op)) * (uint32_t)q_nt + (uint32_t)op_d_col(op); };
             auto mine = [&](int op) { return !two || (((buf ^ (uint32_t)op_next(op)) + (uint32_t)op_region(op)) & 1u) == wsel; };
+            // instruction descriptor of an op: N = width * mma_n (bits 17..22 hold N / 8)
+            auto idesc_of = [&](int op) { return (q_idesc & ~(0x3Fu << 17)) | ((uint32_t)((op_width(op) * q_mma_n) >> 3) << 17); };
             auto commit_only = [&]() { if (kPair) ptx::umma_commit_pair(empty_bar(stage)); else ptx::umma_commit(empty_bar(stage)); };
             if (n_ops == 1 && !mine(st.z)) {
               commit_only();
@@ -561,7 +566,7 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               const bool eye = !kPair && (st.y & kMetaEye) != 0;
               const uint64_t bdesc = ptx::smem_desc_sw128(eye ? base + q_res_off : b_addr_of(st.z));
               if (kPair) ptx::umma_bf16_k64_commit_pair(d_of(st.z), adesc, bdesc, q_idesc, (uint32_t)op_acc(st.z), empty_bar(stage));
-              else ptx::umma_bf16_k64_commit(d_of(st.z), adesc, bdesc, eye ? p.idesc_eye : q_idesc, (uint32_t)op_acc(st.z), empty_bar(stage));
+              else ptx::umma_bf16_k64_commit(d_of(st.z), adesc, bdesc, eye ? p.idesc_eye : idesc_of(st.z), (uint32_t)op_acc(st.z), empty_bar(stage));
             } else {
               // one A tile, several weight tiles: own / next job's accumulators (resident weights only)
               const int all_ops[4] = {st.z, n_ops > 1 ? st.w : st.z, n_ops > 2 ? st2.x : st.z, n_ops > 3 ? st2.y : st.z};
@@ -590,8 +595,12 @@ pixel_gemm_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 for (int o = 0; o < 4; ++o) {
                   dd[o] = d_of(ops[o]); aa[o] = (uint32_t)op_acc(ops[o]); bb[o] = ptx::smem_desc_sw128(b_addr_of(ops[o]));
                 }
-                if (kPair) ptx::umma_bf16_k64x4_commit_pair(dd, adesc, bb, q_idesc, aa, m, empty_bar(stage));
-                else ptx::umma_bf16_k64x4_commit(dd, adesc, bb, q_idesc, aa, m, empty_bar(stage));
+                if (kPair) {
+                  ptx::umma_bf16_k64x4_commit_pair(dd, adesc, bb, q_idesc, aa, m, empty_bar(stage));
+                } else {
+                  const uint32_t ii[4] = {idesc_of(ops[0]), idesc_of(ops[1]), idesc_of(ops[2]), idesc_of(ops[3])};
+                  ptx::umma_bf16_k64x4w_commit(dd, adesc, bb, ii, aa, m, empty_bar(stage));
+                }
               }
             }
           }
@@ -1099,7 +1108,7 @@ pixel_gemm_simt_kernel(const __nv_bfloat16* __restrict__ x, long long x_pitch, c
             if (n >= dc && n < dc + 64) acc = (op_acc(op) ? acc : 0.f) + __bfloat162float(a[n - dc]);
             continue;
           }
-          if (n < dc || n >= dc + p.mma_n) continue;
+          if (n < dc || n >= dc + p.mma_n * op_width(op)) continue;
           if (!op_acc(op)) acc = 0.f;
           const __nv_bfloat16* b = w + (size_t)(op_b_row(op) + n - dc) * kKChunk;
           for (int k = 0; k < kKChunk; ++k) acc += __bfloat162float(a[k]) * __bfloat162float(b[k]);
@@ -1274,6 +1283,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     return fail(PSOB_E_ARG, "psob_layer_create: vec8 needs bf16-only output with 16-byte aligned rows");
   // validate the tables so a bad program can never fault on the device
   if (d->n_chains <= 0 || !d->chains) return fail(PSOB_E_ARG, "psob_layer_create: no chains");
+  bool has_wide = false;          // ops wider than mma_n: solo CTAs only (a pair splits every weight tile by rows between its CTAs)
   for (int s = 0; s < d->n_steps; ++s) {
     const int32_t* st = d->steps + 8 * s;
     if (st[0] < 0 || st[0] % 8 || (d->in_tiled && st[0] % kKChunk))       // the range is checked per job below (a_col = job base + st[0])
@@ -1293,9 +1303,12 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     }
     for (int o = 0; o < n_ops; ++o) {
       if (op_eye(ops[o])) return fail(PSOB_E_ARG, "step %d op %d: identity ops cannot share a step", s, o);
-      const int br = op_b_row(ops[o]), dc = op_d_col(ops[o]);
-      if (br % 8 || br + d->mma_n > d->n_wrows) return fail(PSOB_E_ARG, "step %d op %d: b_row %d out of range", s, o, br);
-      if (dc + d->mma_n > d->nt) return fail(PSOB_E_ARG, "step %d op %d: d_col %d out of range", s, o, dc);
+      const int br = op_b_row(ops[o]), dc = op_d_col(ops[o]), wn = op_width(ops[o]) * d->mma_n;
+      if (op_width(ops[o]) > 1 && (!d->b_resident || wn > 256 || d->solo))
+        return fail(PSOB_E_ARG, "step %d op %d: a wide op (%d columns) needs resident weights, N <= 256 and no residual run", s, o, wn);
+      if (op_width(ops[o]) > 1) has_wide = true;
+      if (br % 8 || br + wn > d->n_wrows) return fail(PSOB_E_ARG, "step %d op %d: b_row %d out of range", s, o, br);
+      if (dc + wn > d->nt) return fail(PSOB_E_ARG, "step %d op %d: d_col %d out of range", s, o, dc);
       has_next = has_next || op_next(ops[o]);
     }
     if (has_next != ((st[1] & kMetaHasNext) != 0)) return fail(PSOB_E_ARG, "step %d: NEXT flag disagrees with its ops", s);
@@ -1379,6 +1392,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     // ops fall inside a region); layers with overlapping column windows (image band) are split by buffer only.
     const char* e = knob("PSOB_ISSUERS");
     l->issuers = e ? (atoi(e) == 2 ? 2 : 1) : 1;
+    if (has_wide) l->issuers = 1;          // a wide op spans both issuers' column regions
     l->issue_split = true;
     std::vector<int32_t> st(d->steps, d->steps + (size_t)8 * d->n_steps);
     for (int s = 0; s < d->n_steps; ++s)
@@ -1457,7 +1471,7 @@ int psob_layer_create(const psob_layer_desc* d, psob_layer** out) {
     const char* e = knob("PSOB_BAND_PAIR");
     if (e ? atoi(e) != 0 : true) l->pair = true;
   }
-  if (l->pair && (!l->tma_store || full_res_bytes / 2 > kMaxPairResident || d->mma_n % 32 || d->n_wrows % d->mma_n ||
+  if (l->pair && (has_wide || !l->tma_store || full_res_bytes / 2 > kMaxPairResident || d->mma_n % 32 || d->n_wrows % d->mma_n ||
                   (d->act != PSOB_ACT_NONE && d->act != PSOB_ACT_RELU && d->act != PSOB_ACT_LEAKY && !(l->band && d->act == PSOB_ACT_TANH)) || l->sm_count < 2)) {
     psob_layer_destroy(l);
     return fail(PSOB_E_UNSUPPORTED, "psob_layer_create: %d B of resident weights need the CTA-pair mode, which this layer cannot use", full_res_bytes);

@@ -272,6 +272,41 @@ __device__ __forceinline__ void umma_bf16_k64x4_commit(const uint32_t (&d)[4], u
                                                        const uint32_t (&acc)[4], int n_ops, uint32_t bar) {
   PSOB_UMMA_K64X4_BODY("1", "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%17];");
 }
+// The same with one instruction descriptor PER OP (ops of different widths N share an A tile; solo CTAs).
+__device__ __forceinline__ void umma_bf16_k64x4w_commit(const uint32_t (&d)[4], uint64_t a_desc, const uint64_t (&b)[4], const uint32_t (&idesc)[4],
+                                                        const uint32_t (&acc)[4], int n_ops, uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred p0, p1, p2, p3, e1, e2, e3, t;\n\t.reg .b64 a1, a2, a3, x1, x2, x3;\n\t"
+      "setp.ne.b32 p0, %10, 0;\n\tsetp.ne.b32 p1, %11, 0;\n\tsetp.ne.b32 p2, %12, 0;\n\tsetp.ne.b32 p3, %13, 0;\n\t"
+      "setp.ne.b32 e1, %14, 0;\n\tsetp.ne.b32 e2, %15, 0;\n\tsetp.ne.b32 e3, %16, 0;\n\t"
+      "setp.eq.u32 t, 0, 0;\n\t"
+      "add.u64 a1, %4, 2;\n\tadd.u64 a2, %4, 4;\n\tadd.u64 a3, %4, 6;\n\t"
+      "add.u64 x1, %5, 2;\n\tadd.u64 x2, %5, 4;\n\tadd.u64 x3, %5, 6;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %4, %5, %9, p0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, x1, %9, t;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a2, x2, %9, t;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], a3, x3, %9, t;\n\t"
+      "add.u64 x1, %6, 2;\n\tadd.u64 x2, %6, 4;\n\tadd.u64 x3, %6, 6;\n\t"
+      "@e1 tcgen05.mma.cta_group::1.kind::f16 [%1], %4, %6, %18, p1;\n\t"
+      "@e1 tcgen05.mma.cta_group::1.kind::f16 [%1], a1, x1, %18, t;\n\t"
+      "@e1 tcgen05.mma.cta_group::1.kind::f16 [%1], a2, x2, %18, t;\n\t"
+      "@e1 tcgen05.mma.cta_group::1.kind::f16 [%1], a3, x3, %18, t;\n\t"
+      "add.u64 x1, %7, 2;\n\tadd.u64 x2, %7, 4;\n\tadd.u64 x3, %7, 6;\n\t"
+      "@e2 tcgen05.mma.cta_group::1.kind::f16 [%2], %4, %7, %19, p2;\n\t"
+      "@e2 tcgen05.mma.cta_group::1.kind::f16 [%2], a1, x1, %19, t;\n\t"
+      "@e2 tcgen05.mma.cta_group::1.kind::f16 [%2], a2, x2, %19, t;\n\t"
+      "@e2 tcgen05.mma.cta_group::1.kind::f16 [%2], a3, x3, %19, t;\n\t"
+      "add.u64 x1, %8, 2;\n\tadd.u64 x2, %8, 4;\n\tadd.u64 x3, %8, 6;\n\t"
+      "@e3 tcgen05.mma.cta_group::1.kind::f16 [%3], %4, %8, %20, p3;\n\t"
+      "@e3 tcgen05.mma.cta_group::1.kind::f16 [%3], a1, x1, %20, t;\n\t"
+      "@e3 tcgen05.mma.cta_group::1.kind::f16 [%3], a2, x2, %20, t;\n\t"
+      "@e3 tcgen05.mma.cta_group::1.kind::f16 [%3], a3, x3, %20, t;\n\t"
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%17];\n\t}"
+      ::"r"(d[0]), "r"(d[1]), "r"(d[2]), "r"(d[3]), "l"(a_desc), "l"(b[0]), "l"(b[1]), "l"(b[2]), "l"(b[3]),
+        "r"(idesc[0]), "r"(acc[0]), "r"(acc[1]), "r"(acc[2]), "r"(acc[3]), "r"((uint32_t)(n_ops > 1)),
+        "r"((uint32_t)(n_ops > 2)), "r"((uint32_t)(n_ops > 3)), "r"(bar), "r"(idesc[1]), "r"(idesc[2]), "r"(idesc[3])
+      : "memory");
+}
 __device__ __forceinline__ void umma_bf16_k64x4_commit_pair(const uint32_t (&d)[4], uint64_t a_desc, const uint64_t (&b)[4], uint32_t idesc,
                                                             const uint32_t (&acc)[4], int n_ops, uint32_t bar) {
   PSOB_UMMA_K64X4_BODY("2", "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%17], %18;");

@@ -34,6 +34,15 @@ MAX_N = 256           # UMMA N limit / TMEM columns per accumulator buffer
 
 ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3, 4
 STEP_ACCUM, STEP_B_RESIDENT, STEP_NEXT, STEP_EYE = 1, 2, 4, 8     # NEXT: the op accumulates into the next job of the chain
+# op width: an op covers (1 + w) * mma_n accumulator columns and weight rows, w = (flags >> STEP_WIDE_SHIFT) & 3.  Neighbouring output
+# pixels of a conv read the same input pixel through neighbouring taps; with the taps' weight tiles stored back to back such ops
+# are ONE tcgen05.mma of N = 128 / 192 / 256 instead of 2-4 of N = 64 (whose cost is the ~90-cycle issue floor, not their width).
+STEP_WIDE_SHIFT = 8
+MERGE_OPS = knob("PSOB_MERGE_OPS", "1") != "0"
+
+
+def op_width(flags):
+    return 1 + ((int(flags) >> STEP_WIDE_SHIFT) & 3)
 ROUND_WEIGHTS = True   # tests switch this off to check the geometry exactly in fp32
 BIAS_IN_K_IMAGE = knob("PSOB_BIAS_IN_K_IMAGE", "1") != "0"   # ... and of the first discriminator / encoder conv (constant K-chunk)
 BIAS_IN_K = knob("PSOB_BIAS_IN_K", "1") != "0"      # first generator layer: bias folded into the K padding of the latent row
@@ -139,7 +148,7 @@ def pack_steps(prog: "LayerProgram") -> np.ndarray:
     def enc(b_row, d_col, flags):
         assert b_row % 16 == 0 and b_row // 16 < 65536 and d_col % 2 == 0 and d_col // 2 < 256
         return ((b_row // 16) | ((d_col // 2) << 16) | ((1 << 24) if flags & STEP_NEXT else 0) | ((1 << 25) if flags & STEP_ACCUM else 0) |
-                ((1 << 26) if flags & STEP_EYE else 0))
+                ((1 << 26) if flags & STEP_EYE else 0) | ((op_width(flags) - 1) << 28))       # bit 27: issuer region (engine)
 
     for i, (a_col, b_row, d_col, flags) in enumerate(prog.steps):
         ops = [(int(b_row), int(d_col), int(flags))] + [tuple(map(int, o)) for o in prog.xops.get(i, [])]
@@ -215,7 +224,8 @@ def _finish(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, tiles, b
     # image of an image layer is only written on request and is not counted); lowerings that share buffers set it themselves
     meta.setdefault("hbm_bytes", 2 * (int(in_pitch) + int(out_pitch)))
     n_eye = int(np.count_nonzero(steps[:, 3] & STEP_EYE)) if steps.size else 0
-    n_ops = int(steps.shape[0]) - n_eye + sum(len(v) for v in xops.values())
+    # issued MACs count an op's width (a merged op covers 1-4 x mma_n columns)
+    n_ops = sum(op_width(fl) for fl in steps[:, 3] if not fl & STEP_EYE) + sum(op_width(o[2]) for v in xops.values() for o in v) if steps.size else 0
     return LayerProgram(name, mma_n, nt, cc, act, in_pitch, out_pitch, out32_pitch, wpack, b_resident, steps, jobs,
                         col_map, col_map32, bias, vec8, xops, chains, int(macs_exact),
                         n_ops * KCHUNK * mma_n + n_eye * KCHUNK * KCHUNK, meta or {})
@@ -932,6 +942,13 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
     wbytes = k * k * nkc * cpo * KCHUNK * 2
     if CONV2D_RESIDENT and shortcut is None and not residual and ncg == 1 and wbytes <= CONV2D_RESIDENT_MAX:
         xops = {}
+        merge = MERGE_OPS and stride == 1
+        if merge:
+            # taps of one kernel row back to back, kx DESCENDING: input pixel ix feeds output pixels ix - kx + pad in ascending order
+            for ky in range(k):
+                for kc in range(nkc):
+                    for kx in reversed(range(k)):
+                        tile((ky, kx, kc, 0), lambda: wp[:, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
         for pix0 in range(0, npix, g):
             sb = len(steps)
             outs = [divmod(pix0 + j, wo) for j in range(min(g, npix - pix0))]
@@ -951,6 +968,17 @@ def lower_conv2d(name, w, b, act, h, wd, stride, pad, in_cp=None, residual=False
                         b_row = tile((ky, kx, kc, 0), lambda: wp[:, kc * KCHUNK:(kc + 1) * KCHUNK, ky, kx].copy())
                         ops.append((b_row, j * mma_n, (STEP_ACCUM if j in started else 0) | STEP_B_RESIDENT))
                         started.add(j)
+                    if merge:        # neighbouring columns x neighbouring weight rows, same accumulate flag -> one wider op
+                        merged = []
+                        for (br, dc, fl) in ops:
+                            if merged:
+                                pb, pd, pf = merged[-1]
+                                wdt = op_width(pf)
+                                if (pf & 0xFF) == fl and br == pb + wdt * mma_n and dc == pd + wdt * mma_n and wdt < 4:
+                                    merged[-1] = (pb, pd, (pf & 0xFF) | (wdt << STEP_WIDE_SHIFT))
+                                    continue
+                            merged.append((br, dc, fl))
+                        ops = merged
                     for o0 in range(0, len(ops), 4):
                         grp = ops[o0:o0 + 4]
                         steps.append(((iy * wd + ix) * cpi + in_base + kc * KCHUNK, grp[0][0], grp[0][1], grp[0][2]))
@@ -1123,11 +1151,12 @@ def emulate(prog: LayerProgram, x: np.ndarray, round_out=True, res: Optional[np.
             else:
                 acc[:, d_col:d_col + KCHUNK] = a.astype(np.float32)
             return
-        contrib = a.astype(np.float32) @ prog.wpack[b_row:b_row + prog.mma_n].T.astype(np.float32)
+        n = prog.mma_n * op_width(flags)
+        contrib = a.astype(np.float32) @ prog.wpack[b_row:b_row + n].T.astype(np.float32)
         if flags & STEP_ACCUM:
-            acc[:, d_col:d_col + prog.mma_n] += contrib
+            acc[:, d_col:d_col + n] += contrib
         else:
-            acc[:, d_col:d_col + prog.mma_n] = contrib
+            acc[:, d_col:d_col + n] = contrib
 
     for jb, jc in prog.chains:
         nxt = None

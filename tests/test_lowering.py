@@ -229,3 +229,37 @@ def test_pack_tables_reconstructs_every_step_list():
             assert np.array_equal(jobs[j, 1:7], ref_jobs[j, 1:7])
     wide = next(p for p in progs if p.meta.get("kind") == "convt_image_band_tiled")
     assert L.pack_tables(wide)[0].shape[0] <= 1024 < wide.n_steps
+
+
+def test_merged_wide_ops_equal_single_ops():
+    """3x3 conv with resident weights (the assessor's stage-1 shape): neighbouring output pixels fed by one input pixel through
+    neighbouring taps are merged into ops of 2-3 x mma_n columns (weight tiles of a kernel row stored back to back).  Same
+    products, same accumulation order per column: the emulation must agree bit for bit with the single-op tables, the op count
+    must drop, and the packed op words must carry the width in bits 28..29."""
+    from psob import lowering as L
+    rng = np.random.default_rng(0)
+    w = (rng.standard_normal((64, 64, 3, 3)) * 0.1).astype(np.float32)
+    b = rng.standard_normal(64).astype(np.float32)
+    x = L.to_bf16_f32(rng.standard_normal((5, 49 * 64)).astype(np.float32))
+    old = L.MERGE_OPS
+    try:
+        L.MERGE_OPS = True
+        pm = L.lower_conv2d("m", w, b, L.ACT_RELU, 7, 7, 1, 1)
+        L.MERGE_OPS = False
+        pu = L.lower_conv2d("u", w, b, L.ACT_RELU, 7, 7, 1, 1)
+    finally:
+        L.MERGE_OPS = old
+    ym, _ = L.emulate(pm, x)
+    yu, _ = L.emulate(pu, x)
+    assert np.array_equal(ym, yu)
+    n_ops = lambda p: p.n_steps + sum(len(v) for v in p.xops.values())
+    assert n_ops(pu) == 361 and n_ops(pm) < 0.65 * n_ops(pu) and pm.n_steps == pu.n_steps
+    assert pm.macs_issued == pu.macs_issued                      # a wide op counts its width
+    st = L.pack_steps(pm)
+    widths = 1 + ((st[:, 2:6].astype(np.int64) >> 28) & 3)
+    assert widths.max() == 3 and ((L.pack_steps(pu)[:, 2:6].astype(np.int64) >> 28) & 3).max() == 0
+    # a wide op stays inside the job's columns and the weight pack
+    for i in range(pm.n_steps):
+        for (br, dc, fl) in [tuple(int(v) for v in pm.steps[i][1:4])] + [tuple(int(v) for v in o) for o in pm.xops.get(i, [])]:
+            n = pm.mma_n * L.op_width(fl)
+            assert dc + n <= pm.nt and br + n <= pm.wpack.shape[0]
